@@ -1,0 +1,199 @@
+/* medvae_b200.h — C ABI of libmedvae_b200.so (sm_100a CUDA kernels for the conditional-VAE
+ * training step of parsakzr/medvae-disentangled-multimodal).
+ *
+ * The reference has no FFI / plugin interface for this path: its boundary is the Python class
+ * surface of src.models / src.losses.  This header is therefore the NEW native
+ * boundary that sits under that surface; each entry point cites the reference code whose leaf
+ * arithmetic it replaces (paths relative to the reference root).  Conventions:
+ *   - every function returns 0 on success, non-zero on failure; mvae_last_error() gives the
+ *     thread-local message.  Nothing falls back to the CPU: without a CUDA device every compute
+ *     entry point fails.
+ *   - all pointers are DEVICE pointers owned by the caller (PyTorch allocates them); no
+ *     ownership is transferred; work is enqueued on `stream` (a cudaStream_t) and not synced.
+ *   - activations are NHWC (channels innermost).  dtype: MVAE_F32 (verification mode) or
+ *     MVAE_BF16 (bf16 storage, fp32 accumulate).  Parameters and their gradients are fp32 in the
+ *     reference's own layouts (OIHW conv weights) so state_dict stays compatible.
+ */
+#ifndef MEDVAE_B200_H
+#define MEDVAE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MVAE_ABI_VERSION 1
+
+enum { MVAE_F32 = 0, MVAE_BF16 = 1 };
+
+/* conv geometry (encoder_decoder.py):
+ *   MVAE_CONV_S1   stride 1, padding (R-1)/2            nn.Conv2d 3x3 p1 / 1x1   (:128-146, :76-81)
+ *   MVAE_CONV_DOWN F.pad(0,1,0,1) + 3x3 stride 2 pad 0  Downsample.forward        (:184-188)
+ *   MVAE_CONV_UP   nearest 2x + 3x3 stride 1 pad 1      Upsample.forward          (:205-209)
+ */
+enum { MVAE_CONV_S1 = 0, MVAE_CONV_DOWN = 1, MVAE_CONV_UP = 2 };
+
+/* engine selection for the conv entry points */
+enum { MVAE_ENGINE_AUTO = 0, MVAE_ENGINE_SIMT = 1, MVAE_ENGINE_UMMA = 2 };
+
+typedef struct mvae_conv_desc {
+    int32_t batch;     /* B                                                        */
+    int32_t in_h;      /* input H (before the implicit pad / upsample)             */
+    int32_t in_w;
+    int32_t in_c;      /* Cin                                                      */
+    int32_t out_c;     /* Cout                                                     */
+    int32_t ksize;     /* 1 or 3 (R == S)                                          */
+    int32_t mode;      /* MVAE_CONV_*                                              */
+    int32_t dtype;     /* MVAE_F32 | MVAE_BF16 : activation + packed-weight dtype  */
+    int32_t engine;    /* MVAE_ENGINE_*                                            */
+} mvae_conv_desc;
+
+const char* mvae_last_error(void);
+int mvae_abi_version(void);
+/* 1 if a CUDA device with compute capability 10.x is present */
+int mvae_device_ok(void);
+/* debug knobs (descriptor variants for bring-up); key/value ints */
+int mvae_set_debug(int key, int value);
+
+/* output spatial size for a conv desc */
+int mvae_conv2d_out_hw(const mvae_conv_desc* d, int32_t* out_h, int32_t* out_w);
+/* number of packed weight slabs ([slab][N][K]): ksize^2, or 16 for MVAE_CONV_UP */
+int mvae_conv2d_num_slabs(const mvae_conv_desc* d);
+/* 1 if the tcgen05 path will be used for this desc (bf16, Cin%64==0, Cout%64==0) */
+int mvae_conv2d_uses_umma(const mvae_conv_desc* d);
+
+/* nn.Conv2d weights (OIHW fp32) -> packed operands.  w_fprop: [slab][Cout][Cin], w_dgrad:
+ * [slab][Cin][Cout] (either may be NULL).  `out_c_total`/`out_c_offset` let several convs
+ * (AttnBlock q,k,v — encoder_decoder.py:76-79) share one packed operand of out_c_total rows. */
+int mvae_conv2d_pack_weights(const mvae_conv_desc* d, const float* w_oihw, void* w_fprop,
+                             void* w_dgrad, int32_t out_c_total, int32_t out_c_offset,
+                             void* stream);
+
+/* y = conv(x) + bias (+ residual).  Replaces nn.Conv2d.forward at encoder_decoder.py:152,162,
+ * 168 (ResnetBlock), :86-88,:105 (AttnBlock 1x1), :187, :208, :308,:327,:426,:450.
+ * `residual` (same shape as y, may be NULL) fuses the `x + h` of :170 / :107. */
+int mvae_conv2d_fprop(const mvae_conv_desc* d, const void* x, const void* w_fprop,
+                      const float* bias, const void* residual, void* y, void* stream);
+
+/* dx = conv_transpose(dy).  The backward of the above w.r.t. its input (autograd of F.conv2d,
+ * F.pad and F.interpolate in the reference). */
+int mvae_conv2d_dgrad(const mvae_conv_desc* d, const void* dy, const void* w_dgrad, void* dx,
+                      void* stream);
+
+/* dW (OIHW fp32 [out_c][in_c][k][k], overwritten) and dbias (fp32 [out_c], may be NULL) from the
+ * layer input x and the output gradient dy.  workspace: mvae_conv2d_wgrad_workspace_bytes(). */
+size_t mvae_conv2d_wgrad_workspace_bytes(const mvae_conv_desc* d);
+int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, float* dw_oihw,
+                      float* dbias, void* workspace, size_t workspace_bytes, void* stream);
+
+/* GroupNorm(min(32,C), eps) [+ x*sigmoid(x)]  — Normalize + nonlinearity,
+ * encoder_decoder.py:13-15,28-33 as used at :150-151,:158-159,:85,:325-326,:446-447.
+ * x,y: [B, HW, C].  stats (out): [B][G][2] fp32 (mean, rstd).  scratch: B*splits*G*2 floats
+ * with splits = mvae_groupnorm_splits(). */
+int mvae_groupnorm_splits(int32_t batch, int32_t hw, int32_t c);
+int mvae_groupnorm_silu_fwd(const void* x, const float* gamma, const float* beta, void* y,
+                            float* stats, float* scratch, int32_t batch, int32_t hw, int32_t c,
+                            int32_t groups, float eps, int32_t apply_silu, int32_t dtype,
+                            void* stream);
+/* dx = d(GN+SiLU)(dy) + dx_add (dx_add may be NULL: fuses the residual-branch gradient);
+ * dgamma/dbeta (fp32) are ACCUMULATED into (caller zeroes). */
+int mvae_groupnorm_silu_bwd(const void* dy, const void* x, const float* gamma, const float* beta,
+                            const float* stats, const void* dx_add, void* dx, float* dgamma,
+                            float* dbeta, float* scratch, int32_t batch, int32_t hw, int32_t c,
+                            int32_t groups, int32_t apply_silu, int32_t dtype, void* stream);
+
+/* AttnBlock core, encoder_decoder.py:91-103: per image, single head of width C.
+ * qkv: [B, T, 3C] (q|k|v along channels), out: [B, T, C].
+ * probs: [B, T, T] fp32 scratch kept for the backward. */
+int mvae_attn_core_fwd(const void* qkv, void* out, float* probs, int32_t batch, int32_t tokens,
+                       int32_t c, int32_t dtype, void* stream);
+/* dqkv from dout; dscratch: [B, T, T] fp32 */
+int mvae_attn_core_bwd(const void* qkv, const float* probs, const void* dout, void* dqkv,
+                       float* dscratch, int32_t batch, int32_t tokens, int32_t c, int32_t dtype,
+                       void* stream);
+
+/* ConditionalVAE.create_condition_map + torch.cat, conditional_vae.py:107-127 (concat path),
+ * and the NCHW->NHWC conversion of x.  cond: [B, cond_dim] fp32 (one-hot or dense);
+ * w: [C*64, cond_dim], b: [C*64] (condition_proj.0).  out: NHWC [B,H,W,out_c] with channels
+ * [0,C) = x, [C,2C) = bilinear(ReLU(Linear(cond))) and [2C,out_c) zero.  With w == NULL only
+ * the layout conversion is done (BaseVAE / BetaVAE input). */
+int mvae_input_pack_fwd(const float* x_nchw, const float* cond, const float* w, const float* b,
+                        void* out, int32_t batch, int32_t c, int32_t h, int32_t w_, int32_t cond_dim,
+                        int32_t out_c, int32_t dtype, void* stream);
+/* gradient of the condition branch: d_in NHWC [B,H,W,out_c] (channels [C,2C) are read) ->
+ * dw [C*64, cond_dim], db [C*64] (fp32, overwritten). */
+int mvae_input_pack_bwd(const void* d_in, const float* cond, const float* w, const float* b,
+                        float* dw, float* db, int32_t batch, int32_t c, int32_t h, int32_t w_,
+                        int32_t cond_dim, int32_t out_c, int32_t dtype, void* stream);
+
+/* layout helpers: NHWC (dtype) <-> NCHW fp32, optional channel window */
+int mvae_nhwc_to_nchw_f32(const void* src, float* dst, int32_t batch, int32_t h, int32_t w,
+                          int32_t c_src, int32_t c_off, int32_t c_dst, int32_t dtype, void* stream);
+int mvae_nchw_f32_to_nhwc(const float* src, void* dst, int32_t batch, int32_t h, int32_t w,
+                          int32_t c, int32_t dtype, void* stream);
+
+/* torch.chunk + BaseVAE.reparameterize (base_vae.py:76,83-87) + the KL integrand of
+ * VAELoss (vae_losses.py:55), one pass.  moments: NHWC [B,R,R,2*zc].  eps: NCHW fp32 or NULL
+ * (then Philox4x32-10 keyed by (seed, offset, element) generates it and, if eps_out != NULL,
+ * stores it).  Outputs NCHW fp32 mean/logvar/z, optionally std = exp(0.5 logvar) (std_out) and
+ * NHWC z (z_nhwc, dtype), both may be NULL.  kl_sum:
+ * one double, ACCUMULATED: sum 0.5(e^lv + mu^2 - 1 - lv).  clamp > 0 applies
+ * clamp(mu,±clamp), clamp(logvar,±clamp) first (disentangled_conditional_vae.py:409-412). */
+int mvae_reparam_kl_fwd(const void* moments, const float* eps, float* eps_out, float* mean,
+                        float* logvar, float* std_out, float* z_nchw, void* z_nhwc, double* kl_sum,
+                        int32_t batch, int32_t zc, int32_t r, float clamp, uint64_t seed,
+                        uint64_t offset, int32_t dtype, void* stream);
+/* d_moments (NHWC dtype) from d_mean, d_logvar, d_z (NCHW fp32, each may be NULL) and the
+ * saved mean/logvar/eps; clamp masks the gradient like torch.clamp. */
+int mvae_reparam_kl_bwd(const float* d_mean, const float* d_logvar, const float* d_z,
+                        const float* mean_raw_unused, const float* logvar, const float* eps,
+                        const void* moments, void* d_moments, int32_t batch, int32_t zc, int32_t r,
+                        float clamp, int32_t dtype, void* stream);
+
+/* VAELoss reconstruction term (vae_losses.py:41-48): kind 0 mse, 1 l1, 2 bce-with-logits.
+ * recon, x: same-shape fp32 arrays of n elements.  loss_sum: one double, ACCUMULATED (un-normalised
+ * sum).  d_unit (may be NULL): d(mean loss)/d(recon) = integrand'/n, written in the same pass. */
+int mvae_recon_loss_fwd_bwd(const float* recon, const float* x, double* loss_sum, float* d_unit,
+                            int64_t n, int32_t kind, void* stream);
+/* KL term alone (for posteriors that did not come from mvae_reparam_kl_fwd) and its gradient:
+ * d_mean = coef*mu, d_logvar = coef*0.5(e^lv-1), coef read from device (*coef_dev) */
+int mvae_kl_fwd(const float* mean, const float* logvar, double* kl_sum, int64_t n, void* stream);
+int mvae_kl_bwd(const float* mean, const float* logvar, const float* coef_dev, float* d_mean,
+                float* d_logvar, int64_t n, void* stream);
+/* out[i] = in[i] * (*scale_dev) */
+int mvae_scale_by_device_scalar(const float* in, const float* scale_dev, float* out, int64_t n,
+                                void* stream);
+
+/* fused multi-tensor AdamW/Adam + global-norm clip + non-finite guard
+ * (lightning_module.py:390-477: optimizer.step, clip_gradients, NaN-grad zeroing).
+ * Pointer tables live on the DEVICE: params/grads/exp_avg/exp_avg_sq[i] -> fp32 arrays of
+ * sizes[i] elements.  Pass 1 (mvae_grad_sqnorm) accumulates sum(g^2) of finite entries into
+ * *sqnorm_dev; pass 2 applies the step with grads scaled by min(1, max_norm/(norm+1e-6)). */
+int mvae_grad_sqnorm(const float* const* grads, const int64_t* sizes, int32_t n_tensors,
+                     double* sqnorm_dev, void* stream);
+int mvae_adamw_clip_step(float* const* params, const float* const* grads, float* const* exp_avg,
+                         float* const* exp_avg_sq, const int64_t* sizes, int32_t n_tensors,
+                         const double* sqnorm_dev, float max_norm, float lr, float beta1,
+                         float beta2, float eps, float weight_decay, int32_t decoupled,
+                         int32_t step, void* stream);
+
+/* DisentangledConditionalVAE per-modality input projector
+ * (disentangled_conditional_vae.py:124-171): out NHWC [B,H,W,out_c]; for modalities whose
+ * channel count is 1, out[:, :3] = w_m * x[:,0] + b_m (Conv2d(1,3,1)), else x passes through.
+ * x: NCHW fp32 with xc channels; idx: int64 [B]; proj_w: [n_mod][3], proj_b: [n_mod][3];
+ * is_gray: int32 [n_mod]. */
+int mvae_dis_input_fwd(const float* x_nchw, const int64_t* idx, const float* proj_w,
+                       const float* proj_b, const int32_t* is_gray, void* out, int32_t batch,
+                       int32_t xc, int32_t h, int32_t w, int32_t n_mod, int32_t out_c,
+                       int32_t dtype, void* stream);
+int mvae_dis_input_bwd(const void* d_in, const float* x_nchw, const int64_t* idx,
+                       const int32_t* is_gray, float* d_proj_w, float* d_proj_b, int32_t batch,
+                       int32_t xc, int32_t h, int32_t w, int32_t n_mod, int32_t out_c,
+                       int32_t dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MEDVAE_B200_H */

@@ -1,0 +1,495 @@
+"""Encoder / Decoder of the VAE: parameter containers that are state_dict-compatible with the
+reference (src/models/encoder_decoder.py) plus the hand-scheduled forward/backward that drives
+the sm_100a kernels.
+
+The nn.Conv2d / nn.GroupNorm children are used ONLY as parameter holders (same names, shapes,
+construction order and default init as the reference, so a seeded construction reproduces the
+reference's initial weights and `load_state_dict` works both ways).  Their `.forward` is never
+called: `Encoder.forward` / `Decoder.forward` run the NHWC kernel schedule below inside one
+`torch.autograd.Function`, whose backward is the reverse schedule (dgrad + wgrad per conv, fused
+GroupNorm+SiLU backward with the residual-gradient add, attention backward).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+from . import ops
+
+GN_EPS = 1e-6
+
+
+def _norm(c: int) -> nn.GroupNorm:
+    """encoder_decoder.py:28-33 — GroupNorm(min(32, C), C, eps=1e-6, affine)."""
+    return nn.GroupNorm(num_groups=min(32, c), num_channels=c, eps=GN_EPS, affine=True)
+
+
+# ----------------------------------------------------------------------------------------------
+# parameter containers
+# ----------------------------------------------------------------------------------------------
+class ResnetBlock(nn.Module):
+    """encoder_decoder.py:110-170 (temb_channels == 0, conv_shortcut == False always)."""
+
+    def __init__(self, in_channels: int, out_channels: Optional[int] = None, dropout: float = 0.0):
+        super().__init__()
+        out_channels = in_channels if out_channels is None else out_channels
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.norm1 = _norm(in_channels)
+        self.conv1 = nn.Conv2d(in_channels, out_channels, 3, 1, 1)
+        self.norm2 = _norm(out_channels)
+        self.dropout = nn.Dropout(dropout)
+        self.conv2 = nn.Conv2d(out_channels, out_channels, 3, 1, 1)
+        if in_channels != out_channels:
+            self.nin_shortcut = nn.Conv2d(in_channels, out_channels, 1, 1, 0)
+
+
+class AttnBlock(nn.Module):
+    """encoder_decoder.py:68-107."""
+
+    def __init__(self, in_channels: int):
+        super().__init__()
+        self.in_channels = in_channels
+        self.norm = _norm(in_channels)
+        self.q = nn.Conv2d(in_channels, in_channels, 1, 1, 0)
+        self.k = nn.Conv2d(in_channels, in_channels, 1, 1, 0)
+        self.v = nn.Conv2d(in_channels, in_channels, 1, 1, 0)
+        self.proj_out = nn.Conv2d(in_channels, in_channels, 1, 1, 0)
+
+
+class Downsample(nn.Module):
+    """encoder_decoder.py:173-191 (with_conv=True: pad (0,1,0,1) + conv3x3 s2 p0)."""
+
+    def __init__(self, in_channels: int, with_conv: bool = True):
+        super().__init__()
+        if not with_conv:
+            raise NotImplementedError("Downsample(with_conv=False) is never built by the reference models")
+        self.with_conv = with_conv
+        self.conv = nn.Conv2d(in_channels, in_channels, 3, 2, 0)
+
+
+class Upsample(nn.Module):
+    """encoder_decoder.py:194-209 (nearest 2x + conv3x3)."""
+
+    def __init__(self, in_channels: int, with_conv: bool = True):
+        super().__init__()
+        if not with_conv:
+            raise NotImplementedError("Upsample(with_conv=False) is never built by the reference models")
+        self.with_conv = with_conv
+        self.conv = nn.Conv2d(in_channels, in_channels, 3, 1, 1)
+
+
+def make_attn(in_channels: int, attn_type: str = "vanilla") -> nn.Module:
+    """encoder_decoder.py:18-25."""
+    if attn_type == "vanilla":
+        return AttnBlock(in_channels)
+    if attn_type == "linear":
+        raise NotImplementedError("attn_type='linear' (LinAttnBlock) is not built yet; no reference config uses it")
+    raise NotImplementedError(f"Attention type {attn_type} not implemented")
+
+
+# ----------------------------------------------------------------------------------------------
+# kernel schedule
+# ----------------------------------------------------------------------------------------------
+class Run:
+    """State of one forward (+ its backward) through a stack: dtype, saved activations and the
+    parameter gradients produced so far."""
+
+    def __init__(self, dtype: torch.dtype, cache: dict, training: bool):
+        self.dtype = dtype
+        self.code = L.code_of(dtype)
+        self.cache = cache            # packed-operand cache owned by the nn.Module
+        self.training = training
+        self.grads: Dict[nn.Parameter, torch.Tensor] = {}
+        self.tape: list = []
+
+    def add_grad(self, p: nn.Parameter, g: torch.Tensor):
+        g = g.view(p.shape)
+        if p in self.grads:
+            self.grads[p] = self.grads[p] + g
+        else:
+            self.grads[p] = g
+
+
+class ConvOp:
+    """One (or several channel-concatenated) nn.Conv2d as packed fprop/dgrad operands."""
+
+    def __init__(self, convs: Sequence[nn.Conv2d], mode: int):
+        self.convs = list(convs)
+        c0 = self.convs[0]
+        self.cin = c0.in_channels
+        self.couts = [c.out_channels for c in self.convs]
+        self.cout = sum(self.couts)
+        self.k = c0.kernel_size[0]
+        self.mode = mode
+
+    def desc(self, run: Run, b: int, h: int, w: int):
+        return ops.conv_desc(b, h, w, self.cin, self.cout, self.k, self.mode, run.code)
+
+    def packed(self, run: Run, device):
+        key = (tuple(id(c.weight) for c in self.convs), run.code, self.mode)
+        ver = tuple((c.weight._version, c.bias._version) for c in self.convs)
+        ent = run.cache.get(key)
+        if ent is None or ent["ver"] != ver or ent["dev"] != device:
+            d1 = ops.conv_desc(1, 8, 8, self.cin, self.cout, self.k, self.mode, run.code)
+            nslabs = ops.conv_num_slabs(d1)
+            wf = torch.empty((nslabs, self.cout, self.cin), dtype=run.dtype, device=device)
+            wd = torch.empty((nslabs, self.cin, self.cout), dtype=run.dtype, device=device)
+            off = 0
+            for c in self.convs:
+                dd = ops.conv_desc(1, 8, 8, self.cin, c.out_channels, self.k, self.mode, run.code)
+                ops.conv_pack_weights(dd, c.weight.detach(), wf, wd, self.cout, off)
+                off += c.out_channels
+            if len(self.convs) == 1:
+                bias = self.convs[0].bias.detach()
+            else:
+                bias = torch.cat([c.bias.detach() for c in self.convs]).contiguous()
+            ent = {"ver": ver, "dev": device, "wf": wf, "wd": wd, "bias": bias}
+            run.cache[key] = ent
+        return ent
+
+    def fwd(self, run: Run, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        b, h, w, _ = x.shape
+        ent = self.packed(run, x.device)
+        return ops.conv_fprop(self.desc(run, b, h, w), x, ent["wf"], ent["bias"], residual)
+
+    def bwd(self, run: Run, x: torch.Tensor, dy: torch.Tensor, need_dx: bool = True):
+        b, h, w, _ = x.shape
+        d = self.desc(run, b, h, w)
+        ent = self.packed(run, x.device)
+        dw, db = ops.conv_wgrad(d, x, dy, True)
+        off = 0
+        for c in self.convs:
+            run.add_grad(c.weight, dw[off:off + c.out_channels])
+            run.add_grad(c.bias, db[off:off + c.out_channels])
+            off += c.out_channels
+        return ops.conv_dgrad(d, dy, ent["wd"]) if need_dx else None
+
+
+def gn_fwd(run: Run, norm: nn.GroupNorm, x, silu: bool):
+    return ops.gn_fwd(x, norm.weight.detach(), norm.bias.detach(), norm.num_groups, norm.eps, silu)
+
+
+def gn_bwd(run: Run, norm: nn.GroupNorm, dy, x, stats, dx_add, silu: bool):
+    dx, dg, db = ops.gn_bwd(dy, x, norm.weight.detach(), norm.bias.detach(), stats, dx_add, norm.num_groups, silu)
+    run.add_grad(norm.weight, dg)
+    run.add_grad(norm.bias, db)
+    return dx
+
+
+class ResOp:
+    """x + conv2(silu(gn2(conv1(silu(gn1(x)))))) with an optional 1x1 shortcut
+    (encoder_decoder.py:148-170).  The residual add is fused into conv2's epilogue; in the
+    backward the shortcut gradient is fused into the GroupNorm-1 backward."""
+
+    def __init__(self, blk: ResnetBlock):
+        self.blk = blk
+        self.c1 = ConvOp([blk.conv1], L.CONV_S1)
+        self.c2 = ConvOp([blk.conv2], L.CONV_S1)
+        self.nin = ConvOp([blk.nin_shortcut], L.CONV_S1) if hasattr(blk, "nin_shortcut") else None
+        if blk.dropout.p > 0.0:
+            self.p_drop = blk.dropout.p
+        else:
+            self.p_drop = 0.0
+
+    def fwd(self, run: Run, x):
+        if self.p_drop > 0.0 and run.training:
+            raise NotImplementedError("dropout > 0 in training mode is not implemented (all full-size reference "
+                                      "configs use dropout 0.0)")
+        a1, st1 = gn_fwd(run, self.blk.norm1, x, True)
+        h1 = self.c1.fwd(run, a1)
+        a2, st2 = gn_fwd(run, self.blk.norm2, h1, True)
+        xs = self.nin.fwd(run, x) if self.nin is not None else x
+        out = self.c2.fwd(run, a2, residual=xs)
+        run.tape.append((self, (x, st1, a1, h1, st2, a2)))
+        return out
+
+    def bwd(self, run: Run, saved, dout):
+        x, st1, a1, h1, st2, a2 = saved
+        d_a2 = self.c2.bwd(run, a2, dout)
+        d_h1 = gn_bwd(run, self.blk.norm2, d_a2, h1, st2, None, True)
+        del d_a2
+        d_a1 = self.c1.bwd(run, a1, d_h1)
+        del d_h1
+        addend = self.nin.bwd(run, x, dout) if self.nin is not None else dout
+        return gn_bwd(run, self.blk.norm1, d_a1, x, st1, addend, True)
+
+
+class AttnOp:
+    """x + proj_out(attn(q,k,v of gn(x)))  (encoder_decoder.py:83-107); q,k,v are one N=3C GEMM."""
+
+    def __init__(self, blk: AttnBlock):
+        self.blk = blk
+        self.qkv = ConvOp([blk.q, blk.k, blk.v], L.CONV_S1)
+        self.proj = ConvOp([blk.proj_out], L.CONV_S1)
+
+    def fwd(self, run: Run, x):
+        hn, st = gn_fwd(run, self.blk.norm, x, False)
+        qkv = self.qkv.fwd(run, hn)
+        o, probs = ops.attn_fwd(qkv)
+        out = self.proj.fwd(run, o, residual=x)
+        run.tape.append((self, (x, st, hn, qkv, o, probs)))
+        return out
+
+    def bwd(self, run: Run, saved, dout):
+        x, st, hn, qkv, o, probs = saved
+        d_o = self.proj.bwd(run, o, dout)
+        d_qkv = ops.attn_bwd(qkv, probs, d_o)
+        del d_o
+        d_hn = self.qkv.bwd(run, hn, d_qkv)
+        del d_qkv
+        return gn_bwd(run, self.blk.norm, d_hn, x, st, dout, False)
+
+
+class PlainConvOp:
+    """a conv that is its own stage (conv_in, Downsample, Upsample)."""
+
+    def __init__(self, conv: nn.Conv2d, mode: int, need_dx: bool = True):
+        self.op = ConvOp([conv], mode)
+        self.need_dx = need_dx
+
+    def fwd(self, run: Run, x):
+        y = self.op.fwd(run, x)
+        run.tape.append((self, (x,)))
+        return y
+
+    def bwd(self, run: Run, saved, dout):
+        return self.op.bwd(run, saved[0], dout, self.need_dx)
+
+
+class HeadOp:
+    """norm_out -> swish -> conv_out (encoder_decoder.py:325-327, :446-450)."""
+
+    def __init__(self, norm: nn.GroupNorm, conv: nn.Conv2d):
+        self.norm = norm
+        self.op = ConvOp([conv], L.CONV_S1)
+
+    def fwd(self, run: Run, x):
+        a, st = gn_fwd(run, self.norm, x, True)
+        y = self.op.fwd(run, a)
+        run.tape.append((self, (x, st, a)))
+        return y
+
+    def bwd(self, run: Run, saved, dout):
+        x, st, a = saved
+        d_a = self.op.bwd(run, a, dout)
+        return gn_bwd(run, self.norm, d_a, x, st, None, True)
+
+
+def run_forward(stages, run: Run, x):
+    for s in stages:
+        x = s.fwd(run, x)
+    return x
+
+
+def run_backward(run: Run, dout):
+    while run.tape:
+        stage, saved = run.tape.pop()
+        dout = stage.bwd(run, saved, dout)
+        del saved
+    return dout
+
+
+# ----------------------------------------------------------------------------------------------
+# Encoder / Decoder modules
+# ----------------------------------------------------------------------------------------------
+class _Stack(nn.Module):
+    """common machinery: dtype selection, packed-operand cache, autograd bridge."""
+
+    def _init_runtime(self):
+        self._pack_cache: dict = {}
+        self.compute_dtype = torch.bfloat16
+
+    def stages(self, need_input_grad: bool):
+        raise NotImplementedError
+
+    def param_list(self) -> List[nn.Parameter]:
+        return list(self.parameters())
+
+    def forward_nhwc(self, x_nhwc: torch.Tensor, need_input_grad: bool):
+        """x NHWC (compute dtype) -> y NHWC, differentiable w.r.t. x and the parameters."""
+        L.require_device()
+        params = self.param_list()
+        return _StackFn.apply(self, need_input_grad, x_nhwc, *params)
+
+
+class _StackFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, stack: "_Stack", need_input_grad: bool, x, *params):
+        run = Run(x.dtype, stack._pack_cache, stack.training)
+        with torch.no_grad():
+            y = run_forward(stack.stages(need_input_grad), run, x)
+        ctx.run = run
+        ctx.params = params
+        ctx.need_input_grad = need_input_grad
+        if not any(ctx.needs_input_grad):
+            run.tape.clear()   # inference: nothing is kept
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        run: Run = ctx.run
+        if not run.tape:
+            raise RuntimeError("backward through a stack whose tape was released (double backward?)")
+        with torch.no_grad():
+            dx = run_backward(run, dy.contiguous())
+        grads = []
+        for p in ctx.params:
+            g = run.grads.get(p)
+            if g is None and p.requires_grad:
+                g = torch.zeros_like(p)
+            grads.append(g)
+        run.grads = {}
+        ctx.run = None
+        return (None, None, dx if ctx.need_input_grad else None, *grads)
+
+
+class Encoder(_Stack):
+    """encoder_decoder.py:212-328."""
+
+    def __init__(self, *, ch: int, out_ch: int, ch_mult: Tuple[int, ...] = (1, 2, 4, 8), num_res_blocks: int,
+                 attn_resolutions: List[int], dropout: float = 0.0, resamp_with_conv: bool = True,
+                 in_channels: int, resolution: int, z_channels: int, double_z: bool = True,
+                 use_linear_attn: bool = False, attn_type: str = "vanilla", **ignore_kwargs):
+        super().__init__()
+        if use_linear_attn:
+            attn_type = "linear"
+        self.ch, self.temb_ch = ch, 0
+        self.num_resolutions = len(ch_mult)
+        self.num_res_blocks = num_res_blocks
+        self.resolution = resolution
+        self.in_channels = in_channels
+        self.conv_in = nn.Conv2d(in_channels, ch, 3, 1, 1)
+        self.in_ch_mult = (1,) + tuple(ch_mult)
+        curr_res = resolution
+        self.down = nn.ModuleList()
+        block_in = ch
+        for lv in range(self.num_resolutions):
+            level = nn.Module()
+            level.block, level.attn = nn.ModuleList(), nn.ModuleList()
+            block_in, block_out = ch * self.in_ch_mult[lv], ch * ch_mult[lv]
+            for _ in range(num_res_blocks):
+                level.block.append(ResnetBlock(block_in, block_out, dropout))
+                block_in = block_out
+                if curr_res in attn_resolutions:
+                    level.attn.append(make_attn(block_in, attn_type))
+            if lv != self.num_resolutions - 1:
+                level.downsample = Downsample(block_in, resamp_with_conv)
+                curr_res //= 2
+            self.down.append(level)
+        self.mid = nn.Module()
+        self.mid.block_1 = ResnetBlock(block_in, block_in, dropout)
+        self.mid.attn_1 = make_attn(block_in, attn_type)
+        self.mid.block_2 = ResnetBlock(block_in, block_in, dropout)
+        self.norm_out = _norm(block_in)
+        self.conv_out = nn.Conv2d(block_in, 2 * z_channels if double_z else z_channels, 3, 1, 1)
+        self._init_runtime()
+
+    def stages(self, need_input_grad: bool):
+        st = [PlainConvOp(self.conv_in, L.CONV_S1, need_dx=need_input_grad)]
+        for lv, level in enumerate(self.down):
+            for ib, blk in enumerate(level.block):
+                st.append(ResOp(blk))
+                if len(level.attn) > 0:
+                    st.append(AttnOp(level.attn[ib]))
+            if hasattr(level, "downsample"):
+                st.append(PlainConvOp(level.downsample.conv, L.CONV_DOWN))
+        st += [ResOp(self.mid.block_1), AttnOp(self.mid.attn_1), ResOp(self.mid.block_2),
+               HeadOp(self.norm_out, self.conv_out)]
+        return st
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """x NCHW fp32 -> (B, 2*z_channels, R, R) NCHW fp32 (same contract as the reference)."""
+        L.require_device()
+        xin = _ToNHWC.apply(x.float().contiguous(), self.compute_dtype)
+        y = self.forward_nhwc(xin, x.requires_grad)
+        return _ToNCHW.apply(y)
+
+
+class Decoder(_Stack):
+    """encoder_decoder.py:331-451."""
+
+    def __init__(self, *, ch: int, out_ch: int, ch_mult: Tuple[int, ...] = (1, 2, 4, 8), num_res_blocks: int,
+                 attn_resolutions: List[int], dropout: float = 0.0, resamp_with_conv: bool = True,
+                 in_channels: int, resolution: int, z_channels: int, give_pre_end: bool = False,
+                 tanh_out: bool = False, use_linear_attn: bool = False, attn_type: str = "vanilla", **ignorekwargs):
+        super().__init__()
+        if use_linear_attn:
+            attn_type = "linear"
+        if give_pre_end or tanh_out:
+            raise NotImplementedError("give_pre_end / tanh_out are never enabled by the reference models")
+        self.ch, self.temb_ch = ch, 0
+        self.num_resolutions = len(ch_mult)
+        self.num_res_blocks = num_res_blocks
+        self.resolution = resolution
+        self.in_channels = in_channels
+        self.give_pre_end, self.tanh_out = give_pre_end, tanh_out
+        block_in = ch * ch_mult[self.num_resolutions - 1]
+        curr_res = resolution // 2 ** (self.num_resolutions - 1)
+        self.z_shape = (1, z_channels, curr_res, curr_res)
+        self.conv_in = nn.Conv2d(z_channels, block_in, 3, 1, 1)
+        self.mid = nn.Module()
+        self.mid.block_1 = ResnetBlock(block_in, block_in, dropout)
+        self.mid.attn_1 = make_attn(block_in, attn_type)
+        self.mid.block_2 = ResnetBlock(block_in, block_in, dropout)
+        self.up = nn.ModuleList()
+        for lv in reversed(range(self.num_resolutions)):
+            level = nn.Module()
+            level.block, level.attn = nn.ModuleList(), nn.ModuleList()
+            block_out = ch * ch_mult[lv]
+            for _ in range(num_res_blocks + 1):
+                level.block.append(ResnetBlock(block_in, block_out, dropout))
+                block_in = block_out
+                if curr_res in attn_resolutions:
+                    level.attn.append(make_attn(block_in, attn_type))
+            if lv != 0:
+                level.upsample = Upsample(block_in, resamp_with_conv)
+                curr_res *= 2
+            self.up.insert(0, level)
+        self.norm_out = _norm(block_in)
+        self.conv_out = nn.Conv2d(block_in, out_ch, 3, 1, 1)
+        self._init_runtime()
+
+    def stages(self, need_input_grad: bool):
+        st = [PlainConvOp(self.conv_in, L.CONV_S1, need_dx=need_input_grad),
+              ResOp(self.mid.block_1), AttnOp(self.mid.attn_1), ResOp(self.mid.block_2)]
+        for lv in reversed(range(self.num_resolutions)):
+            level = self.up[lv]
+            for ib, blk in enumerate(level.block):
+                st.append(ResOp(blk))
+                if len(level.attn) > 0:
+                    st.append(AttnOp(level.attn[ib]))
+            if hasattr(level, "upsample"):
+                st.append(PlainConvOp(level.upsample.conv, L.CONV_UP))
+        st.append(HeadOp(self.norm_out, self.conv_out))
+        return st
+
+    def forward(self, z: torch.Tensor) -> torch.Tensor:
+        """z NCHW fp32 -> reconstruction NCHW fp32."""
+        L.require_device()
+        zin = _ToNHWC.apply(z.float().contiguous(), self.compute_dtype)
+        y = self.forward_nhwc(zin, z.requires_grad)
+        return _ToNCHW.apply(y)
+
+
+class _ToNHWC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_nchw, dtype):
+        return ops.nchw_f32_to_nhwc(x_nchw, dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return ops.nhwc_to_nchw_f32(dy.contiguous()), None
+
+
+class _ToNCHW(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_nhwc):
+        ctx.dtype = x_nhwc.dtype
+        return ops.nhwc_to_nchw_f32(x_nhwc)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return ops.nchw_f32_to_nhwc(dy.float().contiguous(), ctx.dtype)

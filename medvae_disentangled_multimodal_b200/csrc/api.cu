@@ -1,0 +1,312 @@
+// extern "C" surface of libmedvae_b200.so (see include/medvae_b200.h).  Argument validation,
+// engine selection, error reporting.  No CPU fallback anywhere: without a device every compute
+// entry fails with an error string.
+#include <cstdarg>
+#include <cstring>
+
+#include "conv_lower.h"
+
+namespace mvae {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+static int g_knobs[16] = {0};
+int debug_knob(int key) { return (key >= 0 && key < 16) ? g_knobs[key] : 0; }
+
+// implemented in the other translation units
+int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot, int co_off, int dtype, cudaStream_t st);
+int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int splits, cudaStream_t st);
+int colsum_parts(long long M);
+int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dtype, cudaStream_t st);
+int nhwc_to_nchw(const void* src, float* dst, int B, int HW, int Cs, int c_off, int Cd, int dtype, cudaStream_t st);
+int nchw_to_nhwc(const float* src, void* dst, int B, int HW, int C, int dtype, cudaStream_t st);
+int input_pack_fwd(const float* x, const float* cond, const float* w, const float* b, void* out, int B, int C, int H,
+                   int W, int cond_dim, int out_c, int dtype, cudaStream_t st);
+int input_pack_bwd(const void* d_in, const float* cond, const float* w, const float* b, float* dw, float* db, int B,
+                   int C, int H, int W, int cond_dim, int out_c, int dtype, cudaStream_t st);
+int dis_input_fwd(const float* x, const long long* idx, const float* pw, const float* pb, const int* is_gray, void* out,
+                  int B, int xc, int HW, int n_mod, int out_c, int dtype, cudaStream_t st);
+int dis_input_bwd(const void* d_in, const float* x, const long long* idx, const int* is_gray, float* dpw, float* dpb,
+                  int B, int xc, int HW, int n_mod, int out_c, int dtype, cudaStream_t st);
+int gn_splits(int B, int HW, int C);
+int gn_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, float* scratch, int B, int HW,
+           int C, int G, float eps, int silu, int dtype, cudaStream_t st);
+int gn_bwd(const void* dy, const void* x, const float* gamma, const float* beta, const float* stats, const void* dx_add,
+           void* dx, float* dgamma, float* dbeta, float* scratch, int B, int HW, int C, int G, int silu, int dtype,
+           cudaStream_t st);
+int attn_fwd(const void* qkv, void* out, float* probs, int B, int Tn, int C, int dtype, cudaStream_t st);
+int attn_bwd(const void* qkv, const float* probs, const void* dout, void* dqkv, float* ds, int B, int Tn, int C,
+             int dtype, cudaStream_t st);
+int reparam_fwd(const void* mom, const float* eps, float* eps_out, float* mean, float* logvar, float* stdv,
+                float* z_nchw, void* z_nhwc, double* kl_sum, int B, int zc, int R, float clampv, uint64_t seed, uint64_t offset,
+                int dtype, cudaStream_t st);
+int reparam_bwd(const float* d_mean, const float* d_logvar, const float* d_z, const float* logvar, const float* eps,
+                const void* mom, void* d_mom, int B, int zc, int R, float clampv, int dtype, cudaStream_t st);
+int recon_loss(const float* r, const float* x, double* loss_sum, float* d_unit, long long n, int kind, cudaStream_t st);
+int kl_fwd(const float* mean, const float* logvar, double* kl_sum, long long n, cudaStream_t st);
+int kl_bwd(const float* mean, const float* logvar, const float* coef, float* d_mean, float* d_logvar, long long n,
+           cudaStream_t st);
+int scale_dev(const float* in, const float* s, float* out, long long n, cudaStream_t st);
+int grad_sqnorm(const float* const* grads, const long long* sizes, int nt, double* out, cudaStream_t st);
+int adamw_step(float* const* params, const float* const* grads, float* const* m1, float* const* m2,
+               const long long* sizes, int nt, const double* sqnorm, float max_norm, float lr, float b1, float b2,
+               float eps, float wd, int decoupled, int step, cudaStream_t st);
+
+static bool dtype_ok(int d) { return d == MVAE_F32 || d == MVAE_BF16; }
+
+static bool use_umma_gather(const mvae_conv_desc& d, const GatherProblem* ps, int np) {
+    if (d.dtype != MVAE_BF16 || d.engine == MVAE_ENGINE_SIMT) return false;
+    for (int i = 0; i < np; ++i)
+        if (!umma_gather_ok(ps[i])) return false;
+    return true;
+}
+
+}  // namespace mvae
+
+using namespace mvae;
+
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+const char* mvae_last_error(void) { return g_err; }
+int mvae_abi_version(void) { return MVAE_ABI_VERSION; }
+
+int mvae_device_ok(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        return 0;
+    }
+    int dev = 0, major = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    return major == 10 ? 1 : 0;
+}
+
+int mvae_set_debug(int key, int value) {
+    MVAE_CHECK(key >= 0 && key < 16, "debug key out of range");
+    g_knobs[key] = value;
+    return 0;
+}
+
+int mvae_conv2d_out_hw(const mvae_conv_desc* d, int32_t* oh, int32_t* ow) {
+    ConvGeom g;
+    MVAE_CHECK(d && conv_geom(*d, g) == 0, "bad conv descriptor");
+    *oh = g.P; *ow = g.Q;
+    return 0;
+}
+int mvae_conv2d_num_slabs(const mvae_conv_desc* d) {
+    ConvGeom g;
+    if (!d || conv_geom(*d, g)) return -1;
+    return conv_num_slabs(g);
+}
+int mvae_conv2d_uses_umma(const mvae_conv_desc* d) {
+    ConvGeom g;
+    if (!d || conv_geom(*d, g)) return 0;
+    GatherProblem ps[4];
+    int np = lower_fprop(g, ps);
+    return use_umma_gather(*d, ps, np) ? 1 : 0;
+}
+
+int mvae_conv2d_pack_weights(const mvae_conv_desc* d, const float* w, void* wf, void* wd, int32_t out_c_total,
+                             int32_t out_c_offset, void* stream) {
+    ConvGeom g;
+    MVAE_CHECK(d && conv_geom(*d, g) == 0 && dtype_ok(d->dtype), "bad conv descriptor");
+    MVAE_CHECK(w && (wf || wd), "pack_weights: null pointer");
+    MVAE_CHECK(out_c_offset >= 0 && out_c_offset + g.Cout <= out_c_total, "pack_weights: bad channel window");
+    return pack_weights(g, w, wf, wd, out_c_total, out_c_offset, d->dtype, ST(stream));
+}
+
+int mvae_conv2d_fprop(const mvae_conv_desc* d, const void* x, const void* wf, const float* bias, const void* residual,
+                      void* y, void* stream) {
+    ConvGeom g;
+    MVAE_CHECK(d && conv_geom(*d, g) == 0 && dtype_ok(d->dtype), "bad conv descriptor");
+    MVAE_CHECK(x && wf && y, "conv2d_fprop: null pointer");
+    GatherProblem ps[4];
+    int np = lower_fprop(g, ps);
+    bool um = use_umma_gather(*d, ps, np);
+    MVAE_CHECK(um || d->engine != MVAE_ENGINE_UMMA, "conv2d_fprop: tcgen05 engine requested for an unsupported shape");
+    for (int i = 0; i < np; ++i) {
+        int rc = um ? umma_gather(ps[i], x, wf, conv_num_slabs(g), bias, residual, y, ST(stream))
+                    : simt_gather(ps[i], x, wf, bias, residual, y, d->dtype, ST(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int mvae_conv2d_dgrad(const mvae_conv_desc* d, const void* dy, const void* wd, void* dx, void* stream) {
+    ConvGeom g;
+    MVAE_CHECK(d && conv_geom(*d, g) == 0 && dtype_ok(d->dtype), "bad conv descriptor");
+    MVAE_CHECK(dy && wd && dx, "conv2d_dgrad: null pointer");
+    GatherProblem ps[4];
+    int np = lower_dgrad(g, ps);
+    bool um = use_umma_gather(*d, ps, np);
+    MVAE_CHECK(um || d->engine != MVAE_ENGINE_UMMA, "conv2d_dgrad: tcgen05 engine requested for an unsupported shape");
+    for (int i = 0; i < np; ++i) {
+        int rc = um ? umma_gather(ps[i], dy, wd, conv_num_slabs(g), nullptr, nullptr, dx, ST(stream))
+                    : simt_gather(ps[i], dy, wd, nullptr, nullptr, dx, d->dtype, ST(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+static bool use_umma_reduce(const mvae_conv_desc& d, const ReduceProblem& p) {
+    return d.dtype == MVAE_BF16 && d.engine != MVAE_ENGINE_SIMT && umma_reduce_ok(p);
+}
+
+size_t mvae_conv2d_wgrad_workspace_bytes(const mvae_conv_desc* d) {
+    ConvGeom g;
+    if (!d || conv_geom(*d, g)) return 0;
+    ReduceProblem p;
+    lower_wgrad(g, p);
+    int splits = use_umma_reduce(*d, p) ? umma_reduce_splits(p) : 1;
+    size_t partial = sizeof(float) * (size_t)splits * conv_num_slabs(g) * g.Cout * g.Cin;
+    size_t cs = sizeof(float) * (size_t)colsum_parts((long long)g.B * g.P * g.Q) * g.Cout;
+    return partial + cs + 256;
+}
+
+int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+    ConvGeom g;
+    MVAE_CHECK(d && conv_geom(*d, g) == 0 && dtype_ok(d->dtype), "bad conv descriptor");
+    MVAE_CHECK(x && dy && dw && workspace, "conv2d_wgrad: null pointer");
+    MVAE_CHECK(workspace_bytes >= mvae_conv2d_wgrad_workspace_bytes(d), "conv2d_wgrad: workspace too small");
+    ReduceProblem p;
+    lower_wgrad(g, p);
+    bool um = use_umma_reduce(*d, p);
+    MVAE_CHECK(um || d->engine != MVAE_ENGINE_UMMA, "conv2d_wgrad: tcgen05 engine requested for an unsupported shape");
+    int splits = um ? umma_reduce_splits(p) : 1;
+    float* partial = reinterpret_cast<float*>(workspace);
+    size_t partial_elems = (size_t)splits * conv_num_slabs(g) * g.Cout * g.Cin;
+    int rc = um ? umma_reduce(p, x, dy, partial, splits, ST(stream)) : simt_reduce(p, x, dy, partial, d->dtype, ST(stream));
+    if (rc) return rc;
+    if (wgrad_finalize(g, partial, dw, splits, ST(stream))) return 1;
+    if (dbias) {
+        float* cs = partial + ((partial_elems + 63) / 64) * 64;
+        return colsum(dy, dbias, cs, (long long)g.B * g.P * g.Q, g.Cout, d->dtype, ST(stream));
+    }
+    return 0;
+}
+
+int mvae_groupnorm_splits(int32_t batch, int32_t hw, int32_t c) { return gn_splits(batch, hw, c); }
+
+int mvae_groupnorm_silu_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, float* scratch,
+                            int32_t batch, int32_t hw, int32_t c, int32_t groups, float eps, int32_t apply_silu,
+                            int32_t dtype, void* stream) {
+    MVAE_CHECK(x && gamma && beta && y && stats && scratch && dtype_ok(dtype), "groupnorm_silu_fwd: bad argument");
+    return gn_fwd(x, gamma, beta, y, stats, scratch, batch, hw, c, groups, eps, apply_silu, dtype, ST(stream));
+}
+int mvae_groupnorm_silu_bwd(const void* dy, const void* x, const float* gamma, const float* beta, const float* stats,
+                            const void* dx_add, void* dx, float* dgamma, float* dbeta, float* scratch, int32_t batch,
+                            int32_t hw, int32_t c, int32_t groups, int32_t apply_silu, int32_t dtype, void* stream) {
+    MVAE_CHECK(dy && x && gamma && beta && stats && dx && dgamma && dbeta && scratch && dtype_ok(dtype),
+               "groupnorm_silu_bwd: bad argument");
+    return gn_bwd(dy, x, gamma, beta, stats, dx_add, dx, dgamma, dbeta, scratch, batch, hw, c, groups, apply_silu, dtype,
+                  ST(stream));
+}
+
+int mvae_attn_core_fwd(const void* qkv, void* out, float* probs, int32_t batch, int32_t tokens, int32_t c, int32_t dtype,
+                       void* stream) {
+    MVAE_CHECK(qkv && out && probs && dtype_ok(dtype), "attn_core_fwd: bad argument");
+    return attn_fwd(qkv, out, probs, batch, tokens, c, dtype, ST(stream));
+}
+int mvae_attn_core_bwd(const void* qkv, const float* probs, const void* dout, void* dqkv, float* dscratch, int32_t batch,
+                       int32_t tokens, int32_t c, int32_t dtype, void* stream) {
+    MVAE_CHECK(qkv && probs && dout && dqkv && dscratch && dtype_ok(dtype), "attn_core_bwd: bad argument");
+    return attn_bwd(qkv, probs, dout, dqkv, dscratch, batch, tokens, c, dtype, ST(stream));
+}
+
+int mvae_input_pack_fwd(const float* x, const float* cond, const float* w, const float* b, void* out, int32_t batch,
+                        int32_t c, int32_t h, int32_t w_, int32_t cond_dim, int32_t out_c, int32_t dtype, void* stream) {
+    MVAE_CHECK(x && out && dtype_ok(dtype), "input_pack_fwd: bad argument");
+    MVAE_CHECK((w == nullptr) || (cond && b && out_c >= 2 * c), "input_pack_fwd: conditioning needs cond, w, b");
+    MVAE_CHECK(out_c >= c, "input_pack_fwd: out_c < c");
+    return input_pack_fwd(x, cond, w, b, out, batch, c, h, w_, cond_dim, out_c, dtype, ST(stream));
+}
+int mvae_input_pack_bwd(const void* d_in, const float* cond, const float* w, const float* b, float* dw, float* db,
+                        int32_t batch, int32_t c, int32_t h, int32_t w_, int32_t cond_dim, int32_t out_c, int32_t dtype,
+                        void* stream) {
+    MVAE_CHECK(d_in && cond && w && b && dw && db && dtype_ok(dtype), "input_pack_bwd: bad argument");
+    return input_pack_bwd(d_in, cond, w, b, dw, db, batch, c, h, w_, cond_dim, out_c, dtype, ST(stream));
+}
+
+int mvae_nhwc_to_nchw_f32(const void* src, float* dst, int32_t batch, int32_t h, int32_t w, int32_t c_src, int32_t c_off,
+                          int32_t c_dst, int32_t dtype, void* stream) {
+    MVAE_CHECK(src && dst && dtype_ok(dtype) && c_off >= 0 && c_off + c_dst <= c_src, "nhwc_to_nchw: bad argument");
+    return nhwc_to_nchw(src, dst, batch, h * w, c_src, c_off, c_dst, dtype, ST(stream));
+}
+int mvae_nchw_f32_to_nhwc(const float* src, void* dst, int32_t batch, int32_t h, int32_t w, int32_t c, int32_t dtype,
+                          void* stream) {
+    MVAE_CHECK(src && dst && dtype_ok(dtype), "nchw_to_nhwc: bad argument");
+    return nchw_to_nhwc(src, dst, batch, h * w, c, dtype, ST(stream));
+}
+
+int mvae_reparam_kl_fwd(const void* moments, const float* eps, float* eps_out, float* mean, float* logvar,
+                        float* std_out, float* z_nchw, void* z_nhwc, double* kl_sum, int32_t batch, int32_t zc, int32_t r, float clamp, uint64_t seed,
+                        uint64_t offset, int32_t dtype, void* stream) {
+    MVAE_CHECK(moments && mean && logvar && z_nchw && dtype_ok(dtype), "reparam_kl_fwd: bad argument");
+    return reparam_fwd(moments, eps, eps_out, mean, logvar, std_out, z_nchw, z_nhwc, kl_sum, batch, zc, r, clamp, seed, offset,
+                       dtype, ST(stream));
+}
+int mvae_reparam_kl_bwd(const float* d_mean, const float* d_logvar, const float* d_z, const float* mean_unused,
+                        const float* logvar, const float* eps, const void* moments, void* d_moments, int32_t batch,
+                        int32_t zc, int32_t r, float clamp, int32_t dtype, void* stream) {
+    (void)mean_unused;
+    MVAE_CHECK(logvar && eps && moments && d_moments && dtype_ok(dtype), "reparam_kl_bwd: bad argument");
+    return reparam_bwd(d_mean, d_logvar, d_z, logvar, eps, moments, d_moments, batch, zc, r, clamp, dtype, ST(stream));
+}
+
+int mvae_recon_loss_fwd_bwd(const float* recon, const float* x, double* loss_sum, float* d_unit, int64_t n, int32_t kind,
+                            void* stream) {
+    MVAE_CHECK(recon && x && loss_sum && n > 0 && kind >= 0 && kind <= 2, "recon_loss: bad argument");
+    return recon_loss(recon, x, loss_sum, d_unit, n, kind, ST(stream));
+}
+int mvae_kl_fwd(const float* mean, const float* logvar, double* kl_sum, int64_t n, void* stream) {
+    MVAE_CHECK(mean && logvar && kl_sum && n > 0, "kl_fwd: bad argument");
+    return kl_fwd(mean, logvar, kl_sum, n, ST(stream));
+}
+int mvae_kl_bwd(const float* mean, const float* logvar, const float* coef_dev, float* d_mean, float* d_logvar, int64_t n,
+                void* stream) {
+    MVAE_CHECK(mean && logvar && coef_dev && d_mean && d_logvar && n > 0, "kl_bwd: bad argument");
+    return kl_bwd(mean, logvar, coef_dev, d_mean, d_logvar, n, ST(stream));
+}
+int mvae_scale_by_device_scalar(const float* in, const float* scale_dev_, float* out, int64_t n, void* stream) {
+    MVAE_CHECK(in && scale_dev_ && out && n > 0, "scale: bad argument");
+    return scale_dev(in, scale_dev_, out, n, ST(stream));
+}
+
+int mvae_grad_sqnorm(const float* const* grads, const int64_t* sizes, int32_t n_tensors, double* sqnorm_dev, void* stream) {
+    MVAE_CHECK(grads && sizes && sqnorm_dev && n_tensors > 0, "grad_sqnorm: bad argument");
+    return grad_sqnorm(grads, reinterpret_cast<const long long*>(sizes), n_tensors, sqnorm_dev, ST(stream));
+}
+int mvae_adamw_clip_step(float* const* params, const float* const* grads, float* const* exp_avg, float* const* exp_avg_sq,
+                         const int64_t* sizes, int32_t n_tensors, const double* sqnorm_dev, float max_norm, float lr,
+                         float beta1, float beta2, float eps, float weight_decay, int32_t decoupled, int32_t step,
+                         void* stream) {
+    MVAE_CHECK(params && grads && exp_avg && exp_avg_sq && sizes && n_tensors > 0 && step >= 1, "adamw: bad argument");
+    return adamw_step(params, grads, exp_avg, exp_avg_sq, reinterpret_cast<const long long*>(sizes), n_tensors, sqnorm_dev,
+                      max_norm, lr, beta1, beta2, eps, weight_decay, decoupled, step, ST(stream));
+}
+
+int mvae_dis_input_fwd(const float* x, const int64_t* idx, const float* pw, const float* pb, const int32_t* is_gray,
+                       void* out, int32_t batch, int32_t xc, int32_t h, int32_t w, int32_t n_mod, int32_t out_c,
+                       int32_t dtype, void* stream) {
+    MVAE_CHECK(x && idx && pw && pb && is_gray && out && dtype_ok(dtype) && out_c >= 3, "dis_input_fwd: bad argument");
+    return dis_input_fwd(x, reinterpret_cast<const long long*>(idx), pw, pb, is_gray, out, batch, xc, h * w, n_mod, out_c,
+                         dtype, ST(stream));
+}
+int mvae_dis_input_bwd(const void* d_in, const float* x, const int64_t* idx, const int32_t* is_gray, float* dpw, float* dpb,
+                       int32_t batch, int32_t xc, int32_t h, int32_t w, int32_t n_mod, int32_t out_c, int32_t dtype,
+                       void* stream) {
+    MVAE_CHECK(d_in && x && idx && is_gray && dpw && dpb && dtype_ok(dtype), "dis_input_bwd: bad argument");
+    return dis_input_bwd(d_in, x, reinterpret_cast<const long long*>(idx), is_gray, dpw, dpb, batch, xc, h * w, n_mod,
+                         out_c, dtype, ST(stream));
+}
+
+}  // extern "C"

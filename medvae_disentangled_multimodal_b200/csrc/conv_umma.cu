@@ -1,0 +1,544 @@
+// tcgen05 / TMEM / TMA implicit-GEMM execution of conv tap programs (bf16 in, fp32 accumulate).
+//
+//  gather kernel (fprop and dgrad):  D[128 pixels, BN channels] = sum_taps A_tap[128, K] * W_tap[BN, K]^T
+//      A tiles: TMA 4-D boxes {64 ch, bw, bh, bn} over an NHWC view, shifted per tap; the conv's
+//      zero padding (and the Downsample pad) is TMA out-of-bounds zero fill.  K-major, 128B swizzle.
+//      B tiles: TMA 3-D boxes {64 ch, BN, 1 slab} of the packed weights.  K-major, 128B swizzle.
+//      warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM alloc), warps 2-5 = epilogue
+//      (tcgen05.ld -> +bias (+residual) -> bf16 -> global).  Persistent CTAs, 2 TMEM accumulator
+//      stages so the epilogue of tile i overlaps the MMAs of tile i+1.
+//
+//  reduce kernel (wgrad):  D[128 co, BN ci] (per slab, per K-split) = sum_pixels dy[pix, co] * x[pix+tap, ci]
+//      Both operands are "MN-major" (the channel index is contiguous in NHWC), loaded by the same
+//      4-D boxes; 128 pixels per pipeline stage, 8 MMAs (K=16 pixels) per stage.
+#include "conv_lower.h"
+#include "umma.cuh"
+
+namespace mvae {
+using namespace sm100;
+
+// ------------------------------------------------------------------ tensor-map creation (host)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+static int encode_tmap(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims,
+                       const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+    EncodeTiledFn fn = get_encode_fn();
+    MVAE_CHECK(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+    cuuint32_t es[5] = {1, 1, 1, 1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), dims,
+                    strides_bytes, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    MVAE_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rank %d dims %llu %llu %llu)",
+               (int)r, rank, (unsigned long long)dims[0], (unsigned long long)dims[1],
+               (unsigned long long)dims[2]);
+    return 0;
+}
+
+// 4-D map {C, Ws, Hs, B} over a strided NHWC view; box {64, bw, bh, bn}
+static int view_tmap(CUtensorMap* m, const bf16* base, const View& v, int C, int B, int bw, int bh, int bn) {
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)v.Ws, (cuuint64_t)v.Hs, (cuuint64_t)B};
+    cuuint64_t st[3] = {(cuuint64_t)v.sx * 2, (cuuint64_t)v.sy * 2, (cuuint64_t)v.sn * 2};
+    cuuint32_t box[4] = {64u, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+    return encode_tmap(m, base + v.off, 4, dims, st, box);
+}
+
+// pixel-box geometry: 128 GEMM rows = bw x bh x bn pixels of the iteration grid
+struct BoxGeom {
+    int bw, bh, bn, tiles_x, tiles_y, tiles_n, rows;
+};
+static BoxGeom box_geom(int B, int GH, int GW) {
+    BoxGeom g;
+    g.bw = GW < 128 ? GW : 128;
+    int rem = 128 / g.bw;
+    g.bh = GH < rem ? GH : rem;
+    if (g.bh < 1) g.bh = 1;
+    rem = 128 / (g.bw * g.bh);
+    g.bn = B < rem ? B : rem;
+    if (g.bn < 1) g.bn = 1;
+    g.tiles_x = (GW + g.bw - 1) / g.bw;
+    g.tiles_y = (GH + g.bh - 1) / g.bh;
+    g.tiles_n = (B + g.bn - 1) / g.bn;
+    g.rows = g.bw * g.bh * g.bn;
+    return g;
+}
+
+static int num_sms() {
+    static int n = 0;
+    if (!n) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+// ================================================================== gather (fprop / dgrad)
+struct alignas(64) GatherTmaps {
+    CUtensorMap a[MAX_VIEWS];
+    CUtensorMap b;
+};
+struct GatherDev {
+    int bw, bh, bn, rows;
+    int OW, OH, B;
+    int tiles_x, tiles_y, tiles_n, n_tiles, kchunks, total_tiles;
+    int N;
+    long long o_off, o_sn, o_sy, o_sx;
+    const float* bias;
+    const bf16* res;
+    bf16* out;
+    TapProg taps;
+};
+
+constexpr int G_THREADS = 192;
+
+template <int BN>
+struct GatherCfg {
+    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int A_BYTES = 128 * 128;           // 128 rows x 64 bf16
+    static constexpr int B_BYTES = BN * 128;
+    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;   // 128 / 256 / 512: powers of two
+    static constexpr int SMEM = 1024 + STAGES * (A_BYTES + B_BYTES) + 256;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(G_THREADS, 1)
+conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_constant__ GatherDev p) {
+    using Cfg = GatherCfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + STAGES * Cfg::A_BYTES;
+    uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * Cfg::B_BYTES);
+    uint64_t* empty = full + STAGES;
+    uint64_t* tfull = empty + STAGES;
+    uint64_t* tempty = tfull + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (p.rows < 128) {
+        // rows the TMA box never writes feed accumulator rows nobody stores; keep them finite
+        for (int i = threadIdx.x; i < STAGES * Cfg::A_BYTES / 16; i += G_THREADS)
+            reinterpret_cast<uint4*>(sA)[i] = make_uint4(0, 0, 0, 0);
+        fence_proxy_async_smem();
+    }
+    if (warp == 0 && lane == 0) {
+        for (int v = 0; v < MAX_VIEWS; ++v) prefetch_tmap(&tm.a[v]);
+        prefetch_tmap(&tm.b);
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+            for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 128); }
+            fence_barrier_init();
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int kiters = p.taps.ntaps * p.kchunks;
+    const uint32_t stage_bytes = (uint32_t)p.rows * 128u + (uint32_t)Cfg::B_BYTES;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const int nt = tile % p.n_tiles;
+                int mt = tile / p.n_tiles;
+                const int tx = mt % p.tiles_x; mt /= p.tiles_x;
+                const int ty = mt % p.tiles_y;
+                const int tn = mt / p.tiles_y;
+                const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
+                for (int t = 0; t < p.taps.ntaps; ++t) {
+                    const Tap tp = p.taps.t[t];
+                    for (int kc = 0; kc < p.kchunks; ++kc) {
+                        mbar_wait(&empty[stage], phase ^ 1u);
+                        mbar_expect_tx(&full[stage], stage_bytes);
+                        tma_load_4d(sA + stage * Cfg::A_BYTES, &tm.a[tp.view], &full[stage], kc * 64,
+                                    x0 + tp.dx, y0 + tp.dy, n0);
+                        tma_load_3d(sB + stage * Cfg::B_BYTES, &tm.b, &full[stage], kc * 64, nt * BN, tp.slab);
+                        if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(128, BN, 0, 0);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                mbar_wait(&tempty[acc], acc_phase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                for (int it = 0; it < kiters; ++it) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES);
+                    const uint32_t b0 = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint64_t ad = smem_desc_sw128(a0 + k * 32, 16, 1024);
+                        const uint64_t bd = smem_desc_sw128(b0 + k * 32, 16, 1024);
+                        umma_bf16(d_tmem, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(&tfull[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1u;
+            }
+        }
+    } else {
+        const int quarter = warp & 3;            // TMEM lane quarter this warp may read
+        const int row = quarter * 32 + lane;     // GEMM row == pixel within the box
+        const int ix = row % p.bw;
+        const int iy = (row / p.bw) % p.bh;
+        const int in = row / (p.bw * p.bh);
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            const int nt = tile % p.n_tiles;
+            int mt = tile / p.n_tiles;
+            const int tx = mt % p.tiles_x; mt /= p.tiles_x;
+            const int ty = mt % p.tiles_y;
+            const int tn = mt / p.tiles_y;
+            const int x = tx * p.bw + ix, y = ty * p.bh + iy, n = tn * p.bn + in;
+            const bool valid = (row < p.rows) && x < p.OW && y < p.OH && n < p.B;
+            const long long pix = p.o_off + (long long)n * p.o_sn + (long long)y * p.o_sy + (long long)x * p.o_sx;
+            mbar_wait(&tfull[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld_32x32(t0 + (uint32_t)c0, v);
+                tmem_ld_wait();
+                if (valid) {
+                    const int cbase = nt * BN + c0;
+                    float f[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+                    if (p.bias) {
+                        const float4* bp = reinterpret_cast<const float4*>(p.bias + cbase);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            float4 b4 = __ldg(bp + i);
+                            f[4 * i] += b4.x; f[4 * i + 1] += b4.y; f[4 * i + 2] += b4.z; f[4 * i + 3] += b4.w;
+                        }
+                    }
+                    if (p.res) {
+                        const uint4* rp = reinterpret_cast<const uint4*>(p.res + pix + cbase);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            Vec8<bf16> r8; r8.raw = __ldg(rp + i);
+                            float rf[8]; r8.unpack(rf);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) f[8 * i + j] += rf[j];
+                        }
+                    }
+                    uint4* op = reinterpret_cast<uint4*>(p.out + pix + cbase);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        Vec8<bf16> o8; o8.pack(f + 8 * i);
+                        op[i] = o8.raw;
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&tempty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1u;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
+bool umma_gather_ok(const GatherProblem& p) {
+    if (p.K % 64 != 0 || p.N % 64 != 0) return false;
+    if (p.OW > 128 && p.OW % 128 != 0) return false;
+    BoxGeom g = box_geom(p.B, p.OH, p.OW);
+    for (int v = 0; v < p.nviews; ++v)
+        if (p.in_views[v].Ws < g.bw || p.in_views[v].Hs < g.bh) return false;
+    return true;
+}
+
+template <int BN>
+static int launch_gather(const GatherTmaps& tm, GatherDev& d, cudaStream_t st) {
+    using Cfg = GatherCfg<BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::SMEM));
+        attr_set = true;
+    }
+    int grid = d.total_tiles < num_sms() ? d.total_tiles : num_sms();
+    conv_gather_umma_kernel<BN><<<grid, G_THREADS, Cfg::SMEM, st>>>(tm, d);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslabs, const float* bias,
+                const void* residual, void* out, cudaStream_t st) {
+    MVAE_CHECK(umma_gather_ok(p), "umma_gather: unsupported shape K=%d N=%d OW=%d", p.K, p.N, p.OW);
+    BoxGeom g = box_geom(p.B, p.OH, p.OW);
+    const int BN = (p.N % 256 == 0) ? 256 : (p.N % 128 == 0 ? 128 : 64);
+    GatherTmaps tm;
+    memset(&tm, 0, sizeof(tm));
+    for (int v = 0; v < MAX_VIEWS; ++v) {
+        const View& vw = p.in_views[v < p.nviews ? v : 0];
+        if (view_tmap(&tm.a[v], (const bf16*)in, vw, p.K, p.B, g.bw, g.bh, g.bn)) return 1;
+    }
+    {
+        cuuint64_t dims[3] = {(cuuint64_t)p.K, (cuuint64_t)p.N, (cuuint64_t)nslabs};
+        cuuint64_t stb[2] = {(cuuint64_t)p.K * 2, (cuuint64_t)p.K * p.N * 2};
+        cuuint32_t box[3] = {64u, (cuuint32_t)BN, 1u};
+        if (encode_tmap(&tm.b, w, 3, dims, stb, box)) return 1;
+    }
+    GatherDev d;
+    d.bw = g.bw; d.bh = g.bh; d.bn = g.bn; d.rows = g.rows;
+    d.OW = p.OW; d.OH = p.OH; d.B = p.B;
+    d.tiles_x = g.tiles_x; d.tiles_y = g.tiles_y; d.tiles_n = g.tiles_n;
+    d.n_tiles = p.N / BN; d.kchunks = p.K / 64;
+    d.total_tiles = g.tiles_x * g.tiles_y * g.tiles_n * d.n_tiles;
+    d.N = p.N;
+    d.o_off = p.out_view.off; d.o_sn = p.out_view.sn; d.o_sy = p.out_view.sy; d.o_sx = p.out_view.sx;
+    d.bias = bias; d.res = (const bf16*)residual; d.out = (bf16*)out;
+    d.taps = p.taps;
+    if (BN == 256) return launch_gather<256>(tm, d, st);
+    if (BN == 128) return launch_gather<128>(tm, d, st);
+    return launch_gather<64>(tm, d, st);
+}
+
+// ================================================================== reduce (wgrad)
+struct alignas(64) ReduceTmaps {
+    CUtensorMap dy[MAX_VIEWS];
+    CUtensorMap in[MAX_VIEWS];
+};
+struct ReduceDev {
+    int bw, bh, bn, rows;
+    int tiles_x, tiles_y, tiles_n, ptiles;
+    int co_tiles, ci_tiles, nslabs, splits;
+    int Cout, Cin;
+    float* partial;    // [splits][nslabs][Cout][Cin]
+    uint32_t lbo, sbo; // MN-major descriptor strides (debug-overridable)
+    TapProg taps;
+};
+
+constexpr int R_BN = 128;                         // ci per tile
+constexpr int R_STAGES = 3;
+constexpr int R_CHUNK = 128 * 128;                // 128 pixels x 64 channels bf16 = 16 KB
+constexpr int R_A_BYTES = 2 * R_CHUNK;            // 128 co
+constexpr int R_B_BYTES = (R_BN / 64) * R_CHUNK;  // 128 ci
+constexpr int R_SMEM = 1024 + R_STAGES * (R_A_BYTES + R_B_BYTES) + 256;
+
+__global__ void __launch_bounds__(G_THREADS, 1)
+conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_constant__ ReduceDev p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + R_STAGES * R_A_BYTES;
+    uint64_t* full = reinterpret_cast<uint64_t*>(sB + R_STAGES * R_B_BYTES);
+    uint64_t* empty = full + R_STAGES;
+    uint64_t* tfull = empty + R_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // work item -> (split, slab, co tile, ci tile)
+    int w = blockIdx.x;
+    const int cit = w % p.ci_tiles; w /= p.ci_tiles;
+    const int cot = w % p.co_tiles; w /= p.co_tiles;
+    const int slab_i = w % p.nslabs;
+    const int split = w / p.nslabs;
+    const Tap tp = p.taps.t[slab_i];
+    const int pt_beg = (int)(((long long)p.ptiles * split) / p.splits);
+    const int pt_end = (int)(((long long)p.ptiles * (split + 1)) / p.splits);
+    const int kiters = pt_end - pt_beg;
+
+    if (p.rows < 128) {
+        // pixel rows beyond the TMA box take part in the K reduction: they must be zero
+        for (int i = threadIdx.x; i < R_STAGES * (R_A_BYTES + R_B_BYTES) / 16; i += G_THREADS)
+            reinterpret_cast<uint4*>(sA)[i] = make_uint4(0, 0, 0, 0);
+        fence_proxy_async_smem();
+    }
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tm.dy[tp.oview]);
+        prefetch_tmap(&tm.in[tp.view]);
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < R_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+            mbar_init(&tfull[0], 1);
+            fence_barrier_init();
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, R_BN);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t stage_bytes = (uint32_t)p.rows * 128u * (2 + R_BN / 64);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int pt = pt_beg; pt < pt_end; ++pt) {
+                int mt = pt;
+                const int tx = mt % p.tiles_x; mt /= p.tiles_x;
+                const int ty = mt % p.tiles_y;
+                const int tn = mt / p.tiles_y;
+                const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
+                mbar_wait(&empty[stage], phase ^ 1u);
+                mbar_expect_tx(&full[stage], stage_bytes);
+                uint8_t* a = sA + stage * R_A_BYTES;
+                uint8_t* b = sB + stage * R_B_BYTES;
+#pragma unroll
+                for (int c = 0; c < 2; ++c)
+                    tma_load_4d(a + c * R_CHUNK, &tm.dy[tp.oview], &full[stage], cot * 128 + c * 64, x0, y0, n0);
+#pragma unroll
+                for (int c = 0; c < R_BN / 64; ++c)
+                    tma_load_4d(b + c * R_CHUNK, &tm.in[tp.view], &full[stage], cit * R_BN + c * 64,
+                                x0 + tp.dx, y0 + tp.dy, n0);
+                if (++stage == R_STAGES) { stage = 0; phase ^= 1u; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(128, R_BN, 1, 1);
+            int stage = 0; uint32_t phase = 0;
+            for (int it = 0; it < kiters; ++it) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                const uint32_t a0 = smem_u32(sA + stage * R_A_BYTES);
+                const uint32_t b0 = smem_u32(sB + stage * R_B_BYTES);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {   // 16 pixels (= 16 rows of 128 B) per MMA
+                    const uint64_t ad = smem_desc_sw128(a0 + k * 2048, p.lbo, p.sbo);
+                    const uint64_t bd = smem_desc_sw128(b0 + k * 2048, p.lbo, p.sbo);
+                    umma_bf16(tmem_base, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                }
+                umma_commit(&empty[stage]);
+                if (++stage == R_STAGES) { stage = 0; phase ^= 1u; }
+            }
+            umma_commit(&tfull[0]);
+        }
+    } else {
+        const int quarter = warp & 3;
+        const int co = cot * 128 + quarter * 32 + lane;
+        float* dst = p.partial + (((long long)split * p.nslabs + tp.slab) * p.Cout + co) * p.Cin + cit * R_BN;
+        if (kiters > 0) {
+            mbar_wait(&tfull[0], 0);
+            tc_fence_after();
+        }
+        const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+        for (int c0 = 0; c0 < R_BN; c0 += 32) {
+            uint32_t v[32];
+            if (kiters > 0) {
+                tmem_ld_32x32(t0 + (uint32_t)c0, v);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = 0u;
+            }
+            float4* o = reinterpret_cast<float4*>(dst + c0);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                o[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                   __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, R_BN);
+    }
+}
+
+bool umma_reduce_ok(const ReduceProblem& p) {
+    if (p.Cout % 128 != 0 || p.Cin % R_BN != 0) return false;
+    if (p.GW > 128 && p.GW % 128 != 0) return false;
+    BoxGeom g = box_geom(p.B, p.GH, p.GW);
+    for (int v = 0; v < p.n_inviews; ++v)
+        if (p.in_views[v].Ws < g.bw || p.in_views[v].Hs < g.bh) return false;
+    for (int v = 0; v < p.n_dyviews; ++v)
+        if (p.dy_views[v].Ws < g.bw || p.dy_views[v].Hs < g.bh) return false;
+    return true;
+}
+
+int umma_reduce_splits(const ReduceProblem& p) {
+    BoxGeom g = box_geom(p.B, p.GH, p.GW);
+    long long ptiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
+    long long items = (long long)p.taps.ntaps * (p.Cout / 128) * (p.Cin / R_BN);
+    long long want = (2LL * num_sms() + items - 1) / items;
+    if (want < 1) want = 1;
+    long long cap = (ptiles + 3) / 4;   // at least ~4 pixel tiles per split
+    if (cap < 1) cap = 1;
+    if (want > cap) want = cap;
+    if (want > 64) want = 64;
+    return (int)want;
+}
+
+int umma_reduce(const ReduceProblem& p, const void* in, const void* dy, float* partial, int splits,
+                cudaStream_t st) {
+    MVAE_CHECK(umma_reduce_ok(p), "umma_reduce: unsupported shape Cout=%d Cin=%d", p.Cout, p.Cin);
+    BoxGeom g = box_geom(p.B, p.GH, p.GW);
+    ReduceTmaps tm;
+    memset(&tm, 0, sizeof(tm));
+    for (int v = 0; v < MAX_VIEWS; ++v) {
+        const View& vd = p.dy_views[v < p.n_dyviews ? v : 0];
+        const View& vi = p.in_views[v < p.n_inviews ? v : 0];
+        MVAE_CHECK(vd.Ws >= g.bw && vd.Hs >= g.bh && vi.Ws >= g.bw && vi.Hs >= g.bh,
+                   "umma_reduce: view %d smaller than the pixel box", v);
+        if (view_tmap(&tm.dy[v], (const bf16*)dy, vd, p.Cout, p.B, g.bw, g.bh, g.bn)) return 1;
+        if (view_tmap(&tm.in[v], (const bf16*)in, vi, p.Cin, p.B, g.bw, g.bh, g.bn)) return 1;
+    }
+    ReduceDev d;
+    d.bw = g.bw; d.bh = g.bh; d.bn = g.bn; d.rows = g.rows;
+    d.tiles_x = g.tiles_x; d.tiles_y = g.tiles_y; d.tiles_n = g.tiles_n;
+    d.ptiles = g.tiles_x * g.tiles_y * g.tiles_n;
+    d.co_tiles = p.Cout / 128; d.ci_tiles = p.Cin / R_BN; d.nslabs = p.taps.ntaps; d.splits = splits;
+    d.Cout = p.Cout; d.Cin = p.Cin; d.partial = partial;
+    d.lbo = R_CHUNK; d.sbo = 1024;
+    if (debug_knob(1) == 1) { d.lbo = 1024; d.sbo = R_CHUNK; }   // bring-up: swapped LBO/SBO roles
+    d.taps = p.taps;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MVAE_CUDA(cudaFuncSetAttribute(conv_reduce_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, R_SMEM));
+        attr_set = true;
+    }
+    long long grid = (long long)d.co_tiles * d.ci_tiles * d.nslabs * splits;
+    conv_reduce_umma_kernel<<<(unsigned)grid, G_THREADS, R_SMEM, st>>>(tm, d);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace mvae

@@ -1,0 +1,273 @@
+// Latent split + reparameterisation (Philox4x32-10) + KL and reconstruction losses, with their
+// gradients.  Reference: base_vae.py:76,83-87; src/losses/vae_losses.py:41-58;
+// disentangled_conditional_vae.py:409-412 (clamps), :524-525 (KL sum).
+#include "../../include/medvae_b200.h"
+#include "common.cuh"
+
+namespace mvae {
+
+// ------------------------------------------------------------------ Philox4x32-10 (counter based)
+struct Philox {
+    uint32_t k0, k1;
+    __device__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
+    __device__ __forceinline__ uint4 operator()(uint64_t ctr_lo, uint64_t ctr_hi) const {
+        uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
+        uint32_t a = k0, b = k1;
+#pragma unroll
+        for (int r = 0; r < 10; ++r) {
+            uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+            uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+            uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
+            c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+            a += 0x9E3779B9u; b += 0xBB67AE85u;
+        }
+        return make_uint4(c0, c1, c2, c3);
+    }
+};
+__device__ __forceinline__ float u01(uint32_t x) { return ((float)(x >> 8) + 0.5f) * (1.0f / 16777216.0f); }
+// one standard normal for element `e` of stream (seed, offset): Box-Muller on words (0,1) or (2,3)
+__device__ __forceinline__ float philox_normal(uint64_t seed, uint64_t offset, uint64_t e) {
+    Philox ph(seed);
+    uint4 r = ph(e >> 1, offset);
+    uint32_t a = (e & 1) ? r.z : r.x, b = (e & 1) ? r.w : r.y;
+    float u1 = u01(a), u2 = u01(b);
+    return sqrtf(-2.0f * __logf(u1)) * __cosf(6.283185307179586f * u2);
+}
+
+// ------------------------------------------------------------------ reparam + KL forward
+// index space: NCHW latent element e = ((n*zc + c)*R + y)*R + x ; moments NHWC [n][y][x][2zc]
+template <typename T>
+__global__ void __launch_bounds__(256) reparam_kl_fwd_kernel(const T* __restrict__ mom, const float* __restrict__ eps_in,
+                                                             float* __restrict__ eps_out, float* __restrict__ mean,
+                                                             float* __restrict__ logvar, float* __restrict__ stdv,
+                                                             float* __restrict__ z_nchw,
+                                                             T* __restrict__ z_nhwc, double* __restrict__ kl_sum,
+                                                             int B, int zc, int RR, float clampv, uint64_t seed,
+                                                             uint64_t offset) {
+    __shared__ double shd[32];
+    const long long total = (long long)B * zc * RR;
+    double acc = 0.0;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+         e += (long long)gridDim.x * blockDim.x) {
+        int p = (int)(e % RR);
+        long long r = e / RR;
+        int c = (int)(r % zc);
+        int n = (int)(r / zc);
+        const T* m = mom + ((long long)n * RR + p) * (2 * zc);
+        float mu = to_f<T>(m[c]), lv = to_f<T>(m[zc + c]);
+        if (clampv > 0.f) {
+            mu = fminf(fmaxf(mu, -clampv), clampv);
+            lv = fminf(fmaxf(lv, -clampv), clampv);
+        }
+        float ep = eps_in ? eps_in[e] : philox_normal(seed, offset, (uint64_t)e);
+        if (eps_out) eps_out[e] = ep;
+        float sd = __expf(0.5f * lv);
+        float zz = fmaf(ep, sd, mu);
+        mean[e] = mu; logvar[e] = lv; z_nchw[e] = zz;
+        if (stdv) stdv[e] = sd;
+        if (z_nhwc) z_nhwc[((long long)n * RR + p) * zc + c] = from_f<T>(zz);
+        acc += 0.5 * ((double)(sd * sd) + (double)mu * mu - 1.0 - (double)lv);
+    }
+    acc = block_sum_d(acc, shd);
+    if (threadIdx.x == 0 && kl_sum) atomicAdd(kl_sum, acc);
+}
+
+// d_moments[n][p][c]      = d_mean + d_z                       (masked by the clamp)
+// d_moments[n][p][zc + c] = d_logvar + d_z * eps * 0.5 * std   (masked by the clamp)
+template <typename T>
+__global__ void __launch_bounds__(256) reparam_kl_bwd_kernel(const float* __restrict__ d_mean,
+                                                             const float* __restrict__ d_logvar,
+                                                             const float* __restrict__ d_z, const float* __restrict__ logvar,
+                                                             const float* __restrict__ eps, const T* __restrict__ mom,
+                                                             T* __restrict__ d_mom, int B, int zc, int RR, float clampv) {
+    const long long total = (long long)B * zc * RR;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+         e += (long long)gridDim.x * blockDim.x) {
+        int p = (int)(e % RR);
+        long long r = e / RR;
+        int c = (int)(r % zc);
+        int n = (int)(r / zc);
+        float dz = d_z ? d_z[e] : 0.f;
+        float gm = (d_mean ? d_mean[e] : 0.f) + dz;
+        float lv = logvar[e];
+        float gl = (d_logvar ? d_logvar[e] : 0.f) + dz * eps[e] * 0.5f * __expf(0.5f * lv);
+        long long o = ((long long)n * RR + p) * (2 * zc);
+        if (clampv > 0.f) {
+            float mu_raw = to_f<T>(mom[o + c]), lv_raw = to_f<T>(mom[o + zc + c]);
+            if (mu_raw < -clampv || mu_raw > clampv) gm = 0.f;
+            if (lv_raw < -clampv || lv_raw > clampv) gl = 0.f;
+        }
+        d_mom[o + c] = from_f<T>(gm);
+        d_mom[o + zc + c] = from_f<T>(gl);
+    }
+}
+
+static int ew_blocks(long long total) {
+    long long b = (total + 255) / 256;
+    if (b > 148LL * 8) b = 148LL * 8;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+int reparam_fwd(const void* mom, const float* eps, float* eps_out, float* mean, float* logvar, float* stdv,
+                float* z_nchw, void* z_nhwc, double* kl_sum, int B, int zc, int R, float clampv, uint64_t seed, uint64_t offset,
+                int dtype, cudaStream_t st) {
+    long long total = (long long)B * zc * R * R;
+    if (dtype == MVAE_F32)
+        reparam_kl_fwd_kernel<float><<<ew_blocks(total), 256, 0, st>>>((const float*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
+                                                                        (float*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset);
+    else
+        reparam_kl_fwd_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>((const bf16*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
+                                                                       (bf16*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+int reparam_bwd(const float* d_mean, const float* d_logvar, const float* d_z, const float* logvar, const float* eps,
+                const void* mom, void* d_mom, int B, int zc, int R, float clampv, int dtype, cudaStream_t st) {
+    long long total = (long long)B * zc * R * R;
+    if (dtype == MVAE_F32)
+        reparam_kl_bwd_kernel<float><<<ew_blocks(total), 256, 0, st>>>(d_mean, d_logvar, d_z, logvar, eps, (const float*)mom,
+                                                                        (float*)d_mom, B, zc, R * R, clampv);
+    else
+        reparam_kl_bwd_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>(d_mean, d_logvar, d_z, logvar, eps, (const bf16*)mom,
+                                                                       (bf16*)d_mom, B, zc, R * R, clampv);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ reconstruction loss (+ unit grad)
+__global__ void __launch_bounds__(256) recon_loss_kernel(const float* __restrict__ r, const float* __restrict__ x,
+                                                         double* __restrict__ loss_sum, float* __restrict__ d_unit,
+                                                         long long n, int kind) {
+    __shared__ double shd[32];
+    const float inv_n = 1.0f / (float)n;
+    double acc = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float rv = r[i], xv = x[i], l, g;
+        if (kind == 0) { float d = rv - xv; l = d * d; g = 2.f * d; }
+        else if (kind == 1) { float d = rv - xv; l = fabsf(d); g = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); }
+        else {
+            // binary_cross_entropy_with_logits: max(r,0) - r*x + log1p(exp(-|r|)); d/dr = sigmoid(r) - x
+            l = fmaxf(rv, 0.f) - rv * xv + log1pf(__expf(-fabsf(rv)));
+            g = 1.f / (1.f + __expf(-rv)) - xv;
+        }
+        acc += (double)l;
+        if (d_unit) d_unit[i] = g * inv_n;
+    }
+    acc = block_sum_d(acc, shd);
+    if (threadIdx.x == 0) atomicAdd(loss_sum, acc);
+}
+int recon_loss(const float* r, const float* x, double* loss_sum, float* d_unit, long long n, int kind, cudaStream_t st) {
+    recon_loss_kernel<<<ew_blocks(n), 256, 0, st>>>(r, x, loss_sum, d_unit, n, kind);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+__global__ void __launch_bounds__(256) kl_fwd_kernel(const float* __restrict__ mean, const float* __restrict__ logvar,
+                                                     double* __restrict__ kl_sum, long long n) {
+    __shared__ double shd[32];
+    double acc = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float mu = mean[i], lv = logvar[i];
+        acc += 0.5 * ((double)__expf(lv) + (double)mu * mu - 1.0 - (double)lv);
+    }
+    acc = block_sum_d(acc, shd);
+    if (threadIdx.x == 0) atomicAdd(kl_sum, acc);
+}
+__global__ void kl_bwd_kernel(const float* __restrict__ mean, const float* __restrict__ logvar,
+                              const float* __restrict__ coef, float* __restrict__ d_mean, float* __restrict__ d_logvar,
+                              long long n) {
+    const float c = *coef;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        d_mean[i] = c * mean[i];
+        d_logvar[i] = c * 0.5f * (__expf(logvar[i]) - 1.f);
+    }
+}
+__global__ void scale_kernel(const float* __restrict__ in, const float* __restrict__ s, float* __restrict__ out, long long n) {
+    const float c = *s;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = in[i] * c;
+}
+int kl_fwd(const float* mean, const float* logvar, double* kl_sum, long long n, cudaStream_t st) {
+    kl_fwd_kernel<<<ew_blocks(n), 256, 0, st>>>(mean, logvar, kl_sum, n);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+int kl_bwd(const float* mean, const float* logvar, const float* coef, float* d_mean, float* d_logvar, long long n,
+           cudaStream_t st) {
+    kl_bwd_kernel<<<ew_blocks(n), 256, 0, st>>>(mean, logvar, coef, d_mean, d_logvar, n);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+int scale_dev(const float* in, const float* s, float* out, long long n, cudaStream_t st) {
+    scale_kernel<<<ew_blocks(n), 256, 0, st>>>(in, s, out, n);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ optimizer
+// pass 1: sum of squares of finite gradient entries (non-finite entries are treated as zero,
+// as lightning_module.py:468-477 zeroes them before clipping)
+__global__ void __launch_bounds__(256) grad_sqnorm_kernel(const float* const* __restrict__ grads,
+                                                          const long long* __restrict__ sizes, int nt,
+                                                          double* __restrict__ out) {
+    __shared__ double shd[32];
+    double acc = 0.0;
+    for (int t = blockIdx.y; t < nt; t += gridDim.y) {
+        const float* g = grads[t];
+        long long n = sizes[t];
+        for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+            float v = g[i];
+            if (isfinite(v)) acc += (double)v * v;
+        }
+    }
+    acc = block_sum_d(acc, shd);
+    if (threadIdx.x == 0 && acc != 0.0) atomicAdd(out, acc);
+}
+__global__ void __launch_bounds__(256) adamw_kernel(float* const* __restrict__ params, const float* const* __restrict__ grads,
+                                                    float* const* __restrict__ m1, float* const* __restrict__ m2,
+                                                    const long long* __restrict__ sizes, int nt,
+                                                    const double* __restrict__ sqnorm, float max_norm, float lr, float b1,
+                                                    float b2, float eps, float wd, int decoupled, float bc1, float bc2) {
+    float clip = 1.f;
+    if (max_norm > 0.f && sqnorm) {
+        float norm = (float)sqrt(*sqnorm);
+        float c = max_norm / (norm + 1e-6f);
+        clip = c < 1.f ? c : 1.f;
+    }
+    for (int t = blockIdx.y; t < nt; t += gridDim.y) {
+        float* p = params[t];
+        const float* g = grads[t];
+        float* a = m1[t];
+        float* b = m2[t];
+        long long n = sizes[t];
+        for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+            float gv = g[i];
+            gv = isfinite(gv) ? gv * clip : 0.f;
+            float pv = p[i];
+            if (decoupled) pv *= (1.f - lr * wd); else gv = fmaf(wd, pv, gv);
+            float m = fmaf(b1, a[i], (1.f - b1) * gv);
+            float v = fmaf(b2, b[i], (1.f - b2) * gv * gv);
+            a[i] = m; b[i] = v;
+            float denom = sqrtf(v) / sqrtf(bc2) + eps;
+            p[i] = pv - (lr / bc1) * (m / denom);
+        }
+    }
+}
+int grad_sqnorm(const float* const* grads, const long long* sizes, int nt, double* out, cudaStream_t st) {
+    dim3 grid(32, nt < 64 ? nt : 64);
+    grad_sqnorm_kernel<<<grid, 256, 0, st>>>(grads, sizes, nt, out);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+int adamw_step(float* const* params, const float* const* grads, float* const* m1, float* const* m2,
+               const long long* sizes, int nt, const double* sqnorm, float max_norm, float lr, float b1, float b2,
+               float eps, float wd, int decoupled, int step, cudaStream_t st) {
+    float bc1 = 1.f - powf(b1, (float)step), bc2 = 1.f - powf(b2, (float)step);
+    dim3 grid(32, nt < 64 ? nt : 64);
+    adamw_kernel<<<grid, 256, 0, st>>>(params, grads, m1, m2, sizes, nt, sqnorm, max_norm, lr, b1, b2, eps, wd, decoupled, bc1, bc2);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace mvae

@@ -1,0 +1,345 @@
+// Fused GroupNorm (+SiLU) forward / backward on NHWC activations.
+// Reference: Normalize = nn.GroupNorm(min(32,C), C, eps=1e-6, affine) followed by
+// nonlinearity = x*sigmoid(x)  (encoder_decoder.py:13-15, 28-33).
+//
+// HBM-bound.  Layout [B][HW][C]; a CTA streams whole pixel rows (all channels, coalesced 16 B
+// vectors), so group statistics are reduced from per-thread channel accumulators:
+//   pass 1 (stats):  grid (splits, B): per-(sample, split, group) shifted sums -> scratch
+//   pass 2 (apply):  grid (splits, B): folds the split partials (fp32, shifted by a per-group
+//                    pivot so E[x^2]-E[x]^2 does not cancel), normalises, applies SiLU.
+// Backward has the same two-pass shape and also fuses the residual-branch gradient add.
+#include "../../include/medvae_b200.h"
+#include "common.cuh"
+
+namespace mvae {
+
+constexpr int GN_THREADS = 256;
+constexpr int MAX_G = 32;
+
+int gn_splits(int B, int HW, int C) {
+    // enough CTAs to fill the machine (~4 per SM), at least 32 pixel rows per CTA
+    long long want = (148LL * 4 + B - 1) / B;
+    long long cap = (HW + 31) / 32;
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    if (want > 64) want = 64;
+    return (int)want;
+}
+
+// thread mapping for a [rows][C] slab processed VEC channels at a time
+struct RowMap {
+    int nvec, tpr, rpi, v, r;   // vectors per row, threads per row, rows per iteration, my vector, my row lane
+    bool active;
+};
+template <int VEC>
+__device__ __forceinline__ RowMap row_map(int C) {
+    RowMap m;
+    m.nvec = C / VEC;
+    m.tpr = m.nvec < GN_THREADS ? m.nvec : GN_THREADS;
+    m.rpi = GN_THREADS / m.tpr;
+    m.v = threadIdx.x % m.tpr;
+    m.r = threadIdx.x / m.tpr;
+    m.active = m.r < m.rpi;
+    return m;
+}
+
+template <typename T, int VEC> struct Ld;
+template <typename T> struct Ld<T, 8> {
+    static __device__ __forceinline__ void load(const T* p, float* f) { Vec8<T> v; v.load(p); v.unpack(f); }
+    static __device__ __forceinline__ void store(T* p, const float* f) { Vec8<T> v; v.pack(f); v.store(p); }
+};
+template <typename T> struct Ld<T, 1> {
+    static __device__ __forceinline__ void load(const T* p, float* f) { f[0] = to_f<T>(*p); }
+    static __device__ __forceinline__ void store(T* p, const float* f) { *p = from_f<T>(f[0]); }
+};
+
+// ------------------------------------------------------------------ forward: statistics
+template <typename T, int VEC>
+__global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const T* __restrict__ x, float* __restrict__ scratch,
+                                                              int HW, int C, int G, int S) {
+    __shared__ float sh_s[MAX_G], sh_q[MAX_G], pivot[MAX_G];
+    const int n = blockIdx.y, sp = blockIdx.x;
+    const int cpg = C / G;
+    const T* xn = x + (long long)n * HW * C;
+    if (threadIdx.x < G) {
+        sh_s[threadIdx.x] = 0.f; sh_q[threadIdx.x] = 0.f;
+        pivot[threadIdx.x] = to_f<T>(xn[threadIdx.x * cpg]);
+    }
+    __syncthreads();
+    const int p0 = (int)(((long long)HW * sp) / S), p1 = (int)(((long long)HW * (sp + 1)) / S);
+    for (int vb = 0; vb < C / VEC; vb += GN_THREADS) {
+        RowMap m = row_map<VEC>(C);
+        int v = vb + m.v;
+        if (m.active && v < m.nvec) {
+            float s[VEC], q[VEC], pv[VEC];
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) { s[j] = 0.f; q[j] = 0.f; pv[j] = pivot[(v * VEC + j) / cpg]; }
+            for (int p = p0 + m.r; p < p1; p += m.rpi) {
+                float f[VEC];
+                Ld<T, VEC>::load(xn + (long long)p * C + v * VEC, f);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) { float d = f[j] - pv[j]; s[j] += d; q[j] = fmaf(d, d, q[j]); }
+            }
+            // fold the channel lanes that share a group before touching shared memory
+            int g_prev = (v * VEC) / cpg; float as = 0.f, aq = 0.f;
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                int g = (v * VEC + j) / cpg;
+                if (g != g_prev) { atomicAdd(&sh_s[g_prev], as); atomicAdd(&sh_q[g_prev], aq); as = 0.f; aq = 0.f; g_prev = g; }
+                as += s[j]; aq += q[j];
+            }
+            atomicAdd(&sh_s[g_prev], as); atomicAdd(&sh_q[g_prev], aq);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < G) {
+        float* o = scratch + (((long long)n * S + sp) * G + threadIdx.x) * 2;
+        o[0] = sh_s[threadIdx.x]; o[1] = sh_q[threadIdx.x];
+    }
+}
+
+// ------------------------------------------------------------------ forward: normalise (+SiLU)
+template <typename T, int VEC>
+__global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ gamma,
+                                                              const float* __restrict__ beta, T* __restrict__ y,
+                                                              float* __restrict__ stats, const float* __restrict__ scratch,
+                                                              int HW, int C, int G, int S, float eps, int silu) {
+    __shared__ float mean[MAX_G], rstd[MAX_G];
+    const int n = blockIdx.y, sp = blockIdx.x;
+    const int cpg = C / G;
+    const T* xn = x + (long long)n * HW * C;
+    T* yn = y + (long long)n * HW * C;
+    if (threadIdx.x < G) {
+        float s = 0.f, q = 0.f;
+        for (int k = 0; k < S; ++k) {
+            const float* o = scratch + (((long long)n * S + k) * G + threadIdx.x) * 2;
+            s += o[0]; q += o[1];
+        }
+        float cnt = (float)HW * (float)cpg;
+        float m = s / cnt;
+        float var = q / cnt - m * m;
+        if (var < 0.f) var = 0.f;
+        float mu = to_f<T>(xn[threadIdx.x * cpg]) + m;
+        float rs = rsqrtf(var + eps);
+        mean[threadIdx.x] = mu; rstd[threadIdx.x] = rs;
+        if (sp == 0) { stats[((long long)n * G + threadIdx.x) * 2] = mu; stats[((long long)n * G + threadIdx.x) * 2 + 1] = rs; }
+    }
+    __syncthreads();
+    const int p0 = (int)(((long long)HW * sp) / S), p1 = (int)(((long long)HW * (sp + 1)) / S);
+    for (int vb = 0; vb < C / VEC; vb += GN_THREADS) {
+        RowMap m = row_map<VEC>(C);
+        int v = vb + m.v;
+        if (m.active && v < m.nvec) {
+            float a[VEC], b[VEC];   // y = x*a + b
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                int c = v * VEC + j, g = c / cpg;
+                a[j] = rstd[g] * gamma[c];
+                b[j] = beta[c] - mean[g] * a[j];
+            }
+            for (int p = p0 + m.r; p < p1; p += m.rpi) {
+                float f[VEC];
+                Ld<T, VEC>::load(xn + (long long)p * C + v * VEC, f);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    float u = fmaf(f[j], a[j], b[j]);
+                    f[j] = silu ? u * sigmoidf_(u) : u;
+                }
+                Ld<T, VEC>::store(yn + (long long)p * C + v * VEC, f);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ backward: reductions
+// per (n, split, g): s1 = sum du*gamma, s2 = sum du*gamma*xhat;  per channel: dgamma += du*xhat,
+// dbeta += du, where u = xhat*gamma+beta and du = dy * silu'(u) (or dy).
+template <typename T, int VEC>
+__global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                                  const float* __restrict__ gamma,
+                                                                  const float* __restrict__ beta,
+                                                                  const float* __restrict__ stats,
+                                                                  float* __restrict__ scratch, float* __restrict__ dgamma,
+                                                                  float* __restrict__ dbeta, int HW, int C, int G, int S,
+                                                                  int silu) {
+    __shared__ float sh1[MAX_G], sh2[MAX_G], mean[MAX_G], rstd[MAX_G];
+    extern __shared__ float chan[];   // [2][C] per-channel dgamma / dbeta of this CTA
+    const int n = blockIdx.y, sp = blockIdx.x;
+    const int cpg = C / G;
+    if (threadIdx.x < G) {
+        sh1[threadIdx.x] = 0.f; sh2[threadIdx.x] = 0.f;
+        mean[threadIdx.x] = stats[((long long)n * G + threadIdx.x) * 2];
+        rstd[threadIdx.x] = stats[((long long)n * G + threadIdx.x) * 2 + 1];
+    }
+    for (int i = threadIdx.x; i < 2 * C; i += GN_THREADS) chan[i] = 0.f;
+    __syncthreads();
+    const T* xn = x + (long long)n * HW * C;
+    const T* dn = dy + (long long)n * HW * C;
+    const int p0 = (int)(((long long)HW * sp) / S), p1 = (int)(((long long)HW * (sp + 1)) / S);
+    for (int vb = 0; vb < C / VEC; vb += GN_THREADS) {
+        RowMap m = row_map<VEC>(C);
+        int v = vb + m.v;
+        if (m.active && v < m.nvec) {
+            float ga[VEC], be[VEC], mu[VEC], rs[VEC], dg[VEC], db[VEC], a1[VEC], a2[VEC];
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                int c = v * VEC + j, g = c / cpg;
+                ga[j] = gamma[c]; be[j] = beta[c]; mu[j] = mean[g]; rs[j] = rstd[g];
+                dg[j] = 0.f; db[j] = 0.f; a1[j] = 0.f; a2[j] = 0.f;
+            }
+            for (int p = p0 + m.r; p < p1; p += m.rpi) {
+                float fx[VEC], fd[VEC];
+                Ld<T, VEC>::load(xn + (long long)p * C + v * VEC, fx);
+                Ld<T, VEC>::load(dn + (long long)p * C + v * VEC, fd);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    float xh = (fx[j] - mu[j]) * rs[j];
+                    float du = fd[j];
+                    if (silu) {
+                        float u = fmaf(xh, ga[j], be[j]);
+                        float sg = sigmoidf_(u);
+                        du *= sg * (1.f + u * (1.f - sg));
+                    }
+                    dg[j] = fmaf(du, xh, dg[j]); db[j] += du;
+                    float dxh = du * ga[j];
+                    a1[j] += dxh; a2[j] = fmaf(dxh, xh, a2[j]);
+                }
+            }
+            int g_prev = (v * VEC) / cpg; float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                int c = v * VEC + j, g = c / cpg;
+                if (g != g_prev) { atomicAdd(&sh1[g_prev], s1); atomicAdd(&sh2[g_prev], s2); s1 = 0.f; s2 = 0.f; g_prev = g; }
+                s1 += a1[j]; s2 += a2[j];
+                atomicAdd(&chan[c], dg[j]); atomicAdd(&chan[C + c], db[j]);
+            }
+            atomicAdd(&sh1[g_prev], s1); atomicAdd(&sh2[g_prev], s2);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < G) {
+        float* o = scratch + (((long long)n * S + sp) * G + threadIdx.x) * 2;
+        o[0] = sh1[threadIdx.x]; o[1] = sh2[threadIdx.x];
+    }
+    for (int c = threadIdx.x; c < C; c += GN_THREADS) {
+        atomicAdd(&dgamma[c], chan[c]);
+        atomicAdd(&dbeta[c], chan[C + c]);
+    }
+}
+
+// ------------------------------------------------------------------ backward: dx
+// dx = rstd * (dxh - (s1 + xhat*s2)/Ng) + dx_add
+template <typename T, int VEC>
+__global__ void __launch_bounds__(GN_THREADS) gn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                                  const float* __restrict__ gamma,
+                                                                  const float* __restrict__ beta,
+                                                                  const float* __restrict__ stats,
+                                                                  const float* __restrict__ scratch,
+                                                                  const T* __restrict__ dx_add, T* __restrict__ dx,
+                                                                  int HW, int C, int G, int S, int silu) {
+    __shared__ float mean[MAX_G], rstd[MAX_G], m1[MAX_G], m2[MAX_G];
+    const int n = blockIdx.y, sp = blockIdx.x;
+    const int cpg = C / G;
+    if (threadIdx.x < G) {
+        float s1 = 0.f, s2 = 0.f;
+        for (int k = 0; k < S; ++k) {
+            const float* o = scratch + (((long long)n * S + k) * G + threadIdx.x) * 2;
+            s1 += o[0]; s2 += o[1];
+        }
+        float cnt = (float)HW * (float)cpg;
+        m1[threadIdx.x] = s1 / cnt; m2[threadIdx.x] = s2 / cnt;
+        mean[threadIdx.x] = stats[((long long)n * G + threadIdx.x) * 2];
+        rstd[threadIdx.x] = stats[((long long)n * G + threadIdx.x) * 2 + 1];
+    }
+    __syncthreads();
+    const long long base = (long long)n * HW * C;
+    const int p0 = (int)(((long long)HW * sp) / S), p1 = (int)(((long long)HW * (sp + 1)) / S);
+    for (int vb = 0; vb < C / VEC; vb += GN_THREADS) {
+        RowMap m = row_map<VEC>(C);
+        int v = vb + m.v;
+        if (m.active && v < m.nvec) {
+            float ga[VEC], be[VEC], mu[VEC], rs[VEC], c1[VEC], c2[VEC];
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                int c = v * VEC + j, g = c / cpg;
+                ga[j] = gamma[c]; be[j] = beta[c]; mu[j] = mean[g]; rs[j] = rstd[g]; c1[j] = m1[g]; c2[j] = m2[g];
+            }
+            for (int p = p0 + m.r; p < p1; p += m.rpi) {
+                long long off = base + (long long)p * C + v * VEC;
+                float fx[VEC], fd[VEC], fa[VEC];
+                Ld<T, VEC>::load(x + off, fx);
+                Ld<T, VEC>::load(dy + off, fd);
+                if (dx_add) Ld<T, VEC>::load(dx_add + off, fa);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    float xh = (fx[j] - mu[j]) * rs[j];
+                    float du = fd[j];
+                    if (silu) {
+                        float u = fmaf(xh, ga[j], be[j]);
+                        float sg = sigmoidf_(u);
+                        du *= sg * (1.f + u * (1.f - sg));
+                    }
+                    float r = rs[j] * (du * ga[j] - c1[j] - xh * c2[j]);
+                    fx[j] = dx_add ? r + fa[j] : r;
+                }
+                Ld<T, VEC>::store(dx + off, fx);
+            }
+        }
+    }
+}
+
+template <typename T, int VEC>
+static int gn_fwd_t(const T* x, const float* gamma, const float* beta, T* y, float* stats, float* scratch, int B,
+                    int HW, int C, int G, float eps, int silu, cudaStream_t st) {
+    int S = gn_splits(B, HW, C);
+    dim3 grid(S, B);
+    gn_stats_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(x, scratch, HW, C, G, S);
+    MVAE_LAUNCH_CHECK();
+    gn_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(x, gamma, beta, y, stats, scratch, HW, C, G, S, eps, silu);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+template <typename T, int VEC>
+static int gn_bwd_t(const T* dy, const T* x, const float* gamma, const float* beta, const float* stats,
+                    const T* dx_add, T* dx, float* dgamma, float* dbeta, float* scratch, int B, int HW, int C, int G,
+                    int silu, cudaStream_t st) {
+    int S = gn_splits(B, HW, C);
+    dim3 grid(S, B);
+    gn_bwd_stats_kernel<T, VEC><<<grid, GN_THREADS, sizeof(float) * 2 * C, st>>>(dy, x, gamma, beta, stats, scratch,
+                                                                                  dgamma, dbeta, HW, C, G, S, silu);
+    MVAE_LAUNCH_CHECK();
+    gn_bwd_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(dy, x, gamma, beta, stats, scratch, dx_add, dx, HW, C, G,
+                                                              S, silu);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+int gn_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, float* scratch, int B, int HW,
+           int C, int G, float eps, int silu, int dtype, cudaStream_t st) {
+    MVAE_CHECK(G >= 1 && G <= MAX_G && C % G == 0, "groupnorm: bad groups %d for C=%d", G, C);
+    const bool vec8 = (C % 8 == 0) && (C / 8 <= GN_THREADS || (C / 8) % GN_THREADS == 0);
+    MVAE_CHECK(vec8 || C <= GN_THREADS, "groupnorm: unsupported channel count %d", C);
+    if (dtype == MVAE_F32)
+        return vec8 ? gn_fwd_t<float, 8>((const float*)x, gamma, beta, (float*)y, stats, scratch, B, HW, C, G, eps, silu, st)
+                    : gn_fwd_t<float, 1>((const float*)x, gamma, beta, (float*)y, stats, scratch, B, HW, C, G, eps, silu, st);
+    return vec8 ? gn_fwd_t<bf16, 8>((const bf16*)x, gamma, beta, (bf16*)y, stats, scratch, B, HW, C, G, eps, silu, st)
+                : gn_fwd_t<bf16, 1>((const bf16*)x, gamma, beta, (bf16*)y, stats, scratch, B, HW, C, G, eps, silu, st);
+}
+int gn_bwd(const void* dy, const void* x, const float* gamma, const float* beta, const float* stats,
+           const void* dx_add, void* dx, float* dgamma, float* dbeta, float* scratch, int B, int HW, int C, int G,
+           int silu, int dtype, cudaStream_t st) {
+    MVAE_CHECK(G >= 1 && G <= MAX_G && C % G == 0, "groupnorm: bad groups %d for C=%d", G, C);
+    const bool vec8 = (C % 8 == 0) && (C / 8 <= GN_THREADS || (C / 8) % GN_THREADS == 0);
+    MVAE_CHECK(vec8 || C <= GN_THREADS, "groupnorm: unsupported channel count %d", C);
+    if (dtype == MVAE_F32)
+        return vec8 ? gn_bwd_t<float, 8>((const float*)dy, (const float*)x, gamma, beta, stats, (const float*)dx_add,
+                                         (float*)dx, dgamma, dbeta, scratch, B, HW, C, G, silu, st)
+                    : gn_bwd_t<float, 1>((const float*)dy, (const float*)x, gamma, beta, stats, (const float*)dx_add,
+                                         (float*)dx, dgamma, dbeta, scratch, B, HW, C, G, silu, st);
+    return vec8 ? gn_bwd_t<bf16, 8>((const bf16*)dy, (const bf16*)x, gamma, beta, stats, (const bf16*)dx_add, (bf16*)dx,
+                                    dgamma, dbeta, scratch, B, HW, C, G, silu, st)
+                : gn_bwd_t<bf16, 1>((const bf16*)dy, (const bf16*)x, gamma, beta, stats, (const bf16*)dx_add, (bf16*)dx,
+                                    dgamma, dbeta, scratch, B, HW, C, G, silu, st);
+}
+
+}  // namespace mvae

@@ -1,0 +1,414 @@
+// Operand packing, wgrad finalisation, bias-gradient column sums, layout conversion and the
+// input stage (NCHW -> NHWC + modality-conditioning map).
+#include "conv_lower.h"
+
+namespace mvae {
+
+// ------------------------------------------------------------------ weight packing
+// nn.Conv2d weight [Cout][Cin][R][R] fp32 -> fprop operand [slab][Ctot][Cin] (rows co_off..)
+// and dgrad operand [slab][Cin][Ctot] (cols co_off..).  UP mode folds the nearest-2x upsample
+// into 16 slabs of 2x2 taps: Weff[a,b,ui,vi] = sum_{r in R(a,ui)} sum_{s in R(b,vi)} W[r,s].
+__device__ __forceinline__ void up_rset(int a, int ui, int& lo, int& hi) {
+    // R(0,0)={0}  R(0,1)={1,2}  R(1,0)={0,1}  R(1,1)={2}
+    if (a == 0) { lo = ui == 0 ? 0 : 1; hi = ui == 0 ? 0 : 2; }
+    else        { lo = ui == 0 ? 0 : 2; hi = ui == 0 ? 1 : 2; }
+}
+
+template <typename T>
+__global__ void pack_weights_kernel(const float* __restrict__ w, T* __restrict__ wf, T* __restrict__ wd,
+                                    int Cout, int Cin, int R, int mode, int nslabs, int Ctot, int co_off) {
+    long long total = (long long)nslabs * Cout * Cin;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        int ci = (int)(i % Cin);
+        long long r_ = i / Cin;
+        int co = (int)(r_ % Cout);
+        int slab = (int)(r_ / Cout);
+        const float* src = w + ((long long)co * Cin + ci) * R * R;
+        float v;
+        if (mode == MVAE_CONV_UP) {
+            int vi = slab & 1, ui = (slab >> 1) & 1, b = (slab >> 2) & 1, a = (slab >> 3) & 1;
+            int rlo, rhi, slo, shi;
+            up_rset(a, ui, rlo, rhi);
+            up_rset(b, vi, slo, shi);
+            v = 0.f;
+            for (int r = rlo; r <= rhi; ++r)
+                for (int s = slo; s <= shi; ++s) v += src[r * 3 + s];
+        } else {
+            v = src[slab];
+        }
+        if (wf) wf[((long long)slab * Ctot + co_off + co) * Cin + ci] = from_f<T>(v);
+        if (wd) wd[((long long)slab * Cin + ci) * Ctot + co_off + co] = from_f<T>(v);
+    }
+}
+
+int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot, int co_off, int dtype,
+                 cudaStream_t st) {
+    int nslabs = conv_num_slabs(g);
+    long long total = (long long)nslabs * g.Cout * g.Cin;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (dtype == MVAE_F32)
+        pack_weights_kernel<float><<<blocks, 256, 0, st>>>(w, (float*)wf, (float*)wd, g.Cout, g.Cin, g.R, g.mode,
+                                                            nslabs, Ctot, co_off);
+    else
+        pack_weights_kernel<bf16><<<blocks, 256, 0, st>>>(w, (bf16*)wf, (bf16*)wd, g.Cout, g.Cin, g.R, g.mode,
+                                                           nslabs, Ctot, co_off);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ wgrad finalisation
+// partial [splits][nslabs][Cout][Cin] fp32 -> dW [Cout][Cin][R][R] fp32 (sum over splits; UP
+// mode: each (r,s) receives the 4 slabs whose R-sets contain it).
+__global__ void wgrad_finalize_kernel(const float* __restrict__ partial, float* __restrict__ dw, int splits,
+                                      int nslabs, int Cout, int Cin, int R, int mode) {
+    long long total = (long long)Cout * Cin * R * R;
+    long long slab_stride = (long long)Cout * Cin;
+    long long split_stride = slab_stride * nslabs;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        // iterate with ci fastest for coalesced partial reads: i -> (rs, co, ci)
+        int ci = (int)(i % Cin);
+        long long r_ = i / Cin;
+        int co = (int)(r_ % Cout);
+        int rs = (int)(r_ / Cout);
+        int r = rs / R, s = rs % R;
+        float acc = 0.f;
+        if (mode == MVAE_CONV_UP) {
+            for (int a = 0; a < 2; ++a) {
+                int ui = (a == 0) ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0);
+                for (int b = 0; b < 2; ++b) {
+                    int vi = (b == 0) ? (s == 0 ? 0 : 1) : (s == 2 ? 1 : 0);
+                    int slab = ((a * 2 + b) * 2 + ui) * 2 + vi;
+                    const float* p = partial + slab * slab_stride + (long long)co * Cin + ci;
+                    for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+                }
+            }
+        } else {
+            const float* p = partial + rs * slab_stride + (long long)co * Cin + ci;
+            for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+        }
+        dw[((long long)co * Cin + ci) * R * R + rs] = acc;
+    }
+}
+
+int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int splits, cudaStream_t st) {
+    long long total = (long long)g.Cout * g.Cin * g.R * g.R;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    wgrad_finalize_kernel<<<blocks, 256, 0, st>>>(partial, dw, splits, conv_num_slabs(g), g.Cout, g.Cin, g.R, g.mode);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ bias gradient: column sums
+// db[c] = sum_rows dy[row][c];  dy dense [M][C].  Two stages (deterministic): per-CTA partial
+// rows in `scratch` ([gridDim.x][C]), then a fold.
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const T* __restrict__ dy, float* __restrict__ scratch,
+                                                             long long M, int C, long long rows_per_cta) {
+    __shared__ float sh[256];
+    const long long r0 = blockIdx.x * rows_per_cta;
+    long long r1 = r0 + rows_per_cta;
+    if (r1 > M) r1 = M;
+    // threads: tc = channel lane, tr = row lane
+    const int tpr = C < 256 ? C : 256;       // threads per row
+    const int rpi = 256 / tpr;               // rows per iteration
+    const int tc = threadIdx.x % tpr, tr = threadIdx.x / tpr;
+    for (int cb = 0; cb < C; cb += tpr) {
+        float acc = 0.f;
+        int c = cb + tc;
+        if (tr < rpi && c < C)
+            for (long long r = r0 + tr; r < r1; r += rpi) acc += to_f<T>(dy[r * C + c]);
+        sh[threadIdx.x] = (tr < rpi) ? acc : 0.f;
+        __syncthreads();
+        if (tr == 0 && c < C) {
+            float s = 0.f;
+            for (int j = 0; j < rpi; ++j) s += sh[j * tpr + tc];
+            scratch[(long long)blockIdx.x * C + c] = s;
+        }
+        __syncthreads();
+    }
+}
+__global__ void colsum_fold_kernel(const float* __restrict__ scratch, float* __restrict__ db, int parts, int C) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float s = 0.f;
+    for (int p = 0; p < parts; ++p) s += scratch[(long long)p * C + c];
+    db[c] = s;
+}
+
+int colsum_parts(long long M) {
+    long long parts = (M + 127) / 128;
+    if (parts > 592) parts = 592;
+    if (parts < 1) parts = 1;
+    return (int)parts;
+}
+
+int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dtype, cudaStream_t st) {
+    int parts = colsum_parts(M);
+    long long rpc = (M + parts - 1) / parts;
+    parts = (int)((M + rpc - 1) / rpc);
+    if (dtype == MVAE_F32)
+        colsum_partial_kernel<float><<<parts, 256, 0, st>>>((const float*)dy, scratch, M, C, rpc);
+    else
+        colsum_partial_kernel<bf16><<<parts, 256, 0, st>>>((const bf16*)dy, scratch, M, C, rpc);
+    MVAE_LAUNCH_CHECK();
+    colsum_fold_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, db, parts, C);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ layout conversion
+template <typename T>
+__global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, float* __restrict__ dst, int B, int HW, int Cs,
+                                    int c_off, int Cd) {
+    long long total = (long long)B * Cd * HW;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        int p = (int)(i % HW);
+        long long r = i / HW;
+        int c = (int)(r % Cd);
+        int n = (int)(r / Cd);
+        dst[i] = to_f<T>(src[((long long)n * HW + p) * Cs + c_off + c]);
+    }
+}
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, T* __restrict__ dst, int B, int HW, int C) {
+    long long total = (long long)B * C * HW;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        int c = (int)(i % C);
+        long long r = i / C;
+        int p = (int)(r % HW);
+        int n = (int)(r / HW);
+        dst[i] = from_f<T>(src[((long long)n * C + c) * HW + p]);
+    }
+}
+
+static int ew_blocks(long long total) {
+    long long b = (total + 255) / 256;
+    if (b > 148LL * 32) b = 148LL * 32;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+int nhwc_to_nchw(const void* src, float* dst, int B, int HW, int Cs, int c_off, int Cd, int dtype, cudaStream_t st) {
+    long long total = (long long)B * Cd * HW;
+    if (dtype == MVAE_F32)
+        nhwc_to_nchw_kernel<float><<<ew_blocks(total), 256, 0, st>>>((const float*)src, dst, B, HW, Cs, c_off, Cd);
+    else
+        nhwc_to_nchw_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>((const bf16*)src, dst, B, HW, Cs, c_off, Cd);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+int nchw_to_nhwc(const float* src, void* dst, int B, int HW, int C, int dtype, cudaStream_t st) {
+    long long total = (long long)B * C * HW;
+    if (dtype == MVAE_F32)
+        nchw_to_nhwc_kernel<float><<<ew_blocks(total), 256, 0, st>>>(src, (float*)dst, B, HW, C);
+    else
+        nchw_to_nhwc_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>(src, (bf16*)dst, B, HW, C);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ input stage
+// F.interpolate(mode="bilinear", align_corners=False) source coordinates for an 8 -> size resize
+__device__ __forceinline__ void bilinear_src(int o, int out_size, int& i0, int& i1, float& l1) {
+    float scale = 8.0f / (float)out_size;
+    float s = ((float)o + 0.5f) * scale - 0.5f;
+    if (s < 0.f) s = 0.f;
+    i0 = (int)s;
+    if (i0 > 7) i0 = 7;
+    i1 = i0 + (i0 < 7 ? 1 : 0);
+    l1 = s - (float)i0;
+}
+
+// out[n,y,x, 0:C) = x ; out[n,y,x, C:2C) = bilinear(ReLU(W cond_n + b)) ; rest zero
+template <typename T>
+__global__ void input_pack_kernel(const float* __restrict__ x, const float* __restrict__ cond,
+                                  const float* __restrict__ w, const float* __restrict__ b, T* __restrict__ out,
+                                  int B, int C, int H, int W, int cond_dim, int out_c) {
+    extern __shared__ float cmap[];   // [C][64] low-res condition map of this image
+    const int n = blockIdx.y;
+    if (w) {
+        for (int i = threadIdx.x; i < C * 64; i += blockDim.x) {
+            float acc = b[i];
+            for (int k = 0; k < cond_dim; ++k) acc = fmaf(w[(long long)i * cond_dim + k], cond[n * cond_dim + k], acc);
+            cmap[i] = acc > 0.f ? acc : 0.f;
+        }
+    }
+    __syncthreads();
+    const int HW = H * W;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += gridDim.x * blockDim.x) {
+        int yy = p / W, xx = p % W;
+        T* o = out + ((long long)n * HW + p) * out_c;
+        for (int c = 0; c < C; ++c) o[c] = from_f<T>(x[((long long)n * C + c) * HW + p]);
+        int c_done = C;
+        if (w) {
+            int y0, y1, x0, x1; float ly, lx;
+            bilinear_src(yy, H, y0, y1, ly);
+            bilinear_src(xx, W, x0, x1, lx);
+            for (int c = 0; c < C; ++c) {
+                const float* m = cmap + c * 64;
+                float v = (1.f - ly) * ((1.f - lx) * m[y0 * 8 + x0] + lx * m[y0 * 8 + x1]) +
+                          ly * ((1.f - lx) * m[y1 * 8 + x0] + lx * m[y1 * 8 + x1]);
+                o[C + c] = from_f<T>(v);
+            }
+            c_done = 2 * C;
+        }
+        for (int c = c_done; c < out_c; ++c) o[c] = from_f<T>(0.f);
+    }
+}
+
+int input_pack_fwd(const float* x, const float* cond, const float* w, const float* b, void* out, int B, int C,
+                   int H, int W, int cond_dim, int out_c, int dtype, cudaStream_t st) {
+    int HW = H * W;
+    dim3 grid((HW + 255) / 256 < 64 ? (HW + 255) / 256 : 64, B);
+    size_t sh = w ? sizeof(float) * C * 64 : 0;
+    if (dtype == MVAE_F32)
+        input_pack_kernel<float><<<grid, 256, sh, st>>>(x, cond, w, b, (float*)out, B, C, H, W, cond_dim, out_c);
+    else
+        input_pack_kernel<bf16><<<grid, 256, sh, st>>>(x, cond, w, b, (bf16*)out, B, C, H, W, cond_dim, out_c);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// backward of the condition branch.  One CTA per (channel c, image-chunk); it first reduces
+// d_map (H x W) of each image onto the 8x8 grid (transpose of the bilinear resize), masks by
+// ReLU, and accumulates dW[c*64+q][k] += g * cond[n][k], db[c*64+q] += g with fp32 atomics.
+template <typename T>
+__global__ void __launch_bounds__(256) input_pack_bwd_kernel(const T* __restrict__ d_in, const float* __restrict__ cond,
+                                                             const float* __restrict__ w, const float* __restrict__ b,
+                                                             float* __restrict__ dw, float* __restrict__ db, int B,
+                                                             int C, int H, int W, int cond_dim, int out_c) {
+    __shared__ float g8[64];
+    const int c = blockIdx.x;
+    const int HW = H * W;
+    for (int n = blockIdx.y; n < B; n += gridDim.y) {
+        if (threadIdx.x < 64) g8[threadIdx.x] = 0.f;
+        __syncthreads();
+        for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+            int yy = p / W, xx = p % W;
+            float g = to_f<T>(d_in[((long long)n * HW + p) * out_c + C + c]);
+            int y0, y1, x0, x1; float ly, lx;
+            bilinear_src(yy, H, y0, y1, ly);
+            bilinear_src(xx, W, x0, x1, lx);
+            atomicAdd(&g8[y0 * 8 + x0], g * (1.f - ly) * (1.f - lx));
+            atomicAdd(&g8[y0 * 8 + x1], g * (1.f - ly) * lx);
+            atomicAdd(&g8[y1 * 8 + x0], g * ly * (1.f - lx));
+            atomicAdd(&g8[y1 * 8 + x1], g * ly * lx);
+        }
+        __syncthreads();
+        if (threadIdx.x < 64) {
+            int row = c * 64 + threadIdx.x;
+            float pre = b[row];
+            for (int k = 0; k < cond_dim; ++k) pre = fmaf(w[(long long)row * cond_dim + k], cond[n * cond_dim + k], pre);
+            float g = pre > 0.f ? g8[threadIdx.x] : 0.f;
+            if (g != 0.f) {
+                atomicAdd(&db[row], g);
+                for (int k = 0; k < cond_dim; ++k) {
+                    float cv = cond[n * cond_dim + k];
+                    if (cv != 0.f) atomicAdd(&dw[(long long)row * cond_dim + k], g * cv);
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+int input_pack_bwd(const void* d_in, const float* cond, const float* w, const float* b, float* dw, float* db,
+                   int B, int C, int H, int W, int cond_dim, int out_c, int dtype, cudaStream_t st) {
+    MVAE_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)C * 64 * cond_dim, st));
+    MVAE_CUDA(cudaMemsetAsync(db, 0, sizeof(float) * (size_t)C * 64, st));
+    dim3 grid(C, B < 128 ? B : 128);
+    if (dtype == MVAE_F32)
+        input_pack_bwd_kernel<float><<<grid, 256, 0, st>>>((const float*)d_in, cond, w, b, dw, db, B, C, H, W,
+                                                            cond_dim, out_c);
+    else
+        input_pack_bwd_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)d_in, cond, w, b, dw, db, B, C, H, W,
+                                                           cond_dim, out_c);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ disentangled input projector
+template <typename T>
+__global__ void dis_input_kernel(const float* __restrict__ x, const long long* __restrict__ idx,
+                                 const float* __restrict__ pw, const float* __restrict__ pb,
+                                 const int* __restrict__ is_gray, T* __restrict__ out, int B, int xc, int HW,
+                                 int n_mod, int out_c) {
+    long long total = (long long)B * HW;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        int p = (int)(i % HW);
+        int n = (int)(i / HW);
+        long long m = idx[n];
+        if (m >= n_mod) m = n_mod - 1;
+        if (m < 0) m = 0;
+        T* o = out + i * out_c;
+        if (is_gray[m]) {
+            float v = x[((long long)n * xc) * HW + p];
+            for (int c = 0; c < 3; ++c) o[c] = from_f<T>(fmaf(pw[m * 3 + c], v, pb[m * 3 + c]));
+        } else {
+            for (int c = 0; c < 3; ++c) o[c] = from_f<T>(c < xc ? x[((long long)n * xc + c) * HW + p] : 0.f);
+        }
+        for (int c = 3; c < out_c; ++c) o[c] = from_f<T>(0.f);
+    }
+}
+int dis_input_fwd(const float* x, const long long* idx, const float* pw, const float* pb, const int* is_gray,
+                  void* out, int B, int xc, int HW, int n_mod, int out_c, int dtype, cudaStream_t st) {
+    long long total = (long long)B * HW;
+    if (dtype == MVAE_F32)
+        dis_input_kernel<float><<<ew_blocks(total), 256, 0, st>>>(x, idx, pw, pb, is_gray, (float*)out, B, xc, HW, n_mod, out_c);
+    else
+        dis_input_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>(x, idx, pw, pb, is_gray, (bf16*)out, B, xc, HW, n_mod, out_c);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+// d_pw[m][c] += sum_p d_in[n,p,c] * x[n,0,p];  d_pb[m][c] += sum_p d_in[n,p,c]  for gray samples
+template <typename T>
+__global__ void __launch_bounds__(256) dis_input_bwd_kernel(const T* __restrict__ d_in, const float* __restrict__ x,
+                                                            const long long* __restrict__ idx,
+                                                            const int* __restrict__ is_gray, float* __restrict__ dpw,
+                                                            float* __restrict__ dpb, int B, int xc, int HW, int n_mod,
+                                                            int out_c) {
+    __shared__ float sh[32];
+    const int n = blockIdx.x;
+    long long m = idx[n];
+    if (m >= n_mod) m = n_mod - 1;
+    if (m < 0) m = 0;
+    if (!is_gray[m]) return;
+    float aw[3] = {0.f, 0.f, 0.f}, ab[3] = {0.f, 0.f, 0.f};
+    for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+        float v = x[((long long)n * xc) * HW + p];
+        const T* g = d_in + ((long long)n * HW + p) * out_c;
+        for (int c = 0; c < 3; ++c) {
+            float gg = to_f<T>(g[c]);
+            aw[c] = fmaf(gg, v, aw[c]);
+            ab[c] += gg;
+        }
+    }
+    for (int c = 0; c < 3; ++c) {
+        float s = block_sum(aw[c], sh);
+        float t = block_sum(ab[c], sh);
+        if (threadIdx.x == 0) {
+            atomicAdd(&dpw[m * 3 + c], s);
+            atomicAdd(&dpb[m * 3 + c], t);
+        }
+    }
+}
+int dis_input_bwd(const void* d_in, const float* x, const long long* idx, const int* is_gray, float* dpw,
+                  float* dpb, int B, int xc, int HW, int n_mod, int out_c, int dtype, cudaStream_t st) {
+    MVAE_CUDA(cudaMemsetAsync(dpw, 0, sizeof(float) * n_mod * 3, st));
+    MVAE_CUDA(cudaMemsetAsync(dpb, 0, sizeof(float) * n_mod * 3, st));
+    if (dtype == MVAE_F32)
+        dis_input_bwd_kernel<float><<<B, 256, 0, st>>>((const float*)d_in, x, idx, is_gray, dpw, dpb, B, xc, HW, n_mod, out_c);
+    else
+        dis_input_bwd_kernel<bf16><<<B, 256, 0, st>>>((const bf16*)d_in, x, idx, is_gray, dpw, dpb, B, xc, HW, n_mod, out_c);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace mvae

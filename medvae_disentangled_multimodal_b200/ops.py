@@ -1,0 +1,198 @@
+"""Tensor-level wrappers over the C ABI (one Python function per entry point family).
+
+All activations are NHWC torch tensors ([B, H, W, C], bf16 or fp32) living on the current CUDA
+device; work is enqueued on torch's current stream.  Nothing here computes with torch ops.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+from ._lib import ConvDesc, check, lib, ptr, stream
+
+_scratch = {}
+
+
+def scratch(name: str, nbytes: int, device) -> torch.Tensor:
+    """grow-only byte scratch buffers, one per (name, device, stream-agnostic): kernels that use
+    them are ordered on the current stream."""
+    key = (name, str(device))
+    t = _scratch.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.empty(max(nbytes, 1024), dtype=torch.uint8, device=device)
+        _scratch[key] = t
+    return t
+
+
+def conv_desc(batch, h, w, cin, cout, ksize, mode, dtype_code, engine=L.ENGINE_AUTO) -> ConvDesc:
+    return ConvDesc(batch, h, w, cin, cout, ksize, mode, dtype_code, engine)
+
+
+def conv_out_hw(d: ConvDesc):
+    oh, ow = C.c_int32(), C.c_int32()
+    check(lib().mvae_conv2d_out_hw(C.byref(d), C.byref(oh), C.byref(ow)), "conv2d_out_hw")
+    return oh.value, ow.value
+
+
+def conv_num_slabs(d: ConvDesc) -> int:
+    return lib().mvae_conv2d_num_slabs(C.byref(d))
+
+
+def conv_pack_weights(d: ConvDesc, w_oihw, wf, wd, ctot, coff):
+    check(lib().mvae_conv2d_pack_weights(C.byref(d), ptr(w_oihw), ptr(wf), ptr(wd), ctot, coff, stream()),
+          "conv2d_pack_weights")
+
+
+def conv_fprop(d: ConvDesc, x, wf, bias, residual, out=None):
+    oh, ow = conv_out_hw(d)
+    y = out if out is not None else torch.empty((d.batch, oh, ow, d.out_c), dtype=x.dtype, device=x.device)
+    check(lib().mvae_conv2d_fprop(C.byref(d), ptr(x), ptr(wf), ptr(bias), ptr(residual), ptr(y), stream()),
+          "conv2d_fprop")
+    return y
+
+
+def conv_dgrad(d: ConvDesc, dy, wd):
+    dx = torch.empty((d.batch, d.in_h, d.in_w, d.in_c), dtype=dy.dtype, device=dy.device)
+    check(lib().mvae_conv2d_dgrad(C.byref(d), ptr(dy), ptr(wd), ptr(dx), stream()), "conv2d_dgrad")
+    return dx
+
+
+def conv_wgrad(d: ConvDesc, x, dy, want_bias=True):
+    dw = torch.empty((d.out_c, d.in_c, d.ksize, d.ksize), dtype=torch.float32, device=x.device)
+    db = torch.empty((d.out_c,), dtype=torch.float32, device=x.device) if want_bias else None
+    nbytes = lib().mvae_conv2d_wgrad_workspace_bytes(C.byref(d))
+    ws = scratch("wgrad", nbytes, x.device)
+    check(lib().mvae_conv2d_wgrad(C.byref(d), ptr(x), ptr(dy), ptr(dw), ptr(db), ptr(ws), ws.numel(), stream()),
+          "conv2d_wgrad")
+    return dw, db
+
+
+def gn_fwd(x, gamma, beta, groups, eps, silu):
+    b, h, w, c = x.shape
+    y = torch.empty_like(x)
+    stats = torch.empty((b, groups, 2), dtype=torch.float32, device=x.device)
+    s = lib().mvae_groupnorm_splits(b, h * w, c)
+    sc = scratch("gn", 4 * b * s * groups * 2, x.device)
+    check(lib().mvae_groupnorm_silu_fwd(ptr(x), ptr(gamma), ptr(beta), ptr(y), ptr(stats), ptr(sc), b, h * w, c,
+                                        groups, eps, int(silu), L.code_of(x.dtype), stream()), "groupnorm_silu_fwd")
+    return y, stats
+
+
+def gn_bwd(dy, x, gamma, beta, stats, dx_add, groups, silu):
+    b, h, w, c = x.shape
+    dx = torch.empty_like(x)
+    dgb = torch.zeros((2, c), dtype=torch.float32, device=x.device)
+    s = lib().mvae_groupnorm_splits(b, h * w, c)
+    sc = scratch("gn", 4 * b * s * groups * 2, x.device)
+    check(lib().mvae_groupnorm_silu_bwd(ptr(dy), ptr(x), ptr(gamma), ptr(beta), ptr(stats), ptr(dx_add), ptr(dx),
+                                        ptr(dgb[0]), ptr(dgb[1]), ptr(sc), b, h * w, c, groups, int(silu),
+                                        L.code_of(x.dtype), stream()), "groupnorm_silu_bwd")
+    return dx, dgb[0], dgb[1]
+
+
+def attn_fwd(qkv):
+    b, h, w, c3 = qkv.shape
+    c, t = c3 // 3, h * w
+    out = torch.empty((b, h, w, c), dtype=qkv.dtype, device=qkv.device)
+    probs = torch.empty((b, t, t), dtype=torch.float32, device=qkv.device)
+    check(lib().mvae_attn_core_fwd(ptr(qkv), ptr(out), ptr(probs), b, t, c, L.code_of(qkv.dtype), stream()),
+          "attn_core_fwd")
+    return out, probs
+
+
+def attn_bwd(qkv, probs, dout):
+    b, h, w, c3 = qkv.shape
+    c, t = c3 // 3, h * w
+    dqkv = torch.empty_like(qkv)
+    ds = scratch("attn_ds", 4 * b * t * t, qkv.device)
+    check(lib().mvae_attn_core_bwd(ptr(qkv), ptr(probs), ptr(dout), ptr(dqkv), ptr(ds), b, t, c,
+                                   L.code_of(qkv.dtype), stream()), "attn_core_bwd")
+    return dqkv
+
+
+def input_pack_fwd(x_nchw, cond, w, b, out_c, dtype):
+    bsz, c, h, wd_ = x_nchw.shape
+    out = torch.empty((bsz, h, wd_, out_c), dtype=dtype, device=x_nchw.device)
+    cond_dim = cond.shape[1] if cond is not None else 0
+    check(lib().mvae_input_pack_fwd(ptr(x_nchw), ptr(cond), ptr(w), ptr(b), ptr(out), bsz, c, h, wd_, cond_dim,
+                                    out_c, L.code_of(dtype), stream()), "input_pack_fwd")
+    return out
+
+
+def input_pack_bwd(d_in, cond, w, b, c):
+    bsz, h, wd_, out_c = d_in.shape
+    dw = torch.empty_like(w)
+    db = torch.empty_like(b)
+    check(lib().mvae_input_pack_bwd(ptr(d_in), ptr(cond), ptr(w), ptr(b), ptr(dw), ptr(db), bsz, c, h, wd_,
+                                    cond.shape[1], out_c, L.code_of(d_in.dtype), stream()), "input_pack_bwd")
+    return dw, db
+
+
+def nhwc_to_nchw_f32(src, c_off=0, c_dst=None):
+    b, h, w, c = src.shape
+    c_dst = c - c_off if c_dst is None else c_dst
+    dst = torch.empty((b, c_dst, h, w), dtype=torch.float32, device=src.device)
+    check(lib().mvae_nhwc_to_nchw_f32(ptr(src), ptr(dst), b, h, w, c, c_off, c_dst, L.code_of(src.dtype), stream()),
+          "nhwc_to_nchw_f32")
+    return dst
+
+
+def nchw_f32_to_nhwc(src, dtype):
+    b, c, h, w = src.shape
+    dst = torch.empty((b, h, w, c), dtype=dtype, device=src.device)
+    check(lib().mvae_nchw_f32_to_nhwc(ptr(src), ptr(dst), b, h, w, c, L.code_of(dtype), stream()), "nchw_f32_to_nhwc")
+    return dst
+
+
+def reparam_kl_fwd(moments, eps, zc, clamp, seed, offset, want_kl=True, want_std=True):
+    b, r, _, c2 = moments.shape
+    dev = moments.device
+    mean = torch.empty((b, zc, r, r), dtype=torch.float32, device=dev)
+    logvar = torch.empty_like(mean)
+    z = torch.empty_like(mean)
+    std = torch.empty_like(mean) if want_std else None
+    eps_out = None
+    if eps is None:
+        eps_out = torch.empty_like(mean)
+    kl = torch.zeros((), dtype=torch.float64, device=dev) if want_kl else None
+    check(lib().mvae_reparam_kl_fwd(ptr(moments), ptr(eps), ptr(eps_out), ptr(mean), ptr(logvar), ptr(std), ptr(z), None,
+                                    ptr(kl), b, zc, r, float(clamp), int(seed), int(offset),
+                                    L.code_of(moments.dtype), stream()), "reparam_kl_fwd")
+    return mean, logvar, z, std, (eps if eps is not None else eps_out), kl
+
+
+def reparam_kl_bwd(d_mean, d_logvar, d_z, logvar, eps, moments, clamp):
+    b, r, _, c2 = moments.shape
+    d_mom = torch.empty_like(moments)
+    check(lib().mvae_reparam_kl_bwd(ptr(d_mean), ptr(d_logvar), ptr(d_z), None, ptr(logvar), ptr(eps), ptr(moments),
+                                    ptr(d_mom), b, c2 // 2, r, float(clamp), L.code_of(moments.dtype), stream()),
+          "reparam_kl_bwd")
+    return d_mom
+
+
+def recon_loss(recon, x, kind, want_grad=True):
+    n = recon.numel()
+    s = torch.zeros((), dtype=torch.float64, device=recon.device)
+    d_unit = torch.empty_like(recon) if want_grad else None
+    check(lib().mvae_recon_loss_fwd_bwd(ptr(recon), ptr(x), ptr(s), ptr(d_unit), n, kind, stream()), "recon_loss")
+    return s, d_unit
+
+
+def kl_sum(mean, logvar):
+    s = torch.zeros((), dtype=torch.float64, device=mean.device)
+    check(lib().mvae_kl_fwd(ptr(mean), ptr(logvar), ptr(s), mean.numel(), stream()), "kl_fwd")
+    return s
+
+
+def kl_bwd(mean, logvar, coef):
+    dm, dl = torch.empty_like(mean), torch.empty_like(logvar)
+    check(lib().mvae_kl_bwd(ptr(mean), ptr(logvar), ptr(coef), ptr(dm), ptr(dl), mean.numel(), stream()), "kl_bwd")
+    return dm, dl
+
+
+def scale_by(t, scale_dev):
+    out = torch.empty_like(t)
+    check(lib().mvae_scale_by_device_scalar(ptr(t), ptr(scale_dev), ptr(out), t.numel(), stream()), "scale")
+    return out

@@ -14,6 +14,7 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "umma: exercises the tcgen05/TMA kernels (subset of gpu)")
 
 
 def pytest_collection_modifyitems(config, items):

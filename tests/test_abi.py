@@ -1,0 +1,91 @@
+"""CPU-side checks of the native boundary: the shared library loads without a GPU, exports every
+symbol include/medvae_b200.h declares, its host-only helpers agree with the reference's conv
+geometry, and every compute entry point refuses to run without a device (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _lib():
+    from medvae_disentangled_multimodal_b200 import _lib as L
+    return L
+
+
+def header_symbols():
+    txt = open(os.path.join(ROOT, "include", "medvae_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(mvae_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    L = _lib()
+    lib = L.lib()
+    syms = header_symbols()
+    assert len(syms) >= 25
+    for s in syms:
+        assert hasattr(lib, s), f"{s} declared in medvae_b200.h but not exported"
+    assert set(L.SIGNATURES) == set(syms), set(L.SIGNATURES) ^ set(syms)
+    assert lib.mvae_abi_version() == 1
+
+
+@pytest.mark.parametrize("h,mode,k,expect", [(28, 0, 3, 28), (28, 1, 3, 14), (14, 1, 3, 7), (7, 1, 3, 3),
+                                             (64, 1, 3, 32), (7, 2, 3, 14), (16, 0, 1, 16)])
+def test_conv_geometry_matches_reference(h, mode, k, expect):
+    """Downsample: pad (0,1,0,1) then conv3x3 s2 p0 -> floor((H-2)/2)+1 (encoder_decoder.py:184-188);
+    Upsample doubles (:205-209)."""
+    L = _lib()
+    from medvae_disentangled_multimodal_b200 import ops
+    d = ops.conv_desc(2, h, h, 8, 8, k, mode, L.F32)
+    assert ops.conv_out_hw(d) == (expect, expect)
+    ref = torch.zeros(1, 1, h, h)
+    if mode == 1:
+        ref = torch.nn.functional.conv2d(torch.nn.functional.pad(ref, (0, 1, 0, 1)), torch.zeros(1, 1, 3, 3), stride=2)
+    elif mode == 2:
+        ref = torch.nn.functional.interpolate(ref, scale_factor=2.0)
+    assert ref.shape[-1] == expect
+    assert ops.conv_num_slabs(d) == (16 if mode == 2 else k * k)
+
+
+def test_engine_selection():
+    L = _lib()
+    from medvae_disentangled_multimodal_b200 import ops
+    lib = L.lib()
+    yes = ops.conv_desc(8, 16, 16, 128, 256, 3, 0, L.BF16)
+    assert lib.mvae_conv2d_uses_umma(C.byref(yes)) == 1
+    for d in (ops.conv_desc(8, 16, 16, 128, 256, 3, 0, L.F32),      # fp32 verification mode
+              ops.conv_desc(8, 16, 16, 6, 128, 3, 0, L.BF16),       # encoder conv_in: K = 54
+              ops.conv_desc(8, 16, 16, 128, 3, 3, 0, L.BF16),       # decoder conv_out: N = 3
+              ops.conv_desc(8, 16, 16, 128, 256, 3, 0, L.BF16, L.ENGINE_SIMT)):
+        assert lib.mvae_conv2d_uses_umma(C.byref(d)) == 0
+    assert lib.mvae_conv2d_wgrad_workspace_bytes(C.byref(yes)) >= 4 * 9 * 128 * 256
+
+
+def test_bad_descriptor_is_an_error_not_a_crash():
+    L = _lib()
+    from medvae_disentangled_multimodal_b200 import ops
+    bad = ops.conv_desc(1, 8, 8, 8, 8, 5, 0, L.F32)
+    oh, ow = C.c_int32(), C.c_int32()
+    assert L.lib().mvae_conv2d_out_hw(C.byref(bad), C.byref(oh), C.byref(ow)) != 0
+    assert "bad conv descriptor" in L.last_error()
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-device behaviour")
+def test_no_cpu_fallback():
+    import medvae_disentangled_multimodal_b200 as M
+    L = _lib()
+    assert L.lib().mvae_device_ok() == 0
+    model = M.BaseVAE(1, 4, 8, [1, 2], 1, [], resolution=16)
+    with pytest.raises(L.MvaeError):
+        model(torch.randn(1, 1, 16, 16))
+    with pytest.raises(L.MvaeError):
+        model.encode(torch.randn(1, 1, 16, 16))
+    with pytest.raises(L.MvaeError):
+        model.decode(torch.randn(1, 4, 8, 8))
+    with pytest.raises(L.MvaeError):
+        M.VAELoss()(inputs=torch.zeros(1), reconstructions=torch.zeros(1),
+                    posteriors=torch.distributions.Normal(torch.zeros(1), torch.ones(1)))
