@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""bench.py — train images/sec of the conditional-VAE training step (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c4|c3|c2|c1]
+
+One "step" = forward + VAELoss + backward (+ data-parallel gradient all-reduce) + clip + AdamW on
+one batch of synthetic MedMNIST-shaped images.  Default workload: BASELINE.json configs[3], the
+configuration the metric is quoted on ("CVAE fwd+bwd, 64x64"): ConditionalVAE 3x64x64, hidden 128,
+ch_mult (1,2,4,8), 2 res blocks, attention at 16x16 and 8x8, latent 128, 1024 images per GPU (weak
+scaling), bf16 storage / fp32 accumulate.  Prints ONE JSON line (rank 0).
+
+  value     : whole-job images/s with the batch already resident in HBM (CUDA events, max over ranks)
+  e2e       : the same through TrainStep.step() with pinned HOST inputs (H2D inside the timed
+              region) and a D2H read of the loss every step
+  roofline  : the dominant kernel family (tcgen05 implicit-GEMM conv, fprop+dgrad) — algorithmic
+              FLOPs / summed launch durations (CUDA events around each launch in one extra,
+              untimed, instrumented step) against MEASURED_PEAKS.json's sustained bf16 figure
+  cpu_baseline : the oracle port of the reference step timed on the host cores (N=1 only)
+
+`--impl reference` times the reference's CPU implementation of the same step (the oracle port;
+the Python reference itself cannot travel to the GPU box) on a bounded sample per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (class, ctor kwargs, loss kwargs, batch per GPU, conditional, GFLOP/img fwd+bwd [SURVEY 8], scaling)
+    "c1": ("BaseVAE", dict(input_channels=1, latent_dim=128, hidden_channels=128, ch_mult=(1, 2, 4), num_res_blocks=2,
+                           attn_resolutions=[14, 7], dropout=0.0, resolution=28),
+           dict(recon_loss_type="mse", kl_weight=1.0, recon_weight=1.0), 64, False, 38.25, "weak"),
+    "c2": ("BetaVAE", dict(beta=4.0, input_channels=3, latent_dim=128, hidden_channels=128, ch_mult=(1, 2, 4),
+                           num_res_blocks=2, attn_resolutions=[14, 7], dropout=0.0, resolution=28),
+           dict(recon_loss_type="mse", kl_weight=4.0, recon_weight=1.0), 512, False, 38.27, "weak"),
+    "c3": ("ConditionalVAE", dict(input_channels=3, latent_dim=128, hidden_channels=128, ch_mult=(1, 2, 4),
+                                  num_res_blocks=2, attn_resolutions=[14, 7], dropout=0.0, resolution=28,
+                                  condition_method="concat"),
+           dict(recon_loss_type="mse", kl_weight=1.0, recon_weight=1.0), 256, True, 38.29, "weak"),
+    "c4": ("ConditionalVAE", dict(input_channels=3, latent_dim=128, hidden_channels=128, ch_mult=(1, 2, 4, 8),
+                                  num_res_blocks=2, attn_resolutions=[16, 8], dropout=0.0, resolution=64,
+                                  condition_method="concat"),
+           dict(recon_loss_type="mse", kl_weight=1.0, recon_weight=1.0), 1024, True, 251.9, "weak"),
+}
+OPT = dict(lr=1e-4, weight_decay=1e-4, betas=(0.9, 0.999), max_norm=1.0)   # configs/training/default.yaml:3-11
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=list(WORKLOADS))
+    ap.add_argument("--batch-per-gpu", type=int, default=None)
+    ap.add_argument("--micro-batch", type=int, default=None, help="images per forward/backward pass (default: 256)")
+    ap.add_argument("--cpu-batch", type=int, default=None, help="images per CPU step (reference arm / cpu_baseline)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference step on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_sample_batch(wl: str, override):
+    if override:
+        return override
+    return {"c1": 8, "c2": 8, "c3": 8, "c4": 2}[wl]
+
+
+def build_state_dict(wl: str):
+    """reference default init under torch.manual_seed(42): the parameter containers of
+    the drop-in classes reproduce the reference's construction order, so seeded init matches."""
+    import torch
+    import medvae_disentangled_multimodal_b200 as M
+    cls, kw, *_ = WORKLOADS[wl]
+    torch.manual_seed(42)
+    model = getattr(M, cls)(**kw)
+    return model, {k: v.detach().clone() for k, v in model.state_dict().items()}
+
+
+def run_cpu_steps(wl: str, sd, batch: int, steps: int, warmup: int, budget_s: float = None):
+    """-> (images/s, steps timed, cores).  Each step: fwd + VAELoss + bwd + NaN guard + clip + AdamW."""
+    import torch
+    from oracle import vae_oracle as O
+    from medvae_disentangled_multimodal_b200.data import synthetic_batch
+    cls, kw, lkw, _b, conditional, _gf, _s = WORKLOADS[wl]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    tr = O.ReferenceTrainer(sd, lr=OPT["lr"], weight_decay=OPT["weight_decay"], betas=OPT["betas"],
+                            max_norm=OPT["max_norm"], loss_kwargs=lkw)
+    x, _lab, onehot, _idx = synthetic_batch(batch, kw["input_channels"], kw["resolution"])
+    r = kw["resolution"] // 2 ** (len(kw["ch_mult"]) - 1)
+    g = torch.Generator().manual_seed(7)
+    done, t_total = 0, 0.0
+    for i in range(warmup + steps):
+        eps = torch.randn(batch, kw["latent_dim"], r, r, generator=g)
+        t0 = time.perf_counter()
+        tr.step(x, eps, onehot if conditional else None)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            done += 1
+            t_total += dt
+            if budget_s is not None and t_total >= budget_s:
+                break
+    return batch * done / t_total, done, cores, t_total
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = args.workload
+    cls, kw, lkw, bpg, conditional, gflop, scaling = WORKLOADS[wl]
+    _model, sd = build_state_dict(wl)
+    b = cpu_sample_batch(wl, args.cpu_batch)
+    ips, done, cores, t_total = run_cpu_steps(wl, sd, b, args.steps, args.warmup)
+    sample = f"{done} steps of {b} images ({cls} {kw['input_channels']}x{kw['resolution']}x{kw['resolution']}, fp32, " \
+             f"fwd+loss+bwd+clip+AdamW) on {cores} host threads"
+    line = {
+        "impl": "reference", "metric": "train images/sec", "value": ips, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": done, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(done, 1), "higher_is_better": True,
+        "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(wl, args, bpg, args.gpus, cpu=True),
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(wl, args, bpg, n, cpu=False):
+    cls, kw, lkw, _b, conditional, gflop, scaling = WORKLOADS[wl]
+    return {
+        "workload": f"{wl}: {cls} {kw['input_channels']}x{kw['resolution']}x{kw['resolution']} hidden {kw['hidden_channels']} "
+                    f"ch_mult {tuple(kw['ch_mult'])} res_blocks {kw['num_res_blocks']} attn {kw['attn_resolutions']} "
+                    f"latent {kw['latent_dim']}, VAELoss {lkw['recon_loss_type']} kl_weight {lkw['kl_weight']}, "
+                    f"AdamW lr 1e-4 wd 1e-4 clip 1.0",
+        "batch_per_gpu": bpg, "global_batch": bpg * n, "micro_batch": None if cpu else (args.micro_batch or min(bpg, 256)),
+        "parallelism": f"dp{n}", "gflop_per_image_fwd_bwd": gflop,
+        "cache": "inputs and activations larger than L2 (126 MB); no L2 flush needed",
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for nme, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return {"bf16_sustained": float(d.get("bf16_tflops_sustained", d.get("bf16_tflops"))),
+                    "bf16_burst": float(d["bf16_tflops"]), "hbm": float(d["hbm_gbs"]), "source": "measured"}
+        except Exception:
+            pass
+    return {"bf16_sustained": 1400.0, "bf16_burst": 1590.0, "hbm": 6650.0, "source": "fallback"}
+
+
+def b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200 import _lib as L
+    from medvae_disentangled_multimodal_b200 import profile as P
+    from medvae_disentangled_multimodal_b200.data import synthetic_batch
+    from medvae_disentangled_multimodal_b200.train import TrainStep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    L.require_device()
+
+    wl = args.workload
+    cls, kw, lkw, bpg, conditional, gflop, scaling = WORKLOADS[wl]
+    bpg = args.batch_per_gpu or bpg
+    micro = args.micro_batch or min(bpg, 256)
+    torch.manual_seed(42)
+    model = getattr(M, cls)(compute_dtype=args.precision, **kw).to(dev)
+    model.rng_seed = 42
+    crit = M.VAELoss(**lkw)
+    ts = TrainStep(model, crit, micro_batch=micro, **OPT)
+    x_h, _lab, onehot_h, _idx = synthetic_batch(bpg, kw["input_channels"], kw["resolution"], first_index=rank * bpg,
+                                                pin=True)
+    cond_h = onehot_h if conditional else None
+    x_d = x_h.to(dev)
+    cond_d = cond_h.to(dev) if conditional else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    last = {}
+
+    def step_resident():
+        last["ld"] = ts.step(x_d, cond_d)
+
+    def step_e2e():
+        ld = ts.step(x_h, cond_h)
+        last["loss_host"] = float(ld["loss"])   # D2H read of the step's result
+
+    for _ in range(args.warmup):
+        step_e2e()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = L.lib().mvae_launch_count()
+    ms_res = timed(step_resident, args.steps)
+    launches = (L.lib().mvae_launch_count() - n0)
+    ms_e2e = timed(step_e2e, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    loss_val = float(last["ld"]["loss"])
+
+    total_imgs = bpg * world * args.steps
+    value = total_imgs / (ms_res / 1e3)
+    e2e_v = total_imgs / (ms_e2e / 1e3)
+    peaks = load_peaks()
+
+    roof = None
+    kernels = {}
+    if not args.no_roofline and rank == 0:
+        timer = P.KernelTimer()
+        P.install(timer)
+        ts.step(x_d, cond_d)
+        P.install(None)
+        summ = timer.summary()
+        for k, d in summ.items():
+            kernels[k] = {"launches": d["launches"], "ms": round(d["ms"], 3),
+                          "tflops": round(d["flops"] / (d["ms"] * 1e9), 2) if d["ms"] > 0 and d["flops"] else None,
+                          "gbs": round(d["bytes"] / (d["ms"] * 1e6), 1) if d["ms"] > 0 and d["bytes"] else None}
+        gk = [k for k in ("conv_fprop_umma", "conv_dgrad_umma") if k in summ]
+        if gk:
+            fl = sum(summ[k]["flops"] for k in gk)
+            ms = sum(summ[k]["ms"] for k in gk)
+            n_l = sum(summ[k]["launches"] for k in gk)
+            ach = fl / (ms * 1e9)
+            roof = {"bound": "tensor", "kernel": "conv_gather_umma_kernel (implicit-GEMM conv fprop+dgrad, tcgen05)",
+                    "achieved": round(ach, 2), "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                    "frac": round(ach / peaks["bf16_sustained"], 4), "traffic": None,
+                    "peak_source": f"{peaks['source']} (sustained: kernel timed inside a long step)",
+                    "launches": n_l, "avg_launch_ms": round(ms / n_l, 4),
+                    "algorithmic_gflop_per_launch": round(fl / n_l / 1e9, 2)}
+    elif world > 1:
+        pass
+    if world > 1:
+        barrier()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        _m, sd = build_state_dict(wl)
+        b = cpu_sample_batch(wl, args.cpu_batch)
+        ips, done, cores, t_total = run_cpu_steps(wl, sd, b, steps=5, warmup=1, budget_s=12.0)
+        cpu = {"value": round(ips, 3), "unit": "images/s", "cores": cores, "kind": "port",
+               "sample": f"{done} steps of {b} images of the same workload (fp32 oracle port of the reference step: "
+                         f"fwd+loss+bwd+clip+AdamW), {t_total:.1f} s"}
+
+    if rank == 0:
+        step_flops = gflop * 1e9 * bpg     # per GPU
+        line = {
+            "metric": "train images/sec", "value": round(value, 2), "unit": "images/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_res / args.steps, 3),
+            "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": args.precision, "data": "synthetic",
+            "config": workload_config(wl, args, bpg, world),
+            "e2e": {"value": round(e2e_v, 2), "unit": "images/s",
+                    "h2d_bytes_per_step": int(x_h.numel() * 4 + (cond_h.numel() * 4 if conditional else 0)),
+                    "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 3)},
+            "gpu_launches": int(launches),
+            "roofline": roof,
+            "step_tflops_per_gpu": round(step_flops / (ms_res / args.steps * 1e9), 2),
+            "step_frac_of_peak": round(step_flops / (ms_res / args.steps * 1e9) / peaks["bf16_sustained"], 4),
+            "kernels": kernels,
+            "cpu_baseline": cpu,
+            "clocks": clocks,
+            "loss": loss_val,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -54,6 +54,8 @@ const char* mvae_last_error(void);
 int mvae_abi_version(void);
 /* 1 if a CUDA device with compute capability 10.x is present */
 int mvae_device_ok(void);
+/* number of CUDA kernels this library has launched in this process (all threads) */
+uint64_t mvae_launch_count(void);
 /* debug knobs (descriptor variants for bring-up); key/value ints */
 int mvae_set_debug(int key, int value);
 
@@ -91,14 +93,15 @@ int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, fl
 /* GroupNorm(min(32,C), eps) [+ x*sigmoid(x)]  — Normalize + nonlinearity,
  * encoder_decoder.py:13-15,28-33 as used at :150-151,:158-159,:85,:325-326,:446-447.
  * x,y: [B, HW, C].  stats (out): [B][G][2] fp32 (mean, rstd).  scratch: B*splits*G*2 floats
- * with splits = mvae_groupnorm_splits(). */
+ * (forward) or B*splits*(2*G + 2*C) floats (backward) with splits = mvae_groupnorm_splits().
+ * All reductions run in a fixed order: results are bitwise reproducible run to run. */
 int mvae_groupnorm_splits(int32_t batch, int32_t hw, int32_t c);
 int mvae_groupnorm_silu_fwd(const void* x, const float* gamma, const float* beta, void* y,
                             float* stats, float* scratch, int32_t batch, int32_t hw, int32_t c,
                             int32_t groups, float eps, int32_t apply_silu, int32_t dtype,
                             void* stream);
 /* dx = d(GN+SiLU)(dy) + dx_add (dx_add may be NULL: fuses the residual-branch gradient);
- * dgamma/dbeta (fp32) are ACCUMULATED into (caller zeroes). */
+ * dgamma/dbeta (fp32 [C]) are overwritten. */
 int mvae_groupnorm_silu_bwd(const void* dy, const void* x, const float* gamma, const float* beta,
                             const float* stats, const void* dx_add, void* dx, float* dgamma,
                             float* dbeta, float* scratch, int32_t batch, int32_t hw, int32_t c,

@@ -38,6 +38,7 @@ SIGNATURES = {
     "mvae_last_error": (C.c_char_p, []),
     "mvae_abi_version": (C.c_int, []),
     "mvae_device_ok": (C.c_int, []),
+    "mvae_launch_count": (C.c_uint64, []),
     "mvae_set_debug": (C.c_int, [C.c_int, C.c_int]),
     "mvae_conv2d_out_hw": (C.c_int, [_dp, C.POINTER(_i32), C.POINTER(_i32)]),
     "mvae_conv2d_num_slabs": (C.c_int, [_dp]),

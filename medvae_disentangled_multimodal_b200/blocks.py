@@ -97,7 +97,8 @@ class Run:
     """State of one forward (+ its backward) through a stack: dtype, saved activations and the
     parameter gradients produced so far."""
 
-    def __init__(self, dtype: torch.dtype, cache: dict, training: bool):
+    def __init__(self, dtype: torch.dtype, cache: dict, training: bool, sink=None):
+        self.sink = sink              # callable(param, grad): takes the gradient instead of autograd
         self.dtype = dtype
         self.code = L.code_of(dtype)
         self.cache = cache            # packed-operand cache owned by the nn.Module
@@ -106,6 +107,9 @@ class Run:
         self.tape: list = []
 
     def add_grad(self, p: nn.Parameter, g: torch.Tensor):
+        if self.sink is not None:
+            self.sink(p, g)
+            return
         g = g.view(p.shape)
         if p in self.grads:
             self.grads[p] = self.grads[p] + g
@@ -127,6 +131,12 @@ class ConvOp:
 
     def desc(self, run: Run, b: int, h: int, w: int):
         return ops.conv_desc(b, h, w, self.cin, self.cout, self.k, self.mode, run.code)
+
+    def params(self):
+        out = []
+        for c in self.convs:
+            out += [c.weight, c.bias]
+        return out
 
     def packed(self, run: Run, device):
         key = (tuple(id(c.weight) for c in self.convs), run.code, self.mode)
@@ -194,6 +204,11 @@ class ResOp:
         else:
             self.p_drop = 0.0
 
+    def params_backward_order(self):
+        b = self.blk
+        return (self.c2.params() + [b.norm2.weight, b.norm2.bias] + self.c1.params()
+                + (self.nin.params() if self.nin is not None else []) + [b.norm1.weight, b.norm1.bias])
+
     def fwd(self, run: Run, x):
         if self.p_drop > 0.0 and run.training:
             raise NotImplementedError("dropout > 0 in training mode is not implemented (all full-size reference "
@@ -225,6 +240,9 @@ class AttnOp:
         self.qkv = ConvOp([blk.q, blk.k, blk.v], L.CONV_S1)
         self.proj = ConvOp([blk.proj_out], L.CONV_S1)
 
+    def params_backward_order(self):
+        return self.proj.params() + self.qkv.params() + [self.blk.norm.weight, self.blk.norm.bias]
+
     def fwd(self, run: Run, x):
         hn, st = gn_fwd(run, self.blk.norm, x, False)
         qkv = self.qkv.fwd(run, hn)
@@ -250,6 +268,9 @@ class PlainConvOp:
         self.op = ConvOp([conv], mode)
         self.need_dx = need_dx
 
+    def params_backward_order(self):
+        return self.op.params()
+
     def fwd(self, run: Run, x):
         y = self.op.fwd(run, x)
         run.tape.append((self, (x,)))
@@ -265,6 +286,9 @@ class HeadOp:
     def __init__(self, norm: nn.GroupNorm, conv: nn.Conv2d):
         self.norm = norm
         self.op = ConvOp([conv], L.CONV_S1)
+
+    def params_backward_order(self):
+        return self.op.params() + [self.norm.weight, self.norm.bias]
 
     def fwd(self, run: Run, x):
         a, st = gn_fwd(run, self.norm, x, True)
@@ -300,6 +324,7 @@ class _Stack(nn.Module):
 
     def _init_runtime(self):
         self._pack_cache: dict = {}
+        self._grad_sink = None        # set by train.TrainStep: gradients go to its flat buckets
         self.compute_dtype = torch.bfloat16
 
     def stages(self, need_input_grad: bool):
@@ -318,7 +343,7 @@ class _Stack(nn.Module):
 class _StackFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, stack: "_Stack", need_input_grad: bool, x, *params):
-        run = Run(x.dtype, stack._pack_cache, stack.training)
+        run = Run(x.dtype, stack._pack_cache, stack.training, stack._grad_sink)
         with torch.no_grad():
             y = run_forward(stack.stages(need_input_grad), run, x)
         ctx.run = run
@@ -338,7 +363,7 @@ class _StackFn(torch.autograd.Function):
         grads = []
         for p in ctx.params:
             g = run.grads.get(p)
-            if g is None and p.requires_grad:
+            if g is None and p.requires_grad and run.sink is None:
                 g = torch.zeros_like(p)
             grads.append(g)
         run.grads = {}

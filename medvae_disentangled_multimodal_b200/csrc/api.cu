@@ -15,6 +15,8 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+static unsigned long long g_launches = 0;
+void count_launch() { __atomic_fetch_add(&g_launches, 1ull, __ATOMIC_RELAXED); }
 static int g_knobs[16] = {0};
 int debug_knob(int key) { return (key >= 0 && key < 16) ? g_knobs[key] : 0; }
 
@@ -88,6 +90,8 @@ int mvae_device_ok(void) {
     cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
     return major == 10 ? 1 : 0;
 }
+
+uint64_t mvae_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
 int mvae_set_debug(int key, int value) {
     MVAE_CHECK(key >= 0 && key < 16, "debug key out of range");

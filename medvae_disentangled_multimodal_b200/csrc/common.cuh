@@ -28,7 +28,12 @@ void set_error(const char* fmt, ...);
             return 1;                                                                     \
         }                                                                                 \
     } while (0)
-#define MVAE_LAUNCH_CHECK() MVAE_CUDA(cudaGetLastError())
+void count_launch();   // api.cu: every kernel launch of this library is counted (mvae_launch_count)
+#define MVAE_LAUNCH_CHECK()          \
+    do {                             \
+        mvae::count_launch();        \
+        MVAE_CUDA(cudaGetLastError()); \
+    } while (0)
 
 int debug_knob(int key);   // api.cu
 

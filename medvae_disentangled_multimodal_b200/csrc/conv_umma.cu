@@ -452,6 +452,7 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     } else {
         const int quarter = warp & 3;
         const int co = cot * 128 + quarter * 32 + lane;
+        const bool co_ok = co < p.Cout;   // Cout % 128 == 64: the upper half of the last tile is TMA zero fill
         float* dst = p.partial + (((long long)split * p.nslabs + tp.slab) * p.Cout + co) * p.Cin + cit * R_BN;
         if (kiters > 0) {
             mbar_wait(&tfull[0], 0);
@@ -468,11 +469,13 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = 0u;
             }
+            if (co_ok && cit * R_BN + c0 < p.Cin) {
             float4* o = reinterpret_cast<float4*>(dst + c0);
 #pragma unroll
             for (int i = 0; i < 8; ++i)
                 o[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
                                    __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+            }
         }
     }
     tc_fence_before();
@@ -484,7 +487,7 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
 }
 
 bool umma_reduce_ok(const ReduceProblem& p) {
-    if (p.Cout % 128 != 0 || p.Cin % R_BN != 0) return false;
+    if (p.Cout % 64 != 0 || p.Cin % 64 != 0) return false;
     if (p.GW > 128 && p.GW % 128 != 0) return false;
     BoxGeom g = box_geom(p.B, p.GH, p.GW);
     for (int v = 0; v < p.n_inviews; ++v)
@@ -497,7 +500,7 @@ bool umma_reduce_ok(const ReduceProblem& p) {
 int umma_reduce_splits(const ReduceProblem& p) {
     BoxGeom g = box_geom(p.B, p.GH, p.GW);
     long long ptiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
-    long long items = (long long)p.taps.ntaps * (p.Cout / 128) * (p.Cin / R_BN);
+    long long items = (long long)p.taps.ntaps * ((p.Cout + 127) / 128) * ((p.Cin + R_BN - 1) / R_BN);
     long long want = (2LL * num_sms() + items - 1) / items;
     if (want < 1) want = 1;
     long long cap = (ptiles + 3) / 4;   // at least ~4 pixel tiles per split
@@ -525,7 +528,7 @@ int umma_reduce(const ReduceProblem& p, const void* in, const void* dy, float* p
     d.bw = g.bw; d.bh = g.bh; d.bn = g.bn; d.rows = g.rows;
     d.tiles_x = g.tiles_x; d.tiles_y = g.tiles_y; d.tiles_n = g.tiles_n;
     d.ptiles = g.tiles_x * g.tiles_y * g.tiles_n;
-    d.co_tiles = p.Cout / 128; d.ci_tiles = p.Cin / R_BN; d.nslabs = p.taps.ntaps; d.splits = splits;
+    d.co_tiles = (p.Cout + 127) / 128; d.ci_tiles = (p.Cin + R_BN - 1) / R_BN; d.nslabs = p.taps.ntaps; d.splits = splits;
     d.Cout = p.Cout; d.Cin = p.Cin; d.partial = partial;
     d.lbo = R_CHUNK; d.sbo = 1024;
     if (debug_knob(1) == 1) { d.lbo = 1024; d.sbo = R_CHUNK; }   // bring-up: swapped LBO/SBO roles

@@ -58,6 +58,7 @@ template <typename T, int VEC>
 __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const T* __restrict__ x, float* __restrict__ scratch,
                                                               int HW, int C, int G, int S) {
     __shared__ float sh_s[MAX_G], sh_q[MAX_G], pivot[MAX_G];
+    extern __shared__ float part[];   // [rows per iteration][C][2]
     const int n = blockIdx.y, sp = blockIdx.x;
     const int cpg = C / G;
     const T* xn = x + (long long)n * HW * C;
@@ -80,16 +81,23 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const T* __restric
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) { float d = f[j] - pv[j]; s[j] += d; q[j] = fmaf(d, d, q[j]); }
             }
-            // fold the channel lanes that share a group before touching shared memory
-            int g_prev = (v * VEC) / cpg; float as = 0.f, aq = 0.f;
+            // per-thread channel partials -> shared [row lane][channel]; folded below in a fixed order
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
-                int g = (v * VEC + j) / cpg;
-                if (g != g_prev) { atomicAdd(&sh_s[g_prev], as); atomicAdd(&sh_q[g_prev], aq); as = 0.f; aq = 0.f; g_prev = g; }
-                as += s[j]; aq += q[j];
+                part[(m.r * C + v * VEC + j) * 2] = s[j];
+                part[(m.r * C + v * VEC + j) * 2 + 1] = q[j];
             }
-            atomicAdd(&sh_s[g_prev], as); atomicAdd(&sh_q[g_prev], aq);
         }
+    }
+    __syncthreads();
+    if (threadIdx.x < G) {
+        RowMap m = row_map<VEC>(C);
+        float as = 0.f, aq = 0.f;
+        for (int r = 0; r < m.rpi; ++r)
+            for (int c = threadIdx.x * cpg; c < (threadIdx.x + 1) * cpg; ++c) {
+                as += part[(r * C + c) * 2]; aq += part[(r * C + c) * 2 + 1];
+            }
+        sh_s[threadIdx.x] = as; sh_q[threadIdx.x] = aq;
     }
     __syncthreads();
     if (threadIdx.x < G) {
@@ -152,26 +160,26 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const T* __restric
 }
 
 // ------------------------------------------------------------------ backward: reductions
-// per (n, split, g): s1 = sum du*gamma, s2 = sum du*gamma*xhat;  per channel: dgamma += du*xhat,
-// dbeta += du, where u = xhat*gamma+beta and du = dy * silu'(u) (or dy).
+// per (n, split, g): s1 = sum du*gamma, s2 = sum du*gamma*xhat;  per channel: dgamma = sum du*xhat,
+// dbeta = sum du, where u = xhat*gamma+beta and du = dy * silu'(u) (or dy).  Everything is folded
+// in a fixed order (bitwise run-to-run reproducible): thread partials -> shared -> per-CTA rows of
+// `scratch` -> gn_param_reduce_kernel.
+// scratch layout: [B*S][G][2] group sums, then [B*S][2][C] channel sums.
 template <typename T, int VEC>
 __global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                                   const float* __restrict__ gamma,
                                                                   const float* __restrict__ beta,
                                                                   const float* __restrict__ stats,
-                                                                  float* __restrict__ scratch, float* __restrict__ dgamma,
-                                                                  float* __restrict__ dbeta, int HW, int C, int G, int S,
-                                                                  int silu) {
-    __shared__ float sh1[MAX_G], sh2[MAX_G], mean[MAX_G], rstd[MAX_G];
-    extern __shared__ float chan[];   // [2][C] per-channel dgamma / dbeta of this CTA
+                                                                  float* __restrict__ scratch, int B, int HW, int C,
+                                                                  int G, int S, int silu) {
+    __shared__ float mean[MAX_G], rstd[MAX_G];
+    extern __shared__ float part[];   // [rows per iteration][C][4] : dg, db, a1, a2
     const int n = blockIdx.y, sp = blockIdx.x;
     const int cpg = C / G;
     if (threadIdx.x < G) {
-        sh1[threadIdx.x] = 0.f; sh2[threadIdx.x] = 0.f;
         mean[threadIdx.x] = stats[((long long)n * G + threadIdx.x) * 2];
         rstd[threadIdx.x] = stats[((long long)n * G + threadIdx.x) * 2 + 1];
     }
-    for (int i = threadIdx.x; i < 2 * C; i += GN_THREADS) chan[i] = 0.f;
     __syncthreads();
     const T* xn = x + (long long)n * HW * C;
     const T* dn = dy + (long long)n * HW * C;
@@ -205,25 +213,50 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __res
                     a1[j] += dxh; a2[j] = fmaf(dxh, xh, a2[j]);
                 }
             }
-            int g_prev = (v * VEC) / cpg; float s1 = 0.f, s2 = 0.f;
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
-                int c = v * VEC + j, g = c / cpg;
-                if (g != g_prev) { atomicAdd(&sh1[g_prev], s1); atomicAdd(&sh2[g_prev], s2); s1 = 0.f; s2 = 0.f; g_prev = g; }
-                s1 += a1[j]; s2 += a2[j];
-                atomicAdd(&chan[c], dg[j]); atomicAdd(&chan[C + c], db[j]);
+                float* o = part + (size_t)(m.r * C + v * VEC + j) * 4;
+                o[0] = dg[j]; o[1] = db[j]; o[2] = a1[j]; o[3] = a2[j];
             }
-            atomicAdd(&sh1[g_prev], s1); atomicAdd(&sh2[g_prev], s2);
         }
     }
     __syncthreads();
+    const RowMap m = row_map<VEC>(C);
+    const long long cta = (long long)n * S + sp;
     if (threadIdx.x < G) {
-        float* o = scratch + (((long long)n * S + sp) * G + threadIdx.x) * 2;
-        o[0] = sh1[threadIdx.x]; o[1] = sh2[threadIdx.x];
+        float s1 = 0.f, s2 = 0.f;
+        for (int r = 0; r < m.rpi; ++r)
+            for (int c = threadIdx.x * cpg; c < (threadIdx.x + 1) * cpg; ++c) {
+                s1 += part[(size_t)(r * C + c) * 4 + 2]; s2 += part[(size_t)(r * C + c) * 4 + 3];
+            }
+        float* o = scratch + (cta * G + threadIdx.x) * 2;
+        o[0] = s1; o[1] = s2;
     }
+    float* chan = scratch + (long long)B * S * G * 2 + cta * 2 * C;
     for (int c = threadIdx.x; c < C; c += GN_THREADS) {
-        atomicAdd(&dgamma[c], chan[c]);
-        atomicAdd(&dbeta[c], chan[C + c]);
+        float dg = 0.f, db = 0.f;
+        for (int r = 0; r < m.rpi; ++r) { dg += part[(size_t)(r * C + c) * 4]; db += part[(size_t)(r * C + c) * 4 + 1]; }
+        chan[c] = dg; chan[C + c] = db;
+    }
+}
+
+// dgamma[c] = sum over the B*S CTA rows of chan[.][0][c], dbeta likewise; 32 columns x 8 row lanes
+// per CTA, fixed summation order.
+__global__ void __launch_bounds__(256) gn_param_reduce_kernel(const float* __restrict__ chan, float* __restrict__ dgamma,
+                                                              float* __restrict__ dbeta, int rows, int C) {
+    __shared__ float sh[8][33];
+    const int col = blockIdx.x * 32 + (threadIdx.x & 31);   // column of the [rows][2C] matrix
+    const int lane = threadIdx.x >> 5;
+    float acc = 0.f;
+    if (col < 2 * C)
+        for (int r = lane; r < rows; r += 8) acc += chan[(long long)r * 2 * C + col];
+    sh[lane][threadIdx.x & 31] = acc;
+    __syncthreads();
+    if (lane == 0 && col < 2 * C) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x];
+        if (col < C) dgamma[col] = t; else dbeta[col - C] = t;
     }
 }
 
@@ -288,12 +321,21 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_apply_kernel(const T* __res
     }
 }
 
+// dynamic shared memory of the stats kernels: [rows per iteration][C][vals] floats
+template <int VEC>
+static size_t gn_part_bytes(int C, int vals) {
+    int nvec = C / VEC;
+    int tpr = nvec < GN_THREADS ? nvec : GN_THREADS;
+    int rpi = GN_THREADS / tpr;
+    return sizeof(float) * (size_t)rpi * C * vals;
+}
+
 template <typename T, int VEC>
 static int gn_fwd_t(const T* x, const float* gamma, const float* beta, T* y, float* stats, float* scratch, int B,
                     int HW, int C, int G, float eps, int silu, cudaStream_t st) {
     int S = gn_splits(B, HW, C);
     dim3 grid(S, B);
-    gn_stats_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(x, scratch, HW, C, G, S);
+    gn_stats_kernel<T, VEC><<<grid, GN_THREADS, gn_part_bytes<VEC>(C, 2), st>>>(x, scratch, HW, C, G, S);
     MVAE_LAUNCH_CHECK();
     gn_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(x, gamma, beta, y, stats, scratch, HW, C, G, S, eps, silu);
     MVAE_LAUNCH_CHECK();
@@ -305,8 +347,10 @@ static int gn_bwd_t(const T* dy, const T* x, const float* gamma, const float* be
                     int silu, cudaStream_t st) {
     int S = gn_splits(B, HW, C);
     dim3 grid(S, B);
-    gn_bwd_stats_kernel<T, VEC><<<grid, GN_THREADS, sizeof(float) * 2 * C, st>>>(dy, x, gamma, beta, stats, scratch,
-                                                                                  dgamma, dbeta, HW, C, G, S, silu);
+    gn_bwd_stats_kernel<T, VEC><<<grid, GN_THREADS, gn_part_bytes<VEC>(C, 4), st>>>(dy, x, gamma, beta, stats, scratch,
+                                                                                     B, HW, C, G, S, silu);
+    MVAE_LAUNCH_CHECK();
+    gn_param_reduce_kernel<<<(2 * C + 31) / 32, 256, 0, st>>>(scratch + (long long)B * S * G * 2, dgamma, dbeta, B * S, C);
     MVAE_LAUNCH_CHECK();
     gn_bwd_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(dy, x, gamma, beta, stats, scratch, dx_add, dx, HW, C, G,
                                                               S, silu);

@@ -10,6 +10,7 @@ import ctypes as C
 import torch
 
 from . import _lib as L
+from . import profile as P
 from ._lib import ConvDesc, check, lib, ptr, stream
 
 _scratch = {}
@@ -45,17 +46,34 @@ def conv_pack_weights(d: ConvDesc, w_oihw, wf, wd, ctot, coff):
           "conv2d_pack_weights")
 
 
+def conv_flops(d: ConvDesc) -> float:
+    """algorithmic FLOPs (2*MAC) of one direction of this conv as the reference executes it
+    (Upsample = 9 taps on the 2x grid, although the kernels run 4 taps per output parity)."""
+    oh, ow = conv_out_hw(d)
+    return 2.0 * d.batch * oh * ow * d.out_c * d.in_c * d.ksize * d.ksize
+
+
 def conv_fprop(d: ConvDesc, x, wf, bias, residual, out=None):
     oh, ow = conv_out_hw(d)
     y = out if out is not None else torch.empty((d.batch, oh, ow, d.out_c), dtype=x.dtype, device=x.device)
-    check(lib().mvae_conv2d_fprop(C.byref(d), ptr(x), ptr(wf), ptr(bias), ptr(residual), ptr(y), stream()),
-          "conv2d_fprop")
+    if P.active() is None:
+        check(lib().mvae_conv2d_fprop(C.byref(d), ptr(x), ptr(wf), ptr(bias), ptr(residual), ptr(y), stream()),
+              "conv2d_fprop")
+        return y
+    kind = "conv_fprop_umma" if lib().mvae_conv2d_uses_umma(C.byref(d)) else "conv_fprop_simt"
+    with P.region(kind, conv_flops(d), (x.numel() + y.numel()) * x.element_size()):
+        check(lib().mvae_conv2d_fprop(C.byref(d), ptr(x), ptr(wf), ptr(bias), ptr(residual), ptr(y), stream()),
+              "conv2d_fprop")
     return y
 
 
 def conv_dgrad(d: ConvDesc, dy, wd):
     dx = torch.empty((d.batch, d.in_h, d.in_w, d.in_c), dtype=dy.dtype, device=dy.device)
-    check(lib().mvae_conv2d_dgrad(C.byref(d), ptr(dy), ptr(wd), ptr(dx), stream()), "conv2d_dgrad")
+    kind = "conv_dgrad"
+    if P.active() is not None:
+        kind = "conv_dgrad_umma" if lib().mvae_conv2d_uses_umma(C.byref(d)) else "conv_dgrad_simt"
+    with P.region(kind, conv_flops(d) if P.active() else 0.0, (dy.numel() + dx.numel()) * dy.element_size()):
+        check(lib().mvae_conv2d_dgrad(C.byref(d), ptr(dy), ptr(wd), ptr(dx), stream()), "conv2d_dgrad")
     return dx
 
 
@@ -64,8 +82,12 @@ def conv_wgrad(d: ConvDesc, x, dy, want_bias=True):
     db = torch.empty((d.out_c,), dtype=torch.float32, device=x.device) if want_bias else None
     nbytes = lib().mvae_conv2d_wgrad_workspace_bytes(C.byref(d))
     ws = scratch("wgrad", nbytes, x.device)
-    check(lib().mvae_conv2d_wgrad(C.byref(d), ptr(x), ptr(dy), ptr(dw), ptr(db), ptr(ws), ws.numel(), stream()),
-          "conv2d_wgrad")
+    kind = "conv_wgrad"
+    if P.active() is not None:
+        kind = "conv_wgrad_umma" if lib().mvae_conv2d_uses_umma(C.byref(d)) else "conv_wgrad_simt"
+    with P.region(kind, conv_flops(d) if P.active() else 0.0, (x.numel() + dy.numel()) * x.element_size()):
+        check(lib().mvae_conv2d_wgrad(C.byref(d), ptr(x), ptr(dy), ptr(dw), ptr(db), ptr(ws), ws.numel(), stream()),
+              "conv2d_wgrad")
     return dw, db
 
 
@@ -75,20 +97,23 @@ def gn_fwd(x, gamma, beta, groups, eps, silu):
     stats = torch.empty((b, groups, 2), dtype=torch.float32, device=x.device)
     s = lib().mvae_groupnorm_splits(b, h * w, c)
     sc = scratch("gn", 4 * b * s * groups * 2, x.device)
-    check(lib().mvae_groupnorm_silu_fwd(ptr(x), ptr(gamma), ptr(beta), ptr(y), ptr(stats), ptr(sc), b, h * w, c,
-                                        groups, eps, int(silu), L.code_of(x.dtype), stream()), "groupnorm_silu_fwd")
+    with P.region("groupnorm_fwd", 0.0, 2 * x.numel() * x.element_size()):
+        check(lib().mvae_groupnorm_silu_fwd(ptr(x), ptr(gamma), ptr(beta), ptr(y), ptr(stats), ptr(sc), b, h * w, c,
+                                            groups, eps, int(silu), L.code_of(x.dtype), stream()),
+              "groupnorm_silu_fwd")
     return y, stats
 
 
 def gn_bwd(dy, x, gamma, beta, stats, dx_add, groups, silu):
     b, h, w, c = x.shape
     dx = torch.empty_like(x)
-    dgb = torch.zeros((2, c), dtype=torch.float32, device=x.device)
+    dgb = torch.empty((2, c), dtype=torch.float32, device=x.device)
     s = lib().mvae_groupnorm_splits(b, h * w, c)
-    sc = scratch("gn", 4 * b * s * groups * 2, x.device)
-    check(lib().mvae_groupnorm_silu_bwd(ptr(dy), ptr(x), ptr(gamma), ptr(beta), ptr(stats), ptr(dx_add), ptr(dx),
-                                        ptr(dgb[0]), ptr(dgb[1]), ptr(sc), b, h * w, c, groups, int(silu),
-                                        L.code_of(x.dtype), stream()), "groupnorm_silu_bwd")
+    sc = scratch("gn", 4 * b * s * (2 * groups + 2 * c), x.device)
+    with P.region("groupnorm_bwd", 0.0, (3 + (dx_add is not None)) * x.numel() * x.element_size()):
+        check(lib().mvae_groupnorm_silu_bwd(ptr(dy), ptr(x), ptr(gamma), ptr(beta), ptr(stats), ptr(dx_add), ptr(dx),
+                                            ptr(dgb[0]), ptr(dgb[1]), ptr(sc), b, h * w, c, groups, int(silu),
+                                            L.code_of(x.dtype), stream()), "groupnorm_silu_bwd")
     return dx, dgb[0], dgb[1]
 
 
@@ -97,8 +122,9 @@ def attn_fwd(qkv):
     c, t = c3 // 3, h * w
     out = torch.empty((b, h, w, c), dtype=qkv.dtype, device=qkv.device)
     probs = torch.empty((b, t, t), dtype=torch.float32, device=qkv.device)
-    check(lib().mvae_attn_core_fwd(ptr(qkv), ptr(out), ptr(probs), b, t, c, L.code_of(qkv.dtype), stream()),
-          "attn_core_fwd")
+    with P.region("attn_fwd", 4.0 * b * t * t * c, 0.0):
+        check(lib().mvae_attn_core_fwd(ptr(qkv), ptr(out), ptr(probs), b, t, c, L.code_of(qkv.dtype), stream()),
+              "attn_core_fwd")
     return out, probs
 
 
@@ -107,8 +133,9 @@ def attn_bwd(qkv, probs, dout):
     c, t = c3 // 3, h * w
     dqkv = torch.empty_like(qkv)
     ds = scratch("attn_ds", 4 * b * t * t, qkv.device)
-    check(lib().mvae_attn_core_bwd(ptr(qkv), ptr(probs), ptr(dout), ptr(dqkv), ptr(ds), b, t, c,
-                                   L.code_of(qkv.dtype), stream()), "attn_core_bwd")
+    with P.region("attn_bwd", 8.0 * b * t * t * c, 0.0):
+        check(lib().mvae_attn_core_bwd(ptr(qkv), ptr(probs), ptr(dout), ptr(dqkv), ptr(ds), b, t, c,
+                                       L.code_of(qkv.dtype), stream()), "attn_core_bwd")
     return dqkv
 
 

@@ -1,0 +1,114 @@
+"""Optimizer side of the training step on the fused multi-tensor kernels.
+
+Replaces, for the hot path, what the reference's Lightning module does around ``loss.backward()``
+(src/lightning_module.py:390-477): per-parameter NaN/Inf gradient zeroing
+(``on_before_optimizer_step``), global-norm clipping (``configure_gradient_clipping``,
+gradient_clip_val 1.0 by default) and ``torch.optim.Adam`` / ``AdamW`` (``configure_optimizers``).
+Two kernel launches per step (sum of squares of the finite gradient entries; clip + Adam update),
+no host synchronisation.  The arithmetic follows torch.optim.Adam/AdamW (single-tensor path):
+bias corrections 1-beta^t, denom = sqrt(v)/sqrt(bc2) + eps, step size lr/bc1; AdamW decays the
+parameter by (1 - lr*wd) first, Adam adds wd*p to the gradient.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Iterable, List, Optional
+
+import torch
+
+from . import _lib as L
+from ._lib import check, lib, ptr, stream
+
+
+class FusedAdamW:
+    """Adam / AdamW with fused global-norm clipping over a fixed list of fp32 parameters.
+
+    ``step()`` consumes ``p.grad`` of every parameter (a missing grad is treated as zeros by
+    skipping the tensor).  ``max_norm <= 0`` disables clipping.  State tensors are named as in
+    torch.optim (``exp_avg``, ``exp_avg_sq``) so ``state_dict()`` can be handed to a torch optimizer.
+    """
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-4, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-4, decoupled: bool = True, max_norm: float = 1.0):
+        self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
+        if not self.params:
+            raise ValueError("FusedAdamW got an empty parameter list")
+        for p in self.params:
+            if p.dtype != torch.float32 or not p.is_cuda or not p.is_contiguous():
+                raise L.MvaeError("FusedAdamW needs contiguous fp32 CUDA parameters (there is no CPU fallback)")
+        self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
+        self.weight_decay, self.decoupled, self.max_norm = float(weight_decay), bool(decoupled), float(max_norm)
+        self.step_count = 0
+        dev = self.params[0].device
+        self.exp_avg = [torch.zeros_like(p) for p in self.params]
+        self.exp_avg_sq = [torch.zeros_like(p) for p in self.params]
+        self._sqnorm = torch.zeros((), dtype=torch.float64, device=dev)
+        self._tables = None   # (grad data_ptrs tuple) -> device pointer tables
+        self._dev = dev
+
+    # ------------------------------------------------------------------ pointer tables
+    def _ptr_table(self, tensors) -> torch.Tensor:
+        return torch.tensor([t.data_ptr() for t in tensors], dtype=torch.int64).to(self._dev, non_blocking=False)
+
+    def _ensure_tables(self, plist, grads):
+        key = (tuple(p.data_ptr() for p in plist), tuple(g.data_ptr() for g in grads))
+        if self._tables is None or self._tables["key"] != key:
+            self._tables = {
+                "key": key,
+                "p": self._ptr_table(plist),
+                "g": self._ptr_table(grads),
+                "m": self._ptr_table([self._state_for(p)[0] for p in plist]),
+                "v": self._ptr_table([self._state_for(p)[1] for p in plist]),
+                "n": torch.tensor([p.numel() for p in plist], dtype=torch.int64).to(self._dev),
+                "count": len(plist),
+            }
+        return self._tables
+
+    def _state_for(self, p):
+        if not hasattr(self, "_index"):
+            self._index = {id(q): i for i, q in enumerate(self.params)}
+        i = self._index[id(p)]
+        return self.exp_avg[i], self.exp_avg_sq[i]
+
+    # ------------------------------------------------------------------ API
+    def zero_grad(self, set_to_none: bool = False):
+        for p in self.params:
+            if p.grad is not None:
+                if set_to_none:
+                    p.grad = None
+                else:
+                    p.grad.zero_()
+
+    def grad_norm(self) -> torch.Tensor:
+        """global L2 norm (fp64, 0-d device tensor) of the finite gradient entries seen by the last step()."""
+        return self._sqnorm.sqrt()
+
+    @torch.no_grad()
+    def step(self, lr: Optional[float] = None):
+        L.require_device()
+        plist = [p for p in self.params if p.grad is not None]
+        if not plist:
+            return
+        grads = []
+        for p in plist:
+            g = p.grad
+            if g.dtype != torch.float32 or not g.is_contiguous():
+                g = g.float().contiguous()
+                p.grad = g
+            grads.append(g)
+        t = self._ensure_tables(plist, grads)
+        self.step_count += 1
+        self._sqnorm.zero_()
+        check(lib().mvae_grad_sqnorm(ptr(t["g"]), ptr(t["n"]), t["count"], ptr(self._sqnorm), stream()), "grad_sqnorm")
+        check(lib().mvae_adamw_clip_step(ptr(t["p"]), ptr(t["g"]), ptr(t["m"]), ptr(t["v"]), ptr(t["n"]), t["count"],
+                                         ptr(self._sqnorm), self.max_norm, float(self.lr if lr is None else lr),
+                                         self.betas[0], self.betas[1], self.eps, self.weight_decay,
+                                         int(self.decoupled), self.step_count, stream()), "adamw_clip_step")
+        # parameters changed in place behind autograd's back: bump versions so the packed bf16
+        # operand caches (blocks.ConvOp.packed) are refreshed on the next forward
+        torch._C._increment_version(plist)
+
+    def state_dict(self):
+        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,
+                "lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay,
+                "decoupled": self.decoupled, "max_norm": self.max_norm}

@@ -1,0 +1,209 @@
+"""The training step as one object: forward -> VAELoss -> backward -> (data-parallel gradient
+all-reduce) -> clip + Adam/AdamW, restating what the reference's Lightning module does around the
+hot path (src/lightning_module.py:98-218 training_step, :390-477 optimizer / clipping / NaN guard)
+and what Lightning's DDP strategy adds when ``devices > 1`` (main.py:86-99): batch sharding, one
+process per GPU, gradients averaged over ranks by a bucketed all-reduce that overlaps backward.
+
+Pieces:
+  * ``GradBuckets``  — one flat fp32 gradient buffer laid out in reverse execution order and cut
+    into buckets; every parameter's ``.grad`` is a view into it.  A bucket is all-reduced (NCCL on
+    the GPU box, gloo in the CPU tests) the moment its last gradient has been written, while the
+    rest of the backward schedule keeps running.
+  * ``TrainStep``    — owns model + criterion + FusedAdamW + GradBuckets; ``step(x, cond)`` accepts
+    host (pinned) or device tensors, optionally splits the per-GPU batch into micro-batches
+    (gradients accumulate in the flat buffer; GroupNorm / attention are per sample, so the result
+    is the same as one big batch) and returns the loss dict as 0-d device tensors.
+  * ``shard_batch``  — the batch split DDP's DistributedSampler would do.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+
+def shard_batch(n: int, rank: int, world: int):
+    """contiguous, equal shards (n must divide by world): -> slice of the global batch for `rank`."""
+    if n % world != 0:
+        raise ValueError(f"global batch {n} is not divisible by world size {world}")
+    per = n // world
+    return slice(rank * per, (rank + 1) * per)
+
+
+class GradBuckets:
+    """Flat gradient storage + bucketed all-reduce.
+
+    params must be given in the order their gradients become ready during backward (last layer
+    first).  ``mark_ready(p)`` is called once per parameter per reduction round; when every
+    parameter of a bucket is ready the bucket's slice of the flat buffer is all-reduced
+    asynchronously (op AVG where the backend has it, else SUM followed by a scale).
+    ``finish()`` waits for all outstanding reductions.
+    """
+
+    def __init__(self, params: Sequence[nn.Parameter], bucket_bytes: int = 32 << 20, group=None):
+        self.params = list(params)
+        self.group = group
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        dev = self.params[0].device
+        total = sum(p.numel() for p in self.params)
+        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.views: Dict[int, torch.Tensor] = {}
+        self.bucket_of: Dict[int, int] = {}
+        self.bounds: List[List[int]] = []       # [start, end) element offsets per bucket
+        self.members: List[int] = []            # parameters per bucket
+        off, start, count = 0, 0, 0
+        for p in self.params:
+            n = p.numel()
+            self.views[id(p)] = self.flat[off:off + n].view(p.shape)
+            self.bucket_of[id(p)] = len(self.bounds)
+            off += n
+            count += 1
+            if (off - start) * 4 >= bucket_bytes:
+                self.bounds.append([start, off]); self.members.append(count)
+                start, count = off, 0
+        if count:
+            self.bounds.append([start, off]); self.members.append(count)
+        self._pending = list(self.members)
+        self._works: list = []
+        self.reduce_enabled = True
+        self.launched = 0
+        for p in self.params:
+            p.grad = self.views[id(p)]
+
+    # ---- per step
+    def zero(self):
+        self.flat.zero_()
+        self._pending = list(self.members)
+
+    def begin_round(self):
+        self._pending = list(self.members)
+
+    def accumulate(self, p: nn.Parameter, g: torch.Tensor):
+        """grad sink used by the encoder/decoder backward schedules: add into the flat view."""
+        self.views[id(p)].add_(g.view(p.shape))
+        self.mark_ready(p)
+
+    def mark_ready(self, p: nn.Parameter):
+        b = self.bucket_of.get(id(p))
+        if b is None:
+            return
+        self._pending[b] -= 1
+        if self._pending[b] == 0 and self.reduce_enabled and self.world > 1:
+            self._launch(b)
+
+    def _launch(self, b: int):
+        s, e = self.bounds[b]
+        t = self.flat[s:e]
+        backend = dist.get_backend(self.group)
+        if backend == "nccl":
+            w = dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group, async_op=True)
+            self._works.append((w, None))
+        else:
+            w = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            self._works.append((w, t))
+        self.launched += 1
+
+    def finish(self):
+        """wait for every outstanding bucket; buckets that never filled (unused parameters) are
+        reduced now so all ranks stay in step."""
+        if self.world > 1 and self.reduce_enabled:
+            for b, left in enumerate(self._pending):
+                if left > 0:
+                    self._pending[b] = 0
+                    self._launch(b)
+        for w, t in self._works:
+            w.wait()
+            if t is not None:
+                t.div_(self.world)
+        self._works = []
+
+
+def backward_order(model: nn.Module) -> List[nn.Parameter]:
+    """parameters in the order backward produces their gradients: decoder (last stage first), then
+    encoder, then whatever is left (condition_proj, projector heads ...)."""
+    seen, out = set(), []
+
+    def push(ps):
+        for p in ps:
+            if id(p) not in seen and p.requires_grad:
+                seen.add(id(p)); out.append(p)
+
+    for name in ("decoder", "encoder"):
+        stack = getattr(model, name, None)
+        if stack is not None and hasattr(stack, "stages"):
+            for st in reversed(stack.stages(True)):
+                push(st.params_backward_order())
+            push(stack.parameters())
+    push(model.parameters())
+    return out
+
+
+class TrainStep:
+    """One optimisation step of a BaseVAE / BetaVAE / ConditionalVAE on this rank's shard."""
+
+    def __init__(self, model: nn.Module, criterion: nn.Module, *, lr: float = 1e-4, weight_decay: float = 1e-4,
+                 betas=(0.9, 0.999), eps: float = 1e-8, decoupled: bool = True, max_norm: float = 1.0,
+                 micro_batch: Optional[int] = None, bucket_bytes: int = 32 << 20, group=None):
+        from .optim import FusedAdamW
+        self.model, self.criterion = model, criterion
+        self.micro_batch = micro_batch
+        self.order = backward_order(model)
+        self.buckets = GradBuckets(self.order, bucket_bytes, group)
+        self.optimizer = FusedAdamW(self.order, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
+                                    decoupled=decoupled, max_norm=max_norm)
+        self.device = self.order[0].device
+        self._hooks = []
+        sunk = set()
+        for name in ("decoder", "encoder"):
+            stack = getattr(model, name, None)
+            if stack is not None and hasattr(stack, "stages"):
+                stack._grad_sink = self.buckets.accumulate
+                sunk.update(id(p) for p in stack.parameters())
+        for p in self.order:
+            if id(p) not in sunk:
+                self._hooks.append(p.register_post_accumulate_grad_hook(self.buckets.mark_ready))
+
+    def close(self):
+        for h in self._hooks:
+            h.remove()
+        for name in ("decoder", "encoder"):
+            stack = getattr(self.model, name, None)
+            if stack is not None and hasattr(stack, "_grad_sink"):
+                stack._grad_sink = None
+
+    def _to_device(self, t):
+        if t is None or t.device == self.device:
+            return t
+        return t.to(self.device, non_blocking=True)
+
+    def step(self, x: torch.Tensor, cond: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        """x: (B, C, H, W) fp32 in [-1, 1]; cond: (B, n_modalities) one-hot or None.  Host tensors
+        are copied to the device here (use pinned memory for an asynchronous copy)."""
+        x, cond = self._to_device(x), self._to_device(cond)
+        n = x.shape[0]
+        mb = self.micro_batch or n
+        chunks = [(i, min(i + mb, n)) for i in range(0, n, mb)]
+        self.buckets.zero()
+        totals: Dict[str, torch.Tensor] = {}
+        for ci, (a, b) in enumerate(chunks):
+            last = ci == len(chunks) - 1
+            self.buckets.reduce_enabled = last
+            self.buckets.begin_round()
+            xs = x[a:b]
+            if cond is not None:
+                out = self.model(xs, cond[a:b])
+            else:
+                out = self.model(xs)
+            ld = self.criterion(inputs=xs, reconstructions=out["reconstruction"], posteriors=out["posterior"],
+                                priors=out["prior"])
+            w = (b - a) / n
+            (ld["loss"] * w if len(chunks) > 1 else ld["loss"]).backward()
+            for k, v in ld.items():
+                v = v.detach() * w if len(chunks) > 1 else v.detach()
+                totals[k] = v if k not in totals else totals[k] + v
+            del out, ld
+        self.buckets.finish()
+        self.optimizer.step()
+        return totals

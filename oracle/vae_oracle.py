@@ -301,3 +301,31 @@ def synthetic_batch(batch: int, channels: int, res: int, n_modalities: int = 12,
         for m in gray:
             x[idx == m, 1:] = 0.0
     return x, onehot, idx
+
+
+class ReferenceTrainer:
+    """The reference's optimisation step without Lightning (src/lightning_module.py:98-218 forward +
+    criterion, :468-477 NaN/Inf gradient zeroing, :452-466 clip_gradients(norm, 1.0), :390-406
+    AdamW(lr, weight_decay) / Adam) on the functional model above.  Used by the loss-curve parity
+    test and timed by bench.py as the CPU baseline ("port")."""
+
+    def __init__(self, sd: SD, lr=1e-4, weight_decay=1e-4, betas=(0.9, 0.999), max_norm=1.0, decoupled=True,
+                 loss_kwargs=None):
+        self.params = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+        cls = torch.optim.AdamW if decoupled else torch.optim.Adam
+        self.opt = cls(list(self.params.values()), lr=lr, weight_decay=weight_decay, betas=betas)
+        self.max_norm = max_norm
+        self.loss_kwargs = loss_kwargs or {}
+
+    def step(self, x, eps, condition=None):
+        out = vae_forward(self.params, x, eps, condition)
+        ld = vae_loss(out["reconstruction"], x, out["mean"], out["logvar"], **self.loss_kwargs)
+        self.opt.zero_grad(set_to_none=True)
+        ld["loss"].backward()
+        for p in self.params.values():
+            if p.grad is not None:
+                torch.nan_to_num_(p.grad, nan=0.0, posinf=0.0, neginf=0.0)
+        if self.max_norm and self.max_norm > 0:
+            torch.nn.utils.clip_grad_norm_(list(self.params.values()), self.max_norm)
+        self.opt.step()
+        return {k: float(v.detach()) for k, v in ld.items()}

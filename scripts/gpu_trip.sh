@@ -2,6 +2,7 @@
 # One GPU visit: each stage under its own timeout so a hung kernel cannot eat the whole lease.
 # usage: scripts/gpu_trip.sh <stage>...   (stages: simt umma model bench)
 mkdir -p gpurun_out
+rm -f gpurun_out/rc.txt
 export PYTHONUNBUFFERED=1
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
 for stage in "$@"; do
@@ -13,6 +14,9 @@ for stage in "$@"; do
     probe) timeout 300 python scripts/umma_probe.py > gpurun_out/probe.log 2>&1; echo "probe rc=$?" >> gpurun_out/rc.txt;;
     smoke) timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/rc.txt;;
     bench) timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/rc.txt;;
+    bench_c3) timeout 600 python bench.py --workload c3 --steps 5 --warmup 3 > gpurun_out/bench_c3.log 2>&1; echo "bench_c3 rc=$?" >> gpurun_out/rc.txt;;
+    bench_c4s) timeout 600 python bench.py --workload c4 --batch-per-gpu 128 --micro-batch 64 --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/bench_c4s.log 2>&1; echo "bench_c4s rc=$?" >> gpurun_out/rc.txt;;
+    kernels) timeout 900 python -m pytest tests/test_kernels_gpu.py -q -m gpu --timeout 300 > gpurun_out/t_kernels.log 2>&1; echo "kernels rc=$?" >> gpurun_out/rc.txt;;
   esac
 done
 cat gpurun_out/rc.txt

@@ -44,3 +44,21 @@ def rel_err(a, b):
     a = a.detach().double().cpu()
     b = b.detach().double().cpu()
     return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def grad_rel_err(name, grad, ref_grads):
+    """relative error of one parameter gradient.  Biases whose true gradient is analytically zero
+    come out of the reference as ~1e-10 rounding noise: a conv bias whose every path to the loss
+    crosses a GroupNorm with one channel per group (all trunk biases of the hidden<=32 golden
+    models), and AttnBlock.k.bias (softmax is shift-invariant along the keys).  Such a bias
+    (reference norm < 1e-4 x its layer's weight-gradient norm) only has to stay small in absolute
+    terms: <= 5e-2 x the weight-gradient norm, reported as error 0."""
+    ref = ref_grads[name].detach().double().cpu()
+    got = grad.detach().double().cpu()
+    if name.endswith(".bias"):
+        w = ref_grads.get(name[:-len(".bias")] + ".weight")
+        if w is not None:
+            wn = float(w.double().norm())
+            if float(ref.norm()) < 1e-4 * wn:
+                return 0.0 if float(got.norm()) <= 5e-2 * wn else float("inf")
+    return float((got - ref).norm() / max(float(ref.norm()), 1e-30))
