@@ -92,10 +92,12 @@ int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, fl
 
 /* GroupNorm(min(32,C), eps) [+ x*sigmoid(x)]  — Normalize + nonlinearity,
  * encoder_decoder.py:13-15,28-33 as used at :150-151,:158-159,:85,:325-326,:446-447.
- * x,y: [B, HW, C].  stats (out): [B][G][2] fp32 (mean, rstd).  scratch: B*splits*G*2 floats
- * (forward) or B*splits*(2*G + 2*C) floats (backward) with splits = mvae_groupnorm_splits().
+ * x,y: [B, HW, C].  stats (out): [B][G][2] fp32 (mean, rstd).  scratch: fp32 workspace of
+ * mvae_groupnorm_scratch_floats(batch, hw, c, groups, backward = 0 | 1) elements.
  * All reductions run in a fixed order: results are bitwise reproducible run to run. */
 int mvae_groupnorm_splits(int32_t batch, int32_t hw, int32_t c);
+int64_t mvae_groupnorm_scratch_floats(int32_t batch, int32_t hw, int32_t c, int32_t groups,
+                                      int32_t backward);
 int mvae_groupnorm_silu_fwd(const void* x, const float* gamma, const float* beta, void* y,
                             float* stats, float* scratch, int32_t batch, int32_t hw, int32_t c,
                             int32_t groups, float eps, int32_t apply_silu, int32_t dtype,

@@ -117,10 +117,19 @@ class Run:
             self.grads[p] = g
 
 
-class ConvOp:
-    """One (or several channel-concatenated) nn.Conv2d as packed fprop/dgrad operands."""
+PAD_C = 64   # skinny convs are zero-padded to one tcgen05 K / N tile in bf16 mode
 
-    def __init__(self, convs: Sequence[nn.Conv2d], mode: int):
+
+class ConvOp:
+    """One (or several channel-concatenated) nn.Conv2d as packed fprop/dgrad operands.
+
+    pad_in / pad_out: in bf16 mode a conv whose Cin (encoder conv_in: 1..6 channels) or Cout
+    (decoder conv_out: 1..3 channels) is below one tensor-core tile is run with that dimension
+    zero-padded to 64, so it takes the tcgen05 path instead of the SIMT one (these two
+    layers are bandwidth-bound; the padded MMA work is negligible).  The caller supplies / receives
+    activations with the padded channel count (`cin_of`, `cout_of`)."""
+
+    def __init__(self, convs: Sequence[nn.Conv2d], mode: int, pad_in: bool = False, pad_out: bool = False):
         self.convs = list(convs)
         c0 = self.convs[0]
         self.cin = c0.in_channels
@@ -128,9 +137,20 @@ class ConvOp:
         self.cout = sum(self.couts)
         self.k = c0.kernel_size[0]
         self.mode = mode
+        self.pad_in, self.pad_out = pad_in, pad_out
+
+    def cin_of(self, dtype) -> int:
+        if self.pad_in and dtype == torch.bfloat16 and self.cin < PAD_C and self.cout % 64 == 0:
+            return PAD_C
+        return self.cin
+
+    def cout_of(self, dtype) -> int:
+        if self.pad_out and dtype == torch.bfloat16 and self.cout < PAD_C and self.cin % 64 == 0:
+            return PAD_C
+        return self.cout
 
     def desc(self, run: Run, b: int, h: int, w: int):
-        return ops.conv_desc(b, h, w, self.cin, self.cout, self.k, self.mode, run.code)
+        return ops.conv_desc(b, h, w, self.cin_of(run.dtype), self.cout_of(run.dtype), self.k, self.mode, run.code)
 
     def params(self):
         out = []
@@ -143,19 +163,28 @@ class ConvOp:
         ver = tuple((c.weight._version, c.bias._version) for c in self.convs)
         ent = run.cache.get(key)
         if ent is None or ent["ver"] != ver or ent["dev"] != device:
-            d1 = ops.conv_desc(1, 8, 8, self.cin, self.cout, self.k, self.mode, run.code)
+            cin_p, cout_p = self.cin_of(run.dtype), self.cout_of(run.dtype)
+            d1 = ops.conv_desc(1, 8, 8, cin_p, cout_p, self.k, self.mode, run.code)
             nslabs = ops.conv_num_slabs(d1)
-            wf = torch.empty((nslabs, self.cout, self.cin), dtype=run.dtype, device=device)
-            wd = torch.empty((nslabs, self.cin, self.cout), dtype=run.dtype, device=device)
-            off = 0
-            for c in self.convs:
-                dd = ops.conv_desc(1, 8, 8, self.cin, c.out_channels, self.k, self.mode, run.code)
-                ops.conv_pack_weights(dd, c.weight.detach(), wf, wd, self.cout, off)
-                off += c.out_channels
-            if len(self.convs) == 1:
-                bias = self.convs[0].bias.detach()
+            wf = torch.empty((nslabs, cout_p, cin_p), dtype=run.dtype, device=device)
+            wd = torch.empty((nslabs, cin_p, cout_p), dtype=run.dtype, device=device)
+            if cin_p != self.cin or cout_p != self.cout:
+                c = self.convs[0]
+                wpad = torch.zeros((cout_p, cin_p, self.k, self.k), dtype=torch.float32, device=device)
+                wpad[:self.cout, :self.cin] = c.weight.detach()
+                ops.conv_pack_weights(d1, wpad, wf, wd, cout_p, 0)
+                bias = torch.zeros((cout_p,), dtype=torch.float32, device=device)
+                bias[:self.cout] = c.bias.detach()
             else:
-                bias = torch.cat([c.bias.detach() for c in self.convs]).contiguous()
+                off = 0
+                for c in self.convs:
+                    dd = ops.conv_desc(1, 8, 8, self.cin, c.out_channels, self.k, self.mode, run.code)
+                    ops.conv_pack_weights(dd, c.weight.detach(), wf, wd, self.cout, off)
+                    off += c.out_channels
+                if len(self.convs) == 1:
+                    bias = self.convs[0].bias.detach()
+                else:
+                    bias = torch.cat([c.bias.detach() for c in self.convs]).contiguous()
             ent = {"ver": ver, "dev": device, "wf": wf, "wd": wd, "bias": bias}
             run.cache[key] = ent
         return ent
@@ -170,6 +199,9 @@ class ConvOp:
         d = self.desc(run, b, h, w)
         ent = self.packed(run, x.device)
         dw, db = ops.conv_wgrad(d, x, dy, True)
+        if d.in_c != self.cin or d.out_c != self.cout:
+            dw = dw[:self.cout, :self.cin].contiguous()
+            db = db[:self.cout]
         off = 0
         for c in self.convs:
             run.add_grad(c.weight, dw[off:off + c.out_channels])
@@ -264,8 +296,8 @@ class AttnOp:
 class PlainConvOp:
     """a conv that is its own stage (conv_in, Downsample, Upsample)."""
 
-    def __init__(self, conv: nn.Conv2d, mode: int, need_dx: bool = True):
-        self.op = ConvOp([conv], mode)
+    def __init__(self, conv: nn.Conv2d, mode: int, need_dx: bool = True, pad_in: bool = False):
+        self.op = ConvOp([conv], mode, pad_in=pad_in)
         self.need_dx = need_dx
 
     def params_backward_order(self):
@@ -283,9 +315,9 @@ class PlainConvOp:
 class HeadOp:
     """norm_out -> swish -> conv_out (encoder_decoder.py:325-327, :446-450)."""
 
-    def __init__(self, norm: nn.GroupNorm, conv: nn.Conv2d):
+    def __init__(self, norm: nn.GroupNorm, conv: nn.Conv2d, pad_out: bool = False):
         self.norm = norm
-        self.op = ConvOp([conv], L.CONV_S1)
+        self.op = ConvOp([conv], L.CONV_S1, pad_out=pad_out)
 
     def params_backward_order(self):
         return self.op.params() + [self.norm.weight, self.norm.bias]
@@ -413,7 +445,7 @@ class Encoder(_Stack):
         self._init_runtime()
 
     def stages(self, need_input_grad: bool):
-        st = [PlainConvOp(self.conv_in, L.CONV_S1, need_dx=need_input_grad)]
+        st = [PlainConvOp(self.conv_in, L.CONV_S1, need_dx=need_input_grad, pad_in=True)]
         for lv, level in enumerate(self.down):
             for ib, blk in enumerate(level.block):
                 st.append(ResOp(blk))
@@ -425,12 +457,16 @@ class Encoder(_Stack):
                HeadOp(self.norm_out, self.conv_out)]
         return st
 
+    def in_channels_nhwc(self, dtype) -> int:
+        """channel count forward_nhwc() expects (conv_in zero-padded to 64 in bf16 mode)"""
+        return ConvOp([self.conv_in], L.CONV_S1, pad_in=True).cin_of(dtype)
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """x NCHW fp32 -> (B, 2*z_channels, R, R) NCHW fp32 (same contract as the reference)."""
         L.require_device()
-        xin = _ToNHWC.apply(x.float().contiguous(), self.compute_dtype)
+        xin = _ToNHWC.apply(x.float().contiguous(), self.compute_dtype, self.in_channels_nhwc(self.compute_dtype))
         y = self.forward_nhwc(xin, x.requires_grad)
-        return _ToNCHW.apply(y)
+        return _ToNCHW.apply(y, y.shape[-1])
 
 
 class Decoder(_Stack):
@@ -488,33 +524,43 @@ class Decoder(_Stack):
                     st.append(AttnOp(level.attn[ib]))
             if hasattr(level, "upsample"):
                 st.append(PlainConvOp(level.upsample.conv, L.CONV_UP))
-        st.append(HeadOp(self.norm_out, self.conv_out))
+        st.append(HeadOp(self.norm_out, self.conv_out, pad_out=True))
         return st
+
+    def out_channels_nhwc(self, dtype) -> int:
+        """channel count of forward_nhwc()'s output (conv_out zero-padded to 64 in bf16 mode)"""
+        return ConvOp([self.conv_out], L.CONV_S1, pad_out=True).cout_of(dtype)
 
     def forward(self, z: torch.Tensor) -> torch.Tensor:
         """z NCHW fp32 -> reconstruction NCHW fp32."""
         L.require_device()
-        zin = _ToNHWC.apply(z.float().contiguous(), self.compute_dtype)
+        zin = _ToNHWC.apply(z.float().contiguous(), self.compute_dtype, z.shape[1])
         y = self.forward_nhwc(zin, z.requires_grad)
-        return _ToNCHW.apply(y)
+        return _ToNCHW.apply(y, self.conv_out.out_channels)
 
 
 class _ToNHWC(torch.autograd.Function):
+    """NCHW fp32 -> NHWC compute dtype, channels zero-padded to c_out"""
+
     @staticmethod
-    def forward(ctx, x_nchw, dtype):
-        return ops.nchw_f32_to_nhwc(x_nchw, dtype)
+    def forward(ctx, x_nchw, dtype, c_out):
+        ctx.c = x_nchw.shape[1]
+        return ops.input_pack_fwd(x_nchw, None, None, None, c_out, dtype)
 
     @staticmethod
     def backward(ctx, dy):
-        return ops.nhwc_to_nchw_f32(dy.contiguous()), None
+        return ops.nhwc_to_nchw_f32(dy.contiguous(), 0, ctx.c), None, None
 
 
 class _ToNCHW(torch.autograd.Function):
+    """NHWC -> NCHW fp32, first c_real channels (the rest is tcgen05 tile padding)"""
+
     @staticmethod
-    def forward(ctx, x_nhwc):
+    def forward(ctx, x_nhwc, c_real):
         ctx.dtype = x_nhwc.dtype
-        return ops.nhwc_to_nchw_f32(x_nhwc)
+        ctx.c_pad = x_nhwc.shape[-1]
+        return ops.nhwc_to_nchw_f32(x_nhwc, 0, c_real)
 
     @staticmethod
     def backward(ctx, dy):
-        return ops.nchw_f32_to_nhwc(dy.float().contiguous(), ctx.dtype)
+        return ops.input_pack_fwd(dy.float().contiguous(), None, None, None, ctx.c_pad, ctx.dtype), None

@@ -36,6 +36,7 @@ int dis_input_fwd(const float* x, const long long* idx, const float* pw, const f
 int dis_input_bwd(const void* d_in, const float* x, const long long* idx, const int* is_gray, float* dpw, float* dpb,
                   int B, int xc, int HW, int n_mod, int out_c, int dtype, cudaStream_t st);
 int gn_splits(int B, int HW, int C);
+long long gn_scratch_floats(int B, int HW, int C, int G, int backward);
 int gn_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, float* scratch, int B, int HW,
            int C, int G, float eps, int silu, int dtype, cudaStream_t st);
 int gn_bwd(const void* dy, const void* x, const float* gamma, const float* beta, const float* stats, const void* dx_add,
@@ -199,6 +200,9 @@ int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, fl
 }
 
 int mvae_groupnorm_splits(int32_t batch, int32_t hw, int32_t c) { return gn_splits(batch, hw, c); }
+int64_t mvae_groupnorm_scratch_floats(int32_t batch, int32_t hw, int32_t c, int32_t groups, int32_t backward) {
+    return gn_scratch_floats(batch, hw, c, groups, backward);
+}
 
 int mvae_groupnorm_silu_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, float* scratch,
                             int32_t batch, int32_t hw, int32_t c, int32_t groups, float eps, int32_t apply_silu,

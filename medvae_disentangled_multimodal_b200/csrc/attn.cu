@@ -168,12 +168,22 @@ static int attn_bwd_t(const T* qkv, const float* probs, const T* dout, T* dqkv, 
     return bgemm<float, T, T>(ds, qkv, dqkv + C, g, st);
 }
 
+// attn_umma.cu: tensor-core path (bf16, C % 64 == 0, T <= 256)
+bool attn_umma_ok(int Tn, int C);
+int attn_fwd_umma(const bf16* qkv, bf16* out, void* probs, int B, int Tn, int C, cudaStream_t st);
+int attn_bwd_umma(const bf16* qkv, const void* probs, const bf16* dout, bf16* dqkv, void* ds, int B, int Tn, int C,
+                  cudaStream_t st);
+
 int attn_fwd(const void* qkv, void* out, float* probs, int B, int Tn, int C, int dtype, cudaStream_t st) {
+    if (dtype == MVAE_BF16 && attn_umma_ok(Tn, C) && debug_knob(2) == 0)
+        return attn_fwd_umma((const bf16*)qkv, (bf16*)out, probs, B, Tn, C, st);
     if (dtype == MVAE_F32) return attn_fwd_t<float>((const float*)qkv, (float*)out, probs, B, Tn, C, st);
     return attn_fwd_t<bf16>((const bf16*)qkv, (bf16*)out, probs, B, Tn, C, st);
 }
 int attn_bwd(const void* qkv, const float* probs, const void* dout, void* dqkv, float* ds, int B, int Tn, int C,
              int dtype, cudaStream_t st) {
+    if (dtype == MVAE_BF16 && attn_umma_ok(Tn, C) && debug_knob(2) == 0)
+        return attn_bwd_umma((const bf16*)qkv, probs, (const bf16*)dout, (bf16*)dqkv, ds, B, Tn, C, st);
     if (dtype == MVAE_F32)
         return attn_bwd_t<float>((const float*)qkv, probs, (const float*)dout, (float*)dqkv, ds, B, Tn, C, st);
     return attn_bwd_t<bf16>((const bf16*)qkv, probs, (const bf16*)dout, (bf16*)dqkv, ds, B, Tn, C, st);

@@ -57,6 +57,16 @@ static int view_tmap(CUtensorMap* m, const bf16* base, const View& v, int C, int
     return encode_tmap(m, base + v.off, 4, dims, st, box);
 }
 
+// 3-D map {inner, rows, batch} over a pitched bf16 matrix stack (attn_umma.cu)
+int encode_tmap_3d_bf16(CUtensorMap* m, const void* base, unsigned long long inner, unsigned long long rows,
+                        unsigned long long batch, unsigned long long pitch_elems, unsigned long long batch_elems,
+                        unsigned box_inner, unsigned box_rows) {
+    cuuint64_t dims[3] = {inner, rows, batch};
+    cuuint64_t st[2] = {pitch_elems * 2, batch_elems * 2};
+    cuuint32_t box[3] = {box_inner, box_rows, 1u};
+    return encode_tmap(m, base, 3, dims, st, box);
+}
+
 // pixel-box geometry: 128 GEMM rows = bw x bh x bn pixels of the iteration grid
 struct BoxGeom {
     int bw, bh, bn, tiles_x, tiles_y, tiles_n, rows;

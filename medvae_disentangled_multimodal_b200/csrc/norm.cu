@@ -16,16 +16,40 @@ namespace mvae {
 constexpr int GN_THREADS = 256;
 constexpr int MAX_G = 32;
 
-int gn_splits(int B, int HW, int C) {
+// The two passes of each direction (statistics, then apply) run over CHUNKS of samples small enough
+// that the slab(s) read by the first pass are still in the 126 MB L2 when the second pass reads
+// them again: HBM then sees each tensor once.
+int gn_chunk(int B, int HW, int C, int tensors) {
+    const long long budget = 12LL << 20;   // elements per chunk over all re-read tensors (24 MB of bf16)
+    long long per = (long long)HW * C * tensors;
+    long long nb = budget / (per > 0 ? per : 1);
+    if (nb < 1) nb = 1;
+    if (nb > B) nb = B;
+    return (int)nb;
+}
+static int gn_splits_for(int nb, int HW) {
     // enough CTAs to fill the machine (~4 per SM), at least 32 pixel rows per CTA
-    long long want = (148LL * 4 + B - 1) / B;
+    long long want = (148LL * 4 + nb - 1) / nb;
     long long cap = (HW + 31) / 32;
     if (want > cap) want = cap;
     if (want < 1) want = 1;
     if (want > 64) want = 64;
     return (int)want;
 }
-
+// floats of scratch the forward (backward = 0) or backward (= 1) entry point needs
+long long gn_scratch_floats(int B, int HW, int C, int G, int backward) {
+    const int nb = gn_chunk(B, HW, C, backward ? 2 : 1);
+    const int S = gn_splits_for(nb, HW);
+    const long long chunks = (B + nb - 1) / nb;
+    long long n = (long long)nb * S * G * 2;
+    if (backward) n += chunks * nb * S * 2 * C;
+    return n;
+}
+int gn_splits(int B, int HW, int C) {
+    // legacy sizing helper: the larger of the two directions' split counts
+    int a = gn_splits_for(gn_chunk(B, HW, C, 1), HW), b = gn_splits_for(gn_chunk(B, HW, C, 2), HW);
+    return a > b ? a : b;
+}
 // thread mapping for a [rows][C] slab processed VEC channels at a time
 struct RowMap {
     int nvec, tpr, rpi, v, r;   // vectors per row, threads per row, rows per iteration, my vector, my row lane
@@ -75,7 +99,17 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const T* __restric
             float s[VEC], q[VEC], pv[VEC];
 #pragma unroll
             for (int j = 0; j < VEC; ++j) { s[j] = 0.f; q[j] = 0.f; pv[j] = pivot[(v * VEC + j) / cpg]; }
-            for (int p = p0 + m.r; p < p1; p += m.rpi) {
+            int p = p0 + m.r;
+            for (; p + 3 * m.rpi < p1; p += 4 * m.rpi) {
+                float f[4][VEC];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) Ld<T, VEC>::load(xn + (long long)(p + u * m.rpi) * C + v * VEC, f[u]);
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) { float d = f[u][j] - pv[j]; s[j] += d; q[j] = fmaf(d, d, q[j]); }
+            }
+            for (; p < p1; p += m.rpi) {
                 float f[VEC];
                 Ld<T, VEC>::load(xn + (long long)p * C + v * VEC, f);
 #pragma unroll
@@ -145,7 +179,22 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const T* __restric
                 a[j] = rstd[g] * gamma[c];
                 b[j] = beta[c] - mean[g] * a[j];
             }
-            for (int p = p0 + m.r; p < p1; p += m.rpi) {
+            int p = p0 + m.r;
+            for (; p + 3 * m.rpi < p1; p += 4 * m.rpi) {
+                float f[4][VEC];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) Ld<T, VEC>::load(xn + (long long)(p + u * m.rpi) * C + v * VEC, f[u]);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) {
+                        float t = fmaf(f[u][j], a[j], b[j]);
+                        f[u][j] = silu ? t * sigmoidf_(t) : t;
+                    }
+                    Ld<T, VEC>::store(yn + (long long)(p + u * m.rpi) * C + v * VEC, f[u]);
+                }
+            }
+            for (; p < p1; p += m.rpi) {
                 float f[VEC];
                 Ld<T, VEC>::load(xn + (long long)p * C + v * VEC, f);
 #pragma unroll
@@ -170,7 +219,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __res
                                                                   const float* __restrict__ gamma,
                                                                   const float* __restrict__ beta,
                                                                   const float* __restrict__ stats,
-                                                                  float* __restrict__ scratch, int B, int HW, int C,
+                                                                  float* __restrict__ scratch,
+                                                                  float* __restrict__ chan_scratch, int HW, int C,
                                                                   int G, int S, int silu) {
     __shared__ float mean[MAX_G], rstd[MAX_G];
     extern __shared__ float part[];   // [rows per iteration][C][4] : dg, db, a1, a2
@@ -195,10 +245,7 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __res
                 ga[j] = gamma[c]; be[j] = beta[c]; mu[j] = mean[g]; rs[j] = rstd[g];
                 dg[j] = 0.f; db[j] = 0.f; a1[j] = 0.f; a2[j] = 0.f;
             }
-            for (int p = p0 + m.r; p < p1; p += m.rpi) {
-                float fx[VEC], fd[VEC];
-                Ld<T, VEC>::load(xn + (long long)p * C + v * VEC, fx);
-                Ld<T, VEC>::load(dn + (long long)p * C + v * VEC, fd);
+            auto accum = [&](const float* fx, const float* fd) {
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
                     float xh = (fx[j] - mu[j]) * rs[j];
@@ -212,6 +259,23 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __res
                     float dxh = du * ga[j];
                     a1[j] += dxh; a2[j] = fmaf(dxh, xh, a2[j]);
                 }
+            };
+            int p = p0 + m.r;
+            for (; p + m.rpi < p1; p += 2 * m.rpi) {
+                float fx[2][VEC], fd[2][VEC];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    Ld<T, VEC>::load(xn + (long long)(p + u * m.rpi) * C + v * VEC, fx[u]);
+                    Ld<T, VEC>::load(dn + (long long)(p + u * m.rpi) * C + v * VEC, fd[u]);
+                }
+                accum(fx[0], fd[0]);
+                accum(fx[1], fd[1]);
+            }
+            for (; p < p1; p += m.rpi) {
+                float fx[VEC], fd[VEC];
+                Ld<T, VEC>::load(xn + (long long)p * C + v * VEC, fx);
+                Ld<T, VEC>::load(dn + (long long)p * C + v * VEC, fd);
+                accum(fx, fd);
             }
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
@@ -232,7 +296,7 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __res
         float* o = scratch + (cta * G + threadIdx.x) * 2;
         o[0] = s1; o[1] = s2;
     }
-    float* chan = scratch + (long long)B * S * G * 2 + cta * 2 * C;
+    float* chan = chan_scratch + cta * 2 * C;
     for (int c = threadIdx.x; c < C; c += GN_THREADS) {
         float dg = 0.f, db = 0.f;
         for (int r = 0; r < m.rpi; ++r) { dg += part[(size_t)(r * C + c) * 4]; db += part[(size_t)(r * C + c) * 4 + 1]; }
@@ -297,12 +361,7 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_apply_kernel(const T* __res
                 int c = v * VEC + j, g = c / cpg;
                 ga[j] = gamma[c]; be[j] = beta[c]; mu[j] = mean[g]; rs[j] = rstd[g]; c1[j] = m1[g]; c2[j] = m2[g];
             }
-            for (int p = p0 + m.r; p < p1; p += m.rpi) {
-                long long off = base + (long long)p * C + v * VEC;
-                float fx[VEC], fd[VEC], fa[VEC];
-                Ld<T, VEC>::load(x + off, fx);
-                Ld<T, VEC>::load(dy + off, fd);
-                if (dx_add) Ld<T, VEC>::load(dx_add + off, fa);
+            auto one = [&](float* fx, const float* fd, const float* fa) {
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
                     float xh = (fx[j] - mu[j]) * rs[j];
@@ -315,6 +374,31 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_apply_kernel(const T* __res
                     float r = rs[j] * (du * ga[j] - c1[j] - xh * c2[j]);
                     fx[j] = dx_add ? r + fa[j] : r;
                 }
+            };
+            int p = p0 + m.r;
+            for (; p + m.rpi < p1; p += 2 * m.rpi) {
+                float fx[2][VEC], fd[2][VEC], fa[2][VEC];
+                long long off[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    off[u] = base + (long long)(p + u * m.rpi) * C + v * VEC;
+                    Ld<T, VEC>::load(x + off[u], fx[u]);
+                    Ld<T, VEC>::load(dy + off[u], fd[u]);
+                    if (dx_add) Ld<T, VEC>::load(dx_add + off[u], fa[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    one(fx[u], fd[u], fa[u]);
+                    Ld<T, VEC>::store(dx + off[u], fx[u]);
+                }
+            }
+            for (; p < p1; p += m.rpi) {
+                long long off = base + (long long)p * C + v * VEC;
+                float fx[VEC], fd[VEC], fa[VEC];
+                Ld<T, VEC>::load(x + off, fx);
+                Ld<T, VEC>::load(dy + off, fd);
+                if (dx_add) Ld<T, VEC>::load(dx_add + off, fa);
+                one(fx, fd, fa);
                 Ld<T, VEC>::store(dx + off, fx);
             }
         }
@@ -333,27 +417,43 @@ static size_t gn_part_bytes(int C, int vals) {
 template <typename T, int VEC>
 static int gn_fwd_t(const T* x, const float* gamma, const float* beta, T* y, float* stats, float* scratch, int B,
                     int HW, int C, int G, float eps, int silu, cudaStream_t st) {
-    int S = gn_splits(B, HW, C);
-    dim3 grid(S, B);
-    gn_stats_kernel<T, VEC><<<grid, GN_THREADS, gn_part_bytes<VEC>(C, 2), st>>>(x, scratch, HW, C, G, S);
-    MVAE_LAUNCH_CHECK();
-    gn_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(x, gamma, beta, y, stats, scratch, HW, C, G, S, eps, silu);
-    MVAE_LAUNCH_CHECK();
+    const int nb = gn_chunk(B, HW, C, 1);
+    const int S = gn_splits_for(nb, HW);
+    for (int n0 = 0; n0 < B; n0 += nb) {
+        const int n = (B - n0 < nb) ? (B - n0) : nb;
+        const long long off = (long long)n0 * HW * C;
+        dim3 grid(S, n);
+        gn_stats_kernel<T, VEC><<<grid, GN_THREADS, gn_part_bytes<VEC>(C, 2), st>>>(x + off, scratch, HW, C, G, S);
+        MVAE_LAUNCH_CHECK();
+        gn_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(x + off, gamma, beta, y + off, stats + (long long)n0 * G * 2,
+                                                              scratch, HW, C, G, S, eps, silu);
+        MVAE_LAUNCH_CHECK();
+    }
     return 0;
 }
 template <typename T, int VEC>
 static int gn_bwd_t(const T* dy, const T* x, const float* gamma, const float* beta, const float* stats,
                     const T* dx_add, T* dx, float* dgamma, float* dbeta, float* scratch, int B, int HW, int C, int G,
                     int silu, cudaStream_t st) {
-    int S = gn_splits(B, HW, C);
-    dim3 grid(S, B);
-    gn_bwd_stats_kernel<T, VEC><<<grid, GN_THREADS, gn_part_bytes<VEC>(C, 4), st>>>(dy, x, gamma, beta, stats, scratch,
-                                                                                     B, HW, C, G, S, silu);
-    MVAE_LAUNCH_CHECK();
-    gn_param_reduce_kernel<<<(2 * C + 31) / 32, 256, 0, st>>>(scratch + (long long)B * S * G * 2, dgamma, dbeta, B * S, C);
-    MVAE_LAUNCH_CHECK();
-    gn_bwd_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(dy, x, gamma, beta, stats, scratch, dx_add, dx, HW, C, G,
-                                                              S, silu);
+    const int nb = gn_chunk(B, HW, C, 2);
+    const int S = gn_splits_for(nb, HW);
+    float* chan = scratch + (long long)nb * S * G * 2;
+    long long rows = 0;
+    for (int n0 = 0; n0 < B; n0 += nb) {
+        const int n = (B - n0 < nb) ? (B - n0) : nb;
+        const long long off = (long long)n0 * HW * C;
+        const float* st_n = stats + (long long)n0 * G * 2;
+        dim3 grid(S, n);
+        gn_bwd_stats_kernel<T, VEC><<<grid, GN_THREADS, gn_part_bytes<VEC>(C, 4), st>>>(
+            dy + off, x + off, gamma, beta, st_n, scratch, chan + rows * 2 * C, HW, C, G, S, silu);
+        MVAE_LAUNCH_CHECK();
+        gn_bwd_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(dy + off, x + off, gamma, beta, st_n, scratch,
+                                                                  dx_add ? dx_add + off : nullptr, dx + off, HW, C, G,
+                                                                  S, silu);
+        MVAE_LAUNCH_CHECK();
+        rows += (long long)n * S;
+    }
+    gn_param_reduce_kernel<<<(2 * C + 31) / 32, 256, 0, st>>>(chan, dgamma, dbeta, (int)rows, C);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

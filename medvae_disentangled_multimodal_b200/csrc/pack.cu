@@ -61,40 +61,47 @@ int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot
 // ------------------------------------------------------------------ wgrad finalisation
 // partial [splits][nslabs][Cout][Cin] fp32 -> dW [Cout][Cin][R][R] fp32 (sum over splits; UP
 // mode: each (r,s) receives the 4 slabs whose R-sets contain it).
-__global__ void wgrad_finalize_kernel(const float* __restrict__ partial, float* __restrict__ dw, int splits,
-                                      int nslabs, int Cout, int Cin, int R, int mode) {
-    long long total = (long long)Cout * Cin * R * R;
-    long long slab_stride = (long long)Cout * Cin;
-    long long split_stride = slab_stride * nslabs;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+__global__ void __launch_bounds__(256) wgrad_finalize_kernel(const float* __restrict__ partial, float* __restrict__ dw,
+                                                             int splits, int nslabs, int Cout, int Cin, int R, int mode) {
+    // one thread per (co, ci): reads of every slab are coalesced along ci, and the thread's R*R
+    // outputs are contiguous in OIHW, so a warp writes one contiguous 32*R*R*4-byte span.
+    const long long pairs = (long long)Cout * Cin;
+    const long long slab_stride = pairs;
+    const long long split_stride = slab_stride * nslabs;
+    const int RR = R * R;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < pairs;
          i += (long long)gridDim.x * blockDim.x) {
-        // iterate with ci fastest for coalesced partial reads: i -> (rs, co, ci)
-        int ci = (int)(i % Cin);
-        long long r_ = i / Cin;
-        int co = (int)(r_ % Cout);
-        int rs = (int)(r_ / Cout);
-        int r = rs / R, s = rs % R;
-        float acc = 0.f;
-        if (mode == MVAE_CONV_UP) {
-            for (int a = 0; a < 2; ++a) {
-                int ui = (a == 0) ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0);
-                for (int b = 0; b < 2; ++b) {
-                    int vi = (b == 0) ? (s == 0 ? 0 : 1) : (s == 2 ? 1 : 0);
-                    int slab = ((a * 2 + b) * 2 + ui) * 2 + vi;
-                    const float* p = partial + slab * slab_stride + (long long)co * Cin + ci;
-                    for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+        float out[9];
+#pragma unroll
+        for (int rs = 0; rs < 9; ++rs) {
+            if (rs >= RR) break;
+            float acc = 0.f;
+            if (mode == MVAE_CONV_UP) {
+                const int r = rs / 3, s_ = rs % 3;
+                for (int a = 0; a < 2; ++a) {
+                    int ui = (a == 0) ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0);
+                    for (int b = 0; b < 2; ++b) {
+                        int vi = (b == 0) ? (s_ == 0 ? 0 : 1) : (s_ == 2 ? 1 : 0);
+                        int slab = ((a * 2 + b) * 2 + ui) * 2 + vi;
+                        const float* p = partial + slab * slab_stride + i;
+                        for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+                    }
                 }
+            } else {
+                const float* p = partial + rs * slab_stride + i;
+                for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
             }
-        } else {
-            const float* p = partial + rs * slab_stride + (long long)co * Cin + ci;
-            for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+            out[rs] = acc;
         }
-        dw[((long long)co * Cin + ci) * R * R + rs] = acc;
+        float* o = dw + i * RR;
+#pragma unroll
+        for (int rs = 0; rs < 9; ++rs)
+            if (rs < RR) o[rs] = out[rs];
     }
 }
 
 int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int splits, cudaStream_t st) {
-    long long total = (long long)g.Cout * g.Cin * g.R * g.R;
+    long long total = (long long)g.Cout * g.Cin;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
     wgrad_finalize_kernel<<<blocks, 256, 0, st>>>(partial, dw, splits, conv_num_slabs(g), g.Cout, g.Cin, g.R, g.mode);
@@ -131,17 +138,76 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const T* __restrict
         __syncthreads();
     }
 }
+// vectorised variant (C % 8 == 0): 16-byte (bf16) / 32-byte (fp32) loads, 4 independent rows in
+// flight per thread; HBM-bound (one read of dy).
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __restrict__ dy, float* __restrict__ scratch,
+                                                                 long long M, int C, long long rows_per_cta) {
+    __shared__ float sh[256 * 8];
+    const long long r0 = blockIdx.x * rows_per_cta;
+    long long r1 = r0 + rows_per_cta;
+    if (r1 > M) r1 = M;
+    const int nvec = C / 8;
+    const int tpr = nvec < 256 ? nvec : 256;
+    const int rpi = 256 / tpr;
+    const int tv = threadIdx.x % tpr, tr = threadIdx.x / tpr;
+    for (int vb = 0; vb < nvec; vb += tpr) {
+        const int v = vb + tv;
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        if (tr < rpi && v < nvec) {
+            const T* base = dy + (long long)v * 8;
+            long long r = r0 + tr;
+            for (; r + 3LL * rpi < r1; r += 4LL * rpi) {
+                Vec8<T> a, b, c, d;
+                a.load(base + r * C); b.load(base + (r + rpi) * C);
+                c.load(base + (r + 2LL * rpi) * C); d.load(base + (r + 3LL * rpi) * C);
+                float fa[8], fb[8], fc[8], fd[8];
+                a.unpack(fa); b.unpack(fb); c.unpack(fc); d.unpack(fd);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += (fa[j] + fb[j]) + (fc[j] + fd[j]);
+            }
+            for (; r < r1; r += rpi) {
+                Vec8<T> a; a.load(base + r * C);
+                float fa[8]; a.unpack(fa);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += fa[j];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sh[threadIdx.x * 8 + j] = acc[j];
+        __syncthreads();
+        if (tr == 0 && v < nvec) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float t = 0.f;
+                for (int q = 0; q < rpi; ++q) t += sh[(q * tpr + tv) * 8 + j];
+                scratch[(long long)blockIdx.x * C + v * 8 + j] = t;
+            }
+        }
+        __syncthreads();
+    }
+}
 __global__ void colsum_fold_kernel(const float* __restrict__ scratch, float* __restrict__ db, int parts, int C) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+    __shared__ float sh[8][33];
+    const int c = blockIdx.x * 32 + threadIdx.x;
     float s = 0.f;
-    for (int p = 0; p < parts; ++p) s += scratch[(long long)p * C + c];
-    db[c] = s;
+    if (c < C)
+        for (int p = threadIdx.y; p < parts; p += 8) s += scratch[(long long)p * C + c];
+    sh[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x];
+        db[c] = t;
+    }
 }
 
 int colsum_parts(long long M) {
     long long parts = (M + 127) / 128;
-    if (parts > 592) parts = 592;
+    if (parts > 1184) parts = 1184;   // 8 CTAs per SM
     if (parts < 1) parts = 1;
     return (int)parts;
 }
@@ -150,12 +216,17 @@ int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dt
     int parts = colsum_parts(M);
     long long rpc = (M + parts - 1) / parts;
     parts = (int)((M + rpc - 1) / rpc);
-    if (dtype == MVAE_F32)
+    if (C % 8 == 0) {
+        if (dtype == MVAE_F32)
+            colsum_partial_vec_kernel<float><<<parts, 256, 0, st>>>((const float*)dy, scratch, M, C, rpc);
+        else
+            colsum_partial_vec_kernel<bf16><<<parts, 256, 0, st>>>((const bf16*)dy, scratch, M, C, rpc);
+    } else if (dtype == MVAE_F32)
         colsum_partial_kernel<float><<<parts, 256, 0, st>>>((const float*)dy, scratch, M, C, rpc);
     else
         colsum_partial_kernel<bf16><<<parts, 256, 0, st>>>((const bf16*)dy, scratch, M, C, rpc);
     MVAE_LAUNCH_CHECK();
-    colsum_fold_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, db, parts, C);
+    colsum_fold_kernel<<<(C + 31) / 32, dim3(32, 8), 0, st>>>(scratch, db, parts, C);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
@@ -244,21 +315,30 @@ __global__ void input_pack_kernel(const float* __restrict__ x, const float* __re
     for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += gridDim.x * blockDim.x) {
         int yy = p / W, xx = p % W;
         T* o = out + ((long long)n * HW + p) * out_c;
-        for (int c = 0; c < C; ++c) o[c] = from_f<T>(x[((long long)n * C + c) * HW + p]);
-        int c_done = C;
+        int y0 = 0, y1 = 0, x0 = 0, x1 = 0; float ly = 0.f, lx = 0.f;
         if (w) {
-            int y0, y1, x0, x1; float ly, lx;
             bilinear_src(yy, H, y0, y1, ly);
             bilinear_src(xx, W, x0, x1, lx);
-            for (int c = 0; c < C; ++c) {
-                const float* m = cmap + c * 64;
-                float v = (1.f - ly) * ((1.f - lx) * m[y0 * 8 + x0] + lx * m[y0 * 8 + x1]) +
-                          ly * ((1.f - lx) * m[y1 * 8 + x0] + lx * m[y1 * 8 + x1]);
-                o[C + c] = from_f<T>(v);
-            }
-            c_done = 2 * C;
         }
-        for (int c = c_done; c < out_c; ++c) o[c] = from_f<T>(0.f);
+        auto value = [&](int c) -> float {
+            if (c < C) return x[((long long)n * C + c) * HW + p];
+            if (w && c < 2 * C) {
+                const float* m = cmap + (c - C) * 64;
+                return (1.f - ly) * ((1.f - lx) * m[y0 * 8 + x0] + lx * m[y0 * 8 + x1]) +
+                       ly * ((1.f - lx) * m[y1 * 8 + x0] + lx * m[y1 * 8 + x1]);
+            }
+            return 0.f;
+        };
+        if (out_c % 8 == 0) {
+            for (int c0 = 0; c0 < out_c; c0 += 8) {
+                float f[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = (c0 < 2 * C) ? value(c0 + j) : 0.f;
+                Vec8<T> v8; v8.pack(f); v8.store(o + c0);
+            }
+        } else {
+            for (int c = 0; c < out_c; ++c) o[c] = from_f<T>(value(c));
+        }
     }
 }
 

@@ -95,8 +95,7 @@ def gn_fwd(x, gamma, beta, groups, eps, silu):
     b, h, w, c = x.shape
     y = torch.empty_like(x)
     stats = torch.empty((b, groups, 2), dtype=torch.float32, device=x.device)
-    s = lib().mvae_groupnorm_splits(b, h * w, c)
-    sc = scratch("gn", 4 * b * s * groups * 2, x.device)
+    sc = scratch("gn", 4 * lib().mvae_groupnorm_scratch_floats(b, h * w, c, groups, 0), x.device)
     with P.region("groupnorm_fwd", 0.0, 2 * x.numel() * x.element_size()):
         check(lib().mvae_groupnorm_silu_fwd(ptr(x), ptr(gamma), ptr(beta), ptr(y), ptr(stats), ptr(sc), b, h * w, c,
                                             groups, eps, int(silu), L.code_of(x.dtype), stream()),
@@ -108,8 +107,7 @@ def gn_bwd(dy, x, gamma, beta, stats, dx_add, groups, silu):
     b, h, w, c = x.shape
     dx = torch.empty_like(x)
     dgb = torch.empty((2, c), dtype=torch.float32, device=x.device)
-    s = lib().mvae_groupnorm_splits(b, h * w, c)
-    sc = scratch("gn", 4 * b * s * (2 * groups + 2 * c), x.device)
+    sc = scratch("gn", 4 * lib().mvae_groupnorm_scratch_floats(b, h * w, c, groups, 1), x.device)
     with P.region("groupnorm_bwd", 0.0, (3 + (dx_add is not None)) * x.numel() * x.element_size()):
         check(lib().mvae_groupnorm_silu_bwd(ptr(dy), ptr(x), ptr(gamma), ptr(beta), ptr(stats), ptr(dx_add), ptr(dx),
                                             ptr(dgb[0]), ptr(dgb[1]), ptr(sc), b, h * w, c, groups, int(silu),

@@ -139,7 +139,8 @@ class BaseVAE(nn.Module):
 
     # ------------------------------------------------------------------ stages
     def _encoder_input(self, x: torch.Tensor, condition=None) -> torch.Tensor:
-        return _InputPackFn.apply(x.float().contiguous(), None, None, None, x.shape[1], self.compute_dtype)
+        return _InputPackFn.apply(x.float().contiguous(), None, None, None,
+                                  self.encoder.in_channels_nhwc(self.compute_dtype), self.compute_dtype)
 
     def _moments_nhwc(self, x, condition=None):
         L.require_device()
@@ -208,7 +209,7 @@ class BaseVAE(nn.Module):
 
 def ops_to_nchw(y_nhwc):
     from .blocks import _ToNCHW
-    return _ToNCHW.apply(y_nhwc)
+    return _ToNCHW.apply(y_nhwc, y_nhwc.shape[-1])
 
 
 class BetaVAE(BaseVAE):
@@ -274,8 +275,8 @@ class ConditionalVAE(BaseVAE):
             return super()._encoder_input(x)
         lin = self.condition_proj[0]
         cond = self.encode_condition(condition).to(x.device).float().contiguous()
-        return _InputPackFn.apply(x.float().contiguous(), cond, lin.weight, lin.bias, 2 * x.shape[1],
-                                  self.compute_dtype)
+        return _InputPackFn.apply(x.float().contiguous(), cond, lin.weight, lin.bias,
+                                  self.encoder.in_channels_nhwc(self.compute_dtype), self.compute_dtype)
 
     def create_condition_map(self, condition: torch.Tensor, height: int, width: int) -> torch.Tensor:
         """(B, C, H, W) condition map, conditional_vae.py:107-119 (computed by the same kernel
@@ -285,7 +286,7 @@ class ConditionalVAE(BaseVAE):
         dummy = torch.zeros(cond.shape[0], self.input_channels, height, width, device=cond.device)
         packed = self._encoder_input(dummy, cond)
         from .blocks import _ToNCHW
-        return _ToNCHW.apply(packed)[:, self.input_channels:]
+        return _ToNCHW.apply(packed, 2 * self.input_channels)[:, self.input_channels:]
 
     def encode(self, x: torch.Tensor, condition: torch.Tensor) -> tuple:
         h = ops_to_nchw(self._moments_nhwc(x, condition))

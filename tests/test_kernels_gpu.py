@@ -149,7 +149,10 @@ def test_groupnorm_silu(shape, dtype, silu):
     assert rel_err(db.double().cpu(), beta.grad) < 5 * tol
 
 
-@pytest.mark.parametrize("shape", [(2, 7, 7, 16), (3, 4, 4, 8), (2, 14, 14, 32), (2, 8, 8, 128), (1, 16, 16, 64)])
+@pytest.mark.parametrize("shape", [(2, 7, 7, 16), (3, 4, 4, 8), (2, 14, 14, 32), (2, 8, 8, 128), (1, 16, 16, 64),
+                                   # tcgen05 path in bf16 (C % 64 == 0): ragged T = 9, 49, 196 and full tiles
+                                   (5, 3, 3, 64), (2, 7, 7, 64), (3, 7, 7, 512), (2, 14, 14, 256), (2, 16, 16, 128),
+                                   (2, 16, 16, 512), (3, 8, 8, 1024), (1, 12, 20, 192)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_attention_core(shape, dtype):
     L, ops = _mods()

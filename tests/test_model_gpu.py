@@ -84,14 +84,20 @@ def test_golden_fp32_mode(name):
 
 @pytest.mark.parametrize("name", list(GOLDEN))
 def test_golden_bf16_mode(name):
-    """bf16 storage / fp32 accumulate vs the fp32 reference, END TO END through ~30 layers of these
-    very narrow golden models (8-32 channels, reductions of 72-288 terms, 4 levels in cvae_32): a
-    sanity bound only — 1e-1 relative on the final activations, 5e-2 on the whole gradient vector
-    and 0.4 on any single parameter tensor (a few GroupNorm biases inside AttnBlocks carry
-    gradients of ~1e-4 of their layer's and are mostly bf16 noise).  The per-layer 1e-2 bound of north_star is
-    what tests/test_kernels_gpu.py holds for every kernel on identical inputs, and the
+    """bf16 storage / fp32 accumulate vs the reference's fp32 results, END TO END through ~30-60
+    layers of these very narrow golden models (8-32 channels).  The yardstick is the reference
+    itself: tests/golden/bf16_yardstick.json holds how far the UNMODIFIED reference moves under
+    torch.autocast(bfloat16) on the same inputs (oracle/make_bf16_yardstick.py; e.g. cvae_32:
+    6.5e-2 on the reconstruction, 1.4e-1 on the whole gradient).  The CUDA path must stay within
+    max(2e-2, 2x that) on activations, max(5e-2, 1.5x) on the whole gradient vector and 0.4 on any
+    single parameter tensor.  The per-layer 1e-2 bound of north_star is what
+    tests/test_kernels_gpu.py holds for every kernel on identical inputs, and the
     tensor-core-sized models below hold 2e-2 / 6e-2 end to end."""
+    import json
+    import os
     import medvae_disentangled_multimodal_b200 as M
+    from conftest import GOLDEN as GOLDEN_DIR
+    yard = json.load(open(os.path.join(GOLDEN_DIR, "bf16_yardstick.json")))["fixtures"][name]
     cls, kw, lkw, conditional = GOLDEN[name]
     g = load_golden(name)
     model = getattr(M, cls)(compute_dtype="bf16", **kw).to(DEV)
@@ -99,7 +105,9 @@ def test_golden_bf16_mode(name):
     crit = M.VAELoss(**lkw)
     cond = g["cond"].to(DEV) if conditional else None
     out, ld, grads = _step(model, crit, g["x"].to(DEV), cond, g["eps"].to(DEV))
-    _compare(out, ld, grads, g["out"], g["loss"], g["grads"], 1e-1, 0.4, 2e-2, tol_grad_global=5e-2)
+    tol_act = max(2e-2, 2.0 * max(yard[k] for k in ("reconstruction", "mean", "logvar", "z")))
+    _compare(out, ld, grads, g["out"], g["loss"], g["grads"], tol_act, 0.4, 2e-2,
+             tol_grad_global=max(5e-2, 1.5 * yard["whole_gradient"]))
 
 
 BIG = [
