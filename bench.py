@@ -67,6 +67,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--knob", action="append", default=[], help="debug knob key=value for libmedvae_b200 (tuning)")
     return ap.parse_args()
 
 
@@ -238,6 +239,9 @@ def b200_arm(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     L.require_device()
+    for kv in args.knob:
+        k, v = kv.split("=")
+        L.lib().mvae_set_debug(int(k), int(v))
 
     wl = args.workload
     cls, kw, lkw, bpg, conditional, gflop, scaling = WORKLOADS[wl]

@@ -71,13 +71,13 @@ int encode_tmap_3d_bf16(CUtensorMap* m, const void* base, unsigned long long inn
 struct BoxGeom {
     int bw, bh, bn, tiles_x, tiles_y, tiles_n, rows;
 };
-static BoxGeom box_geom(int B, int GH, int GW) {
+static BoxGeom box_geom(int B, int GH, int GW, int budget = 128) {
     BoxGeom g;
-    g.bw = GW < 128 ? GW : 128;
-    int rem = 128 / g.bw;
+    g.bw = GW < budget ? GW : budget;
+    int rem = budget / g.bw;
     g.bh = GH < rem ? GH : rem;
     if (g.bh < 1) g.bh = 1;
-    rem = 128 / (g.bw * g.bh);
+    rem = budget / (g.bw * g.bh);
     g.bn = B < rem ? B : rem;
     if (g.bn < 1) g.bn = 1;
     g.tiles_x = (GW + g.bw - 1) / g.bw;
@@ -347,6 +347,11 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
 }
 
 // ================================================================== reduce (wgrad)
+// D[co, ci] (per slab, per K-split) = sum_pixels dy[pix, co] * x[pix + tap, ci].  Both operands are
+// MN-major (channels contiguous in NHWC); 64 pixels per pipeline stage = 4 MMAs of K = 16.
+// CTA tile = (MT x 128 co) x (BN ci), MT in {1, 2}, BN in {128, 256}: MT * BN <= 512 TMEM columns.
+// Bytes pulled from L2 per MMA cycle fall from 128 B/clk (128 x 128) to 64 B/clk (256 x 256), which
+// is what bounds this kernel (SM ingest), see DESIGN.md.
 struct alignas(64) ReduceTmaps {
     CUtensorMap dy[MAX_VIEWS];
     CUtensorMap in[MAX_VIEWS];
@@ -357,26 +362,34 @@ struct ReduceDev {
     int co_tiles, ci_tiles, nslabs, splits;
     int Cout, Cin;
     float* partial;    // [splits][nslabs][Cout][Cin]
-    uint32_t lbo, sbo; // MN-major descriptor strides (debug-overridable)
     TapProg taps;
 };
 
-constexpr int R_BN = 128;                         // ci per tile
-constexpr int R_STAGES = 3;
-constexpr int R_CHUNK = 128 * 128;                // 128 pixels x 64 channels bf16 = 16 KB
-constexpr int R_A_BYTES = 2 * R_CHUNK;            // 128 co
-constexpr int R_B_BYTES = (R_BN / 64) * R_CHUNK;  // 128 ci
-constexpr int R_SMEM = 1024 + R_STAGES * (R_A_BYTES + R_B_BYTES) + 256;
+constexpr int R_PIX = 64;            // pixels (K) per stage
+constexpr int R_CHUNK = R_PIX * 128; // 64 pixels x 64 channels bf16 = 8 KB
 
+template <int MT, int BN>
+struct ReduceCfg {
+    static constexpr int A_BYTES = MT * 2 * R_CHUNK;
+    static constexpr int B_BYTES = (BN / 64) * R_CHUNK;
+    static constexpr int STAGE = A_BYTES + B_BYTES;
+    static constexpr int STAGES = STAGE <= 32768 ? 6 : (STAGE <= 49152 ? 4 : 3);
+    static constexpr int TMEM_COLS = MT * BN;
+    static constexpr int SMEM = 1024 + STAGES * STAGE + 256;
+};
+
+template <int MT, int BN>
 __global__ void __launch_bounds__(G_THREADS, 1)
 conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_constant__ ReduceDev p) {
+    using Cfg = ReduceCfg<MT, BN>;
+    constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = smem;
-    uint8_t* sB = sA + R_STAGES * R_A_BYTES;
-    uint64_t* full = reinterpret_cast<uint64_t*>(sB + R_STAGES * R_B_BYTES);
-    uint64_t* empty = full + R_STAGES;
-    uint64_t* tfull = empty + R_STAGES;
+    uint8_t* sB = sA + STAGES * Cfg::A_BYTES;
+    uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * Cfg::B_BYTES);
+    uint64_t* empty = full + STAGES;
+    uint64_t* tfull = empty + STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull + 1);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -391,9 +404,9 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     const int pt_end = (int)(((long long)p.ptiles * (split + 1)) / p.splits);
     const int kiters = pt_end - pt_beg;
 
-    if (p.rows < 128) {
+    if (p.rows < R_PIX) {
         // pixel rows beyond the TMA box take part in the K reduction: they must be zero
-        for (int i = threadIdx.x; i < R_STAGES * (R_A_BYTES + R_B_BYTES) / 16; i += G_THREADS)
+        for (int i = threadIdx.x; i < STAGES * Cfg::STAGE / 16; i += G_THREADS)
             reinterpret_cast<uint4*>(sA)[i] = make_uint4(0, 0, 0, 0);
         fence_proxy_async_smem();
     }
@@ -403,18 +416,18 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     }
     if (warp == 1) {
         if (lane == 0) {
-            for (int s = 0; s < R_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+            for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
             mbar_init(&tfull[0], 1);
             fence_barrier_init();
         }
         __syncwarp();
-        tmem_alloc(tmem_slot, R_BN);
+        tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t stage_bytes = (uint32_t)p.rows * 128u * (2 + R_BN / 64);
+    const uint32_t stage_bytes = (uint32_t)p.rows * 128u * (MT * 2 + BN / 64);
 
     if (warp == 0) {
         if (lane == 0) {
@@ -427,64 +440,70 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
                 const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
                 mbar_wait(&empty[stage], phase ^ 1u);
                 mbar_expect_tx(&full[stage], stage_bytes);
-                uint8_t* a = sA + stage * R_A_BYTES;
-                uint8_t* b = sB + stage * R_B_BYTES;
+                uint8_t* a = sA + stage * Cfg::A_BYTES;
+                uint8_t* b = sB + stage * Cfg::B_BYTES;
 #pragma unroll
-                for (int c = 0; c < 2; ++c)
-                    tma_load_4d(a + c * R_CHUNK, &tm.dy[tp.oview], &full[stage], cot * 128 + c * 64, x0, y0, n0);
+                for (int c = 0; c < MT * 2; ++c)
+                    tma_load_4d(a + c * R_CHUNK, &tm.dy[tp.oview], &full[stage], cot * (MT * 128) + c * 64, x0, y0, n0);
 #pragma unroll
-                for (int c = 0; c < R_BN / 64; ++c)
-                    tma_load_4d(b + c * R_CHUNK, &tm.in[tp.view], &full[stage], cit * R_BN + c * 64,
+                for (int c = 0; c < BN / 64; ++c)
+                    tma_load_4d(b + c * R_CHUNK, &tm.in[tp.view], &full[stage], cit * BN + c * 64,
                                 x0 + tp.dx, y0 + tp.dy, n0);
-                if (++stage == R_STAGES) { stage = 0; phase ^= 1u; }
+                if (++stage == STAGES) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_bf16(128, R_BN, 1, 1);
+            constexpr uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);
             int stage = 0; uint32_t phase = 0;
             for (int it = 0; it < kiters; ++it) {
                 mbar_wait(&full[stage], phase);
                 tc_fence_after();
-                const uint32_t a0 = smem_u32(sA + stage * R_A_BYTES);
-                const uint32_t b0 = smem_u32(sB + stage * R_B_BYTES);
+                const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES);
+                const uint32_t b0 = smem_u32(sB + stage * Cfg::B_BYTES);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {   // 16 pixels (= 16 rows of 128 B) per MMA
-                    const uint64_t ad = smem_desc_sw128(a0 + k * 2048, p.lbo, p.sbo);
-                    const uint64_t bd = smem_desc_sw128(b0 + k * 2048, p.lbo, p.sbo);
-                    umma_bf16(tmem_base, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                for (int m = 0; m < MT; ++m) {
+#pragma unroll
+                    for (int k = 0; k < R_PIX / 16; ++k) {   // 16 pixels (= 16 rows of 128 B) per MMA
+                        const uint64_t ad = smem_desc_sw128(a0 + m * 2 * R_CHUNK + k * 2048, R_CHUNK, 1024);
+                        const uint64_t bd = smem_desc_sw128(b0 + k * 2048, R_CHUNK, 1024);
+                        umma_bf16(tmem_base + (uint32_t)(m * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                    }
                 }
                 umma_commit(&empty[stage]);
-                if (++stage == R_STAGES) { stage = 0; phase ^= 1u; }
+                if (++stage == STAGES) { stage = 0; phase ^= 1u; }
             }
             umma_commit(&tfull[0]);
         }
     } else {
         const int quarter = warp & 3;
-        const int co = cot * 128 + quarter * 32 + lane;
-        const bool co_ok = co < p.Cout;   // Cout % 128 == 64: the upper half of the last tile is TMA zero fill
-        float* dst = p.partial + (((long long)split * p.nslabs + tp.slab) * p.Cout + co) * p.Cin + cit * R_BN;
         if (kiters > 0) {
             mbar_wait(&tfull[0], 0);
             tc_fence_after();
         }
-        const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
-        for (int c0 = 0; c0 < R_BN; c0 += 32) {
-            uint32_t v[32];
-            if (kiters > 0) {
-                tmem_ld_32x32(t0 + (uint32_t)c0, v);
-                tmem_ld_wait();
-            } else {
+        for (int m = 0; m < MT; ++m) {
+            const int co = cot * (MT * 128) + m * 128 + quarter * 32 + lane;
+            const bool co_ok = co < p.Cout;   // last co tile may be partly TMA zero fill
+            float* dst = p.partial + (((long long)split * p.nslabs + tp.slab) * p.Cout + co) * p.Cin + cit * BN;
+            const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(m * BN);
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t v[32];
+                if (kiters > 0) {
+                    tmem_ld_32x32(t0 + (uint32_t)c0, v);
+                    tmem_ld_wait();
+                } else {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = 0u;
-            }
-            if (co_ok && cit * R_BN + c0 < p.Cin) {
-            float4* o = reinterpret_cast<float4*>(dst + c0);
+                    for (int i = 0; i < 32; ++i) v[i] = 0u;
+                }
+                if (co_ok && cit * BN + c0 < p.Cin) {
+                    float4* o = reinterpret_cast<float4*>(dst + c0);
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
-                o[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
-                                   __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                    for (int i = 0; i < 8; ++i)
+                        o[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                           __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                }
             }
         }
     }
@@ -492,14 +511,19 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, R_BN);
+        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
     }
+}
+
+static void reduce_tile(const ReduceProblem& p, int& MT, int& BN) {
+    MT = p.Cout >= 256 ? 2 : 1;
+    BN = p.Cin >= 256 ? 256 : 128;
 }
 
 bool umma_reduce_ok(const ReduceProblem& p) {
     if (p.Cout % 64 != 0 || p.Cin % 64 != 0) return false;
-    if (p.GW > 128 && p.GW % 128 != 0) return false;
-    BoxGeom g = box_geom(p.B, p.GH, p.GW);
+    if (p.GW > R_PIX && p.GW % R_PIX != 0) return false;
+    BoxGeom g = box_geom(p.B, p.GH, p.GW, R_PIX);
     for (int v = 0; v < p.n_inviews; ++v)
         if (p.in_views[v].Ws < g.bw || p.in_views[v].Hs < g.bh) return false;
     for (int v = 0; v < p.n_dyviews; ++v)
@@ -508,22 +532,41 @@ bool umma_reduce_ok(const ReduceProblem& p) {
 }
 
 int umma_reduce_splits(const ReduceProblem& p) {
-    BoxGeom g = box_geom(p.B, p.GH, p.GW);
+    int MT, BN;
+    reduce_tile(p, MT, BN);
+    BoxGeom g = box_geom(p.B, p.GH, p.GW, R_PIX);
     long long ptiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
-    long long items = (long long)p.taps.ntaps * ((p.Cout + 127) / 128) * ((p.Cin + R_BN - 1) / R_BN);
-    long long want = (2LL * num_sms() + items - 1) / items;
+    long long items = (long long)p.taps.ntaps * ((p.Cout + MT * 128 - 1) / (MT * 128)) * ((p.Cin + BN - 1) / BN);
+    // one wave of CTAs (one per SM): as many K-splits as fit, each with at least ~8 pixel tiles
+    long long want = num_sms() / items;
     if (want < 1) want = 1;
-    long long cap = (ptiles + 3) / 4;   // at least ~4 pixel tiles per split
+    long long cap = (ptiles + 7) / 8;
     if (cap < 1) cap = 1;
     if (want > cap) want = cap;
     if (want > 64) want = 64;
     return (int)want;
 }
 
+template <int MT, int BN>
+static int launch_reduce(const ReduceTmaps& tm, const ReduceDev& d, long long grid, cudaStream_t st) {
+    using Cfg = ReduceCfg<MT, BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MVAE_CUDA(cudaFuncSetAttribute(conv_reduce_umma_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::SMEM));
+        attr_set = true;
+    }
+    conv_reduce_umma_kernel<MT, BN><<<(unsigned)grid, G_THREADS, Cfg::SMEM, st>>>(tm, d);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
 int umma_reduce(const ReduceProblem& p, const void* in, const void* dy, float* partial, int splits,
                 cudaStream_t st) {
     MVAE_CHECK(umma_reduce_ok(p), "umma_reduce: unsupported shape Cout=%d Cin=%d", p.Cout, p.Cin);
-    BoxGeom g = box_geom(p.B, p.GH, p.GW);
+    int MT, BN;
+    reduce_tile(p, MT, BN);
+    BoxGeom g = box_geom(p.B, p.GH, p.GW, R_PIX);
     ReduceTmaps tm;
     memset(&tm, 0, sizeof(tm));
     for (int v = 0; v < MAX_VIEWS; ++v) {
@@ -538,20 +581,15 @@ int umma_reduce(const ReduceProblem& p, const void* in, const void* dy, float* p
     d.bw = g.bw; d.bh = g.bh; d.bn = g.bn; d.rows = g.rows;
     d.tiles_x = g.tiles_x; d.tiles_y = g.tiles_y; d.tiles_n = g.tiles_n;
     d.ptiles = g.tiles_x * g.tiles_y * g.tiles_n;
-    d.co_tiles = (p.Cout + 127) / 128; d.ci_tiles = (p.Cin + R_BN - 1) / R_BN; d.nslabs = p.taps.ntaps; d.splits = splits;
+    d.co_tiles = (p.Cout + MT * 128 - 1) / (MT * 128); d.ci_tiles = (p.Cin + BN - 1) / BN;
+    d.nslabs = p.taps.ntaps; d.splits = splits;
     d.Cout = p.Cout; d.Cin = p.Cin; d.partial = partial;
-    d.lbo = R_CHUNK; d.sbo = 1024;
-    if (debug_knob(1) == 1) { d.lbo = 1024; d.sbo = R_CHUNK; }   // bring-up: swapped LBO/SBO roles
     d.taps = p.taps;
-    static bool attr_set = false;
-    if (!attr_set) {
-        MVAE_CUDA(cudaFuncSetAttribute(conv_reduce_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, R_SMEM));
-        attr_set = true;
-    }
     long long grid = (long long)d.co_tiles * d.ci_tiles * d.nslabs * splits;
-    conv_reduce_umma_kernel<<<(unsigned)grid, G_THREADS, R_SMEM, st>>>(tm, d);
-    MVAE_LAUNCH_CHECK();
-    return 0;
+    if (MT == 2 && BN == 256) return launch_reduce<2, 256>(tm, d, grid, st);
+    if (MT == 2) return launch_reduce<2, 128>(tm, d, grid, st);
+    if (BN == 256) return launch_reduce<1, 256>(tm, d, grid, st);
+    return launch_reduce<1, 128>(tm, d, grid, st);
 }
 
 }  // namespace mvae

@@ -20,7 +20,8 @@ constexpr int MAX_G = 32;
 // that the slab(s) read by the first pass are still in the 126 MB L2 when the second pass reads
 // them again: HBM then sees each tensor once.
 int gn_chunk(int B, int HW, int C, int tensors) {
-    const long long budget = 12LL << 20;   // elements per chunk over all re-read tensors (24 MB of bf16)
+    // elements per chunk over all re-read tensors; debug knob 3 (in Mi elements) overrides; 0 = one chunk
+    const long long budget = debug_knob(3) > 0 ? ((long long)debug_knob(3) << 20) : (1LL << 40);
     long long per = (long long)HW * C * tensors;
     long long nb = budget / (per > 0 ? per : 1);
     if (nb < 1) nb = 1;

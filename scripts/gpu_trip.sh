@@ -16,6 +16,7 @@ for stage in "$@"; do
     bench) timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/rc.txt;;
     bench_c3) timeout 600 python bench.py --workload c3 --steps 5 --warmup 3 > gpurun_out/bench_c3.log 2>&1; echo "bench_c3 rc=$?" >> gpurun_out/rc.txt;;
     bench_c4s) timeout 600 python bench.py --workload c4 --batch-per-gpu 128 --micro-batch 64 --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/bench_c4s.log 2>&1; echo "bench_c4s rc=$?" >> gpurun_out/rc.txt;;
+    bench_c4m) timeout 600 python bench.py --workload c4 --batch-per-gpu 256 --micro-batch 256 --steps 2 --warmup 3 --no-cpu-baseline $BENCH_ARGS > gpurun_out/bench_c4m$TAG.log 2>&1; echo "bench_c4m rc=$?" >> gpurun_out/rc.txt;;
     kernels) timeout 900 python -m pytest tests/test_kernels_gpu.py -q -m gpu --timeout 300 > gpurun_out/t_kernels.log 2>&1; echo "kernels rc=$?" >> gpurun_out/rc.txt;;
   esac
 done
