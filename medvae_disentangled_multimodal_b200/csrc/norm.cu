@@ -28,10 +28,14 @@ int gn_chunk(int B, int HW, int C, int tensors) {
     if (nb > B) nb = B;
     return (int)nb;
 }
-static int gn_splits_for(int nb, int HW) {
-    // enough CTAs to fill the machine (~4 per SM), at least 32 pixel rows per CTA
-    long long want = (148LL * 4 + nb - 1) / nb;
-    long long cap = (HW + 31) / 32;
+static int gn_splits_for(int nb, int HW, int C) {
+    // ~12 CTAs per SM over the launch (4 waves at 3 resident CTAs); a CTA gets at least 16 K
+    // elements (32 rows of 512 channels, 8 rows of 2048 ...) and at least 4 pixel rows
+    long long want = (148LL * 12 + nb - 1) / nb;
+    long long min_rows = 16384 / (C > 0 ? C : 1);
+    if (min_rows < 4) min_rows = 4;
+    if (min_rows > 32) min_rows = 32;
+    long long cap = (HW + min_rows - 1) / min_rows;
     if (want > cap) want = cap;
     if (want < 1) want = 1;
     if (want > 64) want = 64;
@@ -40,7 +44,7 @@ static int gn_splits_for(int nb, int HW) {
 // floats of scratch the forward (backward = 0) or backward (= 1) entry point needs
 long long gn_scratch_floats(int B, int HW, int C, int G, int backward) {
     const int nb = gn_chunk(B, HW, C, backward ? 2 : 1);
-    const int S = gn_splits_for(nb, HW);
+    const int S = gn_splits_for(nb, HW, C);
     const long long chunks = (B + nb - 1) / nb;
     long long n = (long long)nb * S * G * 2;
     if (backward) n += chunks * nb * S * 2 * C;
@@ -48,7 +52,7 @@ long long gn_scratch_floats(int B, int HW, int C, int G, int backward) {
 }
 int gn_splits(int B, int HW, int C) {
     // legacy sizing helper: the larger of the two directions' split counts
-    int a = gn_splits_for(gn_chunk(B, HW, C, 1), HW), b = gn_splits_for(gn_chunk(B, HW, C, 2), HW);
+    int a = gn_splits_for(gn_chunk(B, HW, C, 1), HW, C), b = gn_splits_for(gn_chunk(B, HW, C, 2), HW, C);
     return a > b ? a : b;
 }
 // thread mapping for a [rows][C] slab processed VEC channels at a time
@@ -70,10 +74,16 @@ __device__ __forceinline__ RowMap row_map(int C) {
 
 template <typename T, int VEC> struct Ld;
 template <typename T> struct Ld<T, 8> {
+    typedef Vec8<T> Raw;
+    static __device__ __forceinline__ void load_raw(const T* p, Raw& r) { r.load(p); }
+    static __device__ __forceinline__ void unpack(const Raw& r, float* f) { r.unpack(f); }
     static __device__ __forceinline__ void load(const T* p, float* f) { Vec8<T> v; v.load(p); v.unpack(f); }
     static __device__ __forceinline__ void store(T* p, const float* f) { Vec8<T> v; v.pack(f); v.store(p); }
 };
 template <typename T> struct Ld<T, 1> {
+    typedef T Raw;
+    static __device__ __forceinline__ void load_raw(const T* p, Raw& r) { r = *p; }
+    static __device__ __forceinline__ void unpack(const Raw& r, float* f) { f[0] = to_f<T>(r); }
     static __device__ __forceinline__ void load(const T* p, float* f) { f[0] = to_f<T>(*p); }
     static __device__ __forceinline__ void store(T* p, const float* f) { *p = from_f<T>(f[0]); }
 };
@@ -190,7 +200,7 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const T* __restric
 #pragma unroll
                     for (int j = 0; j < VEC; ++j) {
                         float t = fmaf(f[u][j], a[j], b[j]);
-                        f[u][j] = silu ? t * sigmoidf_(t) : t;
+                        f[u][j] = silu ? t * sigmoid_t<T>(t) : t;
                     }
                     Ld<T, VEC>::store(yn + (long long)(p + u * m.rpi) * C + v * VEC, f[u]);
                 }
@@ -201,7 +211,7 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const T* __restric
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
                     float u = fmaf(f[j], a[j], b[j]);
-                    f[j] = silu ? u * sigmoidf_(u) : u;
+                    f[j] = silu ? u * sigmoid_t<T>(u) : u;
                 }
                 Ld<T, VEC>::store(yn + (long long)p * C + v * VEC, f);
             }
@@ -210,21 +220,23 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const T* __restric
 }
 
 // ------------------------------------------------------------------ backward: reductions
-// per (n, split, g): s1 = sum du*gamma, s2 = sum du*gamma*xhat;  per channel: dgamma = sum du*xhat,
-// dbeta = sum du, where u = xhat*gamma+beta and du = dy * silu'(u) (or dy).  Everything is folded
-// in a fixed order (bitwise run-to-run reproducible): thread partials -> shared -> per-CTA rows of
-// `scratch` -> gn_param_reduce_kernel.
-// scratch layout: [B*S][G][2] group sums, then [B*S][2][C] channel sums.
+// With u = x*P + Q the pre-activation (P = rstd*gamma, Q = beta - mean*rstd*gamma), xhat = x*R + M
+// (R = rstd, M = -mean*rstd) and du = dy * silu'(u) (or dy):
+//   per channel  dbeta = sum du,  dgamma = sum du*xhat
+//   per group    s1 = sum du*gamma = sum_c gamma_c*dbeta_c,   s2 = sum du*gamma*xhat = sum_c gamma_c*dgamma_c
+// so one pass over (x, dy) accumulates just two numbers per channel.  Everything is folded in a
+// fixed order (bitwise run-to-run reproducible): thread partials -> shared -> per-CTA rows of
+// `scratch` / `chan_scratch` -> gn_param_reduce_kernel.
 template <typename T, int VEC>
-__global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __restrict__ dy, const T* __restrict__ x,
-                                                                  const float* __restrict__ gamma,
-                                                                  const float* __restrict__ beta,
-                                                                  const float* __restrict__ stats,
-                                                                  float* __restrict__ scratch,
-                                                                  float* __restrict__ chan_scratch, int HW, int C,
-                                                                  int G, int S, int silu) {
+__global__ void __launch_bounds__(GN_THREADS, 3) gn_bwd_stats_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                                     const float* __restrict__ gamma,
+                                                                     const float* __restrict__ beta,
+                                                                     const float* __restrict__ stats,
+                                                                     float* __restrict__ scratch,
+                                                                     float* __restrict__ chan_scratch, int HW, int C,
+                                                                     int G, int S, int silu) {
     __shared__ float mean[MAX_G], rstd[MAX_G];
-    extern __shared__ float part[];   // [rows per iteration][C][4] : dg, db, a1, a2
+    extern __shared__ float part[];   // [rows per iteration][C][2] : dgamma, dbeta partials
     const int n = blockIdx.y, sp = blockIdx.x;
     const int cpg = C / G;
     if (threadIdx.x < G) {
@@ -235,42 +247,46 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __res
     const T* xn = x + (long long)n * HW * C;
     const T* dn = dy + (long long)n * HW * C;
     const int p0 = (int)(((long long)HW * sp) / S), p1 = (int)(((long long)HW * (sp + 1)) / S);
+    const RowMap m = row_map<VEC>(C);
     for (int vb = 0; vb < C / VEC; vb += GN_THREADS) {
-        RowMap m = row_map<VEC>(C);
-        int v = vb + m.v;
+        const int v = vb + m.v;
         if (m.active && v < m.nvec) {
-            float ga[VEC], be[VEC], mu[VEC], rs[VEC], dg[VEC], db[VEC], a1[VEC], a2[VEC];
+            // accumulate t = sum du*x and db = sum du; dgamma = R*t + M*db (xhat = x*R + M) afterwards
+            float P[VEC], Q[VEC], dg[VEC], db[VEC];
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
-                int c = v * VEC + j, g = c / cpg;
-                ga[j] = gamma[c]; be[j] = beta[c]; mu[j] = mean[g]; rs[j] = rstd[g];
-                dg[j] = 0.f; db[j] = 0.f; a1[j] = 0.f; a2[j] = 0.f;
+                const int c = v * VEC + j, g = c / cpg;
+                const float rs = rstd[g], ga = gamma[c];
+                P[j] = rs * ga; Q[j] = fmaf(-mean[g] * rs, ga, beta[c]);
+                dg[j] = 0.f; db[j] = 0.f;
             }
             auto accum = [&](const float* fx, const float* fd) {
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
-                    float xh = (fx[j] - mu[j]) * rs[j];
                     float du = fd[j];
                     if (silu) {
-                        float u = fmaf(xh, ga[j], be[j]);
-                        float sg = sigmoidf_(u);
-                        du *= sg * (1.f + u * (1.f - sg));
+                        const float u = fmaf(fx[j], P[j], Q[j]);
+                        const float sg = sigmoid_t<T>(u);
+                        du *= sg * fmaf(u, 1.f - sg, 1.f);
                     }
-                    dg[j] = fmaf(du, xh, dg[j]); db[j] += du;
-                    float dxh = du * ga[j];
-                    a1[j] += dxh; a2[j] = fmaf(dxh, xh, a2[j]);
+                    dg[j] = fmaf(du, fx[j], dg[j]); db[j] += du;
                 }
             };
             int p = p0 + m.r;
             for (; p + m.rpi < p1; p += 2 * m.rpi) {
-                float fx[2][VEC], fd[2][VEC];
+                typename Ld<T, VEC>::Raw rx[2], rd[2];   // raw (packed) loads in flight, unpacked one row at a time
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {
-                    Ld<T, VEC>::load(xn + (long long)(p + u * m.rpi) * C + v * VEC, fx[u]);
-                    Ld<T, VEC>::load(dn + (long long)(p + u * m.rpi) * C + v * VEC, fd[u]);
+                    Ld<T, VEC>::load_raw(xn + (long long)(p + u * m.rpi) * C + v * VEC, rx[u]);
+                    Ld<T, VEC>::load_raw(dn + (long long)(p + u * m.rpi) * C + v * VEC, rd[u]);
                 }
-                accum(fx[0], fd[0]);
-                accum(fx[1], fd[1]);
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    float fx[VEC], fd[VEC];
+                    Ld<T, VEC>::unpack(rx[u], fx);
+                    Ld<T, VEC>::unpack(rd[u], fd);
+                    accum(fx, fd);
+                }
             }
             for (; p < p1; p += m.rpi) {
                 float fx[VEC], fd[VEC];
@@ -280,28 +296,30 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_stats_kernel(const T* __res
             }
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
-                float* o = part + (size_t)(m.r * C + v * VEC + j) * 4;
-                o[0] = dg[j]; o[1] = db[j]; o[2] = a1[j]; o[3] = a2[j];
+                const int g = (v * VEC + j) / cpg;
+                const float rs = rstd[g];
+                float* o = part + (size_t)(m.r * C + v * VEC + j) * 2;
+                o[0] = fmaf(rs, dg[j], -mean[g] * rs * db[j]); o[1] = db[j];
             }
         }
     }
     __syncthreads();
-    const RowMap m = row_map<VEC>(C);
     const long long cta = (long long)n * S + sp;
-    if (threadIdx.x < G) {
-        float s1 = 0.f, s2 = 0.f;
-        for (int r = 0; r < m.rpi; ++r)
-            for (int c = threadIdx.x * cpg; c < (threadIdx.x + 1) * cpg; ++c) {
-                s1 += part[(size_t)(r * C + c) * 4 + 2]; s2 += part[(size_t)(r * C + c) * 4 + 3];
-            }
-        float* o = scratch + (cta * G + threadIdx.x) * 2;
-        o[0] = s1; o[1] = s2;
-    }
     float* chan = chan_scratch + cta * 2 * C;
     for (int c = threadIdx.x; c < C; c += GN_THREADS) {
         float dg = 0.f, db = 0.f;
-        for (int r = 0; r < m.rpi; ++r) { dg += part[(size_t)(r * C + c) * 4]; db += part[(size_t)(r * C + c) * 4 + 1]; }
+        for (int r = 0; r < m.rpi; ++r) { dg += part[(size_t)(r * C + c) * 2]; db += part[(size_t)(r * C + c) * 2 + 1]; }
         chan[c] = dg; chan[C + c] = db;
+    }
+    __syncthreads();   // chan[] written by this CTA is read back below (same CTA: visible after the barrier)
+    if (threadIdx.x < G) {
+        float s1 = 0.f, s2 = 0.f;
+        for (int c = threadIdx.x * cpg; c < (threadIdx.x + 1) * cpg; ++c) {
+            const float ga = gamma[c];
+            s1 = fmaf(ga, chan[C + c], s1); s2 = fmaf(ga, chan[c], s2);
+        }
+        float* o = scratch + (cta * G + threadIdx.x) * 2;
+        o[0] = s1; o[1] = s2;
     }
 }
 
@@ -326,16 +344,16 @@ __global__ void __launch_bounds__(256) gn_param_reduce_kernel(const float* __res
 }
 
 // ------------------------------------------------------------------ backward: dx
-// dx = rstd * (dxh - (s1 + xhat*s2)/Ng) + dx_add
+// dx = rstd * (du*gamma - m1 - xhat*m2) + dx_add  =  du*P - K1 - xhat*K2 + dx_add
 template <typename T, int VEC>
-__global__ void __launch_bounds__(GN_THREADS) gn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x,
-                                                                  const float* __restrict__ gamma,
-                                                                  const float* __restrict__ beta,
-                                                                  const float* __restrict__ stats,
-                                                                  const float* __restrict__ scratch,
-                                                                  const T* __restrict__ dx_add, T* __restrict__ dx,
-                                                                  int HW, int C, int G, int S, int silu) {
-    __shared__ float mean[MAX_G], rstd[MAX_G], m1[MAX_G], m2[MAX_G];
+__global__ void __launch_bounds__(GN_THREADS, 3) gn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                                     const float* __restrict__ gamma,
+                                                                     const float* __restrict__ beta,
+                                                                     const float* __restrict__ stats,
+                                                                     const float* __restrict__ scratch,
+                                                                     const T* __restrict__ dx_add, T* __restrict__ dx,
+                                                                     int HW, int C, int G, int S, int silu) {
+    __shared__ float mean[MAX_G], rstd[MAX_G], k1[MAX_G], k2[MAX_G];
     const int n = blockIdx.y, sp = blockIdx.x;
     const int cpg = C / G;
     if (threadIdx.x < G) {
@@ -344,57 +362,64 @@ __global__ void __launch_bounds__(GN_THREADS) gn_bwd_apply_kernel(const T* __res
             const float* o = scratch + (((long long)n * S + k) * G + threadIdx.x) * 2;
             s1 += o[0]; s2 += o[1];
         }
-        float cnt = (float)HW * (float)cpg;
-        m1[threadIdx.x] = s1 / cnt; m2[threadIdx.x] = s2 / cnt;
+        const float cnt = (float)HW * (float)cpg;
+        const float rs = stats[((long long)n * G + threadIdx.x) * 2 + 1];
         mean[threadIdx.x] = stats[((long long)n * G + threadIdx.x) * 2];
-        rstd[threadIdx.x] = stats[((long long)n * G + threadIdx.x) * 2 + 1];
+        rstd[threadIdx.x] = rs;
+        k1[threadIdx.x] = rs * (s1 / cnt); k2[threadIdx.x] = rs * (s2 / cnt);
     }
     __syncthreads();
     const long long base = (long long)n * HW * C;
     const int p0 = (int)(((long long)HW * sp) / S), p1 = (int)(((long long)HW * (sp + 1)) / S);
+    const RowMap m = row_map<VEC>(C);
     for (int vb = 0; vb < C / VEC; vb += GN_THREADS) {
-        RowMap m = row_map<VEC>(C);
-        int v = vb + m.v;
+        const int v = vb + m.v;
         if (m.active && v < m.nvec) {
-            float ga[VEC], be[VEC], mu[VEC], rs[VEC], c1[VEC], c2[VEC];
+            // dx = du*P - K1 - xhat*K2 = du*P - A - x*Bc  with  A = K1 + M*K2, Bc = R*K2
+            float P[VEC], Q[VEC], A[VEC], Bc[VEC];
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
-                int c = v * VEC + j, g = c / cpg;
-                ga[j] = gamma[c]; be[j] = beta[c]; mu[j] = mean[g]; rs[j] = rstd[g]; c1[j] = m1[g]; c2[j] = m2[g];
+                const int c = v * VEC + j, g = c / cpg;
+                const float rs = rstd[g], ga = gamma[c], mm = -mean[g] * rs;
+                P[j] = rs * ga; Q[j] = fmaf(mm, ga, beta[c]);
+                A[j] = fmaf(mm, k2[g], k1[g]); Bc[j] = rs * k2[g];
             }
             auto one = [&](float* fx, const float* fd, const float* fa) {
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
-                    float xh = (fx[j] - mu[j]) * rs[j];
                     float du = fd[j];
                     if (silu) {
-                        float u = fmaf(xh, ga[j], be[j]);
-                        float sg = sigmoidf_(u);
-                        du *= sg * (1.f + u * (1.f - sg));
+                        const float u = fmaf(fx[j], P[j], Q[j]);
+                        const float sg = sigmoid_t<T>(u);
+                        du *= sg * fmaf(u, 1.f - sg, 1.f);
                     }
-                    float r = rs[j] * (du * ga[j] - c1[j] - xh * c2[j]);
+                    const float r = fmaf(du, P[j], -fmaf(fx[j], Bc[j], A[j]));
                     fx[j] = dx_add ? r + fa[j] : r;
                 }
             };
             int p = p0 + m.r;
             for (; p + m.rpi < p1; p += 2 * m.rpi) {
-                float fx[2][VEC], fd[2][VEC], fa[2][VEC];
+                typename Ld<T, VEC>::Raw rx[2], rd[2], ra[2];
                 long long off[2];
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {
                     off[u] = base + (long long)(p + u * m.rpi) * C + v * VEC;
-                    Ld<T, VEC>::load(x + off[u], fx[u]);
-                    Ld<T, VEC>::load(dy + off[u], fd[u]);
-                    if (dx_add) Ld<T, VEC>::load(dx_add + off[u], fa[u]);
+                    Ld<T, VEC>::load_raw(x + off[u], rx[u]);
+                    Ld<T, VEC>::load_raw(dy + off[u], rd[u]);
+                    if (dx_add) Ld<T, VEC>::load_raw(dx_add + off[u], ra[u]);
                 }
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {
-                    one(fx[u], fd[u], fa[u]);
-                    Ld<T, VEC>::store(dx + off[u], fx[u]);
+                    float fx[VEC], fd[VEC], fa[VEC];
+                    Ld<T, VEC>::unpack(rx[u], fx);
+                    Ld<T, VEC>::unpack(rd[u], fd);
+                    if (dx_add) Ld<T, VEC>::unpack(ra[u], fa);
+                    one(fx, fd, fa);
+                    Ld<T, VEC>::store(dx + off[u], fx);
                 }
             }
             for (; p < p1; p += m.rpi) {
-                long long off = base + (long long)p * C + v * VEC;
+                const long long off = base + (long long)p * C + v * VEC;
                 float fx[VEC], fd[VEC], fa[VEC];
                 Ld<T, VEC>::load(x + off, fx);
                 Ld<T, VEC>::load(dy + off, fd);
@@ -419,7 +444,7 @@ template <typename T, int VEC>
 static int gn_fwd_t(const T* x, const float* gamma, const float* beta, T* y, float* stats, float* scratch, int B,
                     int HW, int C, int G, float eps, int silu, cudaStream_t st) {
     const int nb = gn_chunk(B, HW, C, 1);
-    const int S = gn_splits_for(nb, HW);
+    const int S = gn_splits_for(nb, HW, C);
     for (int n0 = 0; n0 < B; n0 += nb) {
         const int n = (B - n0 < nb) ? (B - n0) : nb;
         const long long off = (long long)n0 * HW * C;
@@ -437,7 +462,7 @@ static int gn_bwd_t(const T* dy, const T* x, const float* gamma, const float* be
                     const T* dx_add, T* dx, float* dgamma, float* dbeta, float* scratch, int B, int HW, int C, int G,
                     int silu, cudaStream_t st) {
     const int nb = gn_chunk(B, HW, C, 2);
-    const int S = gn_splits_for(nb, HW);
+    const int S = gn_splits_for(nb, HW, C);
     float* chan = scratch + (long long)nb * S * G * 2;
     long long rows = 0;
     for (int n0 = 0; n0 < B; n0 += nb) {
@@ -445,7 +470,7 @@ static int gn_bwd_t(const T* dy, const T* x, const float* gamma, const float* be
         const long long off = (long long)n0 * HW * C;
         const float* st_n = stats + (long long)n0 * G * 2;
         dim3 grid(S, n);
-        gn_bwd_stats_kernel<T, VEC><<<grid, GN_THREADS, gn_part_bytes<VEC>(C, 4), st>>>(
+        gn_bwd_stats_kernel<T, VEC><<<grid, GN_THREADS, gn_part_bytes<VEC>(C, 2), st>>>(
             dy + off, x + off, gamma, beta, st_n, scratch, chan + rows * 2 * C, HW, C, G, S, silu);
         MVAE_LAUNCH_CHECK();
         gn_bwd_apply_kernel<T, VEC><<<grid, GN_THREADS, 0, st>>>(dy + off, x + off, gamma, beta, st_n, scratch,
