@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define MVAE_ABI_VERSION 1
+#define MVAE_ABI_VERSION 2
 
 enum { MVAE_F32 = 0, MVAE_BF16 = 1 };
 
@@ -108,6 +108,39 @@ int mvae_groupnorm_silu_bwd(const void* dy, const void* x, const float* gamma, c
                             const float* stats, const void* dx_add, void* dx, float* dgamma,
                             float* dbeta, float* scratch, int32_t batch, int32_t hw, int32_t c,
                             int32_t groups, int32_t apply_silu, int32_t dtype, void* stream);
+
+/* ---- GroupNorm fused into the convs either side of it (bf16 tcgen05 path only) -----------------
+ * In ResnetBlock / AttnBlock / the heads every Normalize (encoder_decoder.py:150,158,85,325,446)
+ * reads a conv output and (in the backward) receives its gradient from a conv dgrad.  These entry
+ * points move the two REDUCTION passes of GroupNorm into those convs' epilogues, leaving one
+ * streaming pass per direction:
+ *   mvae_conv2d_fprop_gn   = mvae_conv2d_fprop + gn_sums[n][g] = (sum y, sum y^2) over the group
+ *                            (fp32 [B][groups][2], zeroed by the call; fp32 atomics)
+ *   mvae_groupnorm_apply_fwd : y = [silu](GN(x)) from those sums; writes stats (mean, rstd)
+ *   mvae_conv2d_dgrad_gn   = mvae_conv2d_dgrad whose output da = dL/d[silu](GN(gn_x)) is turned
+ *                            into du = dL/d(xhat*gamma+beta) in the epilogue (stored instead of da),
+ *                            + gn_s12[n][g] = (sum du*gamma, sum du*gamma*xhat)
+ *   mvae_groupnorm_apply_bwd : dx = rstd*(du*gamma - s1/cnt - xhat*s2/cnt) + dx_add, and in the
+ *                            same pass out3[0] = dgamma, out3[1] = dbeta, out3[2] = column sums of dx
+ *                            (= bias gradient of the conv that produced x).  out3: fp32 [3][C].
+ * mvae_conv2d_fuses_gn(d, groups, direction): 1 if the conv (direction 0: fprop, output channels
+ * normalised; 1: dgrad, input channels) can carry the hook: tcgen05 path, channels/groups a power
+ * of two >= 4.  mvae_groupnorm_fused_ok(c, groups): the one-pass kernels support this shape. */
+int mvae_conv2d_fuses_gn(const mvae_conv_desc* d, int32_t groups, int32_t direction);
+int mvae_conv2d_fprop_gn(const mvae_conv_desc* d, const void* x, const void* w_fprop, const float* bias,
+                         const void* residual, void* y, float* gn_sums, int32_t groups, void* stream);
+int mvae_conv2d_dgrad_gn(const mvae_conv_desc* d, const void* dy, const void* w_dgrad, void* du,
+                         const void* gn_x, const float* gn_stats, const float* gamma, const float* beta,
+                         int32_t groups, int32_t apply_silu, float* gn_s12, void* stream);
+int mvae_groupnorm_fused_ok(int32_t c, int32_t groups);
+int64_t mvae_groupnorm_apply_bwd_scratch_floats(int32_t batch, int32_t hw, int32_t c);
+int mvae_groupnorm_apply_fwd(const void* x, const float* gamma, const float* beta, void* y,
+                             const float* sums, float* stats, int32_t batch, int32_t hw, int32_t c,
+                             int32_t groups, float eps, int32_t apply_silu, int32_t dtype, void* stream);
+int mvae_groupnorm_apply_bwd(const void* du, const void* x, const float* gamma, const float* stats,
+                             const float* s12, const void* dx_add, void* dx, float* out3, float* scratch,
+                             int32_t batch, int32_t hw, int32_t c, int32_t groups, int32_t dtype,
+                             void* stream);
 
 /* AttnBlock core, encoder_decoder.py:91-103: per image, single head of width C.
  * qkv: [B, T, 3C] (q|k|v along channels), out: [B, T, C].

@@ -53,6 +53,14 @@ SIGNATURES = {
     "mvae_groupnorm_silu_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _i32, _i32, _vp]),
     "mvae_groupnorm_silu_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32,
                                           _i32, _i32, _vp]),
+    "mvae_conv2d_fuses_gn": (C.c_int, [_dp, _i32, _i32]),
+    "mvae_conv2d_fprop_gn": (C.c_int, [_dp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp]),
+    "mvae_conv2d_dgrad_gn": (C.c_int, [_dp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp]),
+    "mvae_groupnorm_fused_ok": (C.c_int, [_i32, _i32]),
+    "mvae_groupnorm_apply_bwd_scratch_floats": (C.c_int64, [_i32, _i32, _i32]),
+    "mvae_groupnorm_apply_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _i32, _i32, _vp]),
+    "mvae_groupnorm_apply_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32,
+                                           _vp]),
     "mvae_attn_core_fwd": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "mvae_attn_core_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "mvae_input_pack_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),

@@ -11,6 +11,7 @@ GroupNorm+SiLU backward with the residual-gradient add, attention backward).
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -20,6 +21,9 @@ from . import _lib as L
 from . import ops
 
 GN_EPS = 1e-6
+# GroupNorm reductions ride in the epilogues of the neighbouring tcgen05 convs (bf16 mode); set
+# MVAE_GN_FUSE=0 to run the stand-alone two-pass GroupNorm kernels instead (A/B and cross-checks).
+FUSE_GN = os.environ.get("MVAE_GN_FUSE", "1") != "0"
 
 
 def _norm(c: int) -> nn.GroupNorm:
@@ -103,6 +107,7 @@ class Run:
         self.code = L.code_of(dtype)
         self.cache = cache            # packed-operand cache owned by the nn.Module
         self.training = training
+        self.fuse_gn = FUSE_GN and dtype == torch.bfloat16
         self.grads: Dict[nn.Parameter, torch.Tensor] = {}
         self.tape: list = []
 
@@ -189,16 +194,26 @@ class ConvOp:
             run.cache[key] = ent
         return ent
 
-    def fwd(self, run: Run, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def fwd(self, run: Run, x: torch.Tensor, residual: Optional[torch.Tensor] = None, gn_groups: int = 0):
+        """-> (y, sums): sums = per-(sample, group) (sum, sum of squares) of y for the GroupNorm with
+        `gn_groups` groups that consumes y, when the conv kernel can produce them; else None."""
         b, h, w, _ = x.shape
         ent = self.packed(run, x.device)
-        return ops.conv_fprop(self.desc(run, b, h, w), x, ent["wf"], ent["bias"], residual)
+        d = self.desc(run, b, h, w)
+        if gn_groups and run.fuse_gn and ops.conv_fuses_gn(d, gn_groups, 0):
+            return ops.conv_fprop_gn(d, x, ent["wf"], ent["bias"], residual, gn_groups)
+        return ops.conv_fprop(d, x, ent["wf"], ent["bias"], residual), None
 
-    def bwd(self, run: Run, x: torch.Tensor, dy: torch.Tensor, need_dx: bool = True):
+    def bwd(self, run: Run, x: torch.Tensor, dy: torch.Tensor, need_dx: bool = True, dy_colsum=None, gn=None):
+        """parameter gradients + (dx, None), or, with gn = (gn_x, stats, norm, silu) — x is the output
+        of [SiLU](GroupNorm(gn_x)) — (du, s12) from the fused dgrad epilogue when available.
+        dy_colsum: the column sums of dy if the producer of dy already has them (bias gradient)."""
         b, h, w, _ = x.shape
         d = self.desc(run, b, h, w)
         ent = self.packed(run, x.device)
-        dw, db = ops.conv_wgrad(d, x, dy, True)
+        dw, db = ops.conv_wgrad(d, x, dy, dy_colsum is None)
+        if db is None:
+            db = dy_colsum
         if d.in_c != self.cin or d.out_c != self.cout:
             dw = dw[:self.cout, :self.cin].contiguous()
             db = db[:self.cout]
@@ -207,18 +222,34 @@ class ConvOp:
             run.add_grad(c.weight, dw[off:off + c.out_channels])
             run.add_grad(c.bias, db[off:off + c.out_channels])
             off += c.out_channels
-        return ops.conv_dgrad(d, dy, ent["wd"]) if need_dx else None
+        if not need_dx:
+            return None, None
+        if gn is not None and run.fuse_gn:
+            gn_x, stats, norm, silu = gn
+            if ops.conv_fuses_gn(d, norm.num_groups, 1):
+                return ops.conv_dgrad_gn(d, dy, ent["wd"], gn_x, stats, norm.weight.detach(), norm.bias.detach(),
+                                         norm.num_groups, silu)
+        return ops.conv_dgrad(d, dy, ent["wd"]), None
 
 
-def gn_fwd(run: Run, norm: nn.GroupNorm, x, silu: bool):
+def gn_fwd(run: Run, norm: nn.GroupNorm, x, silu: bool, sums=None):
+    """-> (y, stats).  sums: the group sums of x from the conv that produced it (one-pass kernel)."""
+    if sums is not None:
+        return ops.gn_apply_fwd(x, norm.weight.detach(), norm.bias.detach(), sums, norm.num_groups, norm.eps, silu)
     return ops.gn_fwd(x, norm.weight.detach(), norm.bias.detach(), norm.num_groups, norm.eps, silu)
 
 
-def gn_bwd(run: Run, norm: nn.GroupNorm, dy, x, stats, dx_add, silu: bool):
-    dx, dg, db = ops.gn_bwd(dy, x, norm.weight.detach(), norm.bias.detach(), stats, dx_add, norm.num_groups, silu)
+def gn_bwd(run: Run, norm: nn.GroupNorm, dy, x, stats, dx_add, silu: bool, s12=None):
+    """-> (dx, colsum(dx) or None).  With s12, `dy` is already du (fused dgrad epilogue) and the
+    one-pass kernel also returns the column sums of dx."""
+    if s12 is not None:
+        dx, dg, db, cs = ops.gn_apply_bwd(dy, x, norm.weight.detach(), stats, s12, dx_add, norm.num_groups)
+    else:
+        dx, dg, db = ops.gn_bwd(dy, x, norm.weight.detach(), norm.bias.detach(), stats, dx_add, norm.num_groups, silu)
+        cs = None
     run.add_grad(norm.weight, dg)
     run.add_grad(norm.bias, db)
-    return dx
+    return dx, cs
 
 
 class ResOp:
@@ -228,6 +259,7 @@ class ResOp:
 
     def __init__(self, blk: ResnetBlock):
         self.blk = blk
+        self.in_groups, self.out_groups = blk.norm1.num_groups, 0
         self.c1 = ConvOp([blk.conv1], L.CONV_S1)
         self.c2 = ConvOp([blk.conv2], L.CONV_S1)
         self.nin = ConvOp([blk.nin_shortcut], L.CONV_S1) if hasattr(blk, "nin_shortcut") else None
@@ -241,27 +273,29 @@ class ResOp:
         return (self.c2.params() + [b.norm2.weight, b.norm2.bias] + self.c1.params()
                 + (self.nin.params() if self.nin is not None else []) + [b.norm1.weight, b.norm1.bias])
 
-    def fwd(self, run: Run, x):
+    def fwd(self, run: Run, x, x_sums=None):
         if self.p_drop > 0.0 and run.training:
             raise NotImplementedError("dropout > 0 in training mode is not implemented (all full-size reference "
                                       "configs use dropout 0.0)")
-        a1, st1 = gn_fwd(run, self.blk.norm1, x, True)
-        h1 = self.c1.fwd(run, a1)
-        a2, st2 = gn_fwd(run, self.blk.norm2, h1, True)
-        xs = self.nin.fwd(run, x) if self.nin is not None else x
-        out = self.c2.fwd(run, a2, residual=xs)
+        blk = self.blk
+        a1, st1 = gn_fwd(run, blk.norm1, x, True, x_sums)
+        h1, h1_sums = self.c1.fwd(run, a1, gn_groups=blk.norm2.num_groups)
+        a2, st2 = gn_fwd(run, blk.norm2, h1, True, h1_sums)
+        xs = self.nin.fwd(run, x)[0] if self.nin is not None else x
+        out, out_sums = self.c2.fwd(run, a2, residual=xs, gn_groups=self.out_groups)
         run.tape.append((self, (x, st1, a1, h1, st2, a2)))
-        return out
+        return out, out_sums
 
-    def bwd(self, run: Run, saved, dout):
+    def bwd(self, run: Run, saved, dout, dout_cs=None):
         x, st1, a1, h1, st2, a2 = saved
-        d_a2 = self.c2.bwd(run, a2, dout)
-        d_h1 = gn_bwd(run, self.blk.norm2, d_a2, h1, st2, None, True)
+        blk = self.blk
+        d_a2, s12 = self.c2.bwd(run, a2, dout, dy_colsum=dout_cs, gn=(h1, st2, blk.norm2, True))
+        d_h1, h1_cs = gn_bwd(run, blk.norm2, d_a2, h1, st2, None, True, s12)
         del d_a2
-        d_a1 = self.c1.bwd(run, a1, d_h1)
+        d_a1, s12 = self.c1.bwd(run, a1, d_h1, dy_colsum=h1_cs, gn=(x, st1, blk.norm1, True))
         del d_h1
-        addend = self.nin.bwd(run, x, dout) if self.nin is not None else dout
-        return gn_bwd(run, self.blk.norm1, d_a1, x, st1, addend, True)
+        addend = self.nin.bwd(run, x, dout, dy_colsum=dout_cs)[0] if self.nin is not None else dout
+        return gn_bwd(run, blk.norm1, d_a1, x, st1, addend, True, s12)
 
 
 class AttnOp:
@@ -269,28 +303,29 @@ class AttnOp:
 
     def __init__(self, blk: AttnBlock):
         self.blk = blk
+        self.in_groups, self.out_groups = blk.norm.num_groups, 0
         self.qkv = ConvOp([blk.q, blk.k, blk.v], L.CONV_S1)
         self.proj = ConvOp([blk.proj_out], L.CONV_S1)
 
     def params_backward_order(self):
         return self.proj.params() + self.qkv.params() + [self.blk.norm.weight, self.blk.norm.bias]
 
-    def fwd(self, run: Run, x):
-        hn, st = gn_fwd(run, self.blk.norm, x, False)
-        qkv = self.qkv.fwd(run, hn)
+    def fwd(self, run: Run, x, x_sums=None):
+        hn, st = gn_fwd(run, self.blk.norm, x, False, x_sums)
+        qkv, _ = self.qkv.fwd(run, hn)
         o, probs = ops.attn_fwd(qkv)
-        out = self.proj.fwd(run, o, residual=x)
+        out, out_sums = self.proj.fwd(run, o, residual=x, gn_groups=self.out_groups)
         run.tape.append((self, (x, st, hn, qkv, o, probs)))
-        return out
+        return out, out_sums
 
-    def bwd(self, run: Run, saved, dout):
+    def bwd(self, run: Run, saved, dout, dout_cs=None):
         x, st, hn, qkv, o, probs = saved
-        d_o = self.proj.bwd(run, o, dout)
+        d_o, _ = self.proj.bwd(run, o, dout, dy_colsum=dout_cs)
         d_qkv = ops.attn_bwd(qkv, probs, d_o)
         del d_o
-        d_hn = self.qkv.bwd(run, hn, d_qkv)
+        d_hn, s12 = self.qkv.bwd(run, hn, d_qkv, gn=(x, st, self.blk.norm, False))
         del d_qkv
-        return gn_bwd(run, self.blk.norm, d_hn, x, st, dout, False)
+        return gn_bwd(run, self.blk.norm, d_hn, x, st, dout, False, s12)
 
 
 class PlainConvOp:
@@ -299,17 +334,18 @@ class PlainConvOp:
     def __init__(self, conv: nn.Conv2d, mode: int, need_dx: bool = True, pad_in: bool = False):
         self.op = ConvOp([conv], mode, pad_in=pad_in)
         self.need_dx = need_dx
+        self.in_groups, self.out_groups = 0, 0
 
     def params_backward_order(self):
         return self.op.params()
 
-    def fwd(self, run: Run, x):
-        y = self.op.fwd(run, x)
+    def fwd(self, run: Run, x, x_sums=None):
+        y, y_sums = self.op.fwd(run, x, gn_groups=self.out_groups)
         run.tape.append((self, (x,)))
-        return y
+        return y, y_sums
 
-    def bwd(self, run: Run, saved, dout):
-        return self.op.bwd(run, saved[0], dout, self.need_dx)
+    def bwd(self, run: Run, saved, dout, dout_cs=None):
+        return self.op.bwd(run, saved[0], dout, self.need_dx, dy_colsum=dout_cs)[0], None
 
 
 class HeadOp:
@@ -318,32 +354,43 @@ class HeadOp:
     def __init__(self, norm: nn.GroupNorm, conv: nn.Conv2d, pad_out: bool = False):
         self.norm = norm
         self.op = ConvOp([conv], L.CONV_S1, pad_out=pad_out)
+        self.in_groups, self.out_groups = norm.num_groups, 0
 
     def params_backward_order(self):
         return self.op.params() + [self.norm.weight, self.norm.bias]
 
-    def fwd(self, run: Run, x):
-        a, st = gn_fwd(run, self.norm, x, True)
-        y = self.op.fwd(run, a)
+    def fwd(self, run: Run, x, x_sums=None):
+        a, st = gn_fwd(run, self.norm, x, True, x_sums)
+        y, _ = self.op.fwd(run, a)
         run.tape.append((self, (x, st, a)))
-        return y
+        return y, None
 
-    def bwd(self, run: Run, saved, dout):
+    def bwd(self, run: Run, saved, dout, dout_cs=None):
         x, st, a = saved
-        d_a = self.op.bwd(run, a, dout)
-        return gn_bwd(run, self.norm, d_a, x, st, None, True)
+        d_a, s12 = self.op.bwd(run, a, dout, dy_colsum=dout_cs, gn=(x, st, self.norm, True))
+        return gn_bwd(run, self.norm, d_a, x, st, None, True, s12)
+
+
+def link_stages(stages):
+    """tell every stage how many GroupNorm groups the NEXT stage normalises its input with, so
+    its last conv can produce that GroupNorm's statistics in its epilogue."""
+    for cur, nxt in zip(stages[:-1], stages[1:]):
+        cur.out_groups = nxt.in_groups
+    return stages
 
 
 def run_forward(stages, run: Run, x):
+    sums = None
     for s in stages:
-        x = s.fwd(run, x)
+        x, sums = s.fwd(run, x, sums)
     return x
 
 
 def run_backward(run: Run, dout):
+    cs = None
     while run.tape:
         stage, saved = run.tape.pop()
-        dout = stage.bwd(run, saved, dout)
+        dout, cs = stage.bwd(run, saved, dout, cs)
         del saved
     return dout
 
@@ -455,7 +502,7 @@ class Encoder(_Stack):
                 st.append(PlainConvOp(level.downsample.conv, L.CONV_DOWN))
         st += [ResOp(self.mid.block_1), AttnOp(self.mid.attn_1), ResOp(self.mid.block_2),
                HeadOp(self.norm_out, self.conv_out)]
-        return st
+        return link_stages(st)
 
     def in_channels_nhwc(self, dtype) -> int:
         """channel count forward_nhwc() expects (conv_in zero-padded to 64 in bf16 mode)"""
@@ -525,7 +572,7 @@ class Decoder(_Stack):
             if hasattr(level, "upsample"):
                 st.append(PlainConvOp(level.upsample.conv, L.CONV_UP))
         st.append(HeadOp(self.norm_out, self.conv_out, pad_out=True))
-        return st
+        return link_stages(st)
 
     def out_channels_nhwc(self, dtype) -> int:
         """channel count of forward_nhwc()'s output (conv_out zero-padded to 64 in bf16 mode)"""

@@ -42,6 +42,13 @@ int gn_fwd(const void* x, const float* gamma, const float* beta, void* y, float*
 int gn_bwd(const void* dy, const void* x, const float* gamma, const float* beta, const float* stats, const void* dx_add,
            void* dx, float* dgamma, float* dbeta, float* scratch, int B, int HW, int C, int G, int silu, int dtype,
            cudaStream_t st);
+bool gn_pre_ok(int C, int G);
+int gn_bwd_pre_grid(int B, int HW, int C);
+int gn_apply_pre(const void* x, const float* gamma, const float* beta, void* y, const float* sums, float* stats, int B,
+                 int HW, int C, int G, float eps, int silu, int dtype, cudaStream_t st);
+int gn_bwd_pre(const void* du, const void* x, const float* gamma, const float* stats, const float* s12,
+               const void* dx_add, void* dx, float* out3, float* scratch, int B, int HW, int C, int G, int dtype,
+               cudaStream_t st);
 int attn_fwd(const void* qkv, void* out, float* probs, int B, int Tn, int C, int dtype, cudaStream_t st);
 int attn_bwd(const void* qkv, const float* probs, const void* dout, void* dqkv, float* ds, int B, int Tn, int C,
              int dtype, cudaStream_t st);
@@ -159,6 +166,78 @@ int mvae_conv2d_dgrad(const mvae_conv_desc* d, const void* dy, const void* wd, v
         if (rc) return rc;
     }
     return 0;
+}
+
+// GroupNorm over `c` channels in `groups` groups can ride in the tcgen05 gather epilogue
+static int gn_cpg_log2(int c, int groups) {
+    if (groups <= 0 || c % groups != 0) return -1;
+    int cpg = c / groups, l = 0;
+    while ((1 << l) < cpg) ++l;
+    return ((1 << l) == cpg && l >= 2) ? l : -1;
+}
+
+int mvae_conv2d_fuses_gn(const mvae_conv_desc* d, int32_t groups, int32_t direction) {
+    ConvGeom g;
+    if (!d || conv_geom(*d, g)) return 0;
+    GatherProblem ps[4];
+    const int np = direction ? lower_dgrad(g, ps) : lower_fprop(g, ps);
+    if (!use_umma_gather(*d, ps, np)) return 0;
+    const int c = direction ? g.Cin : g.Cout;
+    return (gn_cpg_log2(c, groups) >= 0 && gn_pre_ok(c, groups)) ? 1 : 0;
+}
+
+int mvae_conv2d_fprop_gn(const mvae_conv_desc* d, const void* x, const void* wf, const float* bias, const void* residual,
+                         void* y, float* gn_sums, int32_t groups, void* stream) {
+    ConvGeom g;
+    MVAE_CHECK(d && conv_geom(*d, g) == 0 && dtype_ok(d->dtype), "bad conv descriptor");
+    MVAE_CHECK(x && wf && y && gn_sums, "conv2d_fprop_gn: null pointer");
+    MVAE_CHECK(mvae_conv2d_fuses_gn(d, groups, 0), "conv2d_fprop_gn: this conv / group count cannot fuse GroupNorm statistics");
+    GatherProblem ps[4];
+    int np = lower_fprop(g, ps);
+    MVAE_CUDA(cudaMemsetAsync(gn_sums, 0, sizeof(float) * 2 * (size_t)g.B * groups, ST(stream)));
+    GnHook h;
+    memset(&h, 0, sizeof(h));
+    h.mode = 1; h.G = groups; h.cpg_log2 = gn_cpg_log2(g.Cout, groups); h.sums = gn_sums;
+    for (int i = 0; i < np; ++i)
+        if (umma_gather(ps[i], x, wf, conv_num_slabs(g), bias, residual, y, ST(stream), &h)) return 1;
+    return 0;
+}
+
+int mvae_conv2d_dgrad_gn(const mvae_conv_desc* d, const void* dy, const void* wd, void* du, const void* gn_x,
+                         const float* gn_stats, const float* gamma, const float* beta, int32_t groups, int32_t apply_silu,
+                         float* gn_s12, void* stream) {
+    ConvGeom g;
+    MVAE_CHECK(d && conv_geom(*d, g) == 0 && dtype_ok(d->dtype), "bad conv descriptor");
+    MVAE_CHECK(dy && wd && du && gn_x && gn_stats && gamma && beta && gn_s12, "conv2d_dgrad_gn: null pointer");
+    MVAE_CHECK(mvae_conv2d_fuses_gn(d, groups, 1), "conv2d_dgrad_gn: this conv / group count cannot fuse the GroupNorm backward");
+    GatherProblem ps[4];
+    int np = lower_dgrad(g, ps);
+    MVAE_CUDA(cudaMemsetAsync(gn_s12, 0, sizeof(float) * 2 * (size_t)g.B * groups, ST(stream)));
+    GnHook h;
+    memset(&h, 0, sizeof(h));
+    h.mode = 2; h.G = groups; h.cpg_log2 = gn_cpg_log2(g.Cin, groups); h.silu = apply_silu; h.sums = gn_s12;
+    h.x = gn_x; h.stat = gn_stats; h.gamma = gamma; h.beta = beta;
+    for (int i = 0; i < np; ++i)
+        if (umma_gather(ps[i], dy, wd, conv_num_slabs(g), nullptr, nullptr, du, ST(stream), &h)) return 1;
+    return 0;
+}
+
+int mvae_groupnorm_fused_ok(int32_t c, int32_t groups) { return gn_pre_ok(c, groups) ? 1 : 0; }
+int64_t mvae_groupnorm_apply_bwd_scratch_floats(int32_t batch, int32_t hw, int32_t c) {
+    return (int64_t)gn_bwd_pre_grid(batch, hw, c) * 3 * c;
+}
+int mvae_groupnorm_apply_fwd(const void* x, const float* gamma, const float* beta, void* y, const float* sums,
+                             float* stats, int32_t batch, int32_t hw, int32_t c, int32_t groups, float eps,
+                             int32_t apply_silu, int32_t dtype, void* stream) {
+    MVAE_CHECK(x && gamma && beta && y && sums && stats && dtype_ok(dtype), "groupnorm_apply_fwd: bad argument");
+    return gn_apply_pre(x, gamma, beta, y, sums, stats, batch, hw, c, groups, eps, apply_silu, dtype, ST(stream));
+}
+int mvae_groupnorm_apply_bwd(const void* du, const void* x, const float* gamma, const float* stats, const float* s12,
+                             const void* dx_add, void* dx, float* out3, float* scratch, int32_t batch, int32_t hw,
+                             int32_t c, int32_t groups, int32_t dtype, void* stream) {
+    MVAE_CHECK(du && x && gamma && stats && s12 && dx && out3 && scratch && dtype_ok(dtype),
+               "groupnorm_apply_bwd: bad argument");
+    return gn_bwd_pre(du, x, gamma, stats, s12, dx_add, dx, out3, scratch, batch, hw, c, groups, dtype, ST(stream));
 }
 
 static bool use_umma_reduce(const mvae_conv_desc& d, const ReduceProblem& p) {

@@ -171,6 +171,23 @@ inline void lower_wgrad(const ConvGeom& g, ReduceProblem& p) {
     }
 }
 
+// Optional GroupNorm fusion in the epilogue of the tcgen05 gather kernel (conv_umma.cu):
+//   mode 1 (fprop):  sums[n][g] += (sum y, sum y^2) over the stored outputs: the statistics pass of
+//                    the GroupNorm that consumes y (encoder_decoder.py:28-33) costs no HBM pass.
+//   mode 2 (dgrad):  the accumulator is dL/da with a = [silu](GN(x)); the epilogue turns it into
+//                    du = dL/du (u = xhat*gamma + beta) using x and (mean, rstd), stores du instead, and
+//                    accumulates sums[n][g] += (sum du*gamma, sum du*gamma*xhat): the reduction pass
+//                    of the GroupNorm backward.  x is addressed like the output.
+struct GnHook {
+    int mode;
+    int G, cpg_log2, silu;
+    float* sums;          // [B][G][2], accumulated with fp32 atomics (caller zeroes)
+    const void* x;        // mode 2
+    const float* stat;    // mode 2: [B][G][2] (mean, rstd)
+    const float* gamma;   // mode 2
+    const float* beta;    // mode 2
+};
+
 // launchers (conv_simt.cu / conv_umma.cu)
 int simt_gather(const GatherProblem& p, const void* in, const void* w, const float* bias,
                 const void* residual, void* out, int dtype, cudaStream_t st);
@@ -178,7 +195,7 @@ int simt_reduce(const ReduceProblem& p, const void* in, const void* dy, float* p
                 int dtype, cudaStream_t st);
 bool umma_gather_ok(const GatherProblem& p);
 int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslabs, const float* bias,
-                const void* residual, void* out, cudaStream_t st);
+                const void* residual, void* out, cudaStream_t st, const GnHook* hook = nullptr);
 bool umma_reduce_ok(const ReduceProblem& p);
 int umma_reduce_splits(const ReduceProblem& p);
 int umma_reduce(const ReduceProblem& p, const void* in, const void* dy, float* partial, int splits,

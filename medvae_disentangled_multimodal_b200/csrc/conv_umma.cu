@@ -7,6 +7,11 @@
 //      warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM alloc), warps 2-5 = epilogue
 //      (tcgen05.ld -> +bias (+residual) -> bf16 -> global).  Persistent CTAs, 2 TMEM accumulator
 //      stages so the epilogue of tile i overlaps the MMAs of tile i+1.
+//      Epilogue variants (template EPI): the GroupNorm either side of the conv rides here —
+//      EPI_GN_STATS accumulates the consumer GroupNorm's per-(sample, group) sums of the output,
+//      EPI_GN_BWD turns dL/d[silu(GN(x))] into dL/du and accumulates the GroupNorm-backward group
+//      sums (warps 2-9: two warps per TMEM lane quarter, x / residual strips prefetched before the
+//      accumulator is ready).
 //
 //  reduce kernel (wgrad):  D[128 co, BN ci] (per slab, per K-split) = sum_pixels dy[pix, co] * x[pix+tap, ci]
 //      Both operands are "MN-major" (the channel index is contiguous in NHWC), loaded by the same
@@ -113,9 +118,79 @@ struct GatherDev {
     const bf16* res;
     bf16* out;
     TapProg taps;
+    // GroupNorm fusion (GnHook, conv_lower.h); which one is compiled in is the EPI template argument
+    int gn_G, gn_cpg_log2, gn_silu;
+    float* gn_sums;
+    const bf16* gn_x;
+    const float* gn_stat;
+    const float* gn_gamma;
+    const float* gn_beta;
 };
 
 constexpr int G_THREADS = 192;
+enum { EPI_PLAIN = 0, EPI_GN_STATS = 1, EPI_GN_BWD = 2 };
+// The GroupNorm epilogues do ~15 instructions and a 2-byte global read per element: eight epilogue
+// warps (two per TMEM lane quarter, each taking half of the tile's columns) keep them hidden under
+// the MMAs of the next tile; the plain epilogue keeps four.
+__host__ __device__ constexpr int gather_epi_warps(int epi) { return epi == EPI_PLAIN ? 4 : 8; }
+__host__ __device__ constexpr int gather_threads(int epi) { return 64 + 32 * gather_epi_warps(epi); }
+
+// Sum N per-lane values over the 32 lanes of a warp with a transposing butterfly (N-1 + log2(32/N)
+// shuffles instead of 5N): afterwards lane l holds in v[0] the total of value index l / (32/N).
+template <int N>
+struct WarpReduceScatter {
+    static __device__ __forceinline__ void run(float* v, int lane, int off) {
+        constexpr int H = N / 2;
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+            const float send = up ? v[i] : v[i + H];
+            const float keep = up ? v[i + H] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+        WarpReduceScatter<H>::run(v, lane, off >> 1);
+    }
+};
+template <>
+struct WarpReduceScatter<1> {
+    static __device__ __forceinline__ void run(float* v, int lane, int off) {
+        for (; off > 0; off >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
+    }
+};
+
+// sa / sb: the two per-row partial sums of the eight 4-channel sub-blocks of one 32-channel chunk.
+// NG = GroupNorm groups inside the chunk.  Rows of one warp that all belong to image n_ref are
+// summed in registers first (one atomic per value per warp); otherwise every valid row adds its own.
+// dst -> element (n, first group of the chunk, 0) of the [B][G][2] accumulator, for n = n_ref
+// (uniform) or the thread's own image.
+template <int NG>
+__device__ __forceinline__ void gn_flush(const float* sa, const float* sb, float* dst, int lane, bool uniform,
+                                         bool valid) {
+    constexpr int PER = 8 / NG;
+    float v[2 * NG];
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+        float a = 0.f, b = 0.f;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) { a += sa[g * PER + i]; b += sb[g * PER + i]; }
+        v[2 * g] = a; v[2 * g + 1] = b;
+    }
+    if (uniform) {
+        WarpReduceScatter<2 * NG>::run(v, lane, 16);
+        constexpr int LOW = 32 / (2 * NG);
+        if ((lane & (LOW - 1)) == 0) atomicAdd(dst + lane / LOW, v[0]);
+    } else if (valid) {
+#pragma unroll
+        for (int i = 0; i < 2 * NG; ++i) atomicAdd(dst + i, v[i]);
+    }
+}
+__device__ __forceinline__ void gn_flush_any(int cpg_log2, const float* sa, const float* sb, float* dst, int lane,
+                                             bool uniform, bool valid) {
+    if (cpg_log2 == 2) gn_flush<8>(sa, sb, dst, lane, uniform, valid);
+    else if (cpg_log2 == 3) gn_flush<4>(sa, sb, dst, lane, uniform, valid);
+    else if (cpg_log2 == 4) gn_flush<2>(sa, sb, dst, lane, uniform, valid);
+    else gn_flush<1>(sa, sb, dst, lane, uniform, valid);
+}
 
 template <int BN>
 struct GatherCfg {
@@ -126,8 +201,8 @@ struct GatherCfg {
     static constexpr int SMEM = 1024 + STAGES * (A_BYTES + B_BYTES) + 256;
 };
 
-template <int BN>
-__global__ void __launch_bounds__(G_THREADS, 1)
+template <int BN, int EPI>
+__global__ void __launch_bounds__(gather_threads(EPI), 1)
 conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_constant__ GatherDev p) {
     using Cfg = GatherCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
@@ -145,7 +220,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
 
     if (p.rows < 128) {
         // rows the TMA box never writes feed accumulator rows nobody stores; keep them finite
-        for (int i = threadIdx.x; i < STAGES * Cfg::A_BYTES / 16; i += G_THREADS)
+        for (int i = threadIdx.x; i < STAGES * Cfg::A_BYTES / 16; i += gather_threads(EPI))
             reinterpret_cast<uint4*>(sA)[i] = make_uint4(0, 0, 0, 0);
         fence_proxy_async_smem();
     }
@@ -156,7 +231,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
     if (warp == 1) {
         if (lane == 0) {
             for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-            for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 128); }
+            for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 32 * gather_epi_warps(EPI)); }
             fence_barrier_init();
         }
         __syncwarp();
@@ -237,42 +312,154 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
             const int x = tx * p.bw + ix, y = ty * p.bh + iy, n = tn * p.bn + in;
             const bool valid = (row < p.rows) && x < p.OW && y < p.OH && n < p.B;
             const long long pix = p.o_off + (long long)n * p.o_sn + (long long)y * p.o_sy + (long long)x * p.o_sx;
-            mbar_wait(&tfull[acc], acc_phase);
-            tc_fence_after();
-            const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+            if (EPI == EPI_PLAIN) {
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+                const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 32) {
-                uint32_t v[32];
-                tmem_ld_32x32(t0 + (uint32_t)c0, v);
-                tmem_ld_wait();
-                if (valid) {
-                    const int cbase = nt * BN + c0;
-                    float f[32];
+                for (int c0 = 0; c0 < BN; c0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t0 + (uint32_t)c0, v);
+                    tmem_ld_wait();
+                    if (valid) {
+                        const int cbase = nt * BN + c0;
+                        float f[32];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-                    if (p.bias) {
-                        const float4* bp = reinterpret_cast<const float4*>(p.bias + cbase);
+                        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+                        if (p.bias) {
+                            const float4* bp = reinterpret_cast<const float4*>(p.bias + cbase);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            float4 b4 = __ldg(bp + i);
-                            f[4 * i] += b4.x; f[4 * i + 1] += b4.y; f[4 * i + 2] += b4.z; f[4 * i + 3] += b4.w;
+                            for (int i = 0; i < 8; ++i) {
+                                float4 b4 = __ldg(bp + i);
+                                f[4 * i] += b4.x; f[4 * i + 1] += b4.y; f[4 * i + 2] += b4.z; f[4 * i + 3] += b4.w;
+                            }
                         }
-                    }
-                    if (p.res) {
-                        const uint4* rp = reinterpret_cast<const uint4*>(p.res + pix + cbase);
+                        if (p.res) {
+                            const uint4* rp = reinterpret_cast<const uint4*>(p.res + pix + cbase);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                Vec8<bf16> r8; r8.raw = __ldg(rp + i);
+                                float rf[8]; r8.unpack(rf);
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) f[8 * i + j] += rf[j];
+                            }
+                        }
+                        uint4* op = reinterpret_cast<uint4*>(p.out + pix + cbase);
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            Vec8<bf16> r8; r8.raw = __ldg(rp + i);
-                            float rf[8]; r8.unpack(rf);
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) f[8 * i + j] += rf[j];
+                            Vec8<bf16> o8; o8.pack(f + 8 * i);
+                            op[i] = o8.raw;
                         }
                     }
-                    uint4* op = reinterpret_cast<uint4*>(p.out + pix + cbase);
+                }
+            } else {
+                // this warp's half of the tile's columns: XCH chunks of 32
+                constexpr int CW = BN / 2, XCH = CW / 32;
+                const int chalf = (warp - 2) >> 2;
+                // are all valid rows of this warp in one image?  (then one atomic per value per warp)
+                const unsigned vm = __ballot_sync(0xffffffffu, valid);
+                const bool any_valid = vm != 0u;
+                const int n_ref = __shfl_sync(0xffffffffu, n, any_valid ? (__ffs(vm) - 1) : 0);
+                const bool uniform = __all_sync(0xffffffffu, !valid || n == n_ref);
+                // the per-element global operand (GN input x / residual) does not depend on the
+                // accumulator: fetch the whole strip before waiting for the MMAs
+                uint4 aux[XCH][4];
+                const bf16* auxp = (EPI == EPI_GN_BWD) ? p.gn_x : p.res;
+                const bool have_aux = valid && auxp != nullptr;
+                if (have_aux) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        Vec8<bf16> o8; o8.pack(f + 8 * i);
-                        op[i] = o8.raw;
+                    for (int ci = 0; ci < XCH; ++ci) {
+                        const uint4* ap = reinterpret_cast<const uint4*>(auxp + pix + nt * BN + chalf * CW + ci * 32);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) aux[ci][i] = __ldg(ap + i);
+                    }
+                }
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+                const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + chalf * CW);
+#pragma unroll
+                for (int ci = 0; ci < XCH; ++ci) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t0 + (uint32_t)(ci * 32), v);
+                    tmem_ld_wait();
+                    const int cbase = nt * BN + chalf * CW + ci * 32;
+                    float sa[8], sb[8];   // GN partial sums of the eight 4-channel sub-blocks of this chunk
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { sa[k] = 0.f; sb[k] = 0.f; }
+                    if (valid) {
+                        float f[32];
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+                        if (p.bias) {
+                            const float4* bp = reinterpret_cast<const float4*>(p.bias + cbase);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                float4 b4 = __ldg(bp + i);
+                                f[4 * i] += b4.x; f[4 * i + 1] += b4.y; f[4 * i + 2] += b4.z; f[4 * i + 3] += b4.w;
+                            }
+                        }
+                        if (EPI == EPI_GN_STATS && p.res) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                Vec8<bf16> r8; r8.raw = aux[ci][i];
+                                float rf[8]; r8.unpack(rf);
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) f[8 * i + j] += rf[j];
+                            }
+                        }
+                        if (EPI == EPI_GN_BWD) {
+                            // f = dL/da  ->  du = f * silu'(u), u = xhat*gamma + beta, xhat = (x - mean)*rstd
+                            const float2* stp = reinterpret_cast<const float2*>(p.gn_stat) + (long long)n * p.gn_G;
+                            float rs = 0.f, nm = 0.f; int gprev = -1;
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                Vec8<bf16> x8; x8.raw = aux[ci][i];
+                                float xf[8]; x8.unpack(xf);
+#pragma unroll
+                                for (int h = 0; h < 2; ++h) {
+                                    const int k = 2 * i + h;
+                                    const int g = (cbase + 4 * k) >> p.gn_cpg_log2;
+                                    if (g != gprev) {
+                                        const float2 mr = __ldg(stp + g);
+                                        rs = mr.y; nm = -mr.x * mr.y; gprev = g;
+                                    }
+                                    const float4 ga = __ldg(reinterpret_cast<const float4*>(p.gn_gamma + cbase) + k);
+                                    const float4 be = __ldg(reinterpret_cast<const float4*>(p.gn_beta + cbase) + k);
+                                    const float gam[4] = {ga.x, ga.y, ga.z, ga.w}, bet[4] = {be.x, be.y, be.z, be.w};
+#pragma unroll
+                                    for (int j = 0; j < 4; ++j) {
+                                        const float xh = fmaf(xf[4 * h + j], rs, nm);
+                                        float d = f[4 * k + j];
+                                        if (p.gn_silu) {
+                                            const float u = fmaf(xh, gam[j], bet[j]);
+                                            const float sg = sigmoid_t<bf16>(u);
+                                            d *= sg * fmaf(u, 1.f - sg, 1.f);
+                                            f[4 * k + j] = d;
+                                        }
+                                        const float gd = d * gam[j];
+                                        sa[k] += gd; sb[k] = fmaf(gd, xh, sb[k]);
+                                    }
+                                }
+                            }
+                        }
+                        uint4* op = reinterpret_cast<uint4*>(p.out + pix + cbase);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            Vec8<bf16> o8; o8.pack(f + 8 * i);
+                            op[i] = o8.raw;
+                            if (EPI == EPI_GN_STATS) {
+                                float yf[8]; o8.unpack(yf);   // statistics of the values as stored
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) {
+                                    const int k = 2 * i + (j >> 2);
+                                    sa[k] += yf[j]; sb[k] = fmaf(yf[j], yf[j], sb[k]);
+                                }
+                            }
+                        }
+                    }
+                    if (any_valid) {
+                        float* dst = p.gn_sums + ((long long)(uniform ? n_ref : n) * p.gn_G + (cbase >> p.gn_cpg_log2)) * 2;
+                        gn_flush_any(p.gn_cpg_log2, sa, sb, dst, lane, uniform, valid);
                     }
                 }
             }
@@ -299,23 +486,29 @@ bool umma_gather_ok(const GatherProblem& p) {
     return true;
 }
 
-template <int BN>
-static int launch_gather(const GatherTmaps& tm, GatherDev& d, cudaStream_t st) {
+template <int BN, int EPI>
+static int launch_gather_epi(const GatherTmaps& tm, GatherDev& d, cudaStream_t st) {
     using Cfg = GatherCfg<BN>;
     static bool attr_set = false;
     if (!attr_set) {
-        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg::SMEM));
         attr_set = true;
     }
     int grid = d.total_tiles < num_sms() ? d.total_tiles : num_sms();
-    conv_gather_umma_kernel<BN><<<grid, G_THREADS, Cfg::SMEM, st>>>(tm, d);
+    conv_gather_umma_kernel<BN, EPI><<<grid, gather_threads(EPI), Cfg::SMEM, st>>>(tm, d);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
+template <int BN>
+static int launch_gather(const GatherTmaps& tm, GatherDev& d, int epi, cudaStream_t st) {
+    if (epi == EPI_GN_STATS) return launch_gather_epi<BN, EPI_GN_STATS>(tm, d, st);
+    if (epi == EPI_GN_BWD) return launch_gather_epi<BN, EPI_GN_BWD>(tm, d, st);
+    return launch_gather_epi<BN, EPI_PLAIN>(tm, d, st);
+}
 
 int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslabs, const float* bias,
-                const void* residual, void* out, cudaStream_t st) {
+                const void* residual, void* out, cudaStream_t st, const GnHook* hook) {
     MVAE_CHECK(umma_gather_ok(p), "umma_gather: unsupported shape K=%d N=%d OW=%d", p.K, p.N, p.OW);
     BoxGeom g = box_geom(p.B, p.OH, p.OW);
     const int BN = (p.N % 256 == 0) ? 256 : (p.N % 128 == 0 ? 128 : 64);
@@ -341,9 +534,22 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     d.o_off = p.out_view.off; d.o_sn = p.out_view.sn; d.o_sy = p.out_view.sy; d.o_sx = p.out_view.sx;
     d.bias = bias; d.res = (const bf16*)residual; d.out = (bf16*)out;
     d.taps = p.taps;
-    if (BN == 256) return launch_gather<256>(tm, d, st);
-    if (BN == 128) return launch_gather<128>(tm, d, st);
-    return launch_gather<64>(tm, d, st);
+    int epi = EPI_PLAIN;
+    d.gn_G = 0; d.gn_cpg_log2 = 0; d.gn_silu = 0;
+    d.gn_sums = nullptr; d.gn_x = nullptr; d.gn_stat = nullptr; d.gn_gamma = nullptr; d.gn_beta = nullptr;
+    if (hook && hook->mode != 0) {
+        MVAE_CHECK(hook->cpg_log2 >= 2 && (p.N % (hook->G << hook->cpg_log2)) == 0 && hook->sums,
+                   "umma_gather: GroupNorm hook needs >= 4 channels per group (power of two) over all N channels");
+        MVAE_CHECK(hook->mode == EPI_GN_STATS || (hook->x && hook->stat && hook->gamma && hook->beta),
+                   "umma_gather: GroupNorm backward hook needs x, stats, gamma, beta");
+        epi = hook->mode;
+        d.gn_G = hook->G; d.gn_cpg_log2 = hook->cpg_log2; d.gn_silu = hook->silu;
+        d.gn_sums = hook->sums; d.gn_x = (const bf16*)hook->x; d.gn_stat = hook->stat;
+        d.gn_gamma = hook->gamma; d.gn_beta = hook->beta;
+    }
+    if (BN == 256) return launch_gather<256>(tm, d, epi, st);
+    if (BN == 128) return launch_gather<128>(tm, d, epi, st);
+    return launch_gather<64>(tm, d, epi, st);
 }
 
 // ================================================================== reduce (wgrad)

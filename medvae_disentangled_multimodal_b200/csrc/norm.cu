@@ -431,6 +431,305 @@ __global__ void __launch_bounds__(GN_THREADS, 3) gn_bwd_apply_kernel(const T* __
     }
 }
 
+// ================================================================== one-pass variants
+// When the conv kernel that PRODUCED x has already accumulated the per-(sample, group) sums in its
+// epilogue (GnHook, conv_lower.h), GroupNorm is a single streaming pass in each direction:
+//   forward :  y = [silu](x*a + b)                      reads x, writes y            (4 B/elem in bf16)
+//   backward:  dx = du*P - K1 - xhat*K2 (+ dx_add)      reads du, x (, dx_add), writes dx
+//              and, from the same registers, dgamma = sum du*xhat, dbeta = sum du and the column
+//              sums of dx (= the bias gradient of the conv that produced x).
+// Work items are (sample, row chunk) pairs dealt round-robin to a persistent grid sized to the
+// machine (no tail wave); a thread owns 8 fixed channels, so per-channel coefficients live in
+// registers and are rebuilt only when the sample changes.  Needs C % 8 == 0, C / 8 <= 256.
+constexpr int GN1_THREADS = 256;
+
+struct Gn1Map {
+    int tpr, rpi, v, r;
+    bool active;
+};
+__device__ __forceinline__ Gn1Map gn1_map(int C) {
+    Gn1Map m;
+    m.tpr = C / 8;
+    m.rpi = GN1_THREADS / m.tpr;
+    m.v = threadIdx.x % m.tpr;
+    m.r = threadIdx.x / m.tpr;
+    m.active = m.r < m.rpi;
+    return m;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(GN1_THREADS, 3)
+gn_apply_pre_kernel(const T* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    T* __restrict__ y, const float* __restrict__ sums, float* __restrict__ stats, int B, int HW, int C,
+                    int G, int chunks, int rows_per, float eps, int silu) {
+    const Gn1Map m = gn1_map(C);
+    if (!m.active) return;
+    const int cpg = C / G;
+    const float inv_cnt = 1.f / ((float)HW * (float)cpg);
+    const int items = B * chunks;
+    const int c0 = m.v * 8;
+    float a[8], b[8];
+    int last_n = -1;
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int n = item / chunks, ch = item - n * chunks;
+        if (n != last_n) {
+            last_n = n;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int c = c0 + j, g = c / cpg;
+                const float2 sq = __ldg(reinterpret_cast<const float2*>(sums) + (long long)n * G + g);
+                const float mu = sq.x * inv_cnt;
+                float var = sq.y * inv_cnt - mu * mu;
+                if (var < 0.f) var = 0.f;
+                const float rs = rsqrtf(var + eps);
+                a[j] = rs * __ldg(gamma + c);
+                b[j] = __ldg(beta + c) - mu * a[j];
+                if (ch == 0 && m.r == 0 && c == g * cpg)
+                    *reinterpret_cast<float2*>(stats + ((long long)n * G + g) * 2) = make_float2(mu, rs);
+            }
+        }
+        const int p0 = ch * rows_per;
+        int p1 = p0 + rows_per;
+        if (p1 > HW) p1 = HW;
+        const T* xn = x + ((long long)n * HW) * C + c0;
+        T* yn = y + ((long long)n * HW) * C + c0;
+        int p = p0 + m.r;
+        for (; p + 3 * m.rpi < p1; p += 4 * m.rpi) {
+            Vec8<T> raw[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) raw[u].load(xn + (long long)(p + u * m.rpi) * C);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                float f[8];
+                raw[u].unpack(f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float t = fmaf(f[j], a[j], b[j]);
+                    f[j] = silu ? t * sigmoid_t<T>(t) : t;
+                }
+                raw[u].pack(f);
+                raw[u].store(yn + (long long)(p + u * m.rpi) * C);
+            }
+        }
+        for (; p < p1; p += m.rpi) {
+            Vec8<T> raw;
+            raw.load(xn + (long long)p * C);
+            float f[8];
+            raw.unpack(f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float t = fmaf(f[j], a[j], b[j]);
+                f[j] = silu ? t * sigmoid_t<T>(t) : t;
+            }
+            raw.pack(f);
+            raw.store(yn + (long long)p * C);
+        }
+    }
+}
+
+// GPV = groups per 8-channel vector (1: C/G % 8 == 0;  2: C/G == 4;  4: C/G == 2)
+template <typename T, int GPV>
+__global__ void __launch_bounds__(GN1_THREADS, 2)
+gn_bwd_pre_kernel(const T* __restrict__ du, const T* __restrict__ x, const float* __restrict__ gamma,
+                  const float* __restrict__ stats, const float* __restrict__ s12, const T* __restrict__ dx_add,
+                  T* __restrict__ dx, float* __restrict__ chan_scratch, int B, int HW, int C, int G, int chunks,
+                  int rows_per) {
+    extern __shared__ float part[];   // [rpi][3][C]
+    const Gn1Map m = gn1_map(C);
+    const int cpg = C / G;
+    constexpr int CPV = 8 / GPV;      // channels of one group inside the vector
+    const float inv_cnt = 1.f / ((float)HW * (float)cpg);
+    const int items = B * chunks;
+    const int c0 = m.v * 8;
+    float dg[8], db[8], cs[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dg[j] = 0.f; db[j] = 0.f; cs[j] = 0.f; }
+    if (m.active) {
+        float ga[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ga[j] = __ldg(gamma + c0 + j);
+        float P[8], R[GPV], M[GPV], K1[GPV], K2[GPV];
+        int last_n = -1;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            const int n = item / chunks, ch = item - n * chunks;
+            if (n != last_n) {
+                last_n = n;
+#pragma unroll
+                for (int q = 0; q < GPV; ++q) {
+                    const int g = (c0 + q * CPV) / cpg;
+                    const float2 mr = __ldg(reinterpret_cast<const float2*>(stats) + (long long)n * G + g);
+                    const float2 ss = __ldg(reinterpret_cast<const float2*>(s12) + (long long)n * G + g);
+                    R[q] = mr.y; M[q] = -mr.x * mr.y;
+                    K1[q] = mr.y * ss.x * inv_cnt; K2[q] = mr.y * ss.y * inv_cnt;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) P[j] = R[j / CPV] * ga[j];
+            }
+            const int p0 = ch * rows_per;
+            int p1 = p0 + rows_per;
+            if (p1 > HW) p1 = HW;
+            const long long base = ((long long)n * HW) * C + c0;
+            auto one = [&](const Vec8<T>& rx, const Vec8<T>& rd, const Vec8<T>& ra, long long off) {
+                float fx[8], fd[8], fa[8];
+                rx.unpack(fx); rd.unpack(fd);
+                if (dx_add) ra.unpack(fa);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int q = j / CPV;
+                    const float xh = fmaf(fx[j], R[q], M[q]);
+                    dg[j] = fmaf(fd[j], xh, dg[j]);
+                    db[j] += fd[j];
+                    float r = fmaf(fd[j], P[j], -fmaf(xh, K2[q], K1[q]));
+                    if (dx_add) r += fa[j];
+                    cs[j] += r;
+                    fx[j] = r;
+                }
+                Vec8<T> o; o.pack(fx); o.store(dx + off);
+            };
+            int p = p0 + m.r;
+            for (; p + m.rpi < p1; p += 2 * m.rpi) {
+                Vec8<T> rx[2], rd[2], ra[2];
+                long long off[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    off[u] = base + (long long)(p + u * m.rpi) * C;
+                    rx[u].load(x + off[u]); rd[u].load(du + off[u]);
+                    if (dx_add) ra[u].load(dx_add + off[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u) one(rx[u], rd[u], ra[u], off[u]);
+            }
+            for (; p < p1; p += m.rpi) {
+                Vec8<T> rx, rd, ra;
+                const long long off = base + (long long)p * C;
+                rx.load(x + off); rd.load(du + off);
+                if (dx_add) ra.load(dx_add + off);
+                one(rx, rd, ra, off);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            part[(m.r * 3 + 0) * C + c0 + j] = dg[j];
+            part[(m.r * 3 + 1) * C + c0 + j] = db[j];
+            part[(m.r * 3 + 2) * C + c0 + j] = cs[j];
+        }
+    }
+    __syncthreads();
+    float* dst = chan_scratch + (long long)blockIdx.x * 3 * C;
+    for (int i = threadIdx.x; i < 3 * C; i += GN1_THREADS) {
+        float t = 0.f;
+        for (int r = 0; r < m.rpi; ++r) t += part[r * 3 * C + i];
+        dst[i] = t;
+    }
+}
+
+// out[col] = sum over rows of chan[row][col]; 32 columns x 8 row lanes per CTA, fixed order
+__global__ void __launch_bounds__(256) gn_cols_reduce_kernel(const float* __restrict__ chan, float* __restrict__ out,
+                                                             int rows, int ncols) {
+    __shared__ float sh[8][33];
+    const int col = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int lane = threadIdx.x >> 5;
+    float acc = 0.f;
+    if (col < ncols)
+        for (int r = lane; r < rows; r += 8) acc += chan[(long long)r * ncols + col];
+    sh[lane][threadIdx.x & 31] = acc;
+    __syncthreads();
+    if (lane == 0 && col < ncols) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x];
+        out[col] = t;
+    }
+}
+
+static int gn1_sms() {
+    static int n = 0;
+    if (!n) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+// (sample, row chunk) items of ~elems elements; rows per chunk a multiple of rows-per-iteration
+static void gn1_items(int HW, int C, long long elems, int& chunks, int& rows_per) {
+    const int rpi = GN1_THREADS / (C / 8);
+    long long rows = elems / C;
+    if (rows < 4LL * rpi) rows = 4LL * rpi;
+    if (rows > HW) rows = HW;
+    chunks = (int)((HW + rows - 1) / rows);
+    rows_per = (HW + chunks - 1) / chunks;
+    rows_per = (rows_per + rpi - 1) / rpi * rpi;
+    chunks = (HW + rows_per - 1) / rows_per;
+}
+bool gn_pre_ok(int C, int G) {
+    if (G < 1 || G > MAX_G || C % G != 0 || C % 8 != 0 || C / 8 > GN1_THREADS || GN1_THREADS % (C / 8) != 0) return false;
+    const int cpg = C / G;
+    return cpg % 8 == 0 || cpg == 4 || cpg == 2;
+}
+int gn_bwd_pre_grid(int B, int HW, int C) {
+    int chunks, rows_per;
+    gn1_items(HW, C, 32768, chunks, rows_per);
+    long long items = (long long)B * chunks;
+    long long grid = 2LL * gn1_sms();
+    return (int)(items < grid ? items : grid);
+}
+
+int gn_apply_pre(const void* x, const float* gamma, const float* beta, void* y, const float* sums, float* stats, int B,
+                 int HW, int C, int G, float eps, int silu, int dtype, cudaStream_t st) {
+    MVAE_CHECK(gn_pre_ok(C, G), "groupnorm_apply_fwd: unsupported C=%d G=%d", C, G);
+    int chunks, rows_per;
+    gn1_items(HW, C, 32768, chunks, rows_per);
+    long long items = (long long)B * chunks;
+    long long grid = 3LL * gn1_sms();
+    if (items < grid) grid = items;
+    if (dtype == MVAE_F32)
+        gn_apply_pre_kernel<float><<<(unsigned)grid, GN1_THREADS, 0, st>>>((const float*)x, gamma, beta, (float*)y, sums,
+                                                                            stats, B, HW, C, G, chunks, rows_per, eps, silu);
+    else
+        gn_apply_pre_kernel<bf16><<<(unsigned)grid, GN1_THREADS, 0, st>>>((const bf16*)x, gamma, beta, (bf16*)y, sums,
+                                                                           stats, B, HW, C, G, chunks, rows_per, eps, silu);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+template <typename T>
+static int gn_bwd_pre_t(const T* du, const T* x, const float* gamma, const float* stats, const float* s12,
+                        const T* dx_add, T* dx, float* out3, float* scratch, int B, int HW, int C, int G,
+                        cudaStream_t st) {
+    int chunks, rows_per;
+    gn1_items(HW, C, 32768, chunks, rows_per);
+    const int grid = gn_bwd_pre_grid(B, HW, C);
+    const int rpi = GN1_THREADS / (C / 8);
+    const size_t sh = sizeof(float) * (size_t)rpi * 3 * C;
+    const int cpg = C / G;
+    if (cpg % 8 == 0)
+        gn_bwd_pre_kernel<T, 1><<<grid, GN1_THREADS, sh, st>>>(du, x, gamma, stats, s12, dx_add, dx, scratch, B, HW, C, G,
+                                                               chunks, rows_per);
+    else if (cpg == 4)
+        gn_bwd_pre_kernel<T, 2><<<grid, GN1_THREADS, sh, st>>>(du, x, gamma, stats, s12, dx_add, dx, scratch, B, HW, C, G,
+                                                               chunks, rows_per);
+    else
+        gn_bwd_pre_kernel<T, 4><<<grid, GN1_THREADS, sh, st>>>(du, x, gamma, stats, s12, dx_add, dx, scratch, B, HW, C, G,
+                                                               chunks, rows_per);
+    MVAE_LAUNCH_CHECK();
+    gn_cols_reduce_kernel<<<(3 * C + 31) / 32, 256, 0, st>>>(scratch, out3, grid, 3 * C);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+// out3: [3][C] fp32 = dgamma, dbeta, column sums of dx.  scratch: gn_bwd_pre_grid() * 3 * C floats.
+int gn_bwd_pre(const void* du, const void* x, const float* gamma, const float* stats, const float* s12,
+               const void* dx_add, void* dx, float* out3, float* scratch, int B, int HW, int C, int G, int dtype,
+               cudaStream_t st) {
+    MVAE_CHECK(gn_pre_ok(C, G), "groupnorm_apply_bwd: unsupported C=%d G=%d", C, G);
+    if (dtype == MVAE_F32)
+        return gn_bwd_pre_t<float>((const float*)du, (const float*)x, gamma, stats, s12, (const float*)dx_add, (float*)dx,
+                                   out3, scratch, B, HW, C, G, st);
+    return gn_bwd_pre_t<bf16>((const bf16*)du, (const bf16*)x, gamma, stats, s12, (const bf16*)dx_add, (bf16*)dx, out3,
+                              scratch, B, HW, C, G, st);
+}
+
 // dynamic shared memory of the stats kernels: [rows per iteration][C][vals] floats
 template <int VEC>
 static size_t gn_part_bytes(int C, int vals) {

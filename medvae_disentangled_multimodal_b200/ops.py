@@ -67,6 +67,60 @@ def conv_fprop(d: ConvDesc, x, wf, bias, residual, out=None):
     return y
 
 
+def conv_fuses_gn(d: ConvDesc, groups: int, direction: int) -> bool:
+    """can this conv carry the GroupNorm hook in its epilogue (direction 0: fprop / output channels,
+    1: dgrad / input channels)?"""
+    return bool(lib().mvae_conv2d_fuses_gn(C.byref(d), int(groups), int(direction)))
+
+
+def conv_fprop_gn(d: ConvDesc, x, wf, bias, residual, groups: int):
+    """fprop that also returns the per-(sample, group) (sum, sum of squares) of its output."""
+    oh, ow = conv_out_hw(d)
+    y = torch.empty((d.batch, oh, ow, d.out_c), dtype=x.dtype, device=x.device)
+    sums = torch.empty((d.batch, groups, 2), dtype=torch.float32, device=x.device)
+    with P.region("conv_fprop_umma", conv_flops(d) if P.active() else 0.0, (x.numel() + y.numel()) * x.element_size()):
+        check(lib().mvae_conv2d_fprop_gn(C.byref(d), ptr(x), ptr(wf), ptr(bias), ptr(residual), ptr(y), ptr(sums),
+                                         int(groups), stream()), "conv2d_fprop_gn")
+    return y, sums
+
+
+def conv_dgrad_gn(d: ConvDesc, dy, wd, gn_x, stats, gamma, beta, groups: int, silu: bool):
+    """dgrad whose epilogue applies the SiLU / affine part of the GroupNorm backward:
+    -> (du, s12) with s12[n][g] = (sum du*gamma, sum du*gamma*xhat)."""
+    du = torch.empty((d.batch, d.in_h, d.in_w, d.in_c), dtype=dy.dtype, device=dy.device)
+    s12 = torch.empty((d.batch, groups, 2), dtype=torch.float32, device=dy.device)
+    with P.region("conv_dgrad_umma", conv_flops(d) if P.active() else 0.0,
+                  (dy.numel() + 2 * du.numel()) * dy.element_size()):
+        check(lib().mvae_conv2d_dgrad_gn(C.byref(d), ptr(dy), ptr(wd), ptr(du), ptr(gn_x), ptr(stats), ptr(gamma),
+                                         ptr(beta), int(groups), int(silu), ptr(s12), stream()), "conv2d_dgrad_gn")
+    return du, s12
+
+
+def gn_apply_fwd(x, gamma, beta, sums, groups, eps, silu):
+    """one-pass GroupNorm(+SiLU) from precomputed sums -> (y, stats)"""
+    b, h, w, c = x.shape
+    y = torch.empty_like(x)
+    stats = torch.empty((b, groups, 2), dtype=torch.float32, device=x.device)
+    with P.region("groupnorm_fwd", 0.0, 2 * x.numel() * x.element_size()):
+        check(lib().mvae_groupnorm_apply_fwd(ptr(x), ptr(gamma), ptr(beta), ptr(y), ptr(sums), ptr(stats), b, h * w, c,
+                                             groups, eps, int(silu), L.code_of(x.dtype), stream()),
+              "groupnorm_apply_fwd")
+    return y, stats
+
+
+def gn_apply_bwd(du, x, gamma, stats, s12, dx_add, groups):
+    """one-pass GroupNorm backward from du and the group sums -> (dx, dgamma, dbeta, colsum(dx))"""
+    b, h, w, c = x.shape
+    dx = torch.empty_like(x)
+    out3 = torch.empty((3, c), dtype=torch.float32, device=x.device)
+    sc = scratch("gn1", 4 * lib().mvae_groupnorm_apply_bwd_scratch_floats(b, h * w, c), x.device)
+    with P.region("groupnorm_bwd", 0.0, (3 + (dx_add is not None)) * x.numel() * x.element_size()):
+        check(lib().mvae_groupnorm_apply_bwd(ptr(du), ptr(x), ptr(gamma), ptr(stats), ptr(s12), ptr(dx_add), ptr(dx),
+                                             ptr(out3), ptr(sc), b, h * w, c, groups, L.code_of(x.dtype), stream()),
+              "groupnorm_apply_bwd")
+    return dx, out3[0], out3[1], out3[2]
+
+
 def conv_dgrad(d: ConvDesc, dy, wd):
     dx = torch.empty((d.batch, d.in_h, d.in_w, d.in_c), dtype=dy.dtype, device=dy.device)
     kind = "conv_dgrad"

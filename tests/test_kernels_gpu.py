@@ -282,3 +282,100 @@ def test_layout_roundtrip_and_kl():
     coef = torch.tensor(0.37, device=DEV)
     dm, dl = ops.kl_bwd(mu, lv, coef)
     assert rel_err(dm, 0.37 * mu) < 1e-6 and rel_err(dl, 0.37 * 0.5 * (lv.exp() - 1)) < 1e-5
+
+
+# ------------------------------------------------------------------ GroupNorm fused into the convs
+# (B, H, W, Cin, Cout, k, mode, groups): the GroupNorm normalises the conv OUTPUT (fprop hook) /
+# the conv INPUT (dgrad hook).  Covers 4 / 8 / 16 / 32 channels per group, warps that span several
+# images (7x7, 4x4), every conv geometry, and N tiles of 64 / 128 / 256.
+GN_FUSE_CASES = [
+    (3, 16, 16, 128, 128, 3, 0, 32), (2, 32, 32, 64, 128, 3, 0, 32), (2, 8, 8, 256, 256, 1, 0, 32),
+    (3, 8, 8, 512, 512, 3, 0, 32), (2, 4, 4, 1024, 1024, 1, 0, 32), (5, 7, 7, 512, 512, 3, 0, 32),
+    (2, 14, 14, 256, 256, 3, 0, 32), (4, 4, 4, 128, 128, 3, 0, 32), (2, 64, 64, 128, 128, 3, 0, 32),
+    (2, 32, 32, 128, 128, 3, 1, 32), (2, 16, 16, 256, 256, 3, 2, 32), (2, 16, 16, 64, 64, 3, 0, 16),
+]
+
+
+@pytest.mark.umma
+@pytest.mark.parametrize("case", GN_FUSE_CASES)
+def test_conv_fprop_gn_statistics(case):
+    """fprop with the statistics hook: same y as the plain fprop (bit for bit), sums == per-(sample,
+    group) sum / sum of squares of y; the one-pass apply kernel matches the two-pass GroupNorm."""
+    L, ops = _mods()
+    B, H, W, Cin, Cout, k, mode, G = case
+    g = torch.Generator().manual_seed(3)
+    d = ops.conv_desc(B, H, W, Cin, Cout, k, mode, L.BF16, L.ENGINE_AUTO)
+    assert ops.conv_fuses_gn(d, G, 0)
+    x = torch.randn(B, H, W, Cin, generator=g).to(DEV, torch.bfloat16)
+    w = (torch.randn(Cout, Cin, k, k, generator=g) / math.sqrt(Cin * k * k)).to(DEV)
+    b = torch.randn(Cout, generator=g).to(DEV)
+    ns = ops.conv_num_slabs(d)
+    wf = torch.empty(ns, Cout, Cin, dtype=torch.bfloat16, device=DEV)
+    ops.conv_pack_weights(d, w, wf, None, Cout, 0)
+    oh, ow = ops.conv_out_hw(d)
+    res = torch.randn(B, oh, ow, Cout, generator=g).to(DEV, torch.bfloat16)
+    y0 = ops.conv_fprop(d, x, wf, b, res)
+    y1, sums = ops.conv_fprop_gn(d, x, wf, b, res, G)
+    torch.cuda.synchronize()
+    assert torch.equal(y0, y1)
+    yg = y1.double().view(B, oh * ow, G, Cout // G)
+    ref = torch.stack([yg.sum(dim=(1, 3)), (yg * yg).sum(dim=(1, 3))], dim=-1)
+    assert rel_err(sums, ref) < 1e-5
+    gamma = (1 + 0.3 * torch.randn(Cout, generator=g)).to(DEV)
+    beta = (0.2 * torch.randn(Cout, generator=g)).to(DEV)
+    for silu in (True, False):
+        a0, st0 = ops.gn_fwd(y1, gamma, beta, G, 1e-6, silu)
+        a1, st1 = ops.gn_apply_fwd(y1, gamma, beta, sums, G, 1e-6, silu)
+        torch.cuda.synchronize()
+        assert rel_err(st1, st0) < 1e-4
+        assert rel_err(a1, a0) < 5e-3
+
+
+@pytest.mark.umma
+@pytest.mark.parametrize("case", [c for c in GN_FUSE_CASES if c[6] == 0 and c[3] // c[7] >= 4])
+@pytest.mark.parametrize("silu", [True, False])
+@pytest.mark.parametrize("with_add", [True, False])
+def test_conv_dgrad_gn_backward(case, silu, with_add):
+    """dgrad with the GroupNorm-backward hook + the one-pass apply kernel against (a) the plain dgrad
+    followed by the two-pass GroupNorm backward and (b) torch autograd in fp64."""
+    L, ops = _mods()
+    B, H, W, Cin, Cout, k, mode, G = case
+    g = torch.Generator().manual_seed(4)
+    d = ops.conv_desc(B, H, W, Cin, Cout, k, mode, L.BF16, L.ENGINE_AUTO)
+    assert ops.conv_fuses_gn(d, G, 1)
+    # x -> GN(+SiLU) -> a -> conv -> y ; given dy
+    x = (torch.randn(B, Cin, H, W, generator=g, dtype=torch.float64) * 1.3 + 0.4).bfloat16().double().requires_grad_(True)
+    gamma = (1 + 0.3 * torch.randn(Cin, generator=g, dtype=torch.float64)).requires_grad_(True)
+    beta = (0.2 * torch.randn(Cin, generator=g, dtype=torch.float64)).requires_grad_(True)
+    w = (torch.randn(Cout, Cin, k, k, generator=g, dtype=torch.float64) / math.sqrt(Cin * k * k)).bfloat16().double()
+    a_ref = F.group_norm(x, G, gamma, beta, eps=1e-6)
+    if silu:
+        a_ref = a_ref * torch.sigmoid(a_ref)
+    y_ref = ref_conv(a_ref, w, None, mode)
+    dy = torch.randn(y_ref.shape, generator=g, dtype=torch.float64).bfloat16().double()
+    add = torch.randn(x.shape, generator=g, dtype=torch.float64).bfloat16().double()
+    y_ref.backward(dy)
+    dx_ref = x.grad + (add if with_add else 0.0)
+
+    ns = ops.conv_num_slabs(d)
+    wd = torch.empty(ns, Cin, Cout, dtype=torch.bfloat16, device=DEV)
+    ops.conv_pack_weights(d, w.float().to(DEV), None, wd, Cout, 0)
+    xg = nhwc(x.detach().float(), torch.bfloat16)
+    gam, bet = gamma.detach().float().to(DEV), beta.detach().float().to(DEV)
+    _a, stats = ops.gn_fwd(xg, gam, bet, G, 1e-6, silu)
+    dyg = nhwc(dy.float(), torch.bfloat16)
+    addg = nhwc(add.float(), torch.bfloat16) if with_add else None
+    # two-pass path
+    da = ops.conv_dgrad(d, dyg, wd)
+    dx0, dg0, db0 = ops.gn_bwd(da, xg, gam, bet, stats, addg, G, silu)
+    # fused path
+    du, s12 = ops.conv_dgrad_gn(d, dyg, wd, xg, stats, gam, bet, G, silu)
+    dx1, dg1, db1, cs1 = ops.gn_apply_bwd(du, xg, gam, stats, s12, addg, G)
+    torch.cuda.synchronize()
+    assert rel_err(nchw(dx1), dx_ref) < 1.5e-2, "dx vs autograd"
+    assert rel_err(dx1, dx0) < 1.5e-2, "dx vs two-pass"
+    assert rel_err(dg1.double().cpu(), gamma.grad) < 5e-2
+    assert rel_err(db1.double().cpu(), beta.grad) < 5e-2
+    assert rel_err(dg1, dg0) < 2e-2 and rel_err(db1, db0) < 2e-2
+    cs_ref = dx1.double().sum(dim=(0, 1, 2))
+    assert float((cs1.double() - cs_ref).abs().max()) <= 2e-2 * float(cs_ref.abs().max()) + 1e-3

@@ -171,7 +171,9 @@ def test_api_surface_and_shapes():
     m2, lv2 = model.encode(x)
     z2 = model.reparameterize(m2, lv2, eps=eps)
     assert rel_err(m2, out2["mean"]) < 1e-6 and rel_err(z2, out2["z"]) < 1e-5
-    assert rel_err(model.decode(z2), out2["reconstruction"]) < 1e-6
+    # bf16 mode accumulates the fused GroupNorm statistics with fp32 atomics: two runs agree to bf16
+    # rounding, not bit for bit (MVAE_GN_FUSE=0 restores the bitwise-reproducible two-pass kernels)
+    assert rel_err(model.decode(z2), out2["reconstruction"]) < 2e-2
 
 
 def test_foreign_loss_through_distributions():
