@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(256) reparam_kl_fwd_kernel(const T* __restrict
         }
         float ep = eps_in ? eps_in[e] : philox_normal(seed, offset, (uint64_t)e);
         if (eps_out) eps_out[e] = ep;
-        float sd = __expf(0.5f * lv);
+        float sd = expf(0.5f * lv);
         float zz = fmaf(ep, sd, mu);
         mean[e] = mu; logvar[e] = lv; z_nchw[e] = zz;
         if (stdv) stdv[e] = sd;
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(256) reparam_kl_bwd_kernel(const float* __rest
         float dz = d_z ? d_z[e] : 0.f;
         float gm = (d_mean ? d_mean[e] : 0.f) + dz;
         float lv = logvar[e];
-        float gl = (d_logvar ? d_logvar[e] : 0.f) + dz * eps[e] * 0.5f * __expf(0.5f * lv);
+        float gl = (d_logvar ? d_logvar[e] : 0.f) + dz * eps[e] * 0.5f * expf(0.5f * lv);
         long long o = ((long long)n * RR + p) * (2 * zc);
         if (clampv > 0.f) {
             float mu_raw = to_f<T>(mom[o + c]), lv_raw = to_f<T>(mom[o + zc + c]);
