@@ -231,6 +231,44 @@ int mvae_dis_input_bwd(const void* d_in, const float* x_nchw, const int64_t* idx
                        int32_t xc, int32_t h, int32_t w, int32_t n_mod, int32_t out_c,
                        int32_t dtype, void* stream);
 
+/* DisentangledConditionalVAE.decode per-modality heads (disentangled_conditional_vae.py:241-303):
+ * modality_decoders[m] = Conv2d(3,3,3,1,1) -> ReLU -> Conv2d(3,3,3,1,1), then for 1-channel modalities
+ * modality_output_projectors[m] = Conv2d(3,1,1), zero-padded to out_c channels (1 if the whole batch
+ * is gray, else 3).  r_nhwc: decoder output [B,H,W,r_channels] (dtype; first 3 channels used).
+ * Stacked parameters: w1,w2 [n_mod][3][3][3][3]; b1,b2 [n_mod][3]; proj_w [n_mod][3]; proj_b [n_mod].
+ * hid, y: fp32 [B,H,W,3] kept for the backward.  out: NCHW fp32 [B,out_c,H,W]. */
+int mvae_dis_head_fwd(const void* r_nhwc, int32_t r_channels, const int64_t* idx, const float* w1,
+                      const float* b1, const float* w2, const float* b2, const float* proj_w,
+                      const float* proj_b, const int32_t* is_gray, float* hid, float* y, float* out_nchw,
+                      int32_t batch, int32_t h, int32_t w, int32_t n_mod, int32_t out_c, int32_t dtype,
+                      void* stream);
+/* grads: fp32 [n_mod][172] = (dw1 81, db1 3, dw2 81, db2 3, dproj_w 3, dproj_b 1), overwritten.
+ * d_r_nhwc: channels 0..2 are written (caller zero-fills the tile padding).  scratch: 6*B*H*W floats. */
+int mvae_dis_head_bwd(const float* d_out_nchw, const void* r_nhwc, int32_t r_channels, const float* hid,
+                      const float* y, const int64_t* idx, const float* w1, const float* w2,
+                      const float* proj_w, const int32_t* is_gray, void* d_r_nhwc, float* grads,
+                      float* scratch, int32_t batch, int32_t h, int32_t w, int32_t n_mod, int32_t out_c,
+                      int32_t dtype, void* stream);
+
+/* modality_separation_loss + contrastive_loss (:305-386) on z_flat fp32 [B][flat_dim] (the NCHW latent
+ * flattened as partition_latent does, :195-206): z_modality = z_flat[:, shared : shared+modality_dim].
+ * aux: fp32 workspace of mvae_dis_aux_floats() elements; afterwards aux[0] = separation loss,
+ * aux[1] = contrastive loss (the rest is kept for the backward).  Backward: g_*_dev are device
+ * scalars (NULL = 0); dz_flat columns [shared, shared+modality_dim) are written. */
+int64_t mvae_dis_aux_floats(int32_t batch, int32_t modality_dim, int32_t n_mod);
+int mvae_dis_aux_loss_fwd(const float* z_flat, const int64_t* idx, float* aux, int32_t batch,
+                          int64_t flat_dim, int32_t shared_dim, int32_t modality_dim, int32_t n_mod,
+                          float temperature, void* stream);
+int mvae_dis_aux_loss_bwd(const float* z_flat, const int64_t* idx, const float* aux, const float* g_sep_dev,
+                          const float* g_con_dev, float* dz_flat, int32_t batch, int64_t flat_dim,
+                          int32_t shared_dim, int32_t modality_dim, int32_t n_mod, float temperature,
+                          void* stream);
+/* DisentangledVAELoss total with its NaN/Inf guards (:527-565) from four device scalars: out5 =
+ * (total, recon, kl, separation, contrastive) after the guards; mask4[i] = 1 where gradient flows. */
+int mvae_dis_loss_total(const float* recon, const float* kl, const float* sep, const float* con,
+                        float w_recon, float w_kl, float w_sep, float w_con, float* out5, float* mask4,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -79,6 +79,14 @@ SIGNATURES = {
                                        _i32, _vp]),
     "mvae_dis_input_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_dis_input_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "mvae_dis_head_fwd": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32,
+                                    _i32, _i32, _vp]),
+    "mvae_dis_head_bwd": (C.c_int, [_vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32,
+                                    _i32, _i32, _vp]),
+    "mvae_dis_aux_floats": (C.c_int64, [_i32, _i32, _i32]),
+    "mvae_dis_aux_loss_fwd": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i32, _i32, _i32, _f32, _vp]),
+    "mvae_dis_aux_loss_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _i32, _f32, _vp]),
+    "mvae_dis_loss_total": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _vp, _vp, _vp]),
 }
 
 

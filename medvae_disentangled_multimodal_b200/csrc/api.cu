@@ -35,6 +35,19 @@ int dis_input_fwd(const float* x, const long long* idx, const float* pw, const f
                   int B, int xc, int HW, int n_mod, int out_c, int dtype, cudaStream_t st);
 int dis_input_bwd(const void* d_in, const float* x, const long long* idx, const int* is_gray, float* dpw, float* dpb,
                   int B, int xc, int HW, int n_mod, int out_c, int dtype, cudaStream_t st);
+int dis_head_fwd(const void* r, int r_stride, const long long* idx, const float* w1, const float* b1, const float* w2,
+                 const float* b2, const float* pw, const float* pb, const int* is_gray, float* hid, float* y, float* out,
+                 int B, int H, int W, int n_mod, int out_c, int dtype, cudaStream_t st);
+int dis_head_bwd(const float* d_out, const void* r, int r_stride, const float* hid, const float* y, const long long* idx,
+                 const float* w1, const float* w2, const float* pw, const int* is_gray, void* d_r, float* gflat,
+                 float* scratch, int B, int H, int W, int n_mod, int out_c, int dtype, cudaStream_t st);
+long long dis_aux_floats(int B, int m, int n_mod);
+int dis_aux_fwd(const float* z, const long long* idx, float* aux, int B, long long D, int s0, int m, int n_mod, float tau,
+                cudaStream_t st);
+int dis_aux_bwd(const float* z, const long long* idx, const float* aux, const float* g_sep, const float* g_con, float* dz,
+                int B, long long D, int s0, int m, int n_mod, float tau, cudaStream_t st);
+int dis_total(const float* t0, const float* t1, const float* t2, const float* t3, float w0, float w1, float w2, float w3,
+              float* out, float* mask, cudaStream_t st);
 int gn_splits(int B, int HW, int C);
 long long gn_scratch_floats(int B, int HW, int C, int G, int backward);
 int gn_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, float* scratch, int B, int HW,
@@ -394,6 +407,48 @@ int mvae_dis_input_bwd(const void* d_in, const float* x, const int64_t* idx, con
     MVAE_CHECK(d_in && x && idx && is_gray && dpw && dpb && dtype_ok(dtype), "dis_input_bwd: bad argument");
     return dis_input_bwd(d_in, x, reinterpret_cast<const long long*>(idx), is_gray, dpw, dpb, batch, xc, h * w, n_mod,
                          out_c, dtype, ST(stream));
+}
+
+int mvae_dis_head_fwd(const void* r_nhwc, int32_t r_channels, const int64_t* idx, const float* w1, const float* b1,
+                      const float* w2, const float* b2, const float* proj_w, const float* proj_b, const int32_t* is_gray,
+                      float* hid, float* y, float* out_nchw, int32_t batch, int32_t h, int32_t w, int32_t n_mod,
+                      int32_t out_c, int32_t dtype, void* stream) {
+    MVAE_CHECK(r_nhwc && idx && w1 && b1 && w2 && b2 && proj_w && proj_b && is_gray && hid && y && out_nchw &&
+                   dtype_ok(dtype) && r_channels >= 3 && out_c >= 1 && n_mod >= 1,
+               "dis_head_fwd: bad argument");
+    return dis_head_fwd(r_nhwc, r_channels, reinterpret_cast<const long long*>(idx), w1, b1, w2, b2, proj_w, proj_b,
+                        is_gray, hid, y, out_nchw, batch, h, w, n_mod, out_c, dtype, ST(stream));
+}
+int mvae_dis_head_bwd(const float* d_out_nchw, const void* r_nhwc, int32_t r_channels, const float* hid, const float* y,
+                      const int64_t* idx, const float* w1, const float* w2, const float* proj_w, const int32_t* is_gray,
+                      void* d_r_nhwc, float* grads, float* scratch, int32_t batch, int32_t h, int32_t w, int32_t n_mod,
+                      int32_t out_c, int32_t dtype, void* stream) {
+    MVAE_CHECK(d_out_nchw && r_nhwc && hid && y && idx && w1 && w2 && proj_w && is_gray && d_r_nhwc && grads && scratch &&
+                   dtype_ok(dtype) && r_channels >= 3,
+               "dis_head_bwd: bad argument");
+    return dis_head_bwd(d_out_nchw, r_nhwc, r_channels, hid, y, reinterpret_cast<const long long*>(idx), w1, w2, proj_w,
+                        is_gray, d_r_nhwc, grads, scratch, batch, h, w, n_mod, out_c, dtype, ST(stream));
+}
+int64_t mvae_dis_aux_floats(int32_t batch, int32_t modality_dim, int32_t n_mod) {
+    return dis_aux_floats(batch, modality_dim, n_mod);
+}
+int mvae_dis_aux_loss_fwd(const float* z_flat, const int64_t* idx, float* aux, int32_t batch, int64_t flat_dim,
+                          int32_t shared_dim, int32_t modality_dim, int32_t n_mod, float temperature, void* stream) {
+    MVAE_CHECK(z_flat && idx && aux && temperature > 0.f, "dis_aux_loss_fwd: bad argument");
+    return dis_aux_fwd(z_flat, reinterpret_cast<const long long*>(idx), aux, batch, flat_dim, shared_dim, modality_dim,
+                       n_mod, temperature, ST(stream));
+}
+int mvae_dis_aux_loss_bwd(const float* z_flat, const int64_t* idx, const float* aux, const float* g_sep_dev,
+                          const float* g_con_dev, float* dz_flat, int32_t batch, int64_t flat_dim, int32_t shared_dim,
+                          int32_t modality_dim, int32_t n_mod, float temperature, void* stream) {
+    MVAE_CHECK(z_flat && idx && aux && dz_flat && temperature > 0.f, "dis_aux_loss_bwd: bad argument");
+    return dis_aux_bwd(z_flat, reinterpret_cast<const long long*>(idx), aux, g_sep_dev, g_con_dev, dz_flat, batch, flat_dim,
+                       shared_dim, modality_dim, n_mod, temperature, ST(stream));
+}
+int mvae_dis_loss_total(const float* recon, const float* kl, const float* sep, const float* con, float w_recon, float w_kl,
+                        float w_sep, float w_con, float* out5, float* mask4, void* stream) {
+    MVAE_CHECK(recon && kl && sep && con && out5 && mask4, "dis_loss_total: bad argument");
+    return dis_total(recon, kl, sep, con, w_recon, w_kl, w_sep, w_con, out5, mask4, ST(stream));
 }
 
 }  // extern "C"

@@ -254,3 +254,255 @@ int dis_head_bwd(const float* d_out, const void* r, int r_stride, const float* h
     MVAE_LAUNCH_CHECK();
     return 0;
 }
+
+// ================================================================== auxiliary latent losses
+// zm[i][d] = z_flat[i][s0 + d], d < m  (partition_latent :195-206).  tau = contrastive temperature.
+// aux layout (fp32): [0] separation loss, [1] contrastive loss, [2] rows with a positive, [3] centroid
+// pairs; then inv_norm[B], pos[B], all[B], cents[n_mod][m], dcent[n_mod][m] (unit gradient of the
+// separation loss w.r.t. each centroid), count[n_mod].
+struct AuxLayout {
+    int B, m, n_mod;
+    __host__ __device__ long long inv() const { return 4; }
+    __host__ __device__ long long pos() const { return 4 + (long long)B; }
+    __host__ __device__ long long all() const { return 4 + 2LL * B; }
+    __host__ __device__ long long cents() const { return 4 + 3LL * B; }
+    __host__ __device__ long long dcent() const { return cents() + (long long)n_mod * m; }
+    __host__ __device__ long long count() const { return dcent() + (long long)n_mod * m; }
+    __host__ __device__ long long total() const { return count() + n_mod; }
+};
+
+__global__ void __launch_bounds__(128) aux_norm_kernel(const float* __restrict__ z, long long D, int s0, AuxLayout L,
+                                                       float* __restrict__ aux) {
+    __shared__ float sh[32];
+    const int i = blockIdx.x;
+    float a = 0.f;
+    for (int d = threadIdx.x; d < L.m; d += blockDim.x) {
+        const float v = z[(long long)i * D + s0 + d];
+        a = fmaf(v, v, a);
+    }
+    a = block_sum(a, sh);
+    if (threadIdx.x == 0) aux[L.inv() + i] = 1.f / fmaxf(sqrtf(a), 1e-12f);   // F.normalize eps
+}
+
+// row i: pos_i = sum_{j != i, same modality} exp(S_ij), all_i = sum_{j != i} exp(S_ij)
+__global__ void __launch_bounds__(128) aux_rows_kernel(const float* __restrict__ z, const long long* __restrict__ idx,
+                                                       long long D, int s0, float inv_tau, AuxLayout L,
+                                                       float* __restrict__ aux) {
+    extern __shared__ float zi[];   // [m] normalised row i
+    __shared__ float sh[32];
+    const int i = blockIdx.x;
+    const float inv_i = aux[L.inv() + i];
+    for (int d = threadIdx.x; d < L.m; d += blockDim.x) zi[d] = z[(long long)i * D + s0 + d] * inv_i;
+    __syncthreads();
+    const long long mi = idx[i];
+    float pos = 0.f, all = 0.f;
+    for (int j = threadIdx.x; j < L.B; j += blockDim.x) {
+        if (j == i) continue;
+        const float* zj = z + (long long)j * D + s0;
+        float dot = 0.f;
+        for (int d = 0; d < L.m; ++d) dot = fmaf(zi[d], zj[d], dot);
+        const float e = expf(dot * aux[L.inv() + j] * inv_tau);
+        all += e;
+        if (idx[j] == mi) pos += e;
+    }
+    pos = block_sum(pos, sh);
+    all = block_sum(all, sh);
+    if (threadIdx.x == 0) { aux[L.pos() + i] = pos; aux[L.all() + i] = all; }
+}
+
+// one CTA: centroids, pdist, both loss values, unit centroid gradients
+__global__ void __launch_bounds__(256) aux_final_kernel(const float* __restrict__ z, const long long* __restrict__ idx,
+                                                        long long D, int s0, AuxLayout L, float* __restrict__ aux) {
+    __shared__ float sh[32];
+    __shared__ float dist[128];   // pairwise distances (n_mod <= 16 -> 120 pairs)
+    float* cents = aux + L.cents();
+    float* dcent = aux + L.dcent();
+    float* count = aux + L.count();
+    for (int k = threadIdx.x; k < L.n_mod; k += blockDim.x) {
+        int c = 0;
+        for (int i = 0; i < L.B; ++i) c += (idx[i] == k);
+        count[k] = (float)c;
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < L.n_mod * L.m; t += blockDim.x) {
+        const int k = t / L.m, d = t % L.m;
+        float a = 0.f;
+        for (int i = 0; i < L.B; ++i)
+            if (idx[i] == k) a += z[(long long)i * D + s0 + d];
+        cents[t] = count[k] > 0.f ? a / count[k] : 0.f;
+        dcent[t] = 0.f;
+    }
+    __syncthreads();
+    // pairwise distances between PRESENT modalities (torch.unique order = ascending index)
+    int npairs = 0;
+    for (int a = 0; a < L.n_mod; ++a)
+        for (int b = a + 1; b < L.n_mod; ++b) {
+            if (count[a] > 0.f && count[b] > 0.f) {
+                float s = 0.f;
+                for (int d = threadIdx.x; d < L.m; d += blockDim.x) {
+                    const float df = cents[a * L.m + d] - cents[b * L.m + d];
+                    s = fmaf(df, df, s);
+                }
+                s = block_sum(s, sh);
+                if (threadIdx.x == 0) dist[npairs] = sqrtf(s);
+                ++npairs;
+            }
+        }
+    __syncthreads();
+    float sep = 0.f;
+    if (npairs > 0) {
+        for (int q = 0; q < npairs; ++q) sep += dist[q];
+        sep = -sep / (float)npairs;
+        int q = 0;
+        for (int a = 0; a < L.n_mod; ++a)
+            for (int b = a + 1; b < L.n_mod; ++b) {
+                if (count[a] > 0.f && count[b] > 0.f) {
+                    const float dd = dist[q++];
+                    if (dd > 0.f) {   // torch.pdist backward yields 0 at zero distance
+                        const float c = -1.f / ((float)npairs * dd);
+                        for (int d = threadIdx.x; d < L.m; d += blockDim.x) {
+                            const float df = cents[a * L.m + d] - cents[b * L.m + d];
+                            dcent[a * L.m + d] += c * df;
+                            dcent[b * L.m + d] -= c * df;
+                        }
+                    }
+                }
+            }
+    }
+    // contrastive: mean over rows with a positive of -log(pos/all + 1e-8)
+    float ls = 0.f, nv = 0.f;
+    for (int i = threadIdx.x; i < L.B; i += blockDim.x) {
+        const float p = aux[L.pos() + i];
+        if (p > 0.f) { ls += -logf(p / aux[L.all() + i] + 1e-8f); nv += 1.f; }
+    }
+    ls = block_sum(ls, sh);
+    nv = block_sum(nv, sh);
+    if (threadIdx.x == 0) {
+        aux[0] = sep;
+        aux[1] = nv > 0.f ? ls / nv : 0.f;
+        aux[2] = nv;
+        aux[3] = (float)npairs;
+    }
+}
+
+// dz[k][s0 + d] = g_sep * dcent[mod(k)][d] / count + (normalize backward of) sum_j w_kj zn_j[d]
+__global__ void __launch_bounds__(128) aux_bwd_kernel(const float* __restrict__ z, const long long* __restrict__ idx,
+                                                      long long D, int s0, float inv_tau, AuxLayout L,
+                                                      const float* __restrict__ aux, const float* __restrict__ g_sep,
+                                                      const float* __restrict__ g_con, float* __restrict__ dz) {
+    extern __shared__ float smem[];   // zk[m], w[B]
+    __shared__ float sh[32];
+    float* zk = smem;
+    float* w = smem + L.m;
+    const int k = blockIdx.x;
+    const float inv_k = aux[L.inv() + k];
+    for (int d = threadIdx.x; d < L.m; d += blockDim.x) zk[d] = z[(long long)k * D + s0 + d] * inv_k;
+    __syncthreads();
+    const long long mk = idx[k];
+    const float nv = aux[2];
+    const float gc = (g_con && nv > 0.f) ? (*g_con) / nv : 0.f;
+    const float pos_k = aux[L.pos() + k], all_k = aux[L.all() + k];
+    const float coef_k = pos_k > 0.f ? -gc / (pos_k / all_k + 1e-8f) : 0.f;
+    for (int j = threadIdx.x; j < L.B; j += blockDim.x) {
+        float wj = 0.f;
+        if (j != k && gc != 0.f) {
+            const float* zj = z + (long long)j * D + s0;
+            float dot = 0.f;
+            for (int d = 0; d < L.m; ++d) dot = fmaf(zk[d], zj[d], dot);
+            const float e = expf(dot * aux[L.inv() + j] * inv_tau);
+            const float same = (idx[j] == mk) ? 1.f : 0.f;
+            const float pos_j = aux[L.pos() + j], all_j = aux[L.all() + j];
+            const float coef_j = pos_j > 0.f ? -gc / (pos_j / all_j + 1e-8f) : 0.f;
+            const float a_kj = coef_k * (same / all_k - pos_k / (all_k * all_k));
+            const float a_jk = coef_j * (same / all_j - pos_j / (all_j * all_j));
+            wj = e * inv_tau * (a_kj + a_jk) * aux[L.inv() + j];   // inv_j folded in: zn_j = inv_j * z_j
+        }
+        w[j] = wj;
+    }
+    __syncthreads();
+    // dzn[d] for the dims this thread owns (m <= 4 * 128)
+    float dzn[4] = {0.f, 0.f, 0.f, 0.f};
+    float dotp = 0.f;
+    for (int q = 0; q < 4; ++q) {
+        const int d = threadIdx.x + q * blockDim.x;
+        if (d < L.m) {
+            float a = 0.f;
+            for (int j = 0; j < L.B; ++j) a = fmaf(w[j], z[(long long)j * D + s0 + d], a);
+            dzn[q] = a;
+            dotp = fmaf(a, zk[d], dotp);
+        }
+    }
+    dotp = block_sum(dotp, sh);
+    const int mc = clamp_mod(mk, L.n_mod);
+    const bool in_range = mk >= 0 && mk < L.n_mod;
+    const float gs = g_sep ? *g_sep : 0.f;
+    for (int q = 0; q < 4; ++q) {
+        const int d = threadIdx.x + q * blockDim.x;
+        if (d < L.m) {
+            float g = inv_k * (dzn[q] - zk[d] * dotp);
+            if (in_range && aux[L.count() + mc] > 0.f) g = fmaf(gs, aux[L.dcent() + mc * L.m + d] / aux[L.count() + mc], g);
+            dz[(long long)k * D + s0 + d] = g;
+        }
+    }
+}
+
+long long dis_aux_floats(int B, int m, int n_mod) {
+    AuxLayout L{B, m, n_mod};
+    return L.total();
+}
+
+// z: fp32 [B][D] (flattened NCHW latent); aux: dis_aux_floats() floats; aux[0] = separation loss,
+// aux[1] = contrastive loss afterwards
+int dis_aux_fwd(const float* z, const long long* idx, float* aux, int B, long long D, int s0, int m, int n_mod, float tau,
+                cudaStream_t st) {
+    MVAE_CHECK(m >= 1 && m <= 512 && s0 >= 0 && s0 + m <= D && n_mod >= 1 && n_mod <= 16 && B >= 1,
+               "dis_aux: unsupported sizes (m=%d, n_mod=%d)", m, n_mod);
+    AuxLayout L{B, m, n_mod};
+    aux_norm_kernel<<<B, 128, 0, st>>>(z, D, s0, L, aux);
+    MVAE_LAUNCH_CHECK();
+    aux_rows_kernel<<<B, 128, sizeof(float) * m, st>>>(z, idx, D, s0, 1.f / tau, L, aux);
+    MVAE_LAUNCH_CHECK();
+    aux_final_kernel<<<1, 256, 0, st>>>(z, idx, D, s0, L, aux);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+// dz: fp32 [B][D], columns [s0, s0+m) are written (caller zero-fills the rest)
+int dis_aux_bwd(const float* z, const long long* idx, const float* aux, const float* g_sep, const float* g_con, float* dz,
+                int B, long long D, int s0, int m, int n_mod, float tau, cudaStream_t st) {
+    MVAE_CHECK(m >= 1 && m <= 512 && n_mod <= 16, "dis_aux: unsupported sizes");
+    AuxLayout L{B, m, n_mod};
+    const size_t sh = sizeof(float) * ((size_t)m + B);
+    MVAE_CHECK(sh <= 48 * 1024, "dis_aux_bwd: batch %d too large for one CTA's shared memory", B);
+    aux_bwd_kernel<<<B, 128, sh, st>>>(z, idx, D, s0, 1.f / tau, L, aux, g_sep, g_con, dz);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// ================================================================== guarded total (:527-565)
+// terms[4] = recon, kl, separation, contrastive (device scalars, fp32); out[5] = total + the four terms
+// with NaN/Inf terms replaced by 0 and a NaN/Inf total by 1e6; mask[4] = 1 where the term (and the
+// total) was finite, i.e. where the gradient flows.
+__global__ void dis_total_kernel(const float* t0, const float* t1, const float* t2, const float* t3, float w0, float w1,
+                                 float w2, float w3, float* __restrict__ out, float* __restrict__ mask) {
+    const float w[4] = {w0, w1, w2, w3};
+    const float* terms[4] = {t0, t1, t2, t3};
+    float t[4], ok[4];
+    float total = 0.f;
+    for (int i = 0; i < 4; ++i) {
+        const float v = *terms[i];
+        ok[i] = isfinite(v) ? 1.f : 0.f;
+        t[i] = isfinite(v) ? v : 0.f;
+        total = fmaf(w[i], t[i], total);
+    }
+    const bool tok = isfinite(total);
+    out[0] = tok ? total : 1e6f;
+    for (int i = 0; i < 4; ++i) { out[1 + i] = t[i]; mask[i] = tok ? ok[i] : 0.f; }
+}
+int dis_total(const float* t0, const float* t1, const float* t2, const float* t3, float w0, float w1, float w2, float w3,
+              float* out, float* mask, cudaStream_t st) {
+    dis_total_kernel<<<1, 1, 0, st>>>(t0, t1, t2, t3, w0, w1, w2, w3, out, mask);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace mvae

@@ -64,7 +64,9 @@ __global__ void __launch_bounds__(256) reparam_kl_fwd_kernel(const T* __restrict
         float sd = expf(0.5f * lv);
         float zz = fmaf(ep, sd, mu);
         mean[e] = mu; logvar[e] = lv; z_nchw[e] = zz;
-        if (stdv) stdv[e] = sd;
+        // the disentangled model (the only clamping caller) also clamps std to [1e-6, 10] for its Normal
+        // objects (disentangled_conditional_vae.py:426-427); z above uses the unclamped std as the reference does
+        if (stdv) stdv[e] = clampv > 0.f ? fminf(fmaxf(sd, 1e-6f), 10.f) : sd;
         if (z_nhwc) z_nhwc[((long long)n * RR + p) * zc + c] = from_f<T>(zz);
         acc += 0.5 * ((double)(sd * sd) + (double)mu * mu - 1.0 - (double)lv);
     }

@@ -21,7 +21,7 @@ class _VAELossFn(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, recon, x, mean, logvar, kl_sum, kind: int, rw: float, kw: float):
+    def forward(ctx, recon, x, mean, logvar, kl_sum, kind: int, rw: float, kw: float, kl_denom=None):
         recon_c = recon.float().contiguous()
         x_c = x.float().contiguous()
         need_grad = ctx.needs_input_grad[0]
@@ -30,7 +30,9 @@ class _VAELossFn(torch.autograd.Function):
             kl_sum = ops.kl_sum(mean.float().contiguous(), logvar.float().contiguous())
         # scalar epilogue on two 0-d doubles (normalisation of the device-side sums)
         recon_loss = (rsum / recon_c.numel()).float()
-        kl_loss = (kl_sum / mean.numel()).float()
+        # VAELoss: mean over latent elements; DisentangledVAELoss: sum / targets.numel() (kl_denom)
+        ctx.kl_denom = float(mean.numel() if kl_denom is None else kl_denom)
+        kl_loss = (kl_sum / ctx.kl_denom).float()
         loss = rw * recon_loss + kw * kl_loss
         ctx.save_for_backward(d_unit, mean, logvar)
         ctx.rw, ctx.kw = rw, kw
@@ -46,10 +48,10 @@ class _VAELossFn(torch.autograd.Function):
             s = g_loss * ctx.rw + (g_recon.float() if g_recon is not None else 0.0)
             d_recon = ops.scale_by(d_unit, s.reshape(()).contiguous())
         if ctx.needs_input_grad[2] or ctx.needs_input_grad[3]:
-            coef = (g_loss * ctx.kw + (g_kl.float() if g_kl is not None else 0.0)) / mean.numel()
+            coef = (g_loss * ctx.kw + (g_kl.float() if g_kl is not None else 0.0)) / ctx.kl_denom
             d_mean, d_logvar = ops.kl_bwd(mean.float().contiguous(), logvar.float().contiguous(),
                                           coef.reshape(()).contiguous())
-        return d_recon, None, d_mean, d_logvar, None, None, None, None
+        return d_recon, None, d_mean, d_logvar, None, None, None, None, None
 
 
 class VAELoss(nn.Module):

@@ -275,3 +275,69 @@ def scale_by(t, scale_dev):
     out = torch.empty_like(t)
     check(lib().mvae_scale_by_device_scalar(ptr(t), ptr(scale_dev), ptr(out), t.numel(), stream()), "scale")
     return out
+
+
+# ------------------------------------------------------------------ disentangled model extras
+def dis_input_fwd(x_nchw, idx, pw, pb, is_gray, out_c, dtype):
+    b, xc, h, w = x_nchw.shape
+    out = torch.empty((b, h, w, out_c), dtype=dtype, device=x_nchw.device)
+    check(lib().mvae_dis_input_fwd(ptr(x_nchw), ptr(idx), ptr(pw), ptr(pb), ptr(is_gray), ptr(out), b, xc, h, w,
+                                   pw.shape[0], out_c, L.code_of(dtype), stream()), "dis_input_fwd")
+    return out
+
+
+def dis_input_bwd(d_in, x_nchw, idx, is_gray, n_mod):
+    b, xc, h, w = x_nchw.shape
+    dpw = torch.empty((n_mod, 3), dtype=torch.float32, device=x_nchw.device)
+    dpb = torch.empty((n_mod, 3), dtype=torch.float32, device=x_nchw.device)
+    check(lib().mvae_dis_input_bwd(ptr(d_in), ptr(x_nchw), ptr(idx), ptr(is_gray), ptr(dpw), ptr(dpb), b, xc, h, w, n_mod,
+                                   d_in.shape[-1], L.code_of(d_in.dtype), stream()), "dis_input_bwd")
+    return dpw, dpb
+
+
+def dis_head_fwd(r_nhwc, idx, w1, b1, w2, b2, pw, pb, is_gray, out_c):
+    b, h, w, rc = r_nhwc.shape
+    dev = r_nhwc.device
+    hid = torch.empty((b, h, w, 3), dtype=torch.float32, device=dev)
+    y = torch.empty((b, h, w, 3), dtype=torch.float32, device=dev)
+    out = torch.empty((b, out_c, h, w), dtype=torch.float32, device=dev)
+    check(lib().mvae_dis_head_fwd(ptr(r_nhwc), rc, ptr(idx), ptr(w1), ptr(b1), ptr(w2), ptr(b2), ptr(pw), ptr(pb),
+                                  ptr(is_gray), ptr(hid), ptr(y), ptr(out), b, h, w, w1.shape[0], out_c,
+                                  L.code_of(r_nhwc.dtype), stream()), "dis_head_fwd")
+    return out, hid, y
+
+
+def dis_head_bwd(d_out, r_nhwc, hid, y, idx, w1, w2, pw, is_gray):
+    b, h, w, rc = r_nhwc.shape
+    n_mod = w1.shape[0]
+    d_r = torch.zeros_like(r_nhwc)
+    grads = torch.empty((n_mod, 172), dtype=torch.float32, device=r_nhwc.device)
+    sc = scratch("dis_head", 4 * 6 * b * h * w, r_nhwc.device)
+    check(lib().mvae_dis_head_bwd(ptr(d_out), ptr(r_nhwc), rc, ptr(hid), ptr(y), ptr(idx), ptr(w1), ptr(w2), ptr(pw),
+                                  ptr(is_gray), ptr(d_r), ptr(grads), ptr(sc), b, h, w, n_mod, d_out.shape[1],
+                                  L.code_of(r_nhwc.dtype), stream()), "dis_head_bwd")
+    return d_r, grads
+
+
+def dis_aux_fwd(z_flat, idx, shared, modal, n_mod, tau):
+    b, d = z_flat.shape
+    aux = torch.empty((lib().mvae_dis_aux_floats(b, modal, n_mod),), dtype=torch.float32, device=z_flat.device)
+    check(lib().mvae_dis_aux_loss_fwd(ptr(z_flat), ptr(idx), ptr(aux), b, d, shared, modal, n_mod, float(tau), stream()),
+          "dis_aux_loss_fwd")
+    return aux
+
+
+def dis_aux_bwd(z_flat, idx, aux, g_sep, g_con, shared, modal, n_mod, tau):
+    b, d = z_flat.shape
+    dz = torch.zeros_like(z_flat)
+    check(lib().mvae_dis_aux_loss_bwd(ptr(z_flat), ptr(idx), ptr(aux), ptr(g_sep), ptr(g_con), ptr(dz), b, d, shared,
+                                      modal, n_mod, float(tau), stream()), "dis_aux_loss_bwd")
+    return dz
+
+
+def dis_total(recon, kl, sep, con, weights):
+    out5 = torch.empty((5,), dtype=torch.float32, device=recon.device)
+    mask4 = torch.empty((4,), dtype=torch.float32, device=recon.device)
+    check(lib().mvae_dis_loss_total(ptr(recon), ptr(kl), ptr(sep), ptr(con), *[float(w) for w in weights], ptr(out5),
+                                    ptr(mask4), stream()), "dis_loss_total")
+    return out5, mask4

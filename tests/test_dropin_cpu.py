@@ -70,3 +70,39 @@ def test_seeded_init_equals_reference():
         b = getattr(R, cls)(**kw, **extra).state_dict()
         assert list(a) == list(b)
         assert all(torch.equal(a[k], b[k]) for k in a), cls
+
+
+DIS_KW = dict(num_modalities=5, shared_latent_dim=4, modality_latent_dim=4, resolution=28, hidden_channels=16,
+              ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=[])
+
+
+@pytest.mark.parametrize("name", ["disentangled_28_mixed", "disentangled_28_gray"])
+def test_disentangled_state_dict_is_reference_compatible(name):
+    import medvae_disentangled_multimodal_b200 as M
+    g = load_golden(name)
+    model = M.DisentangledConditionalVAE(**DIS_KW)
+    sd = model.state_dict()
+    assert set(sd) == set(g["sd"]), set(sd) ^ set(g["sd"])
+    for k, v in g["sd"].items():
+        assert tuple(sd[k].shape) == tuple(v.shape), k
+    model.load_state_dict(g["sd"])
+    assert model.latent_dim == 8 and model.input_channels == 3 and model.num_modalities == 5
+    assert model.modality_channels == {0: 1, 1: 3, 2: 3, 3: 1, 4: 3}
+    assert sorted(model.modality_input_projectors) == ["0", "3"] == sorted(model.modality_output_projectors)
+    crit = M.DisentangledVAELoss("l1", 2.0, 1.0, 0.3, 0.4)
+    assert crit.separation_weight == 0.3 and crit.contrastive_weight == 0.4
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src"), reason="reference only exists in the build container")
+def test_disentangled_seeded_init_equals_reference():
+    sys.path.insert(0, "/root/reference")
+    for n in ("lpips", "open_clip"):
+        sys.modules.setdefault(n, types.ModuleType(n))
+    import src.models as R
+    import medvae_disentangled_multimodal_b200 as M
+    torch.manual_seed(5)
+    a = M.DisentangledConditionalVAE(**DIS_KW).state_dict()
+    torch.manual_seed(5)
+    b = R.DisentangledConditionalVAE(**DIS_KW).state_dict()
+    assert list(a) == list(b)
+    assert all(torch.equal(a[k], b[k]) for k in a)

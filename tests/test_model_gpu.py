@@ -198,3 +198,81 @@ def test_foreign_loss_through_distributions():
     ld["loss"].backward()
     for n, p in model.named_parameters():
         assert rel_err(p.grad, g1[n]) < 1e-4 or float((p.grad - g1[n]).abs().max()) < 1e-7, n
+
+
+# ------------------------------------------------------------------ DisentangledConditionalVAE
+DIS_KW = dict(num_modalities=5, shared_latent_dim=4, modality_latent_dim=4, resolution=28, hidden_channels=16,
+              ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=[])
+
+
+def _dis_step(name, dtype):
+    import medvae_disentangled_multimodal_b200 as M
+    g = load_golden(name)
+    model = M.DisentangledConditionalVAE(compute_dtype=dtype, **DIS_KW).to(DEV)
+    model.load_state_dict({k: v.to(DEV) for k, v in g["sd"].items()})
+    model.eps_override = g["eps"].to(DEV)
+    crit = M.DisentangledVAELoss("mse", 1.0, 1.0, 0.1, 0.05)
+    x = g["x"].to(DEV)
+    out = model(x, g["idx"])          # CPU index tensor: no host sync inside
+    ld = crit(out, x)
+    ld["loss"].backward()
+    torch.cuda.synchronize()
+    grads = {n: (p.grad if p.grad is not None else torch.zeros_like(p)) for n, p in model.named_parameters()}
+    return g, out, ld, grads
+
+
+@pytest.mark.parametrize("name", ["disentangled_28_mixed", "disentangled_28_gray"])
+def test_disentangled_golden_fp32_mode(name):
+    """the reference's own test shapes (test_modality_channels.py:50-112, quick_test.py:63-70) with the
+    numbers pinned: outputs, the five loss terms and every parameter gradient."""
+    g, out, ld, grads = _dis_step(name, "fp32")
+    assert out["reconstruction"].shape == g["out"]["reconstruction"].shape
+    for k in ("reconstruction", "mean", "logvar", "z", "separation_loss", "contrastive_loss"):
+        assert rel_err(out[k], g["out"][k]) < 2e-5, f"{k}: {rel_err(out[k], g['out'][k]):.3e}"
+    assert out["mu"] is out["mean"]
+    for k, v in g["loss"].items():
+        assert abs(float(ld[k].detach()) - float(v)) <= 2e-5 * max(1.0, abs(float(v))), k
+    bad = []
+    for n, ref in g["grads"].items():
+        e = grad_rel_err(n, grads[n], g["grads"])
+        if e >= 2e-4 and float((grads[n].cpu().double() - ref.double()).abs().max()) > 1e-7:
+            bad.append((n, e))
+    assert not bad, sorted(bad, key=lambda t: -t[1])[:6]
+
+
+@pytest.mark.parametrize("name", ["disentangled_28_mixed", "disentangled_28_gray"])
+def test_disentangled_golden_bf16_mode(name):
+    g, out, ld, grads = _dis_step(name, "bf16")
+    for k in ("reconstruction", "mean", "logvar", "z"):
+        assert rel_err(out[k], g["out"][k]) < 5e-2, f"{k}: {rel_err(out[k], g['out'][k]):.3e}"
+    for k, v in g["loss"].items():
+        assert abs(float(ld[k].detach()) - float(v)) <= 5e-2 * max(1.0, abs(float(v))), k
+    num = sum(float((grads[n].double().cpu() - r.double()).pow(2).sum()) for n, r in g["grads"].items())
+    den = sum(float(r.double().pow(2).sum()) for r in g["grads"].values())
+    assert (num / den) ** 0.5 < 1e-1
+
+
+def test_disentangled_api_surface():
+    """API the reference's scripts use: encode/decode/partition/reconstruct/sample_conditional and the
+    channel convention (all-gray batch -> 1 channel, mixed -> 3)."""
+    import medvae_disentangled_multimodal_b200 as M
+    model = M.DisentangledConditionalVAE(**DIS_KW).to(DEV)
+    x = torch.rand(4, 3, 28, 28, device=DEV) * 2 - 1
+    idx = torch.tensor([0, 1, 3, 4])
+    out = model(x, idx, return_latents=True)
+    assert out["reconstruction"].shape == (4, 3, 28, 28)
+    assert out["z_shared"].shape == (4, 4) and out["z_modality"].shape == (4, 4)
+    mu, lv = model.encode(x, idx)
+    assert mu.shape == lv.shape == (4, 8, 14, 14)
+    gray = model(x[:2, :1], torch.tensor([0, 3]))
+    assert gray["reconstruction"].shape == (2, 1, 28, 28)
+    with torch.no_grad():
+        assert model.sample_conditional(3, torch.tensor([1, 2, 4]), torch.device(DEV)).shape == (3, 3, 28, 28)
+        assert model.decode(out["z"]).shape == (4, 3, 28, 28)
+    zs, zm = model.partition_latent(out["z"])
+    assert model.reconstruct_latent(zs, zm).shape[0] == 4
+    # GPU-resident indices work too (one host sync for the channel-width decision)
+    out2 = model(x, idx.to(DEV))
+    assert out2["reconstruction"].shape == (4, 3, 28, 28)
+    with pytest.raises(ValueError):
+        M.DisentangledVAELoss("bce")
