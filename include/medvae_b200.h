@@ -90,6 +90,11 @@ size_t mvae_conv2d_wgrad_workspace_bytes(const mvae_conv_desc* d);
 int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, float* dw_oihw,
                       float* dbias, void* workspace, size_t workspace_bytes, void* stream);
 
+/* same, accumulating: dw = beta*dw + dW, dbias = beta*dbias + db (beta = 1: add into a gradient
+ * buffer that already holds earlier micro-batches; beta = 0: overwrite).  dw must be contiguous OIHW. */
+int mvae_conv2d_wgrad_acc(const mvae_conv_desc* d, const void* x, const void* dy, float* dw_oihw,
+                          float* dbias, void* workspace, size_t workspace_bytes, float beta, void* stream);
+
 /* GroupNorm(min(32,C), eps) [+ x*sigmoid(x)]  — Normalize + nonlinearity,
  * encoder_decoder.py:13-15,28-33 as used at :150-151,:158-159,:85,:325-326,:446-447.
  * x,y: [B, HW, C].  stats (out): [B][G][2] fp32 (mean, rstd).  scratch: fp32 workspace of

@@ -48,6 +48,7 @@ SIGNATURES = {
     "mvae_conv2d_dgrad": (C.c_int, [_dp, _vp, _vp, _vp, _vp]),
     "mvae_conv2d_wgrad_workspace_bytes": (_sz, [_dp]),
     "mvae_conv2d_wgrad": (C.c_int, [_dp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "mvae_conv2d_wgrad_acc": (C.c_int, [_dp, _vp, _vp, _vp, _vp, _vp, _sz, _f32, _vp]),
     "mvae_groupnorm_splits": (C.c_int, [_i32, _i32, _i32]),
     "mvae_groupnorm_scratch_floats": (C.c_int64, [_i32, _i32, _i32, _i32, _i32]),
     "mvae_groupnorm_silu_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _f32, _i32, _i32, _vp]),

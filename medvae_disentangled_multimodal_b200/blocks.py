@@ -101,8 +101,9 @@ class Run:
     """State of one forward (+ its backward) through a stack: dtype, saved activations and the
     parameter gradients produced so far."""
 
-    def __init__(self, dtype: torch.dtype, cache: dict, training: bool, sink=None):
+    def __init__(self, dtype: torch.dtype, cache: dict, training: bool, sink=None, views=None):
         self.sink = sink              # callable(param, grad): takes the gradient instead of autograd
+        self.views = views            # train.GradBuckets: kernels accumulate straight into its flat views
         self.dtype = dtype
         self.code = L.code_of(dtype)
         self.cache = cache            # packed-operand cache owned by the nn.Module
@@ -211,17 +212,30 @@ class ConvOp:
         b, h, w, _ = x.shape
         d = self.desc(run, b, h, w)
         ent = self.packed(run, x.device)
-        dw, db = ops.conv_wgrad(d, x, dy, dy_colsum is None)
-        if db is None:
-            db = dy_colsum
-        if d.in_c != self.cin or d.out_c != self.cout:
-            dw = dw[:self.cout, :self.cin].contiguous()
-            db = db[:self.cout]
-        off = 0
-        for c in self.convs:
-            run.add_grad(c.weight, dw[off:off + c.out_channels])
-            run.add_grad(c.bias, db[off:off + c.out_channels])
-            off += c.out_channels
+        vw = vb = None
+        if run.views is not None and len(self.convs) == 1 and d.in_c == self.cin and d.out_c == self.cout:
+            vw, vb = run.views.view_of(self.convs[0].weight), run.views.view_of(self.convs[0].bias)
+        if vw is not None and vb is not None:
+            # the wgrad finalisation adds into the flat gradient buffer (no temporary, no add pass)
+            c = self.convs[0]
+            ops.conv_wgrad_acc(d, x, dy, vw, vb if dy_colsum is None else None, 1.0)
+            run.views.mark_ready(c.weight)
+            if dy_colsum is None:
+                run.views.mark_ready(c.bias)
+            else:
+                run.add_grad(c.bias, dy_colsum)
+        else:
+            dw, db = ops.conv_wgrad(d, x, dy, dy_colsum is None)
+            if db is None:
+                db = dy_colsum
+            if d.in_c != self.cin or d.out_c != self.cout:
+                dw = dw[:self.cout, :self.cin].contiguous()
+                db = db[:self.cout]
+            off = 0
+            for c in self.convs:
+                run.add_grad(c.weight, dw[off:off + c.out_channels])
+                run.add_grad(c.bias, db[off:off + c.out_channels])
+                off += c.out_channels
         if not need_dx:
             return None, None
         if gn is not None and run.fuse_gn:
@@ -404,6 +418,7 @@ class _Stack(nn.Module):
     def _init_runtime(self):
         self._pack_cache: dict = {}
         self._grad_sink = None        # set by train.TrainStep: gradients go to its flat buckets
+        self._grad_views = None       # set by train.TrainStep: the GradBuckets object itself
         self.compute_dtype = torch.bfloat16
 
     def stages(self, need_input_grad: bool):
@@ -422,7 +437,7 @@ class _Stack(nn.Module):
 class _StackFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, stack: "_Stack", need_input_grad: bool, x, *params):
-        run = Run(x.dtype, stack._pack_cache, stack.training, stack._grad_sink)
+        run = Run(x.dtype, stack._pack_cache, stack.training, stack._grad_sink, stack._grad_views)
         with torch.no_grad():
             y = run_forward(stack.stages(need_input_grad), run, x)
         ctx.run = run

@@ -22,9 +22,9 @@ int debug_knob(int key) { return (key >= 0 && key < 16) ? g_knobs[key] : 0; }
 
 // implemented in the other translation units
 int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot, int co_off, int dtype, cudaStream_t st);
-int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int splits, cudaStream_t st);
+int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int splits, float beta, cudaStream_t st);
 int colsum_parts(long long M);
-int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dtype, cudaStream_t st);
+int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dtype, float beta, cudaStream_t st);
 int nhwc_to_nchw(const void* src, float* dst, int B, int HW, int Cs, int c_off, int Cd, int dtype, cudaStream_t st);
 int nchw_to_nhwc(const float* src, void* dst, int B, int HW, int C, int dtype, cudaStream_t st);
 int input_pack_fwd(const float* x, const float* cond, const float* w, const float* b, void* out, int B, int C, int H,
@@ -268,8 +268,8 @@ size_t mvae_conv2d_wgrad_workspace_bytes(const mvae_conv_desc* d) {
     return partial + cs + 256;
 }
 
-int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias, void* workspace,
-                      size_t workspace_bytes, void* stream) {
+static int wgrad_impl(const mvae_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias, void* workspace,
+                      size_t workspace_bytes, float beta, void* stream) {
     ConvGeom g;
     MVAE_CHECK(d && conv_geom(*d, g) == 0 && dtype_ok(d->dtype), "bad conv descriptor");
     MVAE_CHECK(x && dy && dw && workspace, "conv2d_wgrad: null pointer");
@@ -283,12 +283,21 @@ int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, fl
     size_t partial_elems = (size_t)splits * conv_num_slabs(g) * g.Cout * g.Cin;
     int rc = um ? umma_reduce(p, x, dy, partial, splits, ST(stream)) : simt_reduce(p, x, dy, partial, d->dtype, ST(stream));
     if (rc) return rc;
-    if (wgrad_finalize(g, partial, dw, splits, ST(stream))) return 1;
+    if (wgrad_finalize(g, partial, dw, splits, beta, ST(stream))) return 1;
     if (dbias) {
         float* cs = partial + ((partial_elems + 63) / 64) * 64;
-        return colsum(dy, dbias, cs, (long long)g.B * g.P * g.Q, g.Cout, d->dtype, ST(stream));
+        return colsum(dy, dbias, cs, (long long)g.B * g.P * g.Q, g.Cout, d->dtype, beta, ST(stream));
     }
     return 0;
+}
+
+int mvae_conv2d_wgrad(const mvae_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+    return wgrad_impl(d, x, dy, dw, dbias, workspace, workspace_bytes, 0.f, stream);
+}
+int mvae_conv2d_wgrad_acc(const mvae_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias, void* workspace,
+                          size_t workspace_bytes, float beta, void* stream) {
+    return wgrad_impl(d, x, dy, dw, dbias, workspace, workspace_bytes, beta, stream);
 }
 
 int mvae_groupnorm_splits(int32_t batch, int32_t hw, int32_t c) { return gn_splits(batch, hw, c); }

@@ -60,51 +60,57 @@ int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot
 
 // ------------------------------------------------------------------ wgrad finalisation
 // partial [splits][nslabs][Cout][Cin] fp32 -> dW [Cout][Cin][R][R] fp32 (sum over splits; UP
-// mode: each (r,s) receives the 4 slabs whose R-sets contain it).
+// mode: each (r,s) receives the 4 slabs whose R-sets contain it).  dW = beta * dW + sum: beta = 1
+// accumulates straight into the training step's flat gradient buffer (no temporary, no add pass).
+// A CTA owns 256 consecutive (co, ci) pairs: slab reads are coalesced along ci, the R*R values of a
+// pair are transposed through shared memory (stride 9: conflict-free) and the CTA's contiguous
+// 256*R*R-float span of OIHW is written with fully coalesced stores.
 __global__ void __launch_bounds__(256) wgrad_finalize_kernel(const float* __restrict__ partial, float* __restrict__ dw,
-                                                             int splits, int nslabs, int Cout, int Cin, int R, int mode) {
-    // one thread per (co, ci): reads of every slab are coalesced along ci, and the thread's R*R
-    // outputs are contiguous in OIHW, so a warp writes one contiguous 32*R*R*4-byte span.
+                                                             int splits, int nslabs, int Cout, int Cin, int R, int mode,
+                                                             float beta) {
+    __shared__ float tile[256 * 9];
     const long long pairs = (long long)Cout * Cin;
     const long long slab_stride = pairs;
     const long long split_stride = slab_stride * nslabs;
     const int RR = R * R;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < pairs;
-         i += (long long)gridDim.x * blockDim.x) {
-        float out[9];
+    for (long long i0 = blockIdx.x * 256LL; i0 < pairs; i0 += (long long)gridDim.x * 256) {
+        const long long i = i0 + threadIdx.x;
+        if (i < pairs) {
 #pragma unroll
-        for (int rs = 0; rs < 9; ++rs) {
-            if (rs >= RR) break;
-            float acc = 0.f;
-            if (mode == MVAE_CONV_UP) {
-                const int r = rs / 3, s_ = rs % 3;
-                for (int a = 0; a < 2; ++a) {
-                    int ui = (a == 0) ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0);
-                    for (int b = 0; b < 2; ++b) {
-                        int vi = (b == 0) ? (s_ == 0 ? 0 : 1) : (s_ == 2 ? 1 : 0);
-                        int slab = ((a * 2 + b) * 2 + ui) * 2 + vi;
-                        const float* p = partial + slab * slab_stride + i;
-                        for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+            for (int rs = 0; rs < 9; ++rs) {
+                if (rs >= RR) break;
+                float acc = 0.f;
+                if (mode == MVAE_CONV_UP) {
+                    const int r = rs / 3, s_ = rs % 3;
+                    for (int a = 0; a < 2; ++a) {
+                        int ui = (a == 0) ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0);
+                        for (int b = 0; b < 2; ++b) {
+                            int vi = (b == 0) ? (s_ == 0 ? 0 : 1) : (s_ == 2 ? 1 : 0);
+                            int slab = ((a * 2 + b) * 2 + ui) * 2 + vi;
+                            const float* p = partial + slab * slab_stride + i;
+                            for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+                        }
                     }
+                } else {
+                    const float* p = partial + rs * slab_stride + i;
+                    for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
                 }
-            } else {
-                const float* p = partial + rs * slab_stride + i;
-                for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+                tile[threadIdx.x * RR + rs] = acc;
             }
-            out[rs] = acc;
         }
-        float* o = dw + i * RR;
-#pragma unroll
-        for (int rs = 0; rs < 9; ++rs)
-            if (rs < RR) o[rs] = out[rs];
+        __syncthreads();
+        long long span = (pairs - i0 < 256 ? pairs - i0 : 256) * RR;
+        float* o = dw + i0 * RR;
+        for (int k = threadIdx.x; k < span; k += 256) o[k] = (beta != 0.f) ? fmaf(beta, o[k], tile[k]) : tile[k];
+        __syncthreads();
     }
 }
 
-int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int splits, cudaStream_t st) {
+int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int splits, float beta, cudaStream_t st) {
     long long total = (long long)g.Cout * g.Cin;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    wgrad_finalize_kernel<<<blocks, 256, 0, st>>>(partial, dw, splits, conv_num_slabs(g), g.Cout, g.Cin, g.R, g.mode);
+    wgrad_finalize_kernel<<<blocks, 256, 0, st>>>(partial, dw, splits, conv_num_slabs(g), g.Cout, g.Cin, g.R, g.mode, beta);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
@@ -189,7 +195,7 @@ __global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __rest
         __syncthreads();
     }
 }
-__global__ void colsum_fold_kernel(const float* __restrict__ scratch, float* __restrict__ db, int parts, int C) {
+__global__ void colsum_fold_kernel(const float* __restrict__ scratch, float* __restrict__ db, int parts, int C, float beta) {
     __shared__ float sh[8][33];
     const int c = blockIdx.x * 32 + threadIdx.x;
     float s = 0.f;
@@ -201,7 +207,7 @@ __global__ void colsum_fold_kernel(const float* __restrict__ scratch, float* __r
         float t = 0.f;
 #pragma unroll
         for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x];
-        db[c] = t;
+        db[c] = (beta != 0.f) ? fmaf(beta, db[c], t) : t;
     }
 }
 
@@ -212,7 +218,7 @@ int colsum_parts(long long M) {
     return (int)parts;
 }
 
-int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dtype, cudaStream_t st) {
+int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dtype, float beta, cudaStream_t st) {
     int parts = colsum_parts(M);
     long long rpc = (M + parts - 1) / parts;
     parts = (int)((M + rpc - 1) / rpc);
@@ -226,7 +232,7 @@ int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dt
     else
         colsum_partial_kernel<bf16><<<parts, 256, 0, st>>>((const bf16*)dy, scratch, M, C, rpc);
     MVAE_LAUNCH_CHECK();
-    colsum_fold_kernel<<<(C + 31) / 32, dim3(32, 8), 0, st>>>(scratch, db, parts, C);
+    colsum_fold_kernel<<<(C + 31) / 32, dim3(32, 8), 0, st>>>(scratch, db, parts, C, beta);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

@@ -145,6 +145,19 @@ def conv_wgrad(d: ConvDesc, x, dy, want_bias=True):
     return dw, db
 
 
+def conv_wgrad_acc(d: ConvDesc, x, dy, dw_view, db_view, beta=1.0):
+    """wgrad accumulated in place: dw_view = beta*dw_view + dW (contiguous OIHW fp32 view, e.g. a
+    slice of the training step's flat gradient buffer); db_view likewise, or None to skip the bias."""
+    nbytes = lib().mvae_conv2d_wgrad_workspace_bytes(C.byref(d))
+    ws = scratch("wgrad", nbytes, x.device)
+    kind = "conv_wgrad"
+    if P.active() is not None:
+        kind = "conv_wgrad_umma" if lib().mvae_conv2d_uses_umma(C.byref(d)) else "conv_wgrad_simt"
+    with P.region(kind, conv_flops(d) if P.active() else 0.0, (x.numel() + dy.numel()) * x.element_size()):
+        check(lib().mvae_conv2d_wgrad_acc(C.byref(d), ptr(x), ptr(dy), ptr(dw_view), ptr(db_view), ptr(ws), ws.numel(),
+                                          float(beta), stream()), "conv2d_wgrad_acc")
+
+
 def gn_fwd(x, gamma, beta, groups, eps, silu):
     b, h, w, c = x.shape
     y = torch.empty_like(x)

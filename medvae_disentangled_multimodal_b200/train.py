@@ -80,6 +80,11 @@ class GradBuckets:
     def begin_round(self):
         self._pending = list(self.members)
 
+    def view_of(self, p: nn.Parameter):
+        """the slice of the flat buffer that is p.grad (kernels may accumulate into it directly and
+        then call mark_ready), or None for a parameter this object does not own"""
+        return self.views.get(id(p))
+
     def accumulate(self, p: nn.Parameter, g: torch.Tensor):
         """grad sink used by the encoder/decoder backward schedules: add into the flat view."""
         self.views[id(p)].add_(g.view(p.shape))
@@ -160,6 +165,7 @@ class TrainStep:
             stack = getattr(model, name, None)
             if stack is not None and hasattr(stack, "stages"):
                 stack._grad_sink = self.buckets.accumulate
+                stack._grad_views = self.buckets
                 sunk.update(id(p) for p in stack.parameters())
         for p in self.order:
             if id(p) not in sunk:
@@ -172,6 +178,7 @@ class TrainStep:
             stack = getattr(self.model, name, None)
             if stack is not None and hasattr(stack, "_grad_sink"):
                 stack._grad_sink = None
+                stack._grad_views = None
 
     def _to_device(self, t):
         if t is None or t.device == self.device:

@@ -379,3 +379,90 @@ def test_conv_dgrad_gn_backward(case, silu, with_add):
     assert rel_err(dg1, dg0) < 2e-2 and rel_err(db1, db0) < 2e-2
     cs_ref = dx1.double().sum(dim=(0, 1, 2))
     assert float((cs1.double() - cs_ref).abs().max()) <= 2e-2 * float(cs_ref.abs().max()) + 1e-3
+
+
+# ------------------------------------------------------------------ disentangled-model kernels
+def _ref_aux(z, idx, s, m, tau=0.1):
+    zm = z.reshape(z.shape[0], -1)[:, s:s + m]
+    cents = [zm[idx == k].mean(dim=0) for k in torch.unique(idx)]
+    sep = -torch.pdist(torch.stack(cents), p=2).mean() if len(cents) >= 2 else zm.sum() * 0
+    zn = F.normalize(zm, p=2, dim=1)
+    e = torch.exp(zn @ zn.t() / tau)
+    mask = (idx[None, :] == idx[:, None]) & ~torch.eye(len(idx), dtype=torch.bool)
+    pos = (e * mask.to(e.dtype)).sum(dim=1)
+    allsim = e.sum(dim=1) - torch.diag(e)
+    l = -torch.log(pos / allsim + 1e-8)
+    l = l[pos > 0]
+    con = l.mean() if len(l) > 0 else zm.sum() * 0
+    return sep, con
+
+
+@pytest.mark.parametrize("case", [(6, 8, 14, 4, 4, [0, 1, 3, 4, 1, 0]), (2, 8, 14, 4, 4, [0, 3]),
+                                  (3, 8, 7, 4, 4, [2, 2, 2]), (64, 4, 8, 128, 128, None), (33, 2, 8, 8, 100, None)])
+def test_disentangled_aux_losses(case):
+    """modality_separation_loss + contrastive_loss (disentangled_conditional_vae.py:305-386), forward
+    and backward, against torch autograd in fp64."""
+    _, ops = _mods()
+    B, zc, R, s, m, idx = case
+    g = torch.Generator().manual_seed(9)
+    z = torch.randn(B, zc, R, R, generator=g, dtype=torch.float64).float().double().requires_grad_(True)
+    idx = torch.tensor(idx) if idx is not None else torch.randint(0, 5, (B,), generator=g)
+    sep_ref, con_ref = _ref_aux(z, idx, s, m)
+    gs, gc = 0.37, -1.3
+    (gs * sep_ref + gc * con_ref).backward()
+    zf = z.detach().float().reshape(B, -1).contiguous().to(DEV)
+    idx_d = idx.to(DEV)
+    aux = ops.dis_aux_fwd(zf, idx_d, s, m, 5, 0.1)
+    dz = ops.dis_aux_bwd(zf, idx_d, aux, torch.tensor(gs, device=DEV), torch.tensor(gc, device=DEV), s, m, 5, 0.1)
+    torch.cuda.synchronize()
+    assert abs(float(aux[0]) - float(sep_ref)) <= 1e-5 * max(1.0, abs(float(sep_ref)))
+    assert abs(float(aux[1]) - float(con_ref)) <= 1e-5 * max(1.0, abs(float(con_ref)))
+    assert rel_err(dz.view(z.shape), z.grad) < 2e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("idx,xc", [([0, 1, 3, 4, 1, 0], 3), ([0, 3], 1), ([3, 0, 3], 3)])
+def test_disentangled_heads(dtype, idx, xc):
+    """per-modality decoder heads (:241-303): conv3x3-ReLU-conv3x3 (+ 3->1 projector, zero padding)
+    against the per-sample torch loop the reference runs, forward and backward."""
+    _, ops = _mods()
+    B, H, W, n_mod, rc = len(idx), 12, 10, 5, 8
+    g = torch.Generator().manual_seed(2)
+    rnd = lambda *s: torch.randn(*s, generator=g, dtype=torch.float64)
+    r = rnd(B, 3, H, W)
+    if dtype == torch.bfloat16:
+        r = r.bfloat16().double()
+    r.requires_grad_(True)
+    w1, b1, w2, b2 = (rnd(n_mod, 3, 3, 3, 3) * 0.3).requires_grad_(True), rnd(n_mod, 3).requires_grad_(True), \
+        (rnd(n_mod, 3, 3, 3, 3) * 0.3).requires_grad_(True), rnd(n_mod, 3).requires_grad_(True)
+    pw, pb = rnd(n_mod, 3).requires_grad_(True), rnd(n_mod).requires_grad_(True)
+    gray = [1, 0, 0, 1, 0]
+    outs = []
+    for i, m in enumerate(idx):
+        s = F.conv2d(r[i:i + 1], w1[m], b1[m], padding=1)
+        s = F.conv2d(F.relu(s), w2[m], b2[m], padding=1)
+        if gray[m]:
+            s = F.conv2d(s, pw[m].view(1, 3, 1, 1), pb[m].view(1))
+        outs.append(s)
+    out_c = max(o.shape[1] for o in outs)
+    ref = torch.cat([F.pad(o, (0, 0, 0, 0, 0, out_c - o.shape[1])) for o in outs])
+    d_out = rnd(*ref.shape)
+    ref.backward(d_out)
+    r_g = torch.zeros(B, H, W, rc, dtype=dtype, device=DEV)
+    r_g[..., :3] = nhwc(r.detach().float(), dtype)
+    f = lambda t: t.detach().float().contiguous().to(DEV)
+    idx_d = torch.tensor(idx, device=DEV)
+    gray_d = torch.tensor(gray, dtype=torch.int32, device=DEV)
+    out, hid, y = ops.dis_head_fwd(r_g, idx_d, f(w1), f(b1), f(w2), f(b2), f(pw), f(pb), gray_d, out_c)
+    d_r, gr = ops.dis_head_bwd(f(d_out), r_g, hid, y, idx_d, f(w1), f(w2), f(pw), gray_d)
+    torch.cuda.synchronize()
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(out, ref) < tol
+    assert rel_err(nchw(d_r[..., :3]), r.grad) < tol
+    assert float(d_r[..., 3:].float().abs().max()) == 0.0
+    assert rel_err(gr[:, 0:81].reshape(n_mod, 3, 3, 3, 3), w1.grad) < 5 * tol
+    assert rel_err(gr[:, 81:84], b1.grad) < 5 * tol
+    assert rel_err(gr[:, 84:165].reshape(n_mod, 3, 3, 3, 3), w2.grad) < 5 * tol
+    assert rel_err(gr[:, 165:168], b2.grad) < 5 * tol
+    assert rel_err(gr[:, 168:171], pw.grad) < 5 * tol
+    assert rel_err(gr[:, 171], pb.grad) < 5 * tol
