@@ -304,12 +304,14 @@ def b200_arm(args):
 
     roof = None
     kernels = {}
-    if not args.no_roofline and rank == 0:
+    if not args.no_roofline:
+        # one extra, untimed step with CUDA events around every launch; EVERY rank runs it (the step
+        # contains the gradient all-reduces), rank 0 reports
         timer = P.KernelTimer()
         P.install(timer)
         ts.step(x_d, cond_d)
         P.install(None)
-        summ = timer.summary()
+        summ = timer.summary() if rank == 0 else {}
         for k, d in summ.items():
             kernels[k] = {"launches": d["launches"], "ms": round(d["ms"], 3),
                           "tflops": round(d["flops"] / (d["ms"] * 1e9), 2) if d["ms"] > 0 and d["flops"] else None,
@@ -326,8 +328,6 @@ def b200_arm(args):
                     "peak_source": f"{peaks['source']} (sustained: kernel timed inside a long step)",
                     "launches": n_l, "avg_launch_ms": round(ms / n_l, 4),
                     "algorithmic_gflop_per_launch": round(fl / n_l / 1e9, 2)}
-    elif world > 1:
-        pass
     if world > 1:
         barrier()
 
@@ -367,6 +367,10 @@ def b200_arm(args):
 
 def main():
     args = parse()
+    wd = os.environ.get("MVAE_WATCHDOG")
+    if wd:   # debugging aid: dump every thread's stack and exit if the run is still alive after N seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(int(wd), exit=True)
     if args.impl == "reference":
         reference_arm(args)
     else:
