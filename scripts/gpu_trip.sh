@@ -11,6 +11,7 @@ for stage in "$@"; do
     simt_all) timeout 900 python -m pytest tests/test_kernels_gpu.py -q -m "gpu and not umma" --timeout 300 > gpurun_out/t_simt.log 2>&1; echo "simt rc=$?" >> gpurun_out/rc.txt;;
     umma)  timeout 600 python -m pytest tests/test_kernels_gpu.py -q -m "umma" --timeout 120 > gpurun_out/t_umma.log 2>&1; echo "umma rc=$?" >> gpurun_out/rc.txt;;
     model) timeout 900 python -m pytest tests/test_model_gpu.py -q --timeout 300 > gpurun_out/t_model.log 2>&1; echo "model rc=$?" >> gpurun_out/rc.txt;;
+    train) timeout 900 python -m pytest tests/test_train_gpu.py -q --timeout 600 > gpurun_out/t_train.log 2>&1; echo "train rc=$?" >> gpurun_out/rc.txt;;
     probe) timeout 300 python scripts/umma_probe.py > gpurun_out/probe.log 2>&1; echo "probe rc=$?" >> gpurun_out/rc.txt;;
     smoke) timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/rc.txt;;
     bench) timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/rc.txt;;
