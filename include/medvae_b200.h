@@ -222,6 +222,19 @@ int mvae_adamw_clip_step(float* const* params, const float* const* grads, float*
                          float beta2, float eps, float weight_decay, int32_t decoupled,
                          int32_t step, void* stream);
 
+/* the same two passes over a CHUNK TABLE (device arrays): chunk i covers elements
+ * [chunk_offset[i], chunk_offset[i] + chunk_len[i]) of tensor chunk_tensor[i]; equal-sized chunks
+ * balance the CTAs whatever the tensor sizes, and aligned chunks use 16-byte accesses. */
+int mvae_grad_sqnorm_chunked(const float* const* grads, const int32_t* chunk_tensor,
+                             const int64_t* chunk_offset, const int32_t* chunk_len, int32_t n_chunks,
+                             double* sqnorm_dev, void* stream);
+int mvae_adamw_clip_step_chunked(float* const* params, const float* const* grads, float* const* exp_avg,
+                                 float* const* exp_avg_sq, const int32_t* chunk_tensor,
+                                 const int64_t* chunk_offset, const int32_t* chunk_len, int32_t n_chunks,
+                                 const double* sqnorm_dev, float max_norm, float lr, float beta1,
+                                 float beta2, float eps, float weight_decay, int32_t decoupled,
+                                 int32_t step, void* stream);
+
 /* DisentangledConditionalVAE per-modality input projector
  * (disentangled_conditional_vae.py:124-171): out NHWC [B,H,W,out_c]; for modalities whose
  * channel count is 1, out[:, :3] = w_m * x[:,0] + b_m (Conv2d(1,3,1)), else x passes through.

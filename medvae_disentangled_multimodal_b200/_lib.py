@@ -78,6 +78,9 @@ SIGNATURES = {
     "mvae_grad_sqnorm": (C.c_int, [_vp, _vp, _i32, _vp, _vp]),
     "mvae_adamw_clip_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _f32, _f32, _f32, _f32, _f32, _f32, _i32,
                                        _i32, _vp]),
+    "mvae_grad_sqnorm_chunked": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp]),
+    "mvae_adamw_clip_step_chunked": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _f32, _f32, _f32, _f32, _f32,
+                                               _f32, _i32, _i32, _vp]),
     "mvae_dis_input_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_dis_input_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_dis_head_fwd": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32,

@@ -80,6 +80,13 @@ int adamw_step(float* const* params, const float* const* grads, float* const* m1
                const long long* sizes, int nt, const double* sqnorm, float max_norm, float lr, float b1, float b2,
                float eps, float wd, int decoupled, int step, cudaStream_t st);
 
+int grad_sqnorm_chunked(const float* const* grads, const int* ch_tensor, const long long* ch_off, const int* ch_len,
+                        int n_chunks, double* out, cudaStream_t st);
+int adamw_step_chunked(float* const* params, const float* const* grads, float* const* m1, float* const* m2,
+                       const int* ch_tensor, const long long* ch_off, const int* ch_len, int n_chunks,
+                       const double* sqnorm, float max_norm, float lr, float b1, float b2, float eps, float wd,
+                       int decoupled, int step, cudaStream_t st);
+
 static bool dtype_ok(int d) { return d == MVAE_F32 || d == MVAE_BF16; }
 
 static bool use_umma_gather(const mvae_conv_desc& d, const GatherProblem* ps, int np) {
@@ -401,6 +408,24 @@ int mvae_adamw_clip_step(float* const* params, const float* const* grads, float*
     MVAE_CHECK(params && grads && exp_avg && exp_avg_sq && sizes && n_tensors > 0 && step >= 1, "adamw: bad argument");
     return adamw_step(params, grads, exp_avg, exp_avg_sq, reinterpret_cast<const long long*>(sizes), n_tensors, sqnorm_dev,
                       max_norm, lr, beta1, beta2, eps, weight_decay, decoupled, step, ST(stream));
+}
+
+int mvae_grad_sqnorm_chunked(const float* const* grads, const int32_t* chunk_tensor, const int64_t* chunk_offset,
+                             const int32_t* chunk_len, int32_t n_chunks, double* sqnorm_dev, void* stream) {
+    MVAE_CHECK(grads && chunk_tensor && chunk_offset && chunk_len && sqnorm_dev && n_chunks > 0, "grad_sqnorm_chunked: bad argument");
+    return grad_sqnorm_chunked(grads, chunk_tensor, reinterpret_cast<const long long*>(chunk_offset), chunk_len, n_chunks,
+                               sqnorm_dev, ST(stream));
+}
+int mvae_adamw_clip_step_chunked(float* const* params, const float* const* grads, float* const* exp_avg,
+                                 float* const* exp_avg_sq, const int32_t* chunk_tensor, const int64_t* chunk_offset,
+                                 const int32_t* chunk_len, int32_t n_chunks, const double* sqnorm_dev, float max_norm,
+                                 float lr, float beta1, float beta2, float eps, float weight_decay, int32_t decoupled,
+                                 int32_t step, void* stream) {
+    MVAE_CHECK(params && grads && exp_avg && exp_avg_sq && chunk_tensor && chunk_offset && chunk_len && n_chunks > 0 &&
+                   step >= 1, "adamw_chunked: bad argument");
+    return adamw_step_chunked(params, grads, exp_avg, exp_avg_sq, chunk_tensor,
+                              reinterpret_cast<const long long*>(chunk_offset), chunk_len, n_chunks, sqnorm_dev, max_norm,
+                              lr, beta1, beta2, eps, weight_decay, decoupled, step, ST(stream));
 }
 
 int mvae_dis_input_fwd(const float* x, const int64_t* idx, const float* pw, const float* pb, const int32_t* is_gray,

@@ -256,6 +256,126 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* const* __restrict__ p
         }
     }
 }
+// ---- chunked variants: a table of (tensor, offset, length) chunks of <= 64 Ki elements gives every CTA
+// the same amount of work whatever the tensor sizes (the 17 9.4 M-element conv weights of C4 next to
+// 128-element biases), and 16-byte accesses whenever the four pointers allow it.
+__global__ void __launch_bounds__(256) grad_sqnorm_chunked_kernel(const float* const* __restrict__ grads,
+                                                                  const int* __restrict__ ch_tensor,
+                                                                  const long long* __restrict__ ch_off,
+                                                                  const int* __restrict__ ch_len, int n_chunks,
+                                                                  double* __restrict__ out) {
+    __shared__ double shd[32];
+    double acc = 0.0;
+    for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+        const float* g = grads[ch_tensor[c]] + ch_off[c];
+        const int n = ch_len[c];
+        float part = 0.f;
+        if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
+            const float4* g4 = reinterpret_cast<const float4*>(g);
+            for (int i = threadIdx.x; i < n / 4; i += 256) {
+                const float4 v = g4[i];
+                if (isfinite(v.x)) part = fmaf(v.x, v.x, part);
+                if (isfinite(v.y)) part = fmaf(v.y, v.y, part);
+                if (isfinite(v.z)) part = fmaf(v.z, v.z, part);
+                if (isfinite(v.w)) part = fmaf(v.w, v.w, part);
+            }
+            for (int i = (n / 4) * 4 + threadIdx.x; i < n; i += 256) {
+                const float v = g[i];
+                if (isfinite(v)) part = fmaf(v, v, part);
+            }
+        } else {
+            for (int i = threadIdx.x; i < n; i += 256) {
+                const float v = g[i];
+                if (isfinite(v)) part = fmaf(v, v, part);
+            }
+        }
+        acc += (double)part;   // <= 256 fp32 terms per thread per chunk, then fp64
+    }
+    acc = block_sum_d(acc, shd);
+    if (threadIdx.x == 0 && acc != 0.0) atomicAdd(out, acc);
+}
+
+struct AdamArgs {
+    float max_norm, lr, b1, b2, eps, wd, bc1, bc2;
+    int decoupled;
+};
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float clip, const AdamArgs& a) {
+    g = isfinite(g) ? g * clip : 0.f;
+    if (a.decoupled) p *= (1.f - a.lr * a.wd); else g = fmaf(a.wd, p, g);
+    m = fmaf(a.b1, m, (1.f - a.b1) * g);
+    v = fmaf(a.b2, v, (1.f - a.b2) * g * g);
+    const float denom = sqrtf(v) / sqrtf(a.bc2) + a.eps;
+    p -= (a.lr / a.bc1) * (m / denom);
+}
+__global__ void __launch_bounds__(256) adamw_chunked_kernel(float* const* __restrict__ params,
+                                                            const float* const* __restrict__ grads,
+                                                            float* const* __restrict__ m1, float* const* __restrict__ m2,
+                                                            const int* __restrict__ ch_tensor,
+                                                            const long long* __restrict__ ch_off,
+                                                            const int* __restrict__ ch_len, int n_chunks,
+                                                            const double* __restrict__ sqnorm, const AdamArgs a) {
+    float clip = 1.f;
+    if (a.max_norm > 0.f && sqnorm) {
+        const float norm = (float)sqrt(*sqnorm);
+        const float c = a.max_norm / (norm + 1e-6f);
+        clip = c < 1.f ? c : 1.f;
+    }
+    for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+        const int t = ch_tensor[c];
+        const long long off = ch_off[c];
+        const int n = ch_len[c];
+        float* p = params[t] + off;
+        const float* g = grads[t] + off;
+        float* m = m1[t] + off;
+        float* v = m2[t] + off;
+        const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
+                           reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+        int done = 0;
+        if (vec) {
+            for (int i = threadIdx.x; i < n / 4; i += 256) {
+                float4 pv = reinterpret_cast<float4*>(p)[i];
+                const float4 gv = reinterpret_cast<const float4*>(g)[i];
+                float4 mv = reinterpret_cast<float4*>(m)[i];
+                float4 vv = reinterpret_cast<float4*>(v)[i];
+                adam_one(pv.x, gv.x, mv.x, vv.x, clip, a);
+                adam_one(pv.y, gv.y, mv.y, vv.y, clip, a);
+                adam_one(pv.z, gv.z, mv.z, vv.z, clip, a);
+                adam_one(pv.w, gv.w, mv.w, vv.w, clip, a);
+                reinterpret_cast<float4*>(p)[i] = pv;
+                reinterpret_cast<float4*>(m)[i] = mv;
+                reinterpret_cast<float4*>(v)[i] = vv;
+            }
+            done = (n / 4) * 4;
+        }
+        for (int i = done + threadIdx.x; i < n; i += 256) {
+            float pv = p[i], mv = m[i], vv = v[i];
+            adam_one(pv, g[i], mv, vv, clip, a);
+            p[i] = pv; m[i] = mv; v[i] = vv;
+        }
+    }
+}
+static int chunk_grid(int n_chunks) {
+    int g = 148 * 8;
+    return n_chunks < g ? n_chunks : g;
+}
+int grad_sqnorm_chunked(const float* const* grads, const int* ch_tensor, const long long* ch_off, const int* ch_len,
+                        int n_chunks, double* out, cudaStream_t st) {
+    grad_sqnorm_chunked_kernel<<<chunk_grid(n_chunks), 256, 0, st>>>(grads, ch_tensor, ch_off, ch_len, n_chunks, out);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+int adamw_step_chunked(float* const* params, const float* const* grads, float* const* m1, float* const* m2,
+                       const int* ch_tensor, const long long* ch_off, const int* ch_len, int n_chunks,
+                       const double* sqnorm, float max_norm, float lr, float b1, float b2, float eps, float wd,
+                       int decoupled, int step, cudaStream_t st) {
+    AdamArgs a;
+    a.max_norm = max_norm; a.lr = lr; a.b1 = b1; a.b2 = b2; a.eps = eps; a.wd = wd; a.decoupled = decoupled;
+    a.bc1 = 1.f - powf(b1, (float)step); a.bc2 = 1.f - powf(b2, (float)step);
+    adamw_chunked_kernel<<<chunk_grid(n_chunks), 256, 0, st>>>(params, grads, m1, m2, ch_tensor, ch_off, ch_len, n_chunks,
+                                                                sqnorm, a);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
 int grad_sqnorm(const float* const* grads, const long long* sizes, int nt, double* out, cudaStream_t st) {
     dim3 grid(32, nt < 64 ? nt : 64);
     grad_sqnorm_kernel<<<grid, 256, 0, st>>>(grads, sizes, nt, out);

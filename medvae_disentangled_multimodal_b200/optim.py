@@ -28,6 +28,8 @@ class FusedAdamW:
     torch.optim (``exp_avg``, ``exp_avg_sq``) so ``state_dict()`` can be handed to a torch optimizer.
     """
 
+    CHUNK = 1 << 16
+
     def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-4, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 1e-4, decoupled: bool = True, max_norm: float = 1.0):
         self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
@@ -62,6 +64,18 @@ class FusedAdamW:
                 "n": torch.tensor([p.numel() for p in plist], dtype=torch.int64).to(self._dev),
                 "count": len(plist),
             }
+            # chunk table: <= CHUNK elements per entry so every CTA gets the same amount of work
+            ct, co, cl = [], [], []
+            for i, p in enumerate(plist):
+                n = p.numel()
+                for off in range(0, n, self.CHUNK):
+                    ct.append(i); co.append(off); cl.append(min(self.CHUNK, n - off))
+            self._tables.update({
+                "ct": torch.tensor(ct, dtype=torch.int32).to(self._dev),
+                "co": torch.tensor(co, dtype=torch.int64).to(self._dev),
+                "cl": torch.tensor(cl, dtype=torch.int32).to(self._dev),
+                "chunks": len(ct),
+            })
         return self._tables
 
     def _state_for(self, p):
@@ -99,11 +113,13 @@ class FusedAdamW:
         t = self._ensure_tables(plist, grads)
         self.step_count += 1
         self._sqnorm.zero_()
-        check(lib().mvae_grad_sqnorm(ptr(t["g"]), ptr(t["n"]), t["count"], ptr(self._sqnorm), stream()), "grad_sqnorm")
-        check(lib().mvae_adamw_clip_step(ptr(t["p"]), ptr(t["g"]), ptr(t["m"]), ptr(t["v"]), ptr(t["n"]), t["count"],
-                                         ptr(self._sqnorm), self.max_norm, float(self.lr if lr is None else lr),
-                                         self.betas[0], self.betas[1], self.eps, self.weight_decay,
-                                         int(self.decoupled), self.step_count, stream()), "adamw_clip_step")
+        check(lib().mvae_grad_sqnorm_chunked(ptr(t["g"]), ptr(t["ct"]), ptr(t["co"]), ptr(t["cl"]), t["chunks"],
+                                             ptr(self._sqnorm), stream()), "grad_sqnorm")
+        check(lib().mvae_adamw_clip_step_chunked(ptr(t["p"]), ptr(t["g"]), ptr(t["m"]), ptr(t["v"]), ptr(t["ct"]),
+                                                 ptr(t["co"]), ptr(t["cl"]), t["chunks"], ptr(self._sqnorm),
+                                                 self.max_norm, float(self.lr if lr is None else lr), self.betas[0],
+                                                 self.betas[1], self.eps, self.weight_decay, int(self.decoupled),
+                                                 self.step_count, stream()), "adamw_clip_step")
         # parameters changed in place behind autograd's back: bump versions so the packed bf16
         # operand caches (blocks.ConvOp.packed) are refreshed on the next forward
         torch._C._increment_version(plist)

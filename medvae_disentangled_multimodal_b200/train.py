@@ -42,12 +42,15 @@ class GradBuckets:
     ``finish()`` waits for all outstanding reductions.
     """
 
+    ALIGN = 64   # elements
+
     def __init__(self, params: Sequence[nn.Parameter], bucket_bytes: int = 32 << 20, group=None):
         self.params = list(params)
         self.group = group
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         dev = self.params[0].device
-        total = sum(p.numel() for p in self.params)
+        pad = lambda n: (n + self.ALIGN - 1) // self.ALIGN * self.ALIGN   # 256-byte aligned views: 16-byte accesses
+        total = sum(pad(p.numel()) for p in self.params)
         self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
         self.views: Dict[int, torch.Tensor] = {}
         self.bucket_of: Dict[int, int] = {}
@@ -58,7 +61,7 @@ class GradBuckets:
             n = p.numel()
             self.views[id(p)] = self.flat[off:off + n].view(p.shape)
             self.bucket_of[id(p)] = len(self.bounds)
-            off += n
+            off += pad(n)
             count += 1
             if (off - start) * 4 >= bucket_bytes:
                 self.bounds.append([start, off]); self.members.append(count)

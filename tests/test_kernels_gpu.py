@@ -467,3 +467,30 @@ def test_disentangled_heads(dtype, idx, xc):
     assert rel_err(gr[:, 165:168], b2.grad) < 5 * tol
     assert rel_err(gr[:, 168:171], pw.grad) < 5 * tol
     assert rel_err(gr[:, 171], pb.grad) < 5 * tol
+
+
+@pytest.mark.parametrize("decoupled", [True, False])
+def test_fused_adamw_matches_torch(decoupled):
+    """grad_sqnorm + adamw_clip_step (chunk table, 16-byte path and scalar tails, NaN/Inf guard, global-norm
+    clip) against torch.optim.AdamW / Adam preceded by the reference's NaN zeroing and clip_grad_norm_
+    (src/lightning_module.py:390-477), three steps."""
+    from medvae_disentangled_multimodal_b200.optim import FusedAdamW
+    g = torch.Generator().manual_seed(12)
+    shapes = [(70001,), (3,), (128, 9), (1 << 17,), (5, 7, 3)]
+    ref_p = [torch.randn(s, generator=g).requires_grad_(True) for s in shapes]
+    dev_p = [torch.nn.Parameter(p.detach().clone().to(DEV)) for p in ref_p]
+    cls = torch.optim.AdamW if decoupled else torch.optim.Adam
+    ref_opt = cls(ref_p, lr=1e-2, weight_decay=1e-2, betas=(0.9, 0.99))
+    opt = FusedAdamW(dev_p, lr=1e-2, weight_decay=1e-2, betas=(0.9, 0.99), decoupled=decoupled, max_norm=1.0)
+    for step in range(3):
+        grads = [torch.randn(s, generator=g) * (3.0 if step == 0 else 0.01) for s in shapes]
+        grads[0][5] = float("nan"); grads[3][77] = float("inf")
+        for p, d, gr in zip(ref_p, dev_p, grads):
+            p.grad = torch.nan_to_num(gr.clone(), nan=0.0, posinf=0.0, neginf=0.0)
+            d.grad = gr.clone().to(DEV)
+        torch.nn.utils.clip_grad_norm_(ref_p, 1.0)
+        ref_opt.step()
+        opt.step()
+    torch.cuda.synchronize()
+    for p, d in zip(ref_p, dev_p):
+        assert rel_err(d, p) < 2e-6
