@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — train images/sec of the conditional-VAE training step (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c4|c3|c2|c1]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c4|c5|c3|c2|c1]
 
 One "step" = forward + VAELoss + backward (+ data-parallel gradient all-reduce) + clip + AdamW on
 one batch of synthetic MedMNIST-shaped images.  Default workload: BASELINE.json configs[3], the
@@ -50,7 +50,34 @@ WORKLOADS = {
                                   num_res_blocks=2, attn_resolutions=[16, 8], dropout=0.0, resolution=64,
                                   condition_method="concat"),
            dict(recon_loss_type="mse", kl_weight=1.0, recon_weight=1.0), 1024, True, 251.9, "weak"),
+    # C5: ch_mult/attn per SURVEY 8; modality indices i mod 5, gray modalities {0, 3}
+    "c5": ("DisentangledConditionalVAE", dict(num_modalities=5, shared_latent_dim=128, modality_latent_dim=128,
+                                              resolution=128, hidden_channels=128, ch_mult=(1, 2, 4, 8), num_res_blocks=2,
+                                              attn_resolutions=[16], dropout=0.0),
+           dict(recon_loss_type="mse", kl_weight=1.0, recon_weight=1.0, separation_weight=0.1, contrastive_weight=0.05),
+           256, True, 976.7, "weak"),
 }
+
+
+def wl_shape(wl: str):
+    """-> (image channels, latent channels, disentangled?) of a workload"""
+    cls, kw = WORKLOADS[wl][:2]
+    if cls == "DisentangledConditionalVAE":
+        return 3, kw["shared_latent_dim"] + kw["modality_latent_dim"], True
+    return kw["input_channels"], kw["latent_dim"], False
+
+
+def wl_batch(wl: str, batch: int, first_index: int = 0, pin: bool = False):
+    """-> (x, cond) host tensors in the layout TrainStep.step() takes for this workload"""
+    from medvae_disentangled_multimodal_b200.data import GRAY_5, synthetic_batch
+    cls, kw, _lkw, _b, conditional, _gf, _s = WORKLOADS[wl]
+    ch, _z, dis = wl_shape(wl)
+    if dis:
+        x, _lab, _onehot, idx = synthetic_batch(batch, ch, kw["resolution"], n_modalities=5, gray=GRAY_5,
+                                                first_index=first_index, pin=pin)
+        return x, idx.to(__import__("torch").int64)
+    x, _lab, onehot, _idx = synthetic_batch(batch, ch, kw["resolution"], first_index=first_index, pin=pin)
+    return x, (onehot if conditional else None)
 OPT = dict(lr=1e-4, weight_decay=1e-4, betas=(0.9, 0.999), max_norm=1.0)   # configs/training/default.yaml:3-11
 
 
@@ -77,7 +104,7 @@ def parse():
 def cpu_sample_batch(wl: str, override):
     if override:
         return override
-    return {"c1": 8, "c2": 8, "c3": 8, "c4": 2}[wl]
+    return {"c1": 8, "c2": 8, "c3": 8, "c4": 2, "c5": 2}[wl]
 
 
 def build_state_dict(wl: str):
@@ -95,20 +122,21 @@ def run_cpu_steps(wl: str, sd, batch: int, steps: int, warmup: int, budget_s: fl
     """-> (images/s, steps timed, cores).  Each step: fwd + VAELoss + bwd + NaN guard + clip + AdamW."""
     import torch
     from oracle import vae_oracle as O
-    from medvae_disentangled_multimodal_b200.data import synthetic_batch
     cls, kw, lkw, _b, conditional, _gf, _s = WORKLOADS[wl]
+    _ch, zc, dis = wl_shape(wl)
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     tr = O.ReferenceTrainer(sd, lr=OPT["lr"], weight_decay=OPT["weight_decay"], betas=OPT["betas"],
-                            max_norm=OPT["max_norm"], loss_kwargs=lkw)
-    x, _lab, onehot, _idx = synthetic_batch(batch, kw["input_channels"], kw["resolution"])
+                            max_norm=OPT["max_norm"], loss_kwargs=lkw,
+                            disentangled=(kw["shared_latent_dim"], kw["modality_latent_dim"]) if dis else None)
+    x, cond = wl_batch(wl, batch)
     r = kw["resolution"] // 2 ** (len(kw["ch_mult"]) - 1)
     g = torch.Generator().manual_seed(7)
     done, t_total = 0, 0.0
     for i in range(warmup + steps):
-        eps = torch.randn(batch, kw["latent_dim"], r, r, generator=g)
+        eps = torch.randn(batch, zc, r, r, generator=g)
         t0 = time.perf_counter()
-        tr.step(x, eps, onehot if conditional else None)
+        tr.step(x, eps, cond)
         dt = time.perf_counter() - t0
         if i >= warmup:
             done += 1
@@ -127,7 +155,7 @@ def reference_arm(args):
     _model, sd = build_state_dict(wl)
     b = cpu_sample_batch(wl, args.cpu_batch)
     ips, done, cores, t_total = run_cpu_steps(wl, sd, b, args.steps, args.warmup)
-    sample = f"{done} steps of {b} images ({cls} {kw['input_channels']}x{kw['resolution']}x{kw['resolution']}, fp32, " \
+    sample = f"{done} steps of {b} images ({cls} {wl_shape(wl)[0]}x{kw['resolution']}x{kw['resolution']}, fp32, " \
              f"fwd+loss+bwd+clip+AdamW) on {cores} host threads"
     line = {
         "impl": "reference", "metric": "train images/sec", "value": ips, "unit": "images/s", "n_gpus": args.gpus,
@@ -143,11 +171,12 @@ def reference_arm(args):
 
 def workload_config(wl, args, bpg, n, cpu=False):
     cls, kw, lkw, _b, conditional, gflop, scaling = WORKLOADS[wl]
+    ch, zc, dis = wl_shape(wl)
     return {
-        "workload": f"{wl}: {cls} {kw['input_channels']}x{kw['resolution']}x{kw['resolution']} hidden {kw['hidden_channels']} "
+        "workload": f"{wl}: {cls} {ch}x{kw['resolution']}x{kw['resolution']} hidden {kw['hidden_channels']} "
                     f"ch_mult {tuple(kw['ch_mult'])} res_blocks {kw['num_res_blocks']} attn {kw['attn_resolutions']} "
-                    f"latent {kw['latent_dim']}, VAELoss {lkw['recon_loss_type']} kl_weight {lkw['kl_weight']}, "
-                    f"AdamW lr 1e-4 wd 1e-4 clip 1.0",
+                    f"latent {zc}, {'DisentangledVAELoss' if dis else 'VAELoss'} {lkw['recon_loss_type']} "
+                    f"kl_weight {lkw['kl_weight']}, AdamW lr 1e-4 wd 1e-4 clip 1.0",
         "batch_per_gpu": bpg, "global_batch": bpg * n, "micro_batch": None if cpu else (args.micro_batch or min(bpg, 256)),
         "parallelism": f"dp{n}", "gflop_per_image_fwd_bwd": gflop,
         "cache": "inputs and activations larger than L2 (126 MB); no L2 flush needed",
@@ -225,7 +254,6 @@ def b200_arm(args):
     import medvae_disentangled_multimodal_b200 as M
     from medvae_disentangled_multimodal_b200 import _lib as L
     from medvae_disentangled_multimodal_b200 import profile as P
-    from medvae_disentangled_multimodal_b200.data import synthetic_batch
     from medvae_disentangled_multimodal_b200.train import TrainStep
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -250,13 +278,13 @@ def b200_arm(args):
     torch.manual_seed(42)
     model = getattr(M, cls)(compute_dtype=args.precision, **kw).to(dev)
     model.rng_seed = 42
-    crit = M.VAELoss(**lkw)
+    dis = wl_shape(wl)[2]
+    crit = (M.DisentangledVAELoss if dis else M.VAELoss)(**lkw)
     ts = TrainStep(model, crit, micro_batch=micro, **OPT)
-    x_h, _lab, onehot_h, _idx = synthetic_batch(bpg, kw["input_channels"], kw["resolution"], first_index=rank * bpg,
-                                                pin=True)
-    cond_h = onehot_h if conditional else None
+    x_h, cond_h = wl_batch(wl, bpg, first_index=rank * bpg, pin=True)
     x_d = x_h.to(dev)
-    cond_d = cond_h.to(dev) if conditional else None
+    # the disentangled model takes its modality indices from the host (no device->host read in the step)
+    cond_d = cond_h if (dis or cond_h is None) else cond_h.to(dev)
 
     def barrier():
         if world > 1:
@@ -349,7 +377,8 @@ def b200_arm(args):
             "dtype": args.precision, "data": "synthetic",
             "config": workload_config(wl, args, bpg, world),
             "e2e": {"value": round(e2e_v, 2), "unit": "images/s",
-                    "h2d_bytes_per_step": int(x_h.numel() * 4 + (cond_h.numel() * 4 if conditional else 0)),
+                    "h2d_bytes_per_step": int(x_h.numel() * 4 + (cond_h.numel() * cond_h.element_size()
+                                                                 if cond_h is not None else 0)),
                     "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 3)},
             "gpu_launches": int(launches),
             "roofline": roof,

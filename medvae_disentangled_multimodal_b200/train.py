@@ -149,7 +149,8 @@ def backward_order(model: nn.Module) -> List[nn.Parameter]:
 
 
 class TrainStep:
-    """One optimisation step of a BaseVAE / BetaVAE / ConditionalVAE on this rank's shard."""
+    """One optimisation step of a BaseVAE / BetaVAE / ConditionalVAE / DisentangledConditionalVAE on this
+    rank's shard."""
 
     def __init__(self, model: nn.Module, criterion: nn.Module, *, lr: float = 1e-4, weight_decay: float = 1e-4,
                  betas=(0.9, 0.999), eps: float = 1e-8, decoupled: bool = True, max_norm: float = 1.0,
@@ -189,31 +190,50 @@ class TrainStep:
         return t.to(self.device, non_blocking=True)
 
     def step(self, x: torch.Tensor, cond: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
-        """x: (B, C, H, W) fp32 in [-1, 1]; cond: (B, n_modalities) one-hot or None.  Host tensors
-        are copied to the device here (use pinned memory for an asynchronous copy)."""
-        x, cond = self._to_device(x), self._to_device(cond)
+        """x: (B, C, H, W) fp32 in [-1, 1]; cond: (B, n_modalities) one-hot, None, or — for a
+        DisentangledConditionalVAE with DisentangledVAELoss — the (B,) int64 modality indices
+        (lightning_module.py:116-118).  Host tensors are copied to the device here (use pinned
+        memory for an asynchronous copy); a host index vector also stays on the host, which saves
+        the model's one device->host read (the reconstruction-width decision).
+
+        Micro-batching a disentangled step evaluates the two batch-coupled latent losses per
+        micro-batch (what the reference does under ``accumulate_grad_batches``); leave
+        ``micro_batch`` unset to get the whole-shard losses of the reference's plain step."""
+        disentangled = hasattr(self.criterion, "separation_weight")   # the reference's own test (:191)
+        x = self._to_device(x)
+        if not disentangled:
+            cond = self._to_device(cond)
         n = x.shape[0]
         mb = self.micro_batch or n
         chunks = [(i, min(i + mb, n)) for i in range(0, n, mb)]
         self.buckets.zero()
         totals: Dict[str, torch.Tensor] = {}
+        # verification hook: externally supplied reparameterisation noise follows the micro-batch split
+        eps_full = getattr(self.model, "eps_override", None)
         for ci, (a, b) in enumerate(chunks):
             last = ci == len(chunks) - 1
             self.buckets.reduce_enabled = last
             self.buckets.begin_round()
             xs = x[a:b]
+            if eps_full is not None and len(chunks) > 1:
+                self.model.eps_override = eps_full[a:b]
             if cond is not None:
                 out = self.model(xs, cond[a:b])
             else:
                 out = self.model(xs)
-            ld = self.criterion(inputs=xs, reconstructions=out["reconstruction"], posteriors=out["posterior"],
-                                priors=out["prior"])
+            if disentangled:
+                ld = self.criterion(out, xs)
+            else:
+                ld = self.criterion(inputs=xs, reconstructions=out["reconstruction"], posteriors=out["posterior"],
+                                    priors=out["prior"])
             w = (b - a) / n
             (ld["loss"] * w if len(chunks) > 1 else ld["loss"]).backward()
             for k, v in ld.items():
                 v = v.detach() * w if len(chunks) > 1 else v.detach()
                 totals[k] = v if k not in totals else totals[k] + v
             del out, ld
+        if eps_full is not None:
+            self.model.eps_override = eps_full
         self.buckets.finish()
         self.optimizer.step()
         return totals

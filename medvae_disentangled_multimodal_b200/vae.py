@@ -166,6 +166,9 @@ class BaseVAE(nn.Module):
         mom = self._moments_nhwc(x, condition)
         eps = self.eps_override
         if eps is not None:
+            if eps.shape[0] != mom.shape[0] or eps.numel() * 2 != mom.numel():
+                raise ValueError(f"eps_override has shape {tuple(eps.shape)} but the latent of this batch is "
+                                 f"({mom.shape[0]}, {mom.shape[3] // 2}, {mom.shape[1]}, {mom.shape[2]})")
             eps = eps.to(mom.device).float().contiguous()
         return _EncodeSampleFn.apply(self, mom, eps, float(self._latent_clamp))
 

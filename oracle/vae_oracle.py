@@ -310,16 +310,24 @@ class ReferenceTrainer:
     test and timed by bench.py as the CPU baseline ("port")."""
 
     def __init__(self, sd: SD, lr=1e-4, weight_decay=1e-4, betas=(0.9, 0.999), max_norm=1.0, decoupled=True,
-                 loss_kwargs=None):
+                 loss_kwargs=None, disentangled=None):
+        """disentangled = (shared_latent_dim, modality_latent_dim) switches to the
+        DisentangledConditionalVAE forward + DisentangledVAELoss (``condition`` is then the int64
+        modality index vector, lightning_module.py:116-118,191-196)."""
         self.params = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
         cls = torch.optim.AdamW if decoupled else torch.optim.Adam
         self.opt = cls(list(self.params.values()), lr=lr, weight_decay=weight_decay, betas=betas)
         self.max_norm = max_norm
         self.loss_kwargs = loss_kwargs or {}
+        self.disentangled = disentangled
 
     def step(self, x, eps, condition=None):
-        out = vae_forward(self.params, x, eps, condition)
-        ld = vae_loss(out["reconstruction"], x, out["mean"], out["logvar"], **self.loss_kwargs)
+        if self.disentangled is not None:
+            out = dis_forward(self.params, x, condition, eps, *self.disentangled)
+            ld = dis_loss(out, x, **self.loss_kwargs)
+        else:
+            out = vae_forward(self.params, x, eps, condition)
+            ld = vae_loss(out["reconstruction"], x, out["mean"], out["logvar"], **self.loss_kwargs)
         self.opt.zero_grad(set_to_none=True)
         ld["loss"].backward()
         for p in self.params.values():

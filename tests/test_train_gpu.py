@@ -78,3 +78,34 @@ def test_micro_batching_equals_one_batch():
     c2, _r, _ = _curves("fp32", 6, micro_batch=4)
     for a, b in zip(c1, c2):
         assert abs(a - b) <= 2e-5 * abs(a)
+
+
+def test_disentangled_train_step_tracks_the_reference():
+    """TrainStep on DisentangledConditionalVAE + DisentangledVAELoss (modality indices instead of a
+    one-hot, criterion(outputs, x) — lightning_module.py:116-118,191-196): 10 fp32-mode steps against the
+    oracle's restatement, loss terms step by step."""
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200.data import GRAY_5, synthetic_batch
+    from medvae_disentangled_multimodal_b200.train import TrainStep
+    kw = dict(num_modalities=5, shared_latent_dim=8, modality_latent_dim=8, resolution=16, hidden_channels=32,
+              ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=[8])
+    lkw = dict(recon_loss_type="mse", kl_weight=1.0, recon_weight=1.0, separation_weight=0.1, contrastive_weight=0.05)
+    torch.manual_seed(5)
+    model = M.DisentangledConditionalVAE(compute_dtype="fp32", **kw)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    x, _lab, _oh, idx = synthetic_batch(10, 3, 16, n_modalities=5, gray=GRAY_5, seed=9)
+    g = torch.Generator().manual_seed(23)
+    eps = [torch.randn(10, 16, 8, 8, generator=g) for _ in range(10)]
+    ref = O.ReferenceTrainer(sd, loss_kwargs=lkw, disentangled=(8, 8), **OPT)
+    model = model.to(DEV)
+    ts = TrainStep(model, M.DisentangledVAELoss(**lkw), **OPT)
+    first = None
+    for i in range(10):
+        want = ref.step(x, eps[i], idx)
+        first = want["loss"] if first is None else first
+        model.eps_override = eps[i].to(DEV)
+        got = ts.step(x.to(DEV), idx)            # host index vector: no device->host read inside the step
+        for k in ("loss", "recon_loss", "kl_loss", "separation_loss", "contrastive_loss"):
+            assert abs(float(got[k]) - want[k]) <= 1e-3 * max(1.0, abs(want[k])), (i, k, float(got[k]), want[k])
+    ts.close()
+    assert want["loss"] < first          # it trains
