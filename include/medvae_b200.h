@@ -287,6 +287,64 @@ int mvae_dis_loss_total(const float* recon, const float* kl, const float* sep, c
                         float w_recon, float w_kl, float w_sep, float w_con, float* out5, float* mask4,
                         void* stream);
 
+/* ---- callers either side of the training step ------------------------------------ */
+
+/* LinearAttention / LinAttnBlock core (src/models/encoder_decoder.py:36-65; heads=1, dim_head=C) on the
+ * fused NHWC qkv tensor [B][T][3C] (to_qkv output): ks = softmax over tokens of k, ctx = ks^T v,
+ * out = q ctx.  ks: fp32 [B][T][C], ctx: fp32 [B][C][C], both kept for the backward.
+ * Backward scratch: dctx fp32 [B][C][C], dks fp32 [B][T][C]. */
+int mvae_linattn_core_fwd(const void* qkv, void* out, float* ks, float* ctx, int32_t batch, int32_t tokens,
+                          int32_t c, int32_t dtype, void* stream);
+int mvae_linattn_core_bwd(const void* qkv, const float* ks, const float* ctx, const void* dout, void* dqkv,
+                          float* dctx, float* dks, int32_t batch, int32_t tokens, int32_t c, int32_t dtype,
+                          void* stream);
+
+/* nn.Dropout inside ResnetBlock (src/models/encoder_decoder.py:164): y = x * keep / (1-p) over n elements,
+ * keep from Philox4x32-10 (seed, offset, element) or, if mask_in != NULL, from that byte mask
+ * (verification hook).  mask_out (may be NULL) receives the mask used.  The backward is the same call
+ * on the incoming gradient with the same (seed, offset) or mask. */
+int mvae_dropout_apply(const void* x, void* y, int64_t n, float p, uint64_t seed, uint64_t offset,
+                       const uint8_t* mask_in, uint8_t* mask_out, int32_t dtype, void* stream);
+
+/* FiLMLayer (src/models/conditional_vae.py:191-203): out = features * (Ws c + bs) + (Wt c + bt).
+ * features/out: NCHW fp32 [B][C][HW]; cond: [B][K]; Ws, Wt: [C][K]; st: fp32 [2][B][C] receives the
+ * per-sample scale and shift (kept for the backward).  Backward writes d_features, the four parameter
+ * gradients and (if d_cond != NULL) the condition gradient; dst: fp32 scratch [2][B][C]. */
+int mvae_film_fwd(const float* features, const float* cond, const float* w_scale, const float* b_scale,
+                  const float* w_shift, const float* b_shift, float* out, float* st, int32_t batch,
+                  int32_t c, int32_t hw, int32_t k, void* stream);
+int mvae_film_bwd(const float* d_out, const float* features, const float* cond, const float* w_scale,
+                  const float* w_shift, const float* st, float* d_features, float* dst, float* d_w_scale,
+                  float* d_b_scale, float* d_w_shift, float* d_b_shift, float* d_cond, int32_t batch,
+                  int32_t c, int32_t hw, int32_t k, void* stream);
+
+/* Batch feed (src/data/medmnist_data.py:186-251 __getitem__, :372-380 Normalize(0.5, 0.5), :16-72
+ * mixed_modality_collate_fn) over a staged uint8 batch src [B][H][W][src_stride_c] (1 or 3 wide):
+ * per sample, src_c[b] in {1,3} valid source channels and tgt_c[b] in {1,3} the modality's channel count;
+ * u8/255, RGB->gray 0.299/0.587/0.114 or gray->RGB repeat, (v-0.5)/0.5, zero-pad to out_c channels.
+ * x: NCHW fp32 [B][out_c][H][W]; onehot (may be NULL): fp32 [B][n_mod] from idx.  Bit-identical to the
+ * reference's fp32 host arithmetic. */
+int mvae_batch_feed_u8(const uint8_t* src, const int32_t* src_c, const int32_t* tgt_c, const int64_t* idx,
+                       float* x, float* onehot, int32_t batch, int32_t h, int32_t w, int32_t src_stride_c,
+                       int32_t out_c, int32_t n_mod, void* stream);
+
+/* Validation metrics (src/utils/metrics.py:14-102; torchmetrics PSNR / SSIM with data_range as given,
+ * gaussian 11x11 sigma 1.5, k1 0.01, k2 0.03).  All results stay on the device.
+ * recon: original/recon NCHW fp32 with planes = B*C images of H x W; out4 = (mse, mae, psnr, ssim);
+ *        ws: mvae_recon_metrics_ws_doubles() doubles.
+ * kl:    mean/logvar fp32 [B][C][S] (S = product of trailing dims; a "sample" of kl_mean / kl_std is one
+ *        (b, s) pair, as `sum(dim=1)` makes it); out4 = (kl_total, kl_mean, kl_std, kl_per_dim_mean).
+ * latent: z fp32 [B][D]; out3 = (latent_mean_avg, latent_std_avg, latent_sparsity(|z| < thr)).
+ * kl / latent ws: mvae_stat_metrics_ws_doubles() doubles. */
+int64_t mvae_recon_metrics_ws_doubles(int32_t planes, int32_t h, int32_t w);
+int64_t mvae_stat_metrics_ws_doubles(void);
+int mvae_recon_metrics(const float* original, const float* recon, int32_t planes, int32_t h, int32_t w,
+                       float data_range, double* ws, float* out4, void* stream);
+int mvae_kl_metrics(const float* mean, const float* logvar, int32_t batch, int32_t c, int32_t s, double* ws,
+                    float* out4, void* stream);
+int mvae_latent_metrics(const float* z, int32_t batch, int64_t d, float thr, double* ws, float* out3,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

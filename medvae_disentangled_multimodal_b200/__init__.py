@@ -5,12 +5,12 @@ parsakzr/medvae-disentangled-multimodal: same class names, co
 kwargs, methods, output-dict keys and state_dict keys; the arithmetic runs in hand-written CUDA
 kernels behind the C ABI in include/medvae_b200.h.  There is no CPU fallback.
 """
-from .blocks import AttnBlock, Decoder, Downsample, Encoder, ResnetBlock, Upsample
+from .blocks import AttnBlock, Decoder, Downsample, Encoder, LinAttnBlock, LinearAttention, ResnetBlock, Upsample
 from .losses import VAELoss
 from .vae import BaseVAE, BetaVAE, ConditionalVAE, FiLMLayer
 
 __all__ = ["BaseVAE", "BetaVAE", "ConditionalVAE", "Encoder", "Decoder", "VAELoss", "ResnetBlock", "AttnBlock",
-           "Downsample", "Upsample", "FiLMLayer"]
+           "Downsample", "Upsample", "FiLMLayer", "LinearAttention", "LinAttnBlock"]
 
 try:  # the disentangled model lives in its own module
     from .disentangled import DisentangledConditionalVAE, DisentangledVAELoss  # noqa: F401

@@ -85,12 +85,31 @@ class Upsample(nn.Module):
         self.conv = nn.Conv2d(in_channels, in_channels, 3, 1, 1)
 
 
+class LinearAttention(nn.Module):
+    """encoder_decoder.py:36-59 (parameter container; heads * dim_head hidden channels)."""
+
+    def __init__(self, dim: int, heads: int = 4, dim_head: int = 32):
+        super().__init__()
+        self.heads = heads
+        hidden_dim = dim_head * heads
+        self.to_qkv = nn.Conv2d(dim, hidden_dim * 3, 1, bias=False)
+        self.to_out = nn.Conv2d(hidden_dim, dim, 1)
+
+
+class LinAttnBlock(LinearAttention):
+    """encoder_decoder.py:62-65: heads=1, dim_head=in_channels; no GroupNorm, no residual."""
+
+    def __init__(self, in_channels: int):
+        super().__init__(dim=in_channels, heads=1, dim_head=in_channels)
+        self.in_channels = in_channels
+
+
 def make_attn(in_channels: int, attn_type: str = "vanilla") -> nn.Module:
     """encoder_decoder.py:18-25."""
     if attn_type == "vanilla":
         return AttnBlock(in_channels)
     if attn_type == "linear":
-        raise NotImplementedError("attn_type='linear' (LinAttnBlock) is not built yet; no reference config uses it")
+        return LinAttnBlock(in_channels)
     raise NotImplementedError(f"Attention type {attn_type} not implemented")
 
 
@@ -111,6 +130,15 @@ class Run:
         self.fuse_gn = FUSE_GN and dtype == torch.bfloat16
         self.grads: Dict[nn.Parameter, torch.Tensor] = {}
         self.tape: list = []
+        self.dropout_seed = 0          # set by _StackFn from the owning stack
+        self.dropout_offset = 0
+        self.dropout_masks = None      # verification hook: {id(ResnetBlock): uint8 NHWC keep mask}
+
+    def next_dropout(self, blk):
+        """-> (seed, offset, mask override or None) for the next dropout site of this forward"""
+        self.dropout_offset += 1
+        m = self.dropout_masks.get(id(blk)) if self.dropout_masks else None
+        return self.dropout_seed, self.dropout_offset, m
 
     def add_grad(self, p: nn.Parameter, g: torch.Tensor):
         if self.sink is not None:
@@ -161,12 +189,12 @@ class ConvOp:
     def params(self):
         out = []
         for c in self.convs:
-            out += [c.weight, c.bias]
+            out += [c.weight] + ([c.bias] if c.bias is not None else [])
         return out
 
     def packed(self, run: Run, device):
         key = (tuple(id(c.weight) for c in self.convs), run.code, self.mode)
-        ver = tuple((c.weight._version, c.bias._version) for c in self.convs)
+        ver = tuple((c.weight._version, c.bias._version if c.bias is not None else 0) for c in self.convs)
         ent = run.cache.get(key)
         if ent is None or ent["ver"] != ver or ent["dev"] != device:
             cin_p, cout_p = self.cin_of(run.dtype), self.cout_of(run.dtype)
@@ -187,7 +215,9 @@ class ConvOp:
                     dd = ops.conv_desc(1, 8, 8, self.cin, c.out_channels, self.k, self.mode, run.code)
                     ops.conv_pack_weights(dd, c.weight.detach(), wf, wd, self.cout, off)
                     off += c.out_channels
-                if len(self.convs) == 1:
+                if len(self.convs) == 1 and self.convs[0].bias is None:
+                    bias = torch.zeros((self.cout,), dtype=torch.float32, device=device)   # Conv2d(bias=False)
+                elif len(self.convs) == 1:
                     bias = self.convs[0].bias.detach()
                 else:
                     bias = torch.cat([c.bias.detach() for c in self.convs]).contiguous()
@@ -213,9 +243,14 @@ class ConvOp:
         d = self.desc(run, b, h, w)
         ent = self.packed(run, x.device)
         vw = vb = None
-        if run.views is not None and len(self.convs) == 1 and d.in_c == self.cin and d.out_c == self.cout:
+        if len(self.convs) == 1 and self.convs[0].bias is None:
+            dw, _ = ops.conv_wgrad(d, x, dy, False)
+            run.add_grad(self.convs[0].weight, dw)
+        elif run.views is not None and len(self.convs) == 1 and d.in_c == self.cin and d.out_c == self.cout:
             vw, vb = run.views.view_of(self.convs[0].weight), run.views.view_of(self.convs[0].bias)
-        if vw is not None and vb is not None:
+        if len(self.convs) == 1 and self.convs[0].bias is None:
+            pass
+        elif vw is not None and vb is not None:
             # the wgrad finalisation adds into the flat gradient buffer (no temporary, no add pass)
             c = self.convs[0]
             ops.conv_wgrad_acc(d, x, dy, vw, vb if dy_colsum is None else None, 1.0)
@@ -288,22 +323,31 @@ class ResOp:
                 + (self.nin.params() if self.nin is not None else []) + [b.norm1.weight, b.norm1.bias])
 
     def fwd(self, run: Run, x, x_sums=None):
-        if self.p_drop > 0.0 and run.training:
-            raise NotImplementedError("dropout > 0 in training mode is not implemented (all full-size reference "
-                                      "configs use dropout 0.0)")
         blk = self.blk
         a1, st1 = gn_fwd(run, blk.norm1, x, True, x_sums)
         h1, h1_sums = self.c1.fwd(run, a1, gn_groups=blk.norm2.num_groups)
         a2, st2 = gn_fwd(run, blk.norm2, h1, True, h1_sums)
+        drop = None
+        if self.p_drop > 0.0 and run.training:
+            # nn.Dropout between swish(norm2(h)) and conv2 (encoder_decoder.py:164): Philox keep mask, regenerated
+            # in the backward from (seed, offset); a2 below is the dropped tensor conv2 consumes
+            drop = run.next_dropout(blk)
+            a2, _ = ops.dropout_apply(a2, self.p_drop, drop[0], drop[1], mask_in=drop[2])
         xs = self.nin.fwd(run, x)[0] if self.nin is not None else x
         out, out_sums = self.c2.fwd(run, a2, residual=xs, gn_groups=self.out_groups)
-        run.tape.append((self, (x, st1, a1, h1, st2, a2)))
+        run.tape.append((self, (x, st1, a1, h1, st2, a2, drop)))
         return out, out_sums
 
     def bwd(self, run: Run, saved, dout, dout_cs=None):
-        x, st1, a1, h1, st2, a2 = saved
+        x, st1, a1, h1, st2, a2, drop = saved
         blk = self.blk
-        d_a2, s12 = self.c2.bwd(run, a2, dout, dy_colsum=dout_cs, gn=(h1, st2, blk.norm2, True))
+        if drop is not None:
+            # the dropout sits between conv2's dgrad and the GroupNorm backward: no fused epilogue here
+            d_a2, _ = self.c2.bwd(run, a2, dout, dy_colsum=dout_cs)
+            d_a2, _ = ops.dropout_apply(d_a2, self.p_drop, drop[0], drop[1], mask_in=drop[2])
+            s12 = None
+        else:
+            d_a2, s12 = self.c2.bwd(run, a2, dout, dy_colsum=dout_cs, gn=(h1, st2, blk.norm2, True))
         d_h1, h1_cs = gn_bwd(run, blk.norm2, d_a2, h1, st2, None, True, s12)
         del d_a2
         d_a1, s12 = self.c1.bwd(run, a1, d_h1, dy_colsum=h1_cs, gn=(x, st1, blk.norm1, True))
@@ -340,6 +384,38 @@ class AttnOp:
         d_hn, s12 = self.qkv.bwd(run, hn, d_qkv, gn=(x, st, self.blk.norm, False))
         del d_qkv
         return gn_bwd(run, self.blk.norm, d_hn, x, st, dout, False, s12)
+
+
+class LinAttnOp:
+    """to_out(linear_attention(to_qkv(x)))  (encoder_decoder.py:46-59 with heads=1, dim_head=C): softmax of k over
+    the tokens, context = k v^T, out = context^T q.  No GroupNorm and no residual, as in the reference."""
+
+    def __init__(self, blk: LinAttnBlock):
+        self.blk = blk
+        self.in_groups, self.out_groups = 0, 0
+        self.qkv = ConvOp([blk.to_qkv], L.CONV_S1)
+        self.proj = ConvOp([blk.to_out], L.CONV_S1)
+
+    def params_backward_order(self):
+        return self.proj.params() + self.qkv.params()
+
+    def fwd(self, run: Run, x, x_sums=None):
+        qkv, _ = self.qkv.fwd(run, x)
+        o, ks, ctx = ops.linattn_fwd(qkv)
+        out, out_sums = self.proj.fwd(run, o, gn_groups=self.out_groups)
+        run.tape.append((self, (x, qkv, o, ks, ctx)))
+        return out, out_sums
+
+    def bwd(self, run: Run, saved, dout, dout_cs=None):
+        x, qkv, o, ks, ctx = saved
+        d_o, _ = self.proj.bwd(run, o, dout, dy_colsum=dout_cs)
+        d_qkv = ops.linattn_bwd(qkv, ks, ctx, d_o)
+        del d_o
+        return self.qkv.bwd(run, x, d_qkv)[0], None
+
+
+def attn_stage(blk: nn.Module):
+    return LinAttnOp(blk) if isinstance(blk, LinAttnBlock) else AttnOp(blk)
 
 
 class PlainConvOp:
@@ -420,6 +496,9 @@ class _Stack(nn.Module):
         self._grad_sink = None        # set by train.TrainStep: gradients go to its flat buckets
         self._grad_views = None       # set by train.TrainStep: the GradBuckets object itself
         self.compute_dtype = torch.bfloat16
+        self.dropout_seed: Optional[int] = None    # None: torch.initial_seed()
+        self._dropout_step = 0
+        self.dropout_mask_override = None          # verification hook: {ResnetBlock module: uint8 NHWC keep mask}
 
     def stages(self, need_input_grad: bool):
         raise NotImplementedError
@@ -438,6 +517,14 @@ class _StackFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, stack: "_Stack", need_input_grad: bool, x, *params):
         run = Run(x.dtype, stack._pack_cache, stack.training, stack._grad_sink, stack._grad_views)
+        if stack.training:
+            stack._dropout_step += 1
+            seed = stack.dropout_seed if stack.dropout_seed is not None else torch.initial_seed()
+            # one Philox stream per (stack, forward call); sites within the call take consecutive offsets
+            run.dropout_seed = (seed + 0x9E3779B97F4A7C15 * (2 if type(stack).__name__ == "Decoder" else 1)) & 0xFFFFFFFFFFFFFFFF
+            run.dropout_offset = stack._dropout_step << 16
+            if stack.dropout_mask_override:
+                run.dropout_masks = {id(k): v for k, v in stack.dropout_mask_override.items()}
         with torch.no_grad():
             y = run_forward(stack.stages(need_input_grad), run, x)
         ctx.run = run
@@ -512,10 +599,10 @@ class Encoder(_Stack):
             for ib, blk in enumerate(level.block):
                 st.append(ResOp(blk))
                 if len(level.attn) > 0:
-                    st.append(AttnOp(level.attn[ib]))
+                    st.append(attn_stage(level.attn[ib]))
             if hasattr(level, "downsample"):
                 st.append(PlainConvOp(level.downsample.conv, L.CONV_DOWN))
-        st += [ResOp(self.mid.block_1), AttnOp(self.mid.attn_1), ResOp(self.mid.block_2),
+        st += [ResOp(self.mid.block_1), attn_stage(self.mid.attn_1), ResOp(self.mid.block_2),
                HeadOp(self.norm_out, self.conv_out)]
         return link_stages(st)
 
@@ -577,13 +664,13 @@ class Decoder(_Stack):
 
     def stages(self, need_input_grad: bool):
         st = [PlainConvOp(self.conv_in, L.CONV_S1, need_dx=need_input_grad),
-              ResOp(self.mid.block_1), AttnOp(self.mid.attn_1), ResOp(self.mid.block_2)]
+              ResOp(self.mid.block_1), attn_stage(self.mid.attn_1), ResOp(self.mid.block_2)]
         for lv in reversed(range(self.num_resolutions)):
             level = self.up[lv]
             for ib, blk in enumerate(level.block):
                 st.append(ResOp(blk))
                 if len(level.attn) > 0:
-                    st.append(AttnOp(level.attn[ib]))
+                    st.append(attn_stage(level.attn[ib]))
             if hasattr(level, "upsample"):
                 st.append(PlainConvOp(level.upsample.conv, L.CONV_UP))
         st.append(HeadOp(self.norm_out, self.conv_out, pad_out=True))

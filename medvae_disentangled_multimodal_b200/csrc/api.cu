@@ -87,6 +87,25 @@ int adamw_step_chunked(float* const* params, const float* const* grads, float* c
                        const double* sqnorm, float max_norm, float lr, float b1, float b2, float eps, float wd,
                        int decoupled, int step, cudaStream_t st);
 
+int linattn_fwd(const void* qkv, void* out, float* ks, float* ctx, int B, int Tn, int C, int dtype, cudaStream_t st);
+int linattn_bwd(const void* qkv, const float* ks, const float* ctx, const void* dout, void* dqkv, float* dctx, float* dks,
+                int B, int Tn, int C, int dtype, cudaStream_t st);
+int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, const uint8_t* mask_in,
+                  uint8_t* mask_out, int dtype, cudaStream_t st);
+int film_fwd(const float* f, const float* cond, const float* ws, const float* bs, const float* wt, const float* bt, float* out,
+             float* st, int B, int C, int HW, int K, cudaStream_t s);
+int film_bwd(const float* dy, const float* f, const float* cond, const float* ws, const float* wt, const float* st, float* df,
+             float* dst, float* dws, float* dbs, float* dwt, float* dbt, float* dcond, int B, int C, int HW, int K,
+             cudaStream_t s);
+int batch_feed_u8(const uint8_t* src, const int* src_c, const int* tgt_c, const long long* idx, float* x, float* onehot, int B,
+                  int H, int W, int SC, int OC, int n_mod, cudaStream_t st);
+long long recon_metrics_ws_doubles(int planes, int H, int W);
+long long stat_metrics_ws_doubles();
+int recon_metrics(const float* x, const float* r, int planes, int H, int W, float data_range, double* ws, float* out,
+                  cudaStream_t st);
+int kl_metrics(const float* mean, const float* logvar, int B, int C, int S, double* ws, float* out, cudaStream_t st);
+int latent_metrics(const float* z, int B, long long D, float thr, double* ws, float* out, cudaStream_t st);
+
 static bool dtype_ok(int d) { return d == MVAE_F32 || d == MVAE_BF16; }
 
 static bool use_umma_gather(const mvae_conv_desc& d, const GatherProblem* ps, int np) {
@@ -483,6 +502,63 @@ int mvae_dis_loss_total(const float* recon, const float* kl, const float* sep, c
                         float w_sep, float w_con, float* out5, float* mask4, void* stream) {
     MVAE_CHECK(recon && kl && sep && con && out5 && mask4, "dis_loss_total: bad argument");
     return dis_total(recon, kl, sep, con, w_recon, w_kl, w_sep, w_con, out5, mask4, ST(stream));
+}
+
+int mvae_linattn_core_fwd(const void* qkv, void* out, float* ks, float* ctx, int32_t batch, int32_t tokens, int32_t c,
+                          int32_t dtype, void* stream) {
+    MVAE_CHECK(qkv && out && ks && ctx && dtype_ok(dtype) && batch > 0 && tokens > 0 && c > 0, "linattn_core_fwd: bad argument");
+    return linattn_fwd(qkv, out, ks, ctx, batch, tokens, c, dtype, ST(stream));
+}
+int mvae_linattn_core_bwd(const void* qkv, const float* ks, const float* ctx, const void* dout, void* dqkv, float* dctx,
+                          float* dks, int32_t batch, int32_t tokens, int32_t c, int32_t dtype, void* stream) {
+    MVAE_CHECK(qkv && ks && ctx && dout && dqkv && dctx && dks && dtype_ok(dtype), "linattn_core_bwd: bad argument");
+    return linattn_bwd(qkv, ks, ctx, dout, dqkv, dctx, dks, batch, tokens, c, dtype, ST(stream));
+}
+int mvae_dropout_apply(const void* x, void* y, int64_t n, float p, uint64_t seed, uint64_t offset, const uint8_t* mask_in,
+                       uint8_t* mask_out, int32_t dtype, void* stream) {
+    MVAE_CHECK(x && y && n > 0 && dtype_ok(dtype), "dropout_apply: bad argument");
+    MVAE_CHECK(p >= 0.f && p < 1.f, "dropout_apply: p must be in [0, 1), got %f", (double)p);
+    return dropout_apply(x, y, n, p, seed, offset, mask_in, mask_out, dtype, ST(stream));
+}
+int mvae_film_fwd(const float* features, const float* cond, const float* w_scale, const float* b_scale, const float* w_shift,
+                  const float* b_shift, float* out, float* st, int32_t batch, int32_t c, int32_t hw, int32_t k, void* stream) {
+    MVAE_CHECK(features && cond && w_scale && b_scale && w_shift && b_shift && out && st && batch > 0 && c > 0 && hw > 0 && k > 0,
+               "film_fwd: bad argument");
+    return film_fwd(features, cond, w_scale, b_scale, w_shift, b_shift, out, st, batch, c, hw, k, ST(stream));
+}
+int mvae_film_bwd(const float* d_out, const float* features, const float* cond, const float* w_scale, const float* w_shift,
+                  const float* st, float* d_features, float* dst, float* d_w_scale, float* d_b_scale, float* d_w_shift,
+                  float* d_b_shift, float* d_cond, int32_t batch, int32_t c, int32_t hw, int32_t k, void* stream) {
+    MVAE_CHECK(d_out && features && cond && w_scale && w_shift && st && d_features && dst && d_w_scale && d_b_scale &&
+                   d_w_shift && d_b_shift, "film_bwd: bad argument");
+    return film_bwd(d_out, features, cond, w_scale, w_shift, st, d_features, dst, d_w_scale, d_b_scale, d_w_shift, d_b_shift,
+                    d_cond, batch, c, hw, k, ST(stream));
+}
+int mvae_batch_feed_u8(const uint8_t* src, const int32_t* src_c, const int32_t* tgt_c, const int64_t* idx, float* x,
+                       float* onehot, int32_t batch, int32_t h, int32_t w, int32_t src_stride_c, int32_t out_c, int32_t n_mod,
+                       void* stream) {
+    MVAE_CHECK(src && src_c && tgt_c && x && batch > 0 && h > 0 && w > 0, "batch_feed_u8: bad argument");
+    MVAE_CHECK(src_stride_c == 1 || src_stride_c == 3, "batch_feed_u8: staged batches are 1 or 3 channels wide, got %d", src_stride_c);
+    MVAE_CHECK(out_c == 1 || out_c == 3, "batch_feed_u8: out_c must be 1 or 3, got %d", out_c);
+    MVAE_CHECK(onehot == nullptr || (idx && n_mod > 0), "batch_feed_u8: one-hot output needs idx and n_mod");
+    return batch_feed_u8(src, src_c, tgt_c, reinterpret_cast<const long long*>(idx), x, onehot, batch, h, w, src_stride_c,
+                         out_c, n_mod, ST(stream));
+}
+int64_t mvae_recon_metrics_ws_doubles(int32_t planes, int32_t h, int32_t w) { return recon_metrics_ws_doubles(planes, h, w); }
+int64_t mvae_stat_metrics_ws_doubles(void) { return stat_metrics_ws_doubles(); }
+int mvae_recon_metrics(const float* original, const float* recon, int32_t planes, int32_t h, int32_t w, float data_range,
+                       double* ws, float* out4, void* stream) {
+    MVAE_CHECK(original && recon && ws && out4 && planes > 0 && h > 0 && w > 0 && data_range > 0.f, "recon_metrics: bad argument");
+    return recon_metrics(original, recon, planes, h, w, data_range, ws, out4, ST(stream));
+}
+int mvae_kl_metrics(const float* mean, const float* logvar, int32_t batch, int32_t c, int32_t s, double* ws, float* out4,
+                    void* stream) {
+    MVAE_CHECK(mean && logvar && ws && out4 && batch > 0 && c > 0 && s > 0, "kl_metrics: bad argument");
+    return kl_metrics(mean, logvar, batch, c, s, ws, out4, ST(stream));
+}
+int mvae_latent_metrics(const float* z, int32_t batch, int64_t d, float thr, double* ws, float* out3, void* stream) {
+    MVAE_CHECK(z && ws && out3 && batch > 0 && d > 0, "latent_metrics: bad argument");
+    return latent_metrics(z, batch, d, thr, ws, out3, ST(stream));
 }
 
 }  // extern "C"

@@ -168,6 +168,118 @@ static int attn_bwd_t(const T* qkv, const float* probs, const T* dout, T* dqkv, 
     return bgemm<float, T, T>(ds, qkv, dqkv + C, g, st);
 }
 
+// ------------------------------------------------------------------ LinearAttention (encoder_decoder.py:36-65)
+// heads = 1, dim_head = C (LinAttnBlock): per image, on the fused NHWC qkv tensor [T][3C]
+//   ks = softmax over the TOKENS of k (per channel) ; ctx[d][e] = sum_t ks[t][d] v[t][e] ; out[t][e] = sum_d q[t][d] ctx[d][e]
+// No scale factor, no GroupNorm, no residual (the reference's block has none).  Generic SIMT path only: no
+// reference config enables attn_type="linear".
+template <typename T>
+__global__ void __launch_bounds__(256) colsoftmax_kernel(const T* __restrict__ qkv, float* __restrict__ ks, int B, int Tn, int C) {
+    const long long n = (long long)B * C;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(i / C), d = (int)(i % C);
+        const T* k = qkv + (long long)b * Tn * 3 * C + C + d;
+        float* o = ks + (long long)b * Tn * C + d;
+        float mx = -INFINITY;
+        for (int t = 0; t < Tn; ++t) mx = fmaxf(mx, to_f<T>(k[(long long)t * 3 * C]));
+        float sum = 0.f;
+        for (int t = 0; t < Tn; ++t) {
+            float e = expf(to_f<T>(k[(long long)t * 3 * C]) - mx);
+            o[(long long)t * C] = e;
+            sum += e;
+        }
+        const float inv = 1.f / sum;
+        for (int t = 0; t < Tn; ++t) o[(long long)t * C] *= inv;
+    }
+}
+// dk[t][d] = ks[t][d] * (dks[t][d] - sum_t' dks[t'][d] ks[t'][d]) -> dqkv[:, C + d]
+template <typename T>
+__global__ void __launch_bounds__(256) colsoftmax_bwd_kernel(const float* __restrict__ dks, const float* __restrict__ ks,
+                                                             T* __restrict__ dqkv, int B, int Tn, int C) {
+    const long long n = (long long)B * C;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(i / C), d = (int)(i % C);
+        const float* g = dks + (long long)b * Tn * C + d;
+        const float* p = ks + (long long)b * Tn * C + d;
+        T* o = dqkv + (long long)b * Tn * 3 * C + C + d;
+        float dot = 0.f;
+        for (int t = 0; t < Tn; ++t) dot = fmaf(g[(long long)t * C], p[(long long)t * C], dot);
+        for (int t = 0; t < Tn; ++t) o[(long long)t * 3 * C] = from_f<T>(p[(long long)t * C] * (g[(long long)t * C] - dot));
+    }
+}
+static int col_grid(long long n) {
+    long long g = (n + 255) / 256;
+    return (int)(g < 1 ? 1 : (g > 148 * 8 ? 148 * 8 : g));
+}
+
+// ks: fp32 [B][T][C], ctx: fp32 [B][C][C] (both kept for the backward)
+template <typename T>
+static int linattn_fwd_t(const T* qkv, T* out, float* ks, float* ctx, int B, int Tn, int C, cudaStream_t st) {
+    const long long qs = (long long)Tn * 3 * C, ts = (long long)Tn * C, cs = (long long)C * C;
+    colsoftmax_kernel<T><<<col_grid((long long)B * C), 256, 0, st>>>(qkv, ks, B, Tn, C);
+    MVAE_LAUNCH_CHECK();
+    BgemmArgs g;
+    g.batch = B; g.alpha = 1.f;
+    // ctx[d][e] = sum_t ks[t][d] v[t][e]
+    g.M = C; g.N = C; g.K = Tn;
+    g.a_b = ts; g.a_m = 1; g.a_k = C;
+    g.b_b = qs; g.b_k = 3 * C; g.b_n = 1;
+    g.c_b = cs; g.c_m = C;
+    if (bgemm<float, T, float>(ks, qkv + 2 * C, ctx, g, st)) return 1;
+    // out[t][e] = sum_d q[t][d] ctx[d][e]
+    g.M = Tn; g.N = C; g.K = C;
+    g.a_b = qs; g.a_m = 3 * C; g.a_k = 1;
+    g.b_b = cs; g.b_k = C; g.b_n = 1;
+    g.c_b = ts; g.c_m = C;
+    return bgemm<T, float, T>(qkv, ctx, out, g, st);
+}
+
+// dctx: fp32 [B][C][C] scratch, dks: fp32 [B][T][C] scratch
+template <typename T>
+static int linattn_bwd_t(const T* qkv, const float* ks, const float* ctx, const T* dout, T* dqkv, float* dctx, float* dks,
+                         int B, int Tn, int C, cudaStream_t st) {
+    const long long qs = (long long)Tn * 3 * C, ts = (long long)Tn * C, cs = (long long)C * C;
+    BgemmArgs g;
+    g.batch = B; g.alpha = 1.f;
+    // dq[t][d] = sum_e dout[t][e] ctx[d][e]
+    g.M = Tn; g.N = C; g.K = C;
+    g.a_b = ts; g.a_m = C; g.a_k = 1;
+    g.b_b = cs; g.b_k = 1; g.b_n = C;
+    g.c_b = qs; g.c_m = 3 * C;
+    if (bgemm<T, float, T>(dout, ctx, dqkv, g, st)) return 1;
+    // dctx[d][e] = sum_t q[t][d] dout[t][e]
+    g.M = C; g.N = C; g.K = Tn;
+    g.a_b = qs; g.a_m = 1; g.a_k = 3 * C;
+    g.b_b = ts; g.b_k = C; g.b_n = 1;
+    g.c_b = cs; g.c_m = C;
+    if (bgemm<T, T, float>(qkv, dout, dctx, g, st)) return 1;
+    // dv[t][e] = sum_d ks[t][d] dctx[d][e]
+    g.M = Tn; g.N = C; g.K = C;
+    g.a_b = ts; g.a_m = C; g.a_k = 1;
+    g.b_b = cs; g.b_k = C; g.b_n = 1;
+    g.c_b = qs; g.c_m = 3 * C;
+    if (bgemm<float, float, T>(ks, dctx, dqkv + 2 * C, g, st)) return 1;
+    // dks[t][d] = sum_e v[t][e] dctx[d][e]
+    g.a_b = qs; g.a_m = 3 * C; g.a_k = 1;
+    g.b_b = cs; g.b_k = 1; g.b_n = C;
+    g.c_b = ts; g.c_m = C;
+    if (bgemm<T, float, float>(qkv + 2 * C, dctx, dks, g, st)) return 1;
+    colsoftmax_bwd_kernel<T><<<col_grid((long long)B * C), 256, 0, st>>>(dks, ks, dqkv, B, Tn, C);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+int linattn_fwd(const void* qkv, void* out, float* ks, float* ctx, int B, int Tn, int C, int dtype, cudaStream_t st) {
+    if (dtype == MVAE_F32) return linattn_fwd_t<float>((const float*)qkv, (float*)out, ks, ctx, B, Tn, C, st);
+    return linattn_fwd_t<bf16>((const bf16*)qkv, (bf16*)out, ks, ctx, B, Tn, C, st);
+}
+int linattn_bwd(const void* qkv, const float* ks, const float* ctx, const void* dout, void* dqkv, float* dctx, float* dks,
+                int B, int Tn, int C, int dtype, cudaStream_t st) {
+    if (dtype == MVAE_F32)
+        return linattn_bwd_t<float>((const float*)qkv, ks, ctx, (const float*)dout, (float*)dqkv, dctx, dks, B, Tn, C, st);
+    return linattn_bwd_t<bf16>((const bf16*)qkv, ks, ctx, (const bf16*)dout, (bf16*)dqkv, dctx, dks, B, Tn, C, st);
+}
+
 // attn_umma.cu: tensor-core path (bf16, C % 64 == 0, T <= 256)
 bool attn_umma_ok(int Tn, int C);
 int attn_fwd_umma(const bf16* qkv, bf16* out, void* probs, int B, int Tn, int C, cudaStream_t st);

@@ -354,3 +354,95 @@ def dis_total(recon, kl, sep, con, weights):
     check(lib().mvae_dis_loss_total(ptr(recon), ptr(kl), ptr(sep), ptr(con), *[float(w) for w in weights], ptr(out5),
                                     ptr(mask4), stream()), "dis_loss_total")
     return out5, mask4
+
+
+# ------------------------------------------------------------------------------------------------
+# callers either side of the training step: linear attention, dropout, FiLM, batch feed,
+# validation metrics
+# ------------------------------------------------------------------------------------------------
+def linattn_fwd(qkv):
+    """qkv NHWC [B,H,W,3C] -> (out [B,H,W,C], ks fp32 [B,T,C], ctx fp32 [B,C,C])"""
+    b, h, w, c3 = qkv.shape
+    c, t = c3 // 3, h * w
+    out = torch.empty((b, h, w, c), dtype=qkv.dtype, device=qkv.device)
+    ks = torch.empty((b, t, c), dtype=torch.float32, device=qkv.device)
+    ctx = torch.empty((b, c, c), dtype=torch.float32, device=qkv.device)
+    check(lib().mvae_linattn_core_fwd(ptr(qkv), ptr(out), ptr(ks), ptr(ctx), b, t, c, L.code_of(qkv.dtype), stream()),
+          "linattn_core_fwd")
+    return out, ks, ctx
+
+
+def linattn_bwd(qkv, ks, ctx, dout):
+    b, h, w, c3 = qkv.shape
+    c, t = c3 // 3, h * w
+    dqkv = torch.empty_like(qkv)
+    dctx = scratch("linattn_dctx", 4 * b * c * c, qkv.device)
+    dks = scratch("linattn_dks", 4 * b * t * c, qkv.device)
+    check(lib().mvae_linattn_core_bwd(ptr(qkv), ptr(ks), ptr(ctx), ptr(dout), ptr(dqkv), ptr(dctx), ptr(dks), b, t, c,
+                                      L.code_of(qkv.dtype), stream()), "linattn_core_bwd")
+    return dqkv
+
+
+def dropout_apply(x, p, seed, offset, mask_in=None, want_mask=False):
+    """-> (y, mask or None); x any contiguous bf16/fp32 tensor, mask uint8 of the same shape"""
+    y = torch.empty_like(x)
+    mask = torch.empty(x.shape, dtype=torch.uint8, device=x.device) if want_mask else None
+    check(lib().mvae_dropout_apply(ptr(x), ptr(y), x.numel(), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF, int(offset),
+                                   ptr(mask_in), ptr(mask), L.code_of(x.dtype), stream()), "dropout_apply")
+    return y, mask
+
+
+def film_fwd(features, cond, ws, bs, wt, bt):
+    b, c, h, w = features.shape
+    out = torch.empty_like(features)
+    st = torch.empty((2, b, c), dtype=torch.float32, device=features.device)
+    check(lib().mvae_film_fwd(ptr(features), ptr(cond), ptr(ws), ptr(bs), ptr(wt), ptr(bt), ptr(out), ptr(st), b, c, h * w,
+                              cond.shape[1], stream()), "film_fwd")
+    return out, st
+
+
+def film_bwd(d_out, features, cond, ws, wt, st, need_dcond):
+    b, c, h, w = features.shape
+    k = cond.shape[1]
+    dev = features.device
+    df = torch.empty_like(features)
+    dst = torch.empty((2, b, c), dtype=torch.float32, device=dev)
+    dws, dwt = torch.empty((c, k), dtype=torch.float32, device=dev), torch.empty((c, k), dtype=torch.float32, device=dev)
+    dbs, dbt = torch.empty((c,), dtype=torch.float32, device=dev), torch.empty((c,), dtype=torch.float32, device=dev)
+    dcond = torch.empty((b, k), dtype=torch.float32, device=dev) if need_dcond else None
+    check(lib().mvae_film_bwd(ptr(d_out), ptr(features), ptr(cond), ptr(ws), ptr(wt), ptr(st), ptr(df), ptr(dst), ptr(dws),
+                              ptr(dbs), ptr(dwt), ptr(dbt), ptr(dcond), b, c, h * w, k, stream()), "film_bwd")
+    return df, dws, dbs, dwt, dbt, dcond
+
+
+def batch_feed_u8(src, src_c, tgt_c, idx, out_c, n_mod):
+    """src uint8 [B,H,W,SC] (device) -> (x fp32 NCHW [B,out_c,H,W], onehot fp32 [B,n_mod] or None)"""
+    b, h, w, sc = src.shape
+    x = torch.empty((b, out_c, h, w), dtype=torch.float32, device=src.device)
+    onehot = torch.empty((b, n_mod), dtype=torch.float32, device=src.device) if n_mod > 0 else None
+    check(lib().mvae_batch_feed_u8(ptr(src), ptr(src_c), ptr(tgt_c), ptr(idx), ptr(x), ptr(onehot), b, h, w, sc, out_c,
+                                   max(n_mod, 0), stream()), "batch_feed_u8")
+    return x, onehot
+
+
+def recon_metrics(original, recon, data_range, out):
+    """original/recon NCHW fp32 contiguous; out: fp32 device view of 4 elements (mse, mae, psnr, ssim)"""
+    b, c, h, w = original.shape
+    ws = scratch("metrics_ws", 8 * lib().mvae_recon_metrics_ws_doubles(b * c, h, w), original.device)
+    check(lib().mvae_recon_metrics(ptr(original), ptr(recon), b * c, h, w, float(data_range), ptr(ws), ptr(out), stream()),
+          "recon_metrics")
+
+
+def kl_metrics(mean, logvar, out):
+    """mean/logvar fp32 contiguous, >= 2-D; out: 4 floats (kl_total, kl_mean, kl_std, kl_per_dim_mean)"""
+    b, c = mean.shape[0], mean.shape[1]
+    s = mean.numel() // (b * c)
+    ws = scratch("metrics_ws_kl", 8 * lib().mvae_stat_metrics_ws_doubles(), mean.device)
+    check(lib().mvae_kl_metrics(ptr(mean), ptr(logvar), b, c, s, ptr(ws), ptr(out), stream()), "kl_metrics")
+
+
+def latent_metrics(z, thr, out):
+    """z fp32 [B, D] contiguous; out: 3 floats (latent_mean_avg, latent_std_avg, latent_sparsity)"""
+    ws = scratch("metrics_ws_lat", 8 * lib().mvae_stat_metrics_ws_doubles(), z.device)
+    check(lib().mvae_latent_metrics(ptr(z), z.shape[0], z.shape[1], float(thr), ptr(ws), ptr(out), stream()),
+          "latent_metrics")

@@ -237,3 +237,33 @@ class TrainStep:
         self.buckets.finish()
         self.optimizer.step()
         return totals
+
+    @torch.no_grad()
+    def validate(self, x: torch.Tensor, cond: Optional[torch.Tensor] = None, with_latent: bool = False) -> Dict[str, float]:
+        """validation_step of the reference (src/lightning_module.py:220-310): eval-mode forward, the
+        reconstruction / KL metrics of src/utils/metrics.py and the criterion's loss with its NaN/Inf ->
+        1e6 guard.  The metric kernels leave everything on the device; ONE device->host read returns
+        the whole dict (the reference pays one ``.item()`` per metric)."""
+        from .metrics import KL_KEYS, LATENT_KEYS, RECON_KEYS, validation_metrics_device
+        disentangled = hasattr(self.criterion, "separation_weight")
+        x = self._to_device(x)
+        if not disentangled:
+            cond = self._to_device(cond)
+        was_training = self.model.training
+        self.model.eval()
+        try:
+            out = self.model(x, cond) if cond is not None else self.model(x)
+            if disentangled:
+                ld = self.criterion(out, x)
+            else:
+                ld = self.criterion(inputs=x, reconstructions=out["reconstruction"], posteriors=out["posterior"],
+                                    priors=out["prior"])
+            vec = torch.cat([validation_metrics_device(x, out, with_latent), ld["loss"].detach().float().reshape(1)])
+        finally:
+            self.model.train(was_training)
+        vals = vec.tolist()
+        keys = RECON_KEYS + KL_KEYS + (LATENT_KEYS if with_latent else ())
+        res = {f"val/{k}": v for k, v in zip(keys, vals[:-1])}
+        loss = vals[-1]
+        res["val/loss"] = 1e6 if (loss != loss or loss in (float("inf"), float("-inf"))) else loss
+        return res

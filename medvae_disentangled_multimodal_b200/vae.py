@@ -235,9 +235,25 @@ DEFAULT_MODALITIES = ["chest_xray", "pathology", "oct", "pneumonia", "dermatosco
                       "retina", "breast_ultrasound", "abdominal_ct_a", "abdominal_ct_c", "abdominal_ct_s"]
 
 
+class _FiLMFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, features, cond, ws, bs, wt, bt):
+        out, st = ops.film_fwd(features, cond, ws, bs, wt, bt)
+        ctx.save_for_backward(features, cond, ws, wt, st)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        features, cond, ws, wt, st = ctx.saved_tensors
+        df, dws, dbs, dwt, dbt, dcond = ops.film_bwd(d_out.float().contiguous(), features, cond, ws, wt, st,
+                                                     ctx.needs_input_grad[1])
+        return df, dcond, dws, dbs, dwt, dbt
+
+
 class FiLMLayer(nn.Module):
-    """conditional_vae.py:191-203.  Parameters exist for state_dict parity when
-    condition_method="film"; like the reference, no forward path calls it."""
+    """conditional_vae.py:191-203: features * scale(c)[:, :, None, None] + shift(c)[:, :, None, None].
+    Built when condition_method="film"; like the reference, no model forward path calls it — the
+    op itself (one kernel forward, two backward) is provided for callers that do."""
 
     def __init__(self, condition_dim: int, feature_dim: int):
         super().__init__()
@@ -245,7 +261,13 @@ class FiLMLayer(nn.Module):
         self.shift_transform = nn.Linear(condition_dim, feature_dim)
 
     def forward(self, features: torch.Tensor, condition: torch.Tensor) -> torch.Tensor:
-        raise NotImplementedError("FiLMLayer is not wired into any forward path (neither here nor in the reference)")
+        L.require_device()
+        if features.dim() != 4 or condition.dim() != 2 or features.shape[1] != self.scale_transform.out_features:
+            raise RuntimeError(f"FiLMLayer expects features (B, {self.scale_transform.out_features}, H, W) and condition "
+                               f"(B, {self.scale_transform.in_features}), got {tuple(features.shape)} / {tuple(condition.shape)}")
+        return _FiLMFn.apply(features.float().contiguous(), condition.float().contiguous(),
+                             self.scale_transform.weight, self.scale_transform.bias,
+                             self.shift_transform.weight, self.shift_transform.bias)
 
 
 class ConditionalVAE(BaseVAE):

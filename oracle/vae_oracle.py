@@ -45,13 +45,35 @@ def conv(sd: SD, key: str, x, stride=1, padding=0):
     return F.conv2d(x, sd[key + ".weight"], sd[key + ".bias"], stride=stride, padding=padding)
 
 
+_DROPOUT = {"p": 0.0, "masks": None}
+
+
+class dropout_masks:
+    """``with dropout_masks(p, {block key: NCHW keep mask})``: training-mode nn.Dropout(p) of every ResnetBlock
+    (encoder_decoder.py:164) with the keep masks supplied from outside — torch's own dropout RNG cannot be
+    reproduced by another implementation, so parity is checked on identical masks."""
+
+    def __init__(self, p: float, masks: Dict[str, torch.Tensor]):
+        self.p, self.masks = p, masks
+
+    def __enter__(self):
+        self.prev = dict(_DROPOUT)
+        _DROPOUT.update(p=self.p, masks=self.masks)
+
+    def __exit__(self, *exc):
+        _DROPOUT.update(self.prev)
+
+
 def resnet_block(sd: SD, key: str, x, taps: Optional[dict] = None):
-    """encoder_decoder.py:148-170.  GN1-swish-conv1-GN2-swish-(dropout p=0)-conv2, 1x1
+    """encoder_decoder.py:148-170.  GN1-swish-conv1-GN2-swish-dropout-conv2, 1x1
     nin_shortcut iff the channel count changes (key present), output x + h."""
     h = conv(sd, key + ".conv1", swish(group_norm(sd, key + ".norm1", x)), padding=1)
     if taps is not None:
         taps[key + ".conv1"] = h
-    h = conv(sd, key + ".conv2", swish(group_norm(sd, key + ".norm2", h)), padding=1)
+    h = swish(group_norm(sd, key + ".norm2", h))
+    if _DROPOUT["masks"] is not None and _DROPOUT["p"] > 0.0:
+        h = h * _DROPOUT["masks"][key].to(h.dtype) / (1.0 - _DROPOUT["p"])
+    h = conv(sd, key + ".conv2", h, padding=1)
     if (key + ".nin_shortcut.weight") in sd:
         x = conv(sd, key + ".nin_shortcut", x)
     out = x + h
@@ -74,6 +96,29 @@ def attn_block(sd: SD, key: str, x, taps: Optional[dict] = None):
     if taps is not None:
         taps[key] = out
     return out
+
+
+def lin_attn_block(sd: SD, key: str, x, taps: Optional[dict] = None):
+    """encoder_decoder.py:36-65 (LinAttnBlock: heads=1, dim_head=C).  to_qkv (no bias) -> softmax of k over the
+    tokens -> context[d,e] = sum_n k[d,n] v[e,n] -> out[e,n] = sum_d context[d,e] q[d,n] -> to_out.  No norm,
+    no residual."""
+    b, c, hh, ww = x.shape
+    qkv = F.conv2d(x, sd[key + ".to_qkv.weight"])
+    q, k, v = qkv.reshape(b, 3, 1, c, hh * ww).unbind(1)          # "b (qkv heads c) h w -> qkv b heads c (h w)"
+    k = k.softmax(dim=-1)
+    context = torch.einsum("bhdn,bhen->bhde", k, v)
+    out = torch.einsum("bhde,bhdn->bhen", context, q).reshape(b, c, hh, ww)
+    out = conv(sd, key + ".to_out", out)
+    if taps is not None:
+        taps[key] = out
+    return out
+
+
+def any_attn_block(sd: SD, key: str, x, taps: Optional[dict] = None):
+    """make_attn (encoder_decoder.py:18-25): which block was built is visible from the state_dict keys"""
+    if (key + ".to_qkv.weight") in sd:
+        return lin_attn_block(sd, key, x, taps)
+    return attn_block(sd, key, x, taps)
 
 
 def downsample(sd: SD, key: str, x):
@@ -106,13 +151,13 @@ def encoder_forward(sd: SD, x, prefix="encoder", taps: Optional[dict] = None):
         for ib in range(n_blocks):
             h = resnet_block(sd, f"{prefix}.down.{lv}.block.{ib}", h, taps)
             if n_attn > 0:
-                h = attn_block(sd, f"{prefix}.down.{lv}.attn.{ib}", h, taps)
+                h = any_attn_block(sd, f"{prefix}.down.{lv}.attn.{ib}", h, taps)
         if f"{prefix}.down.{lv}.downsample.conv.weight" in sd:
             h = downsample(sd, f"{prefix}.down.{lv}.downsample", h)
             if taps is not None:
                 taps[f"{prefix}.down.{lv}.downsample"] = h
     h = resnet_block(sd, prefix + ".mid.block_1", h, taps)
-    h = attn_block(sd, prefix + ".mid.attn_1", h, taps)
+    h = any_attn_block(sd, prefix + ".mid.attn_1", h, taps)
     h = resnet_block(sd, prefix + ".mid.block_2", h, taps)
     h = swish(group_norm(sd, prefix + ".norm_out", h))
     h = conv(sd, prefix + ".conv_out", h, padding=1)
@@ -127,7 +172,7 @@ def decoder_forward(sd: SD, z, prefix="decoder", taps: Optional[dict] = None):
     if taps is not None:
         taps[prefix + ".conv_in"] = h
     h = resnet_block(sd, prefix + ".mid.block_1", h, taps)
-    h = attn_block(sd, prefix + ".mid.attn_1", h, taps)
+    h = any_attn_block(sd, prefix + ".mid.attn_1", h, taps)
     h = resnet_block(sd, prefix + ".mid.block_2", h, taps)
     n_levels = _count(sd, prefix + ".up")
     for lv in reversed(range(n_levels)):
@@ -136,7 +181,7 @@ def decoder_forward(sd: SD, z, prefix="decoder", taps: Optional[dict] = None):
         for ib in range(n_blocks):
             h = resnet_block(sd, f"{prefix}.up.{lv}.block.{ib}", h, taps)
             if n_attn > 0:
-                h = attn_block(sd, f"{prefix}.up.{lv}.attn.{ib}", h, taps)
+                h = any_attn_block(sd, f"{prefix}.up.{lv}.attn.{ib}", h, taps)
         if f"{prefix}.up.{lv}.upsample.conv.weight" in sd:
             h = upsample(sd, f"{prefix}.up.{lv}.upsample", h)
             if taps is not None:
