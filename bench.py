@@ -248,6 +248,16 @@ def load_peaks():
     return {"bf16_sustained": 1400.0, "bf16_burst": 1590.0, "hbm": 6650.0, "source": "fallback"}
 
 
+def load_traffic(wl):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (C4 only)"""
+    if wl != "c4":
+        return None
+    try:
+        return int(json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def b200_arm(args):
     import torch
     import torch.distributed as dist
@@ -352,7 +362,7 @@ def b200_arm(args):
             ach = fl / (ms * 1e9)
             roof = {"bound": "tensor", "kernel": "conv_gather_umma_kernel (implicit-GEMM conv fprop+dgrad, tcgen05)",
                     "achieved": round(ach, 2), "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
-                    "frac": round(ach / peaks["bf16_sustained"], 4), "traffic": None,
+                    "frac": round(ach / peaks["bf16_sustained"], 4), "traffic": load_traffic(wl),
                     "peak_source": f"{peaks['source']} (sustained: kernel timed inside a long step)",
                     "launches": n_l, "avg_launch_ms": round(ms / n_l, 4),
                     "algorithmic_gflop_per_launch": round(fl / n_l / 1e9, 2)}

@@ -192,19 +192,25 @@ __device__ __forceinline__ void gn_flush_any(int cpg_log2, const float* sa, cons
     else gn_flush<1>(sa, sb, dst, lane, uniform, valid);
 }
 
-template <int BN>
+// MT pixel tiles (128 rows each) share every weight stage: a CTA tile is (MT x 128) pixels x BN channels.
+// What bounds this kernel is the bytes an SM pulls from L2 per MMA cycle: 128 x 128 tiles need
+// (16 + 16) KB per 256 cycles = 128 B/clk, twice what 128 x 256 tiles need per FLOP of B traffic; pairing two
+// pixel tiles on one 128-channel weight stage brings N = 128 layers to (32 + 16) KB per 512 cycles = 96 B/clk,
+// the same as the 128 x 256 configuration.
+constexpr int A_TILE_BYTES = 128 * 128;                 // 128 rows x 64 bf16
+template <int BN, int MT>
 struct GatherCfg {
-    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
-    static constexpr int A_BYTES = 128 * 128;           // 128 rows x 64 bf16
+    static constexpr int A_BYTES = MT * A_TILE_BYTES;
     static constexpr int B_BYTES = BN * 128;
-    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;   // 128 / 256 / 512: powers of two
+    static constexpr int STAGES = (A_BYTES + B_BYTES >= 49152) ? 4 : (A_BYTES + B_BYTES >= 32768 ? 6 : 8);
+    static constexpr int TMEM_COLS = (2 * MT * BN < 32) ? 32 : 2 * MT * BN;   // 128 / 256 / 512: powers of two
     static constexpr int SMEM = 1024 + STAGES * (A_BYTES + B_BYTES) + 256;
 };
 
-template <int BN, int EPI>
+template <int BN, int EPI, int MT>
 __global__ void __launch_bounds__(gather_threads(EPI), 1)
 conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_constant__ GatherDev p) {
-    using Cfg = GatherCfg<BN>;
+    using Cfg = GatherCfg<BN, MT>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -243,25 +249,31 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
     const uint32_t tmem_base = *tmem_slot;
 
     const int kiters = p.taps.ntaps * p.kchunks;
-    const uint32_t stage_bytes = (uint32_t)p.rows * 128u + (uint32_t)Cfg::B_BYTES;
+    const uint32_t stage_bytes = (uint32_t)(MT * p.rows) * 128u + (uint32_t)Cfg::B_BYTES;
 
     if (warp == 0) {
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
                 const int nt = tile % p.n_tiles;
-                int mt = tile / p.n_tiles;
-                const int tx = mt % p.tiles_x; mt /= p.tiles_x;
-                const int ty = mt % p.tiles_y;
-                const int tn = mt / p.tiles_y;
-                const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bn;
+                int x0[MT], y0[MT], n0[MT];
+#pragma unroll
+                for (int j = 0; j < MT; ++j) {
+                    // pixel tile (tile / n_tiles) * MT + j; one past the last decodes to n0 >= B: the box is
+                    // entirely out of bounds, TMA zero-fills it and the epilogue stores nothing
+                    int mt = (tile / p.n_tiles) * MT + j;
+                    const int tx = mt % p.tiles_x; mt /= p.tiles_x;
+                    x0[j] = tx * p.bw; y0[j] = (mt % p.tiles_y) * p.bh; n0[j] = (mt / p.tiles_y) * p.bn;
+                }
                 for (int t = 0; t < p.taps.ntaps; ++t) {
                     const Tap tp = p.taps.t[t];
                     for (int kc = 0; kc < p.kchunks; ++kc) {
                         mbar_wait(&empty[stage], phase ^ 1u);
                         mbar_expect_tx(&full[stage], stage_bytes);
-                        tma_load_4d(sA + stage * Cfg::A_BYTES, &tm.a[tp.view], &full[stage], kc * 64,
-                                    x0 + tp.dx, y0 + tp.dy, n0);
+#pragma unroll
+                        for (int j = 0; j < MT; ++j)
+                            tma_load_4d(sA + stage * Cfg::A_BYTES + j * A_TILE_BYTES, &tm.a[tp.view], &full[stage], kc * 64,
+                                        x0[j] + tp.dx, y0[j] + tp.dy, n0[j]);
                         tma_load_3d(sB + stage * Cfg::B_BYTES, &tm.b, &full[stage], kc * 64, nt * BN, tp.slab);
                         if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                     }
@@ -276,7 +288,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
             for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
                 mbar_wait(&tempty[acc], acc_phase ^ 1u);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * MT * BN);
                 for (int it = 0; it < kiters; ++it) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
@@ -284,9 +296,12 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                     const uint32_t b0 = smem_u32(sB + stage * Cfg::B_BYTES);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        const uint64_t ad = smem_desc_sw128(a0 + k * 32, 16, 1024);
                         const uint64_t bd = smem_desc_sw128(b0 + k * 32, 16, 1024);
-                        umma_bf16(d_tmem, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+#pragma unroll
+                        for (int j = 0; j < MT; ++j) {
+                            const uint64_t ad = smem_desc_sw128(a0 + j * A_TILE_BYTES + k * 32, 16, 1024);
+                            umma_bf16(d_tmem + (uint32_t)(j * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                        }
                     }
                     umma_commit(&empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
@@ -305,7 +320,10 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
         int acc = 0; uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
             const int nt = tile % p.n_tiles;
-            int mt = tile / p.n_tiles;
+#pragma unroll 1
+          for (int j = 0; j < MT; ++j) {
+            const uint32_t acc_col = (uint32_t)(acc * MT * BN + j * BN);
+            int mt = (tile / p.n_tiles) * MT + j;
             const int tx = mt % p.tiles_x; mt /= p.tiles_x;
             const int ty = mt % p.tiles_y;
             const int tn = mt / p.tiles_y;
@@ -315,7 +333,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
             if (EPI == EPI_PLAIN) {
                 mbar_wait(&tfull[acc], acc_phase);
                 tc_fence_after();
-                const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+                const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_col;
 #pragma unroll 1
                 for (int c0 = 0; c0 < BN; c0 += 32) {
                     uint32_t v[32];
@@ -376,7 +394,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 }
                 mbar_wait(&tfull[acc], acc_phase);
                 tc_fence_after();
-                const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + chalf * CW);
+                const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_col + (uint32_t)(chalf * CW);
 #pragma unroll
                 for (int ci = 0; ci < XCH; ++ci) {
                     uint32_t v[32];
@@ -463,6 +481,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                     }
                 }
             }
+          }   // pixel tiles of this CTA tile
             tc_fence_before();
             mbar_arrive(&tempty[acc]);
             acc ^= 1;
@@ -486,25 +505,25 @@ bool umma_gather_ok(const GatherProblem& p) {
     return true;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, int MT>
 static int launch_gather_epi(const GatherTmaps& tm, GatherDev& d, cudaStream_t st) {
-    using Cfg = GatherCfg<BN>;
+    using Cfg = GatherCfg<BN, MT>;
     static bool attr_set = false;
     if (!attr_set) {
-        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg::SMEM));
         attr_set = true;
     }
     int grid = d.total_tiles < num_sms() ? d.total_tiles : num_sms();
-    conv_gather_umma_kernel<BN, EPI><<<grid, gather_threads(EPI), Cfg::SMEM, st>>>(tm, d);
+    conv_gather_umma_kernel<BN, EPI, MT><<<grid, gather_threads(EPI), Cfg::SMEM, st>>>(tm, d);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
-template <int BN>
+template <int BN, int MT>
 static int launch_gather(const GatherTmaps& tm, GatherDev& d, int epi, cudaStream_t st) {
-    if (epi == EPI_GN_STATS) return launch_gather_epi<BN, EPI_GN_STATS>(tm, d, st);
-    if (epi == EPI_GN_BWD) return launch_gather_epi<BN, EPI_GN_BWD>(tm, d, st);
-    return launch_gather_epi<BN, EPI_PLAIN>(tm, d, st);
+    if (epi == EPI_GN_STATS) return launch_gather_epi<BN, EPI_GN_STATS, MT>(tm, d, st);
+    if (epi == EPI_GN_BWD) return launch_gather_epi<BN, EPI_GN_BWD, MT>(tm, d, st);
+    return launch_gather_epi<BN, EPI_PLAIN, MT>(tm, d, st);
 }
 
 int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslabs, const float* bias,
@@ -529,7 +548,10 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     d.OW = p.OW; d.OH = p.OH; d.B = p.B;
     d.tiles_x = g.tiles_x; d.tiles_y = g.tiles_y; d.tiles_n = g.tiles_n;
     d.n_tiles = p.N / BN; d.kchunks = p.K / 64;
-    d.total_tiles = g.tiles_x * g.tiles_y * g.tiles_n * d.n_tiles;
+    // 128-channel tiles take two pixel tiles per weight stage when that still leaves every SM a CTA tile
+    const long long m_tiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
+    const int MT = (BN == 128 && debug_knob(5) == 0 && ((m_tiles + 1) / 2) * d.n_tiles >= num_sms()) ? 2 : 1;
+    d.total_tiles = (int)((m_tiles + MT - 1) / MT) * d.n_tiles;
     d.N = p.N;
     d.o_off = p.out_view.off; d.o_sn = p.out_view.sn; d.o_sy = p.out_view.sy; d.o_sx = p.out_view.sx;
     d.bias = bias; d.res = (const bf16*)residual; d.out = (bf16*)out;
@@ -547,9 +569,10 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
         d.gn_sums = hook->sums; d.gn_x = (const bf16*)hook->x; d.gn_stat = hook->stat;
         d.gn_gamma = hook->gamma; d.gn_beta = hook->beta;
     }
-    if (BN == 256) return launch_gather<256>(tm, d, epi, st);
-    if (BN == 128) return launch_gather<128>(tm, d, epi, st);
-    return launch_gather<64>(tm, d, epi, st);
+    if (BN == 256) return launch_gather<256, 1>(tm, d, epi, st);
+    if (BN == 128 && MT == 2) return launch_gather<128, 2>(tm, d, epi, st);
+    if (BN == 128) return launch_gather<128, 1>(tm, d, epi, st);
+    return launch_gather<64, 1>(tm, d, epi, st);
 }
 
 // ================================================================== reduce (wgrad)
@@ -574,20 +597,24 @@ struct ReduceDev {
 constexpr int R_PIX = 64;            // pixels (K) per stage
 constexpr int R_CHUNK = R_PIX * 128; // 64 pixels x 64 channels bf16 = 8 KB
 
-template <int MT, int BN>
+// NT filter taps per CTA share every dy stage (NT = 3 for 128 x 128 channel tiles: 16 KB of dy + 3 x 16 KB of x
+// per 768 MMA cycles = 85 B/clk instead of 128 B/clk with one tap per CTA).
+template <int MT, int BN, int NT>
 struct ReduceCfg {
     static constexpr int A_BYTES = MT * 2 * R_CHUNK;
-    static constexpr int B_BYTES = (BN / 64) * R_CHUNK;
+    static constexpr int B_TAP = (BN / 64) * R_CHUNK;
+    static constexpr int B_BYTES = NT * B_TAP;
     static constexpr int STAGE = A_BYTES + B_BYTES;
     static constexpr int STAGES = STAGE <= 32768 ? 6 : (STAGE <= 49152 ? 4 : 3);
-    static constexpr int TMEM_COLS = MT * BN;
+    static constexpr int ACC_COLS = MT * BN * NT;
+    static constexpr int TMEM_COLS = ACC_COLS <= 128 ? 128 : (ACC_COLS <= 256 ? 256 : 512);
     static constexpr int SMEM = 1024 + STAGES * STAGE + 256;
 };
 
-template <int MT, int BN>
+template <int MT, int BN, int NT>
 __global__ void __launch_bounds__(G_THREADS, 1)
 conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_constant__ ReduceDev p) {
-    using Cfg = ReduceCfg<MT, BN>;
+    using Cfg = ReduceCfg<MT, BN, NT>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -603,8 +630,9 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     int w = blockIdx.x;
     const int cit = w % p.ci_tiles; w /= p.ci_tiles;
     const int cot = w % p.co_tiles; w /= p.co_tiles;
-    const int slab_i = w % p.nslabs;
-    const int split = w / p.nslabs;
+    const int n_groups = p.nslabs / NT;           // NT consecutive taps (same dy view) per CTA
+    const int slab_i = (w % n_groups) * NT;
+    const int split = w / n_groups;
     const Tap tp = p.taps.t[slab_i];
     const int pt_beg = (int)(((long long)p.ptiles * split) / p.splits);
     const int pt_end = (int)(((long long)p.ptiles * (split + 1)) / p.splits);
@@ -618,7 +646,7 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     }
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tm.dy[tp.oview]);
-        prefetch_tmap(&tm.in[tp.view]);
+        for (int j = 0; j < NT; ++j) prefetch_tmap(&tm.in[p.taps.t[slab_i + j].view]);
     }
     if (warp == 1) {
         if (lane == 0) {
@@ -633,7 +661,7 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t stage_bytes = (uint32_t)p.rows * 128u * (MT * 2 + BN / 64);
+    const uint32_t stage_bytes = (uint32_t)p.rows * 128u * (MT * 2 + NT * (BN / 64));
 
     if (warp == 0) {
         if (lane == 0) {
@@ -652,9 +680,13 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
                 for (int c = 0; c < MT * 2; ++c)
                     tma_load_4d(a + c * R_CHUNK, &tm.dy[tp.oview], &full[stage], cot * (MT * 128) + c * 64, x0, y0, n0);
 #pragma unroll
-                for (int c = 0; c < BN / 64; ++c)
-                    tma_load_4d(b + c * R_CHUNK, &tm.in[tp.view], &full[stage], cit * BN + c * 64,
-                                x0 + tp.dx, y0 + tp.dy, n0);
+                for (int j = 0; j < NT; ++j) {
+                    const Tap tj = p.taps.t[slab_i + j];
+#pragma unroll
+                    for (int c = 0; c < BN / 64; ++c)
+                        tma_load_4d(b + j * Cfg::B_TAP + c * R_CHUNK, &tm.in[tj.view], &full[stage], cit * BN + c * 64,
+                                    x0 + tj.dx, y0 + tj.dy, n0);
+                }
                 if (++stage == STAGES) { stage = 0; phase ^= 1u; }
             }
         }
@@ -672,8 +704,11 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
 #pragma unroll
                     for (int k = 0; k < R_PIX / 16; ++k) {   // 16 pixels (= 16 rows of 128 B) per MMA
                         const uint64_t ad = smem_desc_sw128(a0 + m * 2 * R_CHUNK + k * 2048, R_CHUNK, 1024);
-                        const uint64_t bd = smem_desc_sw128(b0 + k * 2048, R_CHUNK, 1024);
-                        umma_bf16(tmem_base + (uint32_t)(m * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+#pragma unroll
+                        for (int j = 0; j < NT; ++j) {
+                            const uint64_t bd = smem_desc_sw128(b0 + j * Cfg::B_TAP + k * 2048, R_CHUNK, 1024);
+                            umma_bf16(tmem_base + (uint32_t)((m * NT + j) * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                        }
                     }
                 }
                 umma_commit(&empty[stage]);
@@ -688,11 +723,12 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
             tc_fence_after();
         }
 #pragma unroll 1
-        for (int m = 0; m < MT; ++m) {
+        for (int mj = 0; mj < MT * NT; ++mj) {
+            const int m = mj / NT, j = mj % NT;
             const int co = cot * (MT * 128) + m * 128 + quarter * 32 + lane;
             const bool co_ok = co < p.Cout;   // last co tile may be partly TMA zero fill
-            float* dst = p.partial + (((long long)split * p.nslabs + tp.slab) * p.Cout + co) * p.Cin + cit * BN;
-            const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(m * BN);
+            float* dst = p.partial + (((long long)split * p.nslabs + p.taps.t[slab_i + j].slab) * p.Cout + co) * p.Cin + cit * BN;
+            const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mj * BN);
 #pragma unroll 1
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 uint32_t v[32];
@@ -721,9 +757,16 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     }
 }
 
-static void reduce_tile(const ReduceProblem& p, int& MT, int& BN) {
+static void reduce_tile(const ReduceProblem& p, int& MT, int& BN, int& NT) {
     MT = p.Cout >= 256 ? 2 : 1;
     BN = p.Cin >= 256 ? 256 : 128;
+    // 128 x 128 channel tiles: three taps per CTA on one dy stage, when all taps read the same dy view
+    NT = 1;
+    if (MT == 1 && BN == 128 && p.taps.ntaps % 3 == 0 && debug_knob(6) == 0) {
+        NT = 3;
+        for (int t = 1; t < p.taps.ntaps; ++t)
+            if (p.taps.t[t].oview != p.taps.t[0].oview) NT = 1;
+    }
 }
 
 bool umma_reduce_ok(const ReduceProblem& p) {
@@ -738,11 +781,11 @@ bool umma_reduce_ok(const ReduceProblem& p) {
 }
 
 int umma_reduce_splits(const ReduceProblem& p) {
-    int MT, BN;
-    reduce_tile(p, MT, BN);
+    int MT, BN, NT;
+    reduce_tile(p, MT, BN, NT);
     BoxGeom g = box_geom(p.B, p.GH, p.GW, R_PIX);
     long long ptiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
-    long long items = (long long)p.taps.ntaps * ((p.Cout + MT * 128 - 1) / (MT * 128)) * ((p.Cin + BN - 1) / BN);
+    long long items = (long long)(p.taps.ntaps / NT) * ((p.Cout + MT * 128 - 1) / (MT * 128)) * ((p.Cin + BN - 1) / BN);
     // one wave of CTAs (one per SM): as many K-splits as fit, each with at least ~8 pixel tiles
     long long want = num_sms() / items;
     if (want < 1) want = 1;
@@ -753,16 +796,16 @@ int umma_reduce_splits(const ReduceProblem& p) {
     return (int)want;
 }
 
-template <int MT, int BN>
+template <int MT, int BN, int NT>
 static int launch_reduce(const ReduceTmaps& tm, const ReduceDev& d, long long grid, cudaStream_t st) {
-    using Cfg = ReduceCfg<MT, BN>;
+    using Cfg = ReduceCfg<MT, BN, NT>;
     static bool attr_set = false;
     if (!attr_set) {
-        MVAE_CUDA(cudaFuncSetAttribute(conv_reduce_umma_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MVAE_CUDA(cudaFuncSetAttribute(conv_reduce_umma_kernel<MT, BN, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg::SMEM));
         attr_set = true;
     }
-    conv_reduce_umma_kernel<MT, BN><<<(unsigned)grid, G_THREADS, Cfg::SMEM, st>>>(tm, d);
+    conv_reduce_umma_kernel<MT, BN, NT><<<(unsigned)grid, G_THREADS, Cfg::SMEM, st>>>(tm, d);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
@@ -770,8 +813,8 @@ static int launch_reduce(const ReduceTmaps& tm, const ReduceDev& d, long long gr
 int umma_reduce(const ReduceProblem& p, const void* in, const void* dy, float* partial, int splits,
                 cudaStream_t st) {
     MVAE_CHECK(umma_reduce_ok(p), "umma_reduce: unsupported shape Cout=%d Cin=%d", p.Cout, p.Cin);
-    int MT, BN;
-    reduce_tile(p, MT, BN);
+    int MT, BN, NT;
+    reduce_tile(p, MT, BN, NT);
     BoxGeom g = box_geom(p.B, p.GH, p.GW, R_PIX);
     ReduceTmaps tm;
     memset(&tm, 0, sizeof(tm));
@@ -791,11 +834,12 @@ int umma_reduce(const ReduceProblem& p, const void* in, const void* dy, float* p
     d.nslabs = p.taps.ntaps; d.splits = splits;
     d.Cout = p.Cout; d.Cin = p.Cin; d.partial = partial;
     d.taps = p.taps;
-    long long grid = (long long)d.co_tiles * d.ci_tiles * d.nslabs * splits;
-    if (MT == 2 && BN == 256) return launch_reduce<2, 256>(tm, d, grid, st);
-    if (MT == 2) return launch_reduce<2, 128>(tm, d, grid, st);
-    if (BN == 256) return launch_reduce<1, 256>(tm, d, grid, st);
-    return launch_reduce<1, 128>(tm, d, grid, st);
+    long long grid = (long long)d.co_tiles * d.ci_tiles * (d.nslabs / NT) * splits;
+    if (MT == 2 && BN == 256) return launch_reduce<2, 256, 1>(tm, d, grid, st);
+    if (MT == 2) return launch_reduce<2, 128, 1>(tm, d, grid, st);
+    if (BN == 256) return launch_reduce<1, 256, 1>(tm, d, grid, st);
+    if (NT == 3) return launch_reduce<1, 128, 3>(tm, d, grid, st);
+    return launch_reduce<1, 128, 1>(tm, d, grid, st);
 }
 
 }  // namespace mvae
