@@ -202,8 +202,12 @@ template <int BN, int MT>
 struct GatherCfg {
     static constexpr int A_BYTES = MT * A_TILE_BYTES;
     static constexpr int B_BYTES = BN * 128;
-    static constexpr int STAGES = (A_BYTES + B_BYTES >= 49152) ? 4 : (A_BYTES + B_BYTES >= 32768 ? 6 : 8);
-    static constexpr int TMEM_COLS = (2 * MT * BN < 32) ? 32 : 2 * MT * BN;   // 128 / 256 / 512: powers of two
+    static constexpr int STAGES = (A_BYTES + B_BYTES >= 65536) ? 3 : ((A_BYTES + B_BYTES >= 49152) ? 4 : (A_BYTES + B_BYTES >= 32768 ? 6 : 8));
+    // accumulators are double-buffered (the epilogue of one CTA tile runs under the MMAs of the next) while they fit
+    // the 512 TMEM columns; the 256 x 256 tile (MT = 2, BN = 256) uses all 512 for one buffer and pays an exposed
+    // epilogue for halving the bytes pulled per FLOP (64 KB per 1024 MMA cycles = 64 B/clk, the SM's ingest rate)
+    static constexpr int ACC_BUFS = (2 * MT * BN <= 512) ? 2 : 1;
+    static constexpr int TMEM_COLS = (ACC_BUFS * MT * BN < 32) ? 32 : ACC_BUFS * MT * BN;   // powers of two
     static constexpr int SMEM = 1024 + STAGES * (A_BYTES + B_BYTES) + 256;
 };
 
@@ -307,8 +311,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
                 umma_commit(&tfull[acc]);
-                acc ^= 1;
-                if (acc == 0) acc_phase ^= 1u;
+                if (++acc == Cfg::ACC_BUFS) { acc = 0; acc_phase ^= 1u; }
             }
         }
     } else {
@@ -484,8 +487,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
           }   // pixel tiles of this CTA tile
             tc_fence_before();
             mbar_arrive(&tempty[acc]);
-            acc ^= 1;
-            if (acc == 0) acc_phase ^= 1u;
+            if (++acc == Cfg::ACC_BUFS) { acc = 0; acc_phase ^= 1u; }
         }
     }
     tc_fence_before();
@@ -550,7 +552,14 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     d.n_tiles = p.N / BN; d.kchunks = p.K / 64;
     // 128-channel tiles take two pixel tiles per weight stage when that still leaves every SM a CTA tile
     const long long m_tiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
-    const int MT = (BN == 128 && debug_knob(5) == 0 && ((m_tiles + 1) / 2) * d.n_tiles >= num_sms()) ? 2 : 1;
+    int MT = (BN == 128 && debug_knob(5) == 0 && ((m_tiles + 1) / 2) * d.n_tiles >= num_sms()) ? 2 : 1;
+    if (BN == 256 && debug_knob(7) == 1) {
+        // OPT-IN experiment (knob 7): 256 x 256 CTA tiles, 64 instead of 96 B/clk of ingest but a single accumulator
+        // buffer, i.e. an exposed epilogue.  Measured on C4 (r1e): fprop 16.7 -> 17.9 ms, dgrad 19.6 -> 21.6 ms per
+        // 256-image micro-batch — slower, so the default stays 128 x 256 with double-buffered accumulators.
+        const long long t1 = m_tiles * d.n_tiles, t2 = ((m_tiles + 1) / 2) * d.n_tiles, sms = num_sms();
+        if (t2 >= sms && 3 * ((t2 + sms - 1) / sms) < 2 * ((t1 + sms - 1) / sms)) MT = 2;
+    }
     d.total_tiles = (int)((m_tiles + MT - 1) / MT) * d.n_tiles;
     d.N = p.N;
     d.o_off = p.out_view.off; d.o_sn = p.out_view.sn; d.o_sy = p.out_view.sy; d.o_sx = p.out_view.sx;
@@ -569,6 +578,7 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
         d.gn_sums = hook->sums; d.gn_x = (const bf16*)hook->x; d.gn_stat = hook->stat;
         d.gn_gamma = hook->gamma; d.gn_beta = hook->beta;
     }
+    if (BN == 256 && MT == 2) return launch_gather<256, 2>(tm, d, epi, st);
     if (BN == 256) return launch_gather<256, 1>(tm, d, epi, st);
     if (BN == 128 && MT == 2) return launch_gather<128, 2>(tm, d, epi, st);
     if (BN == 128) return launch_gather<128, 1>(tm, d, epi, st);
