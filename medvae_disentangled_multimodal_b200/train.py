@@ -70,6 +70,7 @@ class GradBuckets:
             self.bounds.append([start, off]); self.members.append(count)
         self._pending = list(self.members)
         self._works: list = []
+        self._add_dst, self._add_src, self._add_par = [], [], []
         self.reduce_enabled = True
         self.launched = 0
         for p in self.params:
@@ -81,6 +82,9 @@ class GradBuckets:
         self._pending = list(self.members)
 
     def begin_round(self):
+        if self._add_par:
+            raise RuntimeError("GradBuckets.begin_round(): the previous round still has batched adds pending; "
+                               "call flush() when a backward pass ends")
         self._pending = list(self.members)
 
     def view_of(self, p: nn.Parameter):
@@ -88,10 +92,26 @@ class GradBuckets:
         then call mark_ready), or None for a parameter this object does not own"""
         return self.views.get(id(p))
 
+    FLUSH_AT = 64
+
     def accumulate(self, p: nn.Parameter, g: torch.Tensor):
-        """grad sink used by the encoder/decoder backward schedules: add into the flat view."""
-        self.views[id(p)].add_(g.view(p.shape))
-        self.mark_ready(p)
+        """grad sink used by the encoder/decoder backward schedules: add into the flat view.  The small
+        gradients (GroupNorm affine, biases: ~270 tensors per backward pass at C4) are batched and added
+        by one multi-tensor launch per FLUSH_AT tensors instead of one launch each."""
+        self._add_dst.append(self.views[id(p)])
+        self._add_src.append(g.view(p.shape))
+        self._add_par.append(p)
+        if len(self._add_par) >= self.FLUSH_AT:
+            self.flush()
+
+    def flush(self):
+        """apply the batched adds and report their parameters ready (call before the round ends)"""
+        if self._add_par:
+            torch._foreach_add_(self._add_dst, self._add_src)
+            pars = self._add_par
+            self._add_dst, self._add_src, self._add_par = [], [], []
+            for p in pars:
+                self.mark_ready(p)
 
     def mark_ready(self, p: nn.Parameter):
         b = self.bucket_of.get(id(p))
@@ -116,6 +136,7 @@ class GradBuckets:
     def finish(self):
         """wait for every outstanding bucket; buckets that never filled (unused parameters) are
         reduced now so all ranks stay in step."""
+        self.flush()
         if self.world > 1 and self.reduce_enabled:
             for b, left in enumerate(self._pending):
                 if left > 0:
@@ -228,6 +249,7 @@ class TrainStep:
                                     priors=out["prior"])
             w = (b - a) / n
             (ld["loss"] * w if len(chunks) > 1 else ld["loss"]).backward()
+            self.buckets.flush()
             for k, v in ld.items():
                 v = v.detach() * w if len(chunks) > 1 else v.detach()
                 totals[k] = v if k not in totals else totals[k] + v

@@ -39,6 +39,7 @@ def _worker(rank, world, port, q):
             gb.begin_round()
             for p, gr in zip(params, grads[mb]):
                 gb.accumulate(p, gr)
+            gb.flush()          # end of a backward pass: the batched small adds are applied and reported ready
         launched = gb.launched
         gb.finish()
         # expected: mean over ranks of the per-rank sums
