@@ -95,6 +95,9 @@ def parse():
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--knob", action="append", default=[], help="debug knob key=value for libmedvae_b200 (tuning)")
+    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
+                    help="replay the step as one CUDA graph (auto: on for the 28x28 workloads, whose eager step is bound "
+                         "by host launches)")
     return ap.parse_args()
 
 
@@ -178,6 +181,7 @@ def workload_config(wl, args, bpg, n, cpu=False):
                     f"latent {zc}, {'DisentangledVAELoss' if dis else 'VAELoss'} {lkw['recon_loss_type']} "
                     f"kl_weight {lkw['kl_weight']}, AdamW lr 1e-4 wd 1e-4 clip 1.0",
         "batch_per_gpu": bpg, "global_batch": bpg * n, "micro_batch": None if cpu else (args.micro_batch or min(bpg, 256)),
+        "cuda_graph": False if cpu else (args.graph == "on" or (args.graph == "auto" and wl in ("c1", "c2", "c3"))),
         "parallelism": f"dp{n}", "gflop_per_image_fwd_bwd": gflop,
         "cache": "inputs and activations larger than L2 (126 MB); no L2 flush needed",
     }
@@ -290,7 +294,8 @@ def b200_arm(args):
     model.rng_seed = 42
     dis = wl_shape(wl)[2]
     crit = (M.DisentangledVAELoss if dis else M.VAELoss)(**lkw)
-    ts = TrainStep(model, crit, micro_batch=micro, **OPT)
+    use_graph = args.graph == "on" or (args.graph == "auto" and wl in ("c1", "c2", "c3"))
+    ts = TrainStep(model, crit, micro_batch=micro, use_graph=use_graph, **OPT)
     x_h, cond_h = wl_batch(wl, bpg, first_index=rank * bpg, pin=True)
     x_d = x_h.to(dev)
     # the disentangled model takes its modality indices from the host (no device->host read in the step)
@@ -330,7 +335,7 @@ def b200_arm(args):
         sampler.start()
     n0 = L.lib().mvae_launch_count()
     ms_res = timed(step_resident, args.steps)
-    launches = (L.lib().mvae_launch_count() - n0)
+    launches = (L.lib().mvae_launch_count() - n0) + (ts.graph_launches * args.steps if ts._graph is not None else 0)
     ms_e2e = timed(step_e2e, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     loss_val = float(last["ld"]["loss"])
@@ -347,7 +352,7 @@ def b200_arm(args):
         # contains the gradient all-reduces), rank 0 reports
         timer = P.KernelTimer()
         P.install(timer)
-        ts.step(x_d, cond_d)
+        ts.step_eager(x_d, cond_d)
         P.install(None)
         summ = timer.summary() if rank == 0 else {}
         for k, d in summ.items():

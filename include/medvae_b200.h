@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define MVAE_ABI_VERSION 2
+#define MVAE_ABI_VERSION 3
 
 enum { MVAE_F32 = 0, MVAE_BF16 = 1 };
 
@@ -187,7 +187,7 @@ int mvae_nchw_f32_to_nhwc(const float* src, void* dst, int32_t batch, int32_t h,
 int mvae_reparam_kl_fwd(const void* moments, const float* eps, float* eps_out, float* mean,
                         float* logvar, float* std_out, float* z_nchw, void* z_nhwc, double* kl_sum,
                         int32_t batch, int32_t zc, int32_t r, float clamp, uint64_t seed,
-                        uint64_t offset, int32_t dtype, void* stream);
+                        uint64_t offset, const double* step_state, int32_t dtype, void* stream);
 /* d_moments (NHWC dtype) from d_mean, d_logvar, d_z (NCHW fp32, each may be NULL) and the
  * saved mean/logvar/eps; clamp masks the gradient like torch.clamp. */
 int mvae_reparam_kl_bwd(const float* d_mean, const float* d_logvar, const float* d_z,
@@ -233,7 +233,14 @@ int mvae_adamw_clip_step_chunked(float* const* params, const float* const* grads
                                  const int64_t* chunk_offset, const int32_t* chunk_len, int32_t n_chunks,
                                  const double* sqnorm_dev, float max_norm, float lr, float beta1,
                                  float beta2, float eps, float weight_decay, int32_t decoupled,
-                                 int32_t step, void* stream);
+                                 int32_t step, const double* step_state, void* stream);
+
+/* Device-resident per-step scalars, so that a CUDA-graph capture of the training step does not bake
+ * them into its kernel arguments: step_state = double[3] {optimizer step t, learning rate, Philox
+ * stream position}.  Entry points that take `step_state` (may be NULL = use the by-value arguments)
+ * read t / lr from it (mvae_adamw_clip_step_chunked) or add its position to `offset`
+ * (mvae_reparam_kl_fwd, mvae_dropout_apply).  mvae_step_state_advance: t += 1, position += rng_increment. */
+int mvae_step_state_advance(double* step_state, double rng_increment, void* stream);
 
 /* DisentangledConditionalVAE per-modality input projector
  * (disentangled_conditional_vae.py:124-171): out NHWC [B,H,W,out_c]; for modalities whose
@@ -304,7 +311,8 @@ int mvae_linattn_core_bwd(const void* qkv, const float* ks, const float* ctx, co
  * (verification hook).  mask_out (may be NULL) receives the mask used.  The backward is the same call
  * on the incoming gradient with the same (seed, offset) or mask. */
 int mvae_dropout_apply(const void* x, void* y, int64_t n, float p, uint64_t seed, uint64_t offset,
-                       const uint8_t* mask_in, uint8_t* mask_out, int32_t dtype, void* stream);
+                       const double* step_state, const uint8_t* mask_in, uint8_t* mask_out, int32_t dtype,
+                       void* stream);
 
 /* FiLMLayer (src/models/conditional_vae.py:191-203): out = features * (Ws c + bs) + (Wt c + bt).
  * features/out: NCHW fp32 [B][C][HW]; cond: [B][K]; Ws, Wt: [C][K]; st: fp32 [2][B][C] receives the

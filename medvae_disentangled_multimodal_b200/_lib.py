@@ -69,7 +69,7 @@ SIGNATURES = {
     "mvae_nhwc_to_nchw_f32": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_nchw_f32_to_nhwc": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_reparam_kl_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _f32, _u64, _u64,
-                                      _i32, _vp]),
+                                      _vp, _i32, _vp]),
     "mvae_reparam_kl_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _f32, _i32, _vp]),
     "mvae_recon_loss_fwd_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _vp]),
     "mvae_kl_fwd": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
@@ -80,7 +80,8 @@ SIGNATURES = {
                                        _i32, _vp]),
     "mvae_grad_sqnorm_chunked": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp]),
     "mvae_adamw_clip_step_chunked": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _f32, _f32, _f32, _f32, _f32,
-                                               _f32, _i32, _i32, _vp]),
+                                               _f32, _i32, _i32, _vp, _vp]),
+    "mvae_step_state_advance": (C.c_int, [_vp, C.c_double, _vp]),
     "mvae_dis_input_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_dis_input_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_dis_head_fwd": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32,
@@ -93,7 +94,7 @@ SIGNATURES = {
     "mvae_dis_loss_total": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _vp, _vp, _vp]),
     "mvae_linattn_core_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "mvae_linattn_core_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
-    "mvae_dropout_apply": (C.c_int, [_vp, _vp, _i64, _f32, _u64, _u64, _vp, _vp, _i32, _vp]),
+    "mvae_dropout_apply": (C.c_int, [_vp, _vp, _i64, _f32, _u64, _u64, _vp, _vp, _vp, _i32, _vp]),
     "mvae_film_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "mvae_film_bwd": (C.c_int, [_vp] * 13 + [_i32, _i32, _i32, _i32, _vp]),
     "mvae_batch_feed_u8": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),

@@ -133,6 +133,7 @@ class Run:
         self.dropout_seed = 0          # set by _StackFn from the owning stack
         self.dropout_offset = 0
         self.dropout_masks = None      # verification hook: {id(ResnetBlock): uint8 NHWC keep mask}
+        self.step_state = None         # device-side stream position (TrainStep graph mode)
 
     def next_dropout(self, blk):
         """-> (seed, offset, mask override or None) for the next dropout site of this forward"""
@@ -332,7 +333,7 @@ class ResOp:
             # nn.Dropout between swish(norm2(h)) and conv2 (encoder_decoder.py:164): Philox keep mask, regenerated
             # in the backward from (seed, offset); a2 below is the dropped tensor conv2 consumes
             drop = run.next_dropout(blk)
-            a2, _ = ops.dropout_apply(a2, self.p_drop, drop[0], drop[1], mask_in=drop[2])
+            a2, _ = ops.dropout_apply(a2, self.p_drop, drop[0], drop[1], mask_in=drop[2], step_state=run.step_state)
         xs = self.nin.fwd(run, x)[0] if self.nin is not None else x
         out, out_sums = self.c2.fwd(run, a2, residual=xs, gn_groups=self.out_groups)
         run.tape.append((self, (x, st1, a1, h1, st2, a2, drop)))
@@ -344,7 +345,7 @@ class ResOp:
         if drop is not None:
             # the dropout sits between conv2's dgrad and the GroupNorm backward: no fused epilogue here
             d_a2, _ = self.c2.bwd(run, a2, dout, dy_colsum=dout_cs)
-            d_a2, _ = ops.dropout_apply(d_a2, self.p_drop, drop[0], drop[1], mask_in=drop[2])
+            d_a2, _ = ops.dropout_apply(d_a2, self.p_drop, drop[0], drop[1], mask_in=drop[2], step_state=run.step_state)
             s12 = None
         else:
             d_a2, s12 = self.c2.bwd(run, a2, dout, dy_colsum=dout_cs, gn=(h1, st2, blk.norm2, True))
@@ -499,6 +500,7 @@ class _Stack(nn.Module):
         self.dropout_seed: Optional[int] = None    # None: torch.initial_seed()
         self._dropout_step = 0
         self.dropout_mask_override = None          # verification hook: {ResnetBlock module: uint8 NHWC keep mask}
+        self._step_state = None                    # device-side Philox position (train.TrainStep graph mode)
 
     def stages(self, need_input_grad: bool):
         raise NotImplementedError
@@ -523,6 +525,7 @@ class _StackFn(torch.autograd.Function):
             # one Philox stream per (stack, forward call); sites within the call take consecutive offsets
             run.dropout_seed = (seed + 0x9E3779B97F4A7C15 * (2 if type(stack).__name__ == "Decoder" else 1)) & 0xFFFFFFFFFFFFFFFF
             run.dropout_offset = stack._dropout_step << 16
+            run.step_state = stack._step_state
             if stack.dropout_mask_override:
                 run.dropout_masks = {id(k): v for k, v in stack.dropout_mask_override.items()}
         with torch.no_grad():

@@ -67,7 +67,8 @@ int attn_bwd(const void* qkv, const float* probs, const void* dout, void* dqkv, 
              int dtype, cudaStream_t st);
 int reparam_fwd(const void* mom, const float* eps, float* eps_out, float* mean, float* logvar, float* stdv,
                 float* z_nchw, void* z_nhwc, double* kl_sum, int B, int zc, int R, float clampv, uint64_t seed, uint64_t offset,
-                int dtype, cudaStream_t st);
+                const double* dyn, int dtype, cudaStream_t st);
+int step_state_advance(double* dyn, double rng_inc, cudaStream_t st);
 int reparam_bwd(const float* d_mean, const float* d_logvar, const float* d_z, const float* logvar, const float* eps,
                 const void* mom, void* d_mom, int B, int zc, int R, float clampv, int dtype, cudaStream_t st);
 int recon_loss(const float* r, const float* x, double* loss_sum, float* d_unit, long long n, int kind, cudaStream_t st);
@@ -85,13 +86,13 @@ int grad_sqnorm_chunked(const float* const* grads, const int* ch_tensor, const l
 int adamw_step_chunked(float* const* params, const float* const* grads, float* const* m1, float* const* m2,
                        const int* ch_tensor, const long long* ch_off, const int* ch_len, int n_chunks,
                        const double* sqnorm, float max_norm, float lr, float b1, float b2, float eps, float wd,
-                       int decoupled, int step, cudaStream_t st);
+                       int decoupled, int step, const double* dyn, cudaStream_t st);
 
 int linattn_fwd(const void* qkv, void* out, float* ks, float* ctx, int B, int Tn, int C, int dtype, cudaStream_t st);
 int linattn_bwd(const void* qkv, const float* ks, const float* ctx, const void* dout, void* dqkv, float* dctx, float* dks,
                 int B, int Tn, int C, int dtype, cudaStream_t st);
-int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, const uint8_t* mask_in,
-                  uint8_t* mask_out, int dtype, cudaStream_t st);
+int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, const double* dyn,
+                  const uint8_t* mask_in, uint8_t* mask_out, int dtype, cudaStream_t st);
 int film_fwd(const float* f, const float* cond, const float* ws, const float* bs, const float* wt, const float* bt, float* out,
              float* st, int B, int C, int HW, int K, cudaStream_t s);
 int film_bwd(const float* dy, const float* f, const float* cond, const float* ws, const float* wt, const float* st, float* df,
@@ -384,10 +385,10 @@ int mvae_nchw_f32_to_nhwc(const float* src, void* dst, int32_t batch, int32_t h,
 
 int mvae_reparam_kl_fwd(const void* moments, const float* eps, float* eps_out, float* mean, float* logvar,
                         float* std_out, float* z_nchw, void* z_nhwc, double* kl_sum, int32_t batch, int32_t zc, int32_t r, float clamp, uint64_t seed,
-                        uint64_t offset, int32_t dtype, void* stream) {
+                        uint64_t offset, const double* step_state, int32_t dtype, void* stream) {
     MVAE_CHECK(moments && mean && logvar && z_nchw && dtype_ok(dtype), "reparam_kl_fwd: bad argument");
     return reparam_fwd(moments, eps, eps_out, mean, logvar, std_out, z_nchw, z_nhwc, kl_sum, batch, zc, r, clamp, seed, offset,
-                       dtype, ST(stream));
+                       step_state, dtype, ST(stream));
 }
 int mvae_reparam_kl_bwd(const float* d_mean, const float* d_logvar, const float* d_z, const float* mean_unused,
                         const float* logvar, const float* eps, const void* moments, void* d_moments, int32_t batch,
@@ -439,12 +440,12 @@ int mvae_adamw_clip_step_chunked(float* const* params, const float* const* grads
                                  float* const* exp_avg_sq, const int32_t* chunk_tensor, const int64_t* chunk_offset,
                                  const int32_t* chunk_len, int32_t n_chunks, const double* sqnorm_dev, float max_norm,
                                  float lr, float beta1, float beta2, float eps, float weight_decay, int32_t decoupled,
-                                 int32_t step, void* stream) {
+                                 int32_t step, const double* step_state, void* stream) {
     MVAE_CHECK(params && grads && exp_avg && exp_avg_sq && chunk_tensor && chunk_offset && chunk_len && n_chunks > 0 &&
-                   step >= 1, "adamw_chunked: bad argument");
+                   (step >= 1 || step_state), "adamw_chunked: bad argument");
     return adamw_step_chunked(params, grads, exp_avg, exp_avg_sq, chunk_tensor,
                               reinterpret_cast<const long long*>(chunk_offset), chunk_len, n_chunks, sqnorm_dev, max_norm,
-                              lr, beta1, beta2, eps, weight_decay, decoupled, step, ST(stream));
+                              lr, beta1, beta2, eps, weight_decay, decoupled, step, step_state, ST(stream));
 }
 
 int mvae_dis_input_fwd(const float* x, const int64_t* idx, const float* pw, const float* pb, const int32_t* is_gray,
@@ -514,11 +515,15 @@ int mvae_linattn_core_bwd(const void* qkv, const float* ks, const float* ctx, co
     MVAE_CHECK(qkv && ks && ctx && dout && dqkv && dctx && dks && dtype_ok(dtype), "linattn_core_bwd: bad argument");
     return linattn_bwd(qkv, ks, ctx, dout, dqkv, dctx, dks, batch, tokens, c, dtype, ST(stream));
 }
-int mvae_dropout_apply(const void* x, void* y, int64_t n, float p, uint64_t seed, uint64_t offset, const uint8_t* mask_in,
-                       uint8_t* mask_out, int32_t dtype, void* stream) {
+int mvae_dropout_apply(const void* x, void* y, int64_t n, float p, uint64_t seed, uint64_t offset, const double* step_state,
+                       const uint8_t* mask_in, uint8_t* mask_out, int32_t dtype, void* stream) {
     MVAE_CHECK(x && y && n > 0 && dtype_ok(dtype), "dropout_apply: bad argument");
     MVAE_CHECK(p >= 0.f && p < 1.f, "dropout_apply: p must be in [0, 1), got %f", (double)p);
-    return dropout_apply(x, y, n, p, seed, offset, mask_in, mask_out, dtype, ST(stream));
+    return dropout_apply(x, y, n, p, seed, offset, step_state, mask_in, mask_out, dtype, ST(stream));
+}
+int mvae_step_state_advance(double* step_state, double rng_increment, void* stream) {
+    MVAE_CHECK(step_state && rng_increment >= 0.0, "step_state_advance: bad argument");
+    return step_state_advance(step_state, rng_increment, ST(stream));
 }
 int mvae_film_fwd(const float* features, const float* cond, const float* w_scale, const float* b_scale, const float* w_shift,
                   const float* b_shift, float* out, float* st, int32_t batch, int32_t c, int32_t hw, int32_t k, void* stream) {

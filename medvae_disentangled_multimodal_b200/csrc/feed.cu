@@ -81,8 +81,9 @@ struct Philox4 {
 // The backward is the same call on dy.  4 elements per thread (one Philox block).
 template <typename T>
 __global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, float p,
-                                                      uint64_t seed, uint64_t offset, const uint8_t* __restrict__ mask_in,
-                                                      uint8_t* __restrict__ mask_out) {
+                                                      uint64_t seed, uint64_t offset, const double* __restrict__ dyn,
+                                                      const uint8_t* __restrict__ mask_in, uint8_t* __restrict__ mask_out) {
+    if (dyn) offset += ((uint64_t)dyn[2]) << 20;   // device-side stream position (CUDA-graph replays advance it)
     const float scale = 1.f / (1.f - p);
     const Philox4 ph(seed);
     const long long quads = (n + 3) / 4;
@@ -103,14 +104,14 @@ __global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ x, T
     }
 }
 
-int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, const uint8_t* mask_in,
-                  uint8_t* mask_out, int dtype, cudaStream_t st) {
+int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, const double* dyn,
+                  const uint8_t* mask_in, uint8_t* mask_out, int dtype, cudaStream_t st) {
     long long g = ((n + 3) / 4 + 255) / 256;
     const int grid = (int)(g > 148 * 16 ? 148 * 16 : (g < 1 ? 1 : g));
     if (dtype == MVAE_BF16)
-        dropout_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)x, (bf16*)y, n, p, seed, offset, mask_in, mask_out);
+        dropout_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)x, (bf16*)y, n, p, seed, offset, dyn, mask_in, mask_out);
     else
-        dropout_kernel<float><<<grid, 256, 0, st>>>((const float*)x, (float*)y, n, p, seed, offset, mask_in, mask_out);
+        dropout_kernel<float><<<grid, 256, 0, st>>>((const float*)x, (float*)y, n, p, seed, offset, dyn, mask_in, mask_out);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

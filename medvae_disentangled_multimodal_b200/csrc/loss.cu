@@ -43,8 +43,9 @@ __global__ void __launch_bounds__(256) reparam_kl_fwd_kernel(const T* __restrict
                                                              float* __restrict__ z_nchw,
                                                              T* __restrict__ z_nhwc, double* __restrict__ kl_sum,
                                                              int B, int zc, int RR, float clampv, uint64_t seed,
-                                                             uint64_t offset) {
+                                                             uint64_t offset, const double* __restrict__ dyn) {
     __shared__ double shd[32];
+    if (dyn) offset += (uint64_t)dyn[2];   // device-side Philox stream position (CUDA-graph replays advance it)
     const long long total = (long long)B * zc * RR;
     double acc = 0.0;
     for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
@@ -113,14 +114,14 @@ static int ew_blocks(long long total) {
 
 int reparam_fwd(const void* mom, const float* eps, float* eps_out, float* mean, float* logvar, float* stdv,
                 float* z_nchw, void* z_nhwc, double* kl_sum, int B, int zc, int R, float clampv, uint64_t seed, uint64_t offset,
-                int dtype, cudaStream_t st) {
+                const double* dyn, int dtype, cudaStream_t st) {
     long long total = (long long)B * zc * R * R;
     if (dtype == MVAE_F32)
         reparam_kl_fwd_kernel<float><<<ew_blocks(total), 256, 0, st>>>((const float*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
-                                                                        (float*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset);
+                                                                        (float*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset, dyn);
     else
         reparam_kl_fwd_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>((const bf16*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
-                                                                       (bf16*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset);
+                                                                       (bf16*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset, dyn);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
@@ -313,7 +314,14 @@ __global__ void __launch_bounds__(256) adamw_chunked_kernel(float* const* __rest
                                                             const int* __restrict__ ch_tensor,
                                                             const long long* __restrict__ ch_off,
                                                             const int* __restrict__ ch_len, int n_chunks,
-                                                            const double* __restrict__ sqnorm, const AdamArgs a) {
+                                                            const double* __restrict__ sqnorm, AdamArgs a,
+                                                            const double* __restrict__ dyn) {
+    if (dyn) {   // step count and learning rate live on the device (CUDA-graph replays): dyn = {step, lr, rng}
+        const float t = (float)dyn[0];
+        a.lr = (float)dyn[1];
+        a.bc1 = 1.f - powf(a.b1, t);
+        a.bc2 = 1.f - powf(a.b2, t);
+    }
     float clip = 1.f;
     if (a.max_norm > 0.f && sqnorm) {
         const float norm = (float)sqrt(*sqnorm);
@@ -367,12 +375,12 @@ int grad_sqnorm_chunked(const float* const* grads, const int* ch_tensor, const l
 int adamw_step_chunked(float* const* params, const float* const* grads, float* const* m1, float* const* m2,
                        const int* ch_tensor, const long long* ch_off, const int* ch_len, int n_chunks,
                        const double* sqnorm, float max_norm, float lr, float b1, float b2, float eps, float wd,
-                       int decoupled, int step, cudaStream_t st) {
+                       int decoupled, int step, const double* dyn, cudaStream_t st) {
     AdamArgs a;
     a.max_norm = max_norm; a.lr = lr; a.b1 = b1; a.b2 = b2; a.eps = eps; a.wd = wd; a.decoupled = decoupled;
     a.bc1 = 1.f - powf(b1, (float)step); a.bc2 = 1.f - powf(b2, (float)step);
     adamw_chunked_kernel<<<chunk_grid(n_chunks), 256, 0, st>>>(params, grads, m1, m2, ch_tensor, ch_off, ch_len, n_chunks,
-                                                                sqnorm, a);
+                                                                sqnorm, a, dyn);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
@@ -388,6 +396,19 @@ int adamw_step(float* const* params, const float* const* grads, float* const* m1
     float bc1 = 1.f - powf(b1, (float)step), bc2 = 1.f - powf(b2, (float)step);
     dim3 grid(32, nt < 64 ? nt : 64);
     adamw_kernel<<<grid, 256, 0, st>>>(params, grads, m1, m2, sizes, nt, sqnorm, max_norm, lr, b1, b2, eps, wd, decoupled, bc1, bc2);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// dyn = {optimizer step, learning rate, Philox stream position}: one training step forward
+__global__ void step_state_advance_kernel(double* dyn, double rng_inc) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        dyn[0] += 1.0;
+        dyn[2] += rng_inc;
+    }
+}
+int step_state_advance(double* dyn, double rng_inc, cudaStream_t st) {
+    step_state_advance_kernel<<<1, 32, 0, st>>>(dyn, rng_inc);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

@@ -238,7 +238,7 @@ def nchw_f32_to_nhwc(src, dtype):
     return dst
 
 
-def reparam_kl_fwd(moments, eps, zc, clamp, seed, offset, want_kl=True, want_std=True):
+def reparam_kl_fwd(moments, eps, zc, clamp, seed, offset, want_kl=True, want_std=True, step_state=None):
     b, r, _, c2 = moments.shape
     dev = moments.device
     mean = torch.empty((b, zc, r, r), dtype=torch.float32, device=dev)
@@ -250,7 +250,7 @@ def reparam_kl_fwd(moments, eps, zc, clamp, seed, offset, want_kl=True, want_std
         eps_out = torch.empty_like(mean)
     kl = torch.zeros((), dtype=torch.float64, device=dev) if want_kl else None
     check(lib().mvae_reparam_kl_fwd(ptr(moments), ptr(eps), ptr(eps_out), ptr(mean), ptr(logvar), ptr(std), ptr(z), None,
-                                    ptr(kl), b, zc, r, float(clamp), int(seed), int(offset),
+                                    ptr(kl), b, zc, r, float(clamp), int(seed), int(offset), ptr(step_state),
                                     L.code_of(moments.dtype), stream()), "reparam_kl_fwd")
     return mean, logvar, z, std, (eps if eps is not None else eps_out), kl
 
@@ -383,12 +383,12 @@ def linattn_bwd(qkv, ks, ctx, dout):
     return dqkv
 
 
-def dropout_apply(x, p, seed, offset, mask_in=None, want_mask=False):
+def dropout_apply(x, p, seed, offset, mask_in=None, want_mask=False, step_state=None):
     """-> (y, mask or None); x any contiguous bf16/fp32 tensor, mask uint8 of the same shape"""
     y = torch.empty_like(x)
     mask = torch.empty(x.shape, dtype=torch.uint8, device=x.device) if want_mask else None
     check(lib().mvae_dropout_apply(ptr(x), ptr(y), x.numel(), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF, int(offset),
-                                   ptr(mask_in), ptr(mask), L.code_of(x.dtype), stream()), "dropout_apply")
+                                   ptr(step_state), ptr(mask_in), ptr(mask), L.code_of(x.dtype), stream()), "dropout_apply")
     return y, mask
 
 
@@ -446,3 +446,8 @@ def latent_metrics(z, thr, out):
     ws = scratch("metrics_ws_lat", 8 * lib().mvae_stat_metrics_ws_doubles(), z.device)
     check(lib().mvae_latent_metrics(ptr(z), z.shape[0], z.shape[1], float(thr), ptr(ws), ptr(out), stream()),
           "latent_metrics")
+
+
+def step_state_advance(step_state, rng_increment: float):
+    """step_state: float64 device tensor {optimizer step, learning rate, Philox position}"""
+    check(lib().mvae_step_state_advance(ptr(step_state), float(rng_increment), stream()), "step_state_advance")

@@ -47,6 +47,9 @@ class FusedAdamW:
         self._sqnorm = torch.zeros((), dtype=torch.float64, device=dev)
         self._tables = None   # (grad data_ptrs tuple) -> device pointer tables
         self._dev = dev
+        # device-resident {step, lr, Philox position} (train.TrainStep in CUDA-graph mode): when set, the kernel
+        # reads step / lr from it instead of the by-value arguments
+        self.step_state: Optional[torch.Tensor] = None
 
     # ------------------------------------------------------------------ pointer tables
     def _ptr_table(self, tensors) -> torch.Tensor:
@@ -119,7 +122,7 @@ class FusedAdamW:
                                                  ptr(t["co"]), ptr(t["cl"]), t["chunks"], ptr(self._sqnorm),
                                                  self.max_norm, float(self.lr if lr is None else lr), self.betas[0],
                                                  self.betas[1], self.eps, self.weight_decay, int(self.decoupled),
-                                                 self.step_count, stream()), "adamw_clip_step")
+                                                 self.step_count, ptr(self.step_state), stream()), "adamw_clip_step")
         # parameters changed in place behind autograd's back: bump versions so the packed bf16
         # operand caches (blocks.ConvOp.packed) are refreshed on the next forward
         torch._C._increment_version(plist)

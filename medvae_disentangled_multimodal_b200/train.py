@@ -175,15 +175,33 @@ class TrainStep:
 
     def __init__(self, model: nn.Module, criterion: nn.Module, *, lr: float = 1e-4, weight_decay: float = 1e-4,
                  betas=(0.9, 0.999), eps: float = 1e-8, decoupled: bool = True, max_norm: float = 1.0,
-                 micro_batch: Optional[int] = None, bucket_bytes: int = 32 << 20, group=None):
+                 micro_batch: Optional[int] = None, bucket_bytes: int = 32 << 20, group=None, use_graph: bool = False):
+        """use_graph: capture the whole step (forward, loss, backward, all-reduce, optimizer) in a CUDA graph
+        after two eager steps and replay it afterwards — for shapes whose step is bound by the ~3000 host
+        launches per pass (the 28x28 configs).  The step counter, learning rate and Philox stream position
+        then live on the device (``step_state``) so the captured kernels do not bake them in."""
         from .optim import FusedAdamW
         self.model, self.criterion = model, criterion
+        self.use_graph = bool(use_graph)
+        self._graph = None
+        self._graph_key = None
+        self._graph_eager_steps = 0
+        self.graph_launches = 0            # C-ABI kernel launches captured in the graph (= per replay)
         self.micro_batch = micro_batch
         self.order = backward_order(model)
         self.buckets = GradBuckets(self.order, bucket_bytes, group)
         self.optimizer = FusedAdamW(self.order, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
                                     decoupled=decoupled, max_norm=max_norm)
         self.device = self.order[0].device
+        # device-resident {optimizer step, learning rate, Philox position}, advanced by one kernel per step
+        self.step_state = torch.tensor([0.0, float(lr), 0.0], dtype=torch.float64, device=self.device)
+        if self.use_graph:
+            self.optimizer.step_state = self.step_state
+            model._step_state = self.step_state
+            for name in ("decoder", "encoder"):
+                stack = getattr(model, name, None)
+                if stack is not None and hasattr(stack, "_step_state"):
+                    stack._step_state = self.step_state
         self._hooks = []
         sunk = set()
         for name in ("decoder", "encoder"):
@@ -210,7 +228,68 @@ class TrainStep:
             return t
         return t.to(self.device, non_blocking=True)
 
+    # ------------------------------------------------------------------ CUDA-graph mode
+    def set_lr(self, lr: float):
+        """learning rate for the next steps (what a scheduler calls in graph mode: the captured AdamW kernel
+        reads it from the device)"""
+        self.optimizer.lr = float(lr)
+        self.step_state[1:2].fill_(float(lr))
+
+    def _graph_step(self, x, cond):
+        from . import _lib as L
+        from . import ops
+        disentangled = hasattr(self.criterion, "separation_weight")
+        key = (tuple(x.shape), None if cond is None else tuple(cond.shape), disentangled)
+        if self._graph is None or self._graph_key != key:
+            if self._graph_key != key:
+                self._graph, self._graph_key, self._graph_eager_steps = None, key, 0
+            if self._graph_eager_steps < 2:
+                # eager steps first: packed-operand caches, scratch buffers, optimizer tables, kernel attributes
+                self._graph_eager_steps += 1
+                ops.step_state_advance(self.step_state, 1.0)
+                return self._eager_step(x, cond)
+            if disentangled and cond is not None and cond.device.type != "cpu":
+                raise RuntimeError("graph mode needs the modality indices on the host (the model's output-width "
+                                   "decision would otherwise synchronise inside the capture)")
+            self._gx = torch.empty_like(x, device=self.device)
+            self._gc = None if cond is None else (cond.clone() if disentangled else torch.empty_like(cond, device=self.device))
+            self._gx.copy_(x, non_blocking=True)
+            if self._gc is not None and not disentangled:
+                self._gc.copy_(cond, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            n0 = L.lib().mvae_launch_count()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                ops.step_state_advance(self.step_state, 1.0)
+                self._gout = self._eager_step(self._gx, self._gc)
+            self.graph_launches = int(L.lib().mvae_launch_count() - n0)
+            # the scratch buffers the captured kernels point at must outlive later re-allocations
+            self._graph_keepalive = list(ops._scratch.values())
+            self._graph = g
+            # the capture itself did not run anything: undo its host-side bookkeeping, then fall through to replay
+            self.optimizer.step_count -= 1
+        self._gx.copy_(x, non_blocking=True)
+        if self._gc is not None and not disentangled:
+            self._gc.copy_(cond, non_blocking=True)
+        self._graph.replay()
+        self.optimizer.step_count += 1
+        # parameters changed behind autograd's back: eager consumers (validate, sample) must re-pack
+        torch._C._increment_version(self.optimizer.params)
+        return dict(self._gout)
+
     def step(self, x: torch.Tensor, cond: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        if self.use_graph:
+            return self._graph_step(x, cond)
+        return self._eager_step(x, cond)
+
+    def step_eager(self, x: torch.Tensor, cond: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        """one step launched kernel by kernel even in graph mode (per-launch profiling)"""
+        if self.use_graph:
+            from . import ops
+            ops.step_state_advance(self.step_state, 1.0)
+        return self._eager_step(x, cond)
+
+    def _eager_step(self, x: torch.Tensor, cond: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
         """x: (B, C, H, W) fp32 in [-1, 1]; cond: (B, n_modalities) one-hot, None, or — for a
         DisentangledConditionalVAE with DisentangledVAELoss — the (B,) int64 modality indices
         (lightning_module.py:116-118).  Host tensors are copied to the device here (use pinned

@@ -40,7 +40,8 @@ class _EncodeSampleFn(torch.autograd.Function):
     def forward(ctx, model: "BaseVAE", moments_nhwc, eps, clamp: float):
         seed, offset = model._next_rng()
         mean, logvar, z, std, eps_used, kl = ops.reparam_kl_fwd(
-            moments_nhwc, eps, model.latent_dim, clamp, seed, offset, want_kl=True, want_std=True)
+            moments_nhwc, eps, model.latent_dim, clamp, seed, offset, want_kl=True, want_std=True,
+            step_state=model._step_state)
         ctx.save_for_backward(moments_nhwc, logvar, eps_used, std)
         ctx.clamp = clamp
         ctx.mark_non_differentiable(eps_used, kl)
@@ -123,6 +124,7 @@ class BaseVAE(nn.Module):
         self._rng_step = 0
         self._latent_clamp = 0.0
         self._prior_cache: dict = {}
+        self._step_state: Optional[torch.Tensor] = None   # device-side Philox position (TrainStep graph mode)
 
     # ------------------------------------------------------------------ runtime knobs
     def set_compute_dtype(self, compute_dtype):

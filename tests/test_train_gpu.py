@@ -109,3 +109,50 @@ def test_disentangled_train_step_tracks_the_reference():
             assert abs(float(got[k]) - want[k]) <= 1e-3 * max(1.0, abs(want[k])), (i, k, float(got[k]), want[k])
     ts.close()
     assert want["loss"] < first          # it trains
+
+
+def test_cuda_graph_step_equals_eager_step():
+    """TrainStep(use_graph=True): two eager steps, capture, replays — the same loss sequence and final weights as the
+    eager TrainStep on the same data and noise (fp32 mode; step counter, lr and Philox position live on the device)."""
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200.train import TrainStep
+    batches = [O.synthetic_batch(8, 3, 16, seed=200 + i) for i in range(3)]
+    eps = torch.randn(8, 8, 8, 8, generator=torch.Generator().manual_seed(5)).to(DEV)
+    curves, finals = [], []
+    for use_graph in (False, True):
+        torch.manual_seed(3)
+        model = M.ConditionalVAE(compute_dtype="fp32", **KW).to(DEV)
+        model.eps_override = eps
+        ts = TrainStep(model, M.VAELoss(**LKW), use_graph=use_graph, micro_batch=4, **OPT)
+        curve = []
+        for i in range(7):
+            x, onehot, _ = batches[i % 3]
+            if i == 5:
+                ts.set_lr(3e-4) if use_graph else setattr(ts.optimizer, "lr", 3e-4)
+            curve.append(float(ts.step(x.to(DEV), onehot.to(DEV))["loss"]))
+        assert (ts._graph is not None) == use_graph
+        if use_graph:
+            assert ts.graph_launches > 50 and ts.optimizer.step_count == 7
+            assert float(ts.step_state[0]) == 7.0
+        ts.close()
+        curves.append(curve)
+        finals.append(torch.cat([p.detach().flatten() for p in model.parameters()]).cpu())
+    for a, b in zip(*curves):
+        assert abs(a - b) <= 2e-5 * abs(a), (curves[0], curves[1])
+    assert float((finals[0] - finals[1]).abs().max()) < 1e-6
+
+
+def test_cuda_graph_philox_noise_advances_between_replays():
+    """without injected noise the captured reparameterisation kernel must draw NEW noise on every replay"""
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200.train import TrainStep
+    torch.manual_seed(3)
+    model = M.ConditionalVAE(compute_dtype="fp32", **KW).to(DEV)
+    model.rng_seed = 11
+    ts = TrainStep(model, M.VAELoss(**LKW), use_graph=True, lr=0.0, weight_decay=0.0)
+    x, onehot, _ = O.synthetic_batch(8, 3, 16, seed=1)
+    x, onehot = x.to(DEV), onehot.to(DEV)
+    losses = [float(ts.step(x, onehot)["recon_loss"]) for _ in range(6)]     # lr = 0: only the noise changes
+    ts.close()
+    assert ts._graph is not None
+    assert len(set(losses)) == len(losses), losses
