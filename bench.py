@@ -59,6 +59,11 @@ WORKLOADS = {
 }
 
 
+def default_micro(wl: str) -> int:
+    """images per forward/backward pass: 256 at 64x64 and above (saved activations), 1024 at 28x28"""
+    return 1024 if WORKLOADS[wl][1]["resolution"] <= 32 else 256
+
+
 def wl_shape(wl: str):
     """-> (image channels, latent channels, disentangled?) of a workload"""
     cls, kw = WORKLOADS[wl][:2]
@@ -180,7 +185,7 @@ def workload_config(wl, args, bpg, n, cpu=False):
                     f"ch_mult {tuple(kw['ch_mult'])} res_blocks {kw['num_res_blocks']} attn {kw['attn_resolutions']} "
                     f"latent {zc}, {'DisentangledVAELoss' if dis else 'VAELoss'} {lkw['recon_loss_type']} "
                     f"kl_weight {lkw['kl_weight']}, AdamW lr 1e-4 wd 1e-4 clip 1.0",
-        "batch_per_gpu": bpg, "global_batch": bpg * n, "micro_batch": None if cpu else (args.micro_batch or min(bpg, 256)),
+        "batch_per_gpu": bpg, "global_batch": bpg * n, "micro_batch": None if cpu else (args.micro_batch or min(bpg, default_micro(wl))),
         "cuda_graph": False if cpu else (args.graph == "on" or (args.graph == "auto" and wl in ("c1", "c2", "c3"))),
         "parallelism": f"dp{n}", "gflop_per_image_fwd_bwd": gflop,
         "cache": "inputs and activations larger than L2 (126 MB); no L2 flush needed",
@@ -288,7 +293,7 @@ def b200_arm(args):
     wl = args.workload
     cls, kw, lkw, bpg, conditional, gflop, scaling = WORKLOADS[wl]
     bpg = args.batch_per_gpu or bpg
-    micro = args.micro_batch or min(bpg, 256)
+    micro = args.micro_batch or min(bpg, default_micro(wl))
     torch.manual_seed(42)
     model = getattr(M, cls)(compute_dtype=args.precision, **kw).to(dev)
     model.rng_seed = 42
@@ -406,7 +411,12 @@ def b200_arm(args):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
+        # a captured graph holds NCCL kernels: drop it before the communicator goes away, and do not let a stuck
+        # teardown keep the (already reported) run alive
+        ts.release_graph()
+        threading.Timer(30.0, lambda: os._exit(0)).start()
         dist.destroy_process_group()
+        os._exit(0)
 
 
 def main():

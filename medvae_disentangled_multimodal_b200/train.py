@@ -277,6 +277,17 @@ class TrainStep:
         torch._C._increment_version(self.optimizer.params)
         return dict(self._gout)
 
+    def release_graph(self):
+        """drop the captured graph (before destroying a process group whose collectives it contains)"""
+        import gc
+        self._graph = None
+        self._gout = None
+        self._graph_keepalive = None
+        self._graph_key = None
+        gc.collect()
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+
     def step(self, x: torch.Tensor, cond: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
         if self.use_graph:
             return self._graph_step(x, cond)
