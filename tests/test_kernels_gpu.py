@@ -50,6 +50,11 @@ UMMA_CASES = [
     (2, 16, 16, 64, 64, 3, 1), (2, 32, 32, 128, 128, 3, 1), (3, 14, 14, 64, 64, 3, 1), (2, 28, 28, 64, 64, 3, 1),
     (2, 8, 8, 64, 64, 3, 2), (2, 16, 16, 128, 128, 3, 2), (3, 7, 7, 64, 64, 3, 2), (2, 14, 14, 64, 64, 3, 2),
     (2, 8, 8, 64, 384, 1, 0),
+    # enough pixel tiles (>= 2 x 148) for the paired-tile variant of the 128-channel gather kernel (two pixel tiles
+    # per weight stage): an odd tile count with partial boxes (24-wide rows: 120 of 128 GEMM rows, 305 tiles), a
+    # full-box case, N = 384 (three channel tiles), the strided (Downsample) and the parity (Upsample) lowerings
+    (61, 24, 24, 128, 128, 3, 0), (80, 32, 32, 128, 128, 3, 0), (40, 32, 32, 64, 384, 1, 0),
+    (300, 32, 32, 128, 128, 3, 1), (150, 16, 16, 128, 128, 3, 2),
 ]
 
 
@@ -293,6 +298,7 @@ GN_FUSE_CASES = [
     (3, 8, 8, 512, 512, 3, 0, 32), (2, 4, 4, 1024, 1024, 1, 0, 32), (5, 7, 7, 512, 512, 3, 0, 32),
     (2, 14, 14, 256, 256, 3, 0, 32), (4, 4, 4, 128, 128, 3, 0, 32), (2, 64, 64, 128, 128, 3, 0, 32),
     (2, 32, 32, 128, 128, 3, 1, 32), (2, 16, 16, 256, 256, 3, 2, 32), (2, 16, 16, 64, 64, 3, 0, 16),
+    (77, 32, 32, 128, 128, 3, 0, 32),   # 616 pixel tiles: the paired-tile gather variant with both GroupNorm epilogues
 ]
 
 
