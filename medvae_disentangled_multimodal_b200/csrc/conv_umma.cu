@@ -198,10 +198,13 @@ __device__ __forceinline__ void gn_flush_any(int cpg_log2, const float* sa, cons
 // pixel tiles on one 128-channel weight stage brings N = 128 layers to (32 + 16) KB per 512 cycles = 96 B/clk,
 // the same as the 128 x 256 configuration.
 constexpr int A_TILE_BYTES = 128 * 128;                 // 128 rows x 64 bf16
-template <int BN, int MT>
+// CG = 2: a CTA PAIR (cluster of two, cta_group::2) runs one 256-pixel x BN MMA; each CTA holds its own 128 pixel
+// rows and HALF of the weight tile, so a 128 x 256 accumulator per SM costs (16 + 16) KB per 512 MMA cycles =
+// 64 B/clk of ingest instead of 96, with the accumulators still double-buffered.
+template <int BN, int MT, int CG = 1>
 struct GatherCfg {
     static constexpr int A_BYTES = MT * A_TILE_BYTES;
-    static constexpr int B_BYTES = BN * 128;
+    static constexpr int B_BYTES = BN * 128 / CG;
     static constexpr int STAGES = (A_BYTES + B_BYTES >= 65536) ? 3 : ((A_BYTES + B_BYTES >= 49152) ? 4 : (A_BYTES + B_BYTES >= 32768 ? 6 : 8));
     // accumulators are double-buffered (the epilogue of one CTA tile runs under the MMAs of the next) while they fit
     // the 512 TMEM columns; the 256 x 256 tile (MT = 2, BN = 256) uses all 512 for one buffer and pays an exposed
@@ -211,10 +214,15 @@ struct GatherCfg {
     static constexpr int SMEM = 1024 + STAGES * (A_BYTES + B_BYTES) + 256;
 };
 
-template <int BN, int EPI, int MT>
+template <int BN, int EPI, int MT, int CG>
 __global__ void __launch_bounds__(gather_threads(EPI), 1)
 conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_constant__ GatherDev p) {
-    using Cfg = GatherCfg<BN, MT>;
+    using Cfg = GatherCfg<BN, MT, CG>;
+    static_assert(CG == 1 || MT == 1, "a CTA pair takes one pixel tile per CTA");
+    // CTA pair: rank within the pair, pair index and number of pairs replace blockIdx / gridDim in the tile loop
+    const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
+    const int sched_id = (CG == 2) ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int sched_n = (CG == 2) ? (int)(gridDim.x >> 1) : (int)gridDim.x;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -241,31 +249,35 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
     if (warp == 1) {
         if (lane == 0) {
             for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-            for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 32 * gather_epi_warps(EPI)); }
+            // pair: the epilogue warps of BOTH CTAs release the leader's accumulator barrier
+            for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], CG * 32 * gather_epi_warps(EPI)); }
             fence_barrier_init();
         }
         __syncwarp();
-        tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+        if (CG == 2) tmem_alloc2(tmem_slot, Cfg::TMEM_COLS);
+        else tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
     }
     tc_fence_before();
     __syncthreads();
+    if (CG == 2) cluster_sync_all();   // the peer's barriers exist before anything arrives on them remotely
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
     const int kiters = p.taps.ntaps * p.kchunks;
-    const uint32_t stage_bytes = (uint32_t)(MT * p.rows) * 128u + (uint32_t)Cfg::B_BYTES;
+    // bytes that complete on one "full" barrier: both CTAs' loads land on the leader's barrier in a pair
+    const uint32_t stage_bytes = (uint32_t)CG * ((uint32_t)(MT * p.rows) * 128u + (uint32_t)Cfg::B_BYTES);
 
     if (warp == 0) {
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            for (int tile = sched_id; tile < p.total_tiles; tile += sched_n) {
                 const int nt = tile % p.n_tiles;
                 int x0[MT], y0[MT], n0[MT];
 #pragma unroll
                 for (int j = 0; j < MT; ++j) {
                     // pixel tile (tile / n_tiles) * MT + j; one past the last decodes to n0 >= B: the box is
                     // entirely out of bounds, TMA zero-fills it and the epilogue stores nothing
-                    int mt = (tile / p.n_tiles) * MT + j;
+                    int mt = (CG == 2) ? (tile / p.n_tiles) * 2 + (int)rank : (tile / p.n_tiles) * MT + j;
                     const int tx = mt % p.tiles_x; mt /= p.tiles_x;
                     x0[j] = tx * p.bw; y0[j] = (mt % p.tiles_y) * p.bh; n0[j] = (mt / p.tiles_y) * p.bn;
                 }
@@ -273,6 +285,16 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                     const Tap tp = p.taps.t[t];
                     for (int kc = 0; kc < p.kchunks; ++kc) {
                         mbar_wait(&empty[stage], phase ^ 1u);
+                        if (CG == 2) {
+                            if (rank == 0) mbar_expect_tx(&full[stage], stage_bytes);
+                            const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
+                            tma2_load_4d(sA + stage * Cfg::A_BYTES, &tm.a[tp.view], lead_full, kc * 64, x0[0] + tp.dx,
+                                         y0[0] + tp.dy, n0[0]);
+                            tma2_load_3d(sB + stage * Cfg::B_BYTES, &tm.b, lead_full, kc * 64,
+                                         nt * BN + (int)rank * (BN / 2), tp.slab);
+                            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                            continue;
+                        }
                         mbar_expect_tx(&full[stage], stage_bytes);
 #pragma unroll
                         for (int j = 0; j < MT; ++j)
@@ -285,11 +307,11 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_bf16(128, BN, 0, 0);
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(128 * CG, BN, 0, 0);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            for (int tile = sched_id; tile < p.total_tiles; tile += sched_n) {
                 mbar_wait(&tempty[acc], acc_phase ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * MT * BN);
@@ -304,13 +326,16 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
 #pragma unroll
                         for (int j = 0; j < MT; ++j) {
                             const uint64_t ad = smem_desc_sw128(a0 + j * A_TILE_BYTES + k * 32, 16, 1024);
-                            umma_bf16(d_tmem + (uint32_t)(j * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                            if (CG == 2) umma2_bf16(d_tmem, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                            else umma_bf16(d_tmem + (uint32_t)(j * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
                         }
                     }
-                    umma_commit(&empty[stage]);
+                    if (CG == 2) umma2_commit(&empty[stage]);
+                    else umma_commit(&empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
-                umma_commit(&tfull[acc]);
+                if (CG == 2) umma2_commit(&tfull[acc]);
+                else umma_commit(&tfull[acc]);
                 if (++acc == Cfg::ACC_BUFS) { acc = 0; acc_phase ^= 1u; }
             }
         }
@@ -321,12 +346,12 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
         const int iy = (row / p.bw) % p.bh;
         const int in = row / (p.bw * p.bh);
         int acc = 0; uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        for (int tile = sched_id; tile < p.total_tiles; tile += sched_n) {
             const int nt = tile % p.n_tiles;
 #pragma unroll 1
           for (int j = 0; j < MT; ++j) {
             const uint32_t acc_col = (uint32_t)(acc * MT * BN + j * BN);
-            int mt = (tile / p.n_tiles) * MT + j;
+            int mt = (CG == 2) ? (tile / p.n_tiles) * 2 + (int)rank : (tile / p.n_tiles) * MT + j;
             const int tx = mt % p.tiles_x; mt /= p.tiles_x;
             const int ty = mt % p.tiles_y;
             const int tn = mt / p.tiles_y;
@@ -486,15 +511,18 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
             }
           }   // pixel tiles of this CTA tile
             tc_fence_before();
-            mbar_arrive(&tempty[acc]);
+            if (CG == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty[acc]), 0));   // the leader issues the next MMAs
+            else mbar_arrive(&tempty[acc]);
             if (++acc == Cfg::ACC_BUFS) { acc = 0; acc_phase ^= 1u; }
         }
     }
     tc_fence_before();
     __syncthreads();
+    if (CG == 2) cluster_sync_all();   // neither CTA of a pair frees its TMEM / exits while the other still uses it
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+        if (CG == 2) tmem_dealloc2(tmem_base, Cfg::TMEM_COLS);
+        else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
     }
 }
 
@@ -507,25 +535,44 @@ bool umma_gather_ok(const GatherProblem& p) {
     return true;
 }
 
-template <int BN, int EPI, int MT>
+template <int BN, int EPI, int MT, int CG>
 static int launch_gather_epi(const GatherTmaps& tm, GatherDev& d, cudaStream_t st) {
-    using Cfg = GatherCfg<BN, MT>;
+    using Cfg = GatherCfg<BN, MT, CG>;
     static bool attr_set = false;
     if (!attr_set) {
-        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI, MT, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg::SMEM));
         attr_set = true;
     }
+    if (CG == 2) {
+        // one CTA pair per TPC: a cluster of two, persistent over the tile pairs
+        int pairs = num_sms() / 2;
+        if (d.total_tiles < pairs) pairs = d.total_tiles;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(2 * pairs);
+        cfg.blockDim = dim3(gather_threads(EPI));
+        cfg.dynamicSmemBytes = Cfg::SMEM;
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        count_launch();
+        MVAE_CUDA(cudaLaunchKernelEx(&cfg, conv_gather_umma_kernel<BN, EPI, MT, CG>, tm, d));
+        MVAE_CUDA(cudaGetLastError());
+        return 0;
+    }
     int grid = d.total_tiles < num_sms() ? d.total_tiles : num_sms();
-    conv_gather_umma_kernel<BN, EPI, MT><<<grid, gather_threads(EPI), Cfg::SMEM, st>>>(tm, d);
+    conv_gather_umma_kernel<BN, EPI, MT, CG><<<grid, gather_threads(EPI), Cfg::SMEM, st>>>(tm, d);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
-template <int BN, int MT>
+template <int BN, int MT, int CG = 1>
 static int launch_gather(const GatherTmaps& tm, GatherDev& d, int epi, cudaStream_t st) {
-    if (epi == EPI_GN_STATS) return launch_gather_epi<BN, EPI_GN_STATS, MT>(tm, d, st);
-    if (epi == EPI_GN_BWD) return launch_gather_epi<BN, EPI_GN_BWD, MT>(tm, d, st);
-    return launch_gather_epi<BN, EPI_PLAIN, MT>(tm, d, st);
+    if (epi == EPI_GN_STATS) return launch_gather_epi<BN, EPI_GN_STATS, MT, CG>(tm, d, st);
+    if (epi == EPI_GN_BWD) return launch_gather_epi<BN, EPI_GN_BWD, MT, CG>(tm, d, st);
+    return launch_gather_epi<BN, EPI_PLAIN, MT, CG>(tm, d, st);
 }
 
 int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslabs, const float* bias,
@@ -533,6 +580,13 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     MVAE_CHECK(umma_gather_ok(p), "umma_gather: unsupported shape K=%d N=%d OW=%d", p.K, p.N, p.OW);
     BoxGeom g = box_geom(p.B, p.OH, p.OW);
     const int BN = (p.N % 256 == 0) ? 256 : (p.N % 128 == 0 ? 128 : 64);
+    // CTA pairs (cta_group::2) for 256-channel tiles when there are enough pixel-tile pairs for every TPC
+    int CG = 1;
+    {
+        BoxGeom g0 = box_geom(p.B, p.OH, p.OW);
+        const long long mt0 = (long long)g0.tiles_x * g0.tiles_y * g0.tiles_n;
+        if (BN == 256 && debug_knob(8) == 1 && ((mt0 + 1) / 2) * (p.N / 256) >= num_sms() / 2) CG = 2;
+    }
     GatherTmaps tm;
     memset(&tm, 0, sizeof(tm));
     for (int v = 0; v < MAX_VIEWS; ++v) {
@@ -542,7 +596,7 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     {
         cuuint64_t dims[3] = {(cuuint64_t)p.K, (cuuint64_t)p.N, (cuuint64_t)nslabs};
         cuuint64_t stb[2] = {(cuuint64_t)p.K * 2, (cuuint64_t)p.K * p.N * 2};
-        cuuint32_t box[3] = {64u, (cuuint32_t)BN, 1u};
+        cuuint32_t box[3] = {64u, (cuuint32_t)(BN / CG), 1u};
         if (encode_tmap(&tm.b, w, 3, dims, stb, box)) return 1;
     }
     GatherDev d;
@@ -553,7 +607,9 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     // 128-channel tiles take two pixel tiles per weight stage when that still leaves every SM a CTA tile
     const long long m_tiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
     int MT = (BN == 128 && debug_knob(5) == 0 && ((m_tiles + 1) / 2) * d.n_tiles >= num_sms()) ? 2 : 1;
-    if (BN == 256 && debug_knob(7) == 1) {
+    if (CG == 2) {
+        d.total_tiles = (int)((m_tiles + 1) / 2) * d.n_tiles;
+    } else if (BN == 256 && debug_knob(7) == 1) {
         // OPT-IN experiment (knob 7): 256 x 256 CTA tiles, 64 instead of 96 B/clk of ingest but a single accumulator
         // buffer, i.e. an exposed epilogue.  Measured on C4 (r1e): fprop 16.7 -> 17.9 ms, dgrad 19.6 -> 21.6 ms per
         // 256-image micro-batch — slower, so the default stays 128 x 256 with double-buffered accumulators.
@@ -578,6 +634,7 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
         d.gn_sums = hook->sums; d.gn_x = (const bf16*)hook->x; d.gn_stat = hook->stat;
         d.gn_gamma = hook->gamma; d.gn_beta = hook->beta;
     }
+    if (CG == 2) return launch_gather<256, 1, 2>(tm, d, epi, st);
     if (BN == 256 && MT == 2) return launch_gather<256, 2>(tm, d, epi, st);
     if (BN == 256) return launch_gather<256, 1>(tm, d, epi, st);
     if (BN == 128 && MT == 2) return launch_gather<128, 2>(tm, d, epi, st);

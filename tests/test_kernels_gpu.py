@@ -387,6 +387,33 @@ def test_conv_dgrad_gn_backward(case, silu, with_add):
     assert float((cs1.double() - cs_ref).abs().max()) <= 2e-2 * float(cs_ref.abs().max()) + 1e-3
 
 
+# ------------------------------------------------------------------ CTA pairs (cta_group::2), opt-in knob 8
+PAIR_CASES = [(80, 32, 32, 256, 256, 3, 0), (61, 24, 24, 256, 256, 3, 0), (40, 16, 16, 256, 512, 3, 0),
+              (300, 16, 16, 256, 256, 3, 1), (40, 16, 16, 512, 256, 1, 0)]
+
+
+@pytest.fixture
+def cta_pairs():
+    L, _ = _mods()
+    L.lib().mvae_set_debug(8, 1)
+    yield
+    L.lib().mvae_set_debug(8, 0)
+
+
+@pytest.mark.umma
+@pytest.mark.parametrize("case", PAIR_CASES)
+def test_conv_umma_cta_pair(case, cta_pairs):
+    """256-channel tiles on CTA pairs: 2 x 128 pixel rows per MMA, each CTA loads half of the weight tile"""
+    L, _ = _mods()
+    _conv_case(case, torch.bfloat16, L.ENGINE_UMMA)
+
+
+@pytest.mark.umma
+def test_conv_gn_epilogues_cta_pair(cta_pairs):
+    test_conv_fprop_gn_statistics((77, 32, 32, 256, 256, 3, 0, 32))
+    test_conv_dgrad_gn_backward((77, 32, 32, 256, 256, 3, 0, 32), True, True)
+
+
 # ------------------------------------------------------------------ disentangled-model kernels
 def _ref_aux(z, idx, s, m, tau=0.1):
     zm = z.reshape(z.shape[0], -1)[:, s:s + m]
