@@ -585,7 +585,7 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     {
         BoxGeom g0 = box_geom(p.B, p.OH, p.OW);
         const long long mt0 = (long long)g0.tiles_x * g0.tiles_y * g0.tiles_n;
-        if (BN == 256 && debug_knob(8) == 1 && ((mt0 + 1) / 2) * (p.N / 256) >= num_sms() / 2) CG = 2;
+        if (BN == 256 && debug_knob(8) == 0 && ((mt0 + 1) / 2) * (p.N / 256) >= num_sms() / 2) CG = 2;   // knob 8 = 1: off
     }
     GatherTmaps tm;
     memset(&tm, 0, sizeof(tm));
@@ -607,16 +607,15 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     // 128-channel tiles take two pixel tiles per weight stage when that still leaves every SM a CTA tile
     const long long m_tiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
     int MT = (BN == 128 && debug_knob(5) == 0 && ((m_tiles + 1) / 2) * d.n_tiles >= num_sms()) ? 2 : 1;
-    if (CG == 2) {
-        d.total_tiles = (int)((m_tiles + 1) / 2) * d.n_tiles;
-    } else if (BN == 256 && debug_knob(7) == 1) {
+    if (CG == 1 && BN == 256 && debug_knob(7) == 1) {
         // OPT-IN experiment (knob 7): 256 x 256 CTA tiles, 64 instead of 96 B/clk of ingest but a single accumulator
         // buffer, i.e. an exposed epilogue.  Measured on C4 (r1e): fprop 16.7 -> 17.9 ms, dgrad 19.6 -> 21.6 ms per
         // 256-image micro-batch — slower, so the default stays 128 x 256 with double-buffered accumulators.
         const long long t1 = m_tiles * d.n_tiles, t2 = ((m_tiles + 1) / 2) * d.n_tiles, sms = num_sms();
         if (t2 >= sms && 3 * ((t2 + sms - 1) / sms) < 2 * ((t1 + sms - 1) / sms)) MT = 2;
     }
-    d.total_tiles = (int)((m_tiles + MT - 1) / MT) * d.n_tiles;
+    const int m_per_tile = MT * CG;   // pixel tiles per scheduled tile: MT per CTA, one per CTA of a pair
+    d.total_tiles = (int)((m_tiles + m_per_tile - 1) / m_per_tile) * d.n_tiles;
     d.N = p.N;
     d.o_off = p.out_view.off; d.o_sn = p.out_view.sn; d.o_sy = p.out_view.sy; d.o_sx = p.out_view.sx;
     d.bias = bias; d.res = (const bf16*)residual; d.out = (bf16*)out;

@@ -387,15 +387,15 @@ def test_conv_dgrad_gn_backward(case, silu, with_add):
     assert float((cs1.double() - cs_ref).abs().max()) <= 2e-2 * float(cs_ref.abs().max()) + 1e-3
 
 
-# ------------------------------------------------------------------ CTA pairs (cta_group::2), opt-in knob 8
+# ------------------------------------------------------------------ CTA pairs (cta_group::2); knob 8 = 1 turns them off
 PAIR_CASES = [(80, 32, 32, 256, 256, 3, 0), (61, 24, 24, 256, 256, 3, 0), (40, 16, 16, 256, 512, 3, 0),
               (300, 16, 16, 256, 256, 3, 1), (40, 16, 16, 512, 256, 1, 0)]
 
 
-@pytest.fixture
-def cta_pairs():
+@pytest.fixture(params=[0, 1], ids=["pairs", "single"])
+def cta_pairs(request):
     L, _ = _mods()
-    L.lib().mvae_set_debug(8, 1)
+    L.lib().mvae_set_debug(8, request.param)
     yield
     L.lib().mvae_set_debug(8, 0)
 
@@ -403,7 +403,8 @@ def cta_pairs():
 @pytest.mark.umma
 @pytest.mark.parametrize("case", PAIR_CASES)
 def test_conv_umma_cta_pair(case, cta_pairs):
-    """256-channel tiles on CTA pairs: 2 x 128 pixel rows per MMA, each CTA loads half of the weight tile"""
+    """256-channel tiles with >= 74 pixel-tile pairs run on CTA pairs (2 x 128 pixel rows per MMA, each CTA loads
+    half of the weight tile); the same cases with the variant switched off"""
     L, _ = _mods()
     _conv_case(case, torch.bfloat16, L.ENGINE_UMMA)
 
