@@ -23,13 +23,14 @@ for stage in $STAGES; do
       echo "list rc=$?" >> gpurun_out/rc.txt;;
     full)
       timeout 300 $CMD > gpurun_out/plain_full.log 2>&1 || { echo "plain rc=$?" >> gpurun_out/rc.txt; continue; }
-      timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv_gather_umma -s 4 -c 8 -f -o gpurun_out/prof_gf $CMD > gpurun_out/ncu_gf.log 2>&1
+      # (merged results must stay under 64 MiB: no --import-source here, few launches per report)
+      timeout 600 ncu --set full --clock-control none -k regex:conv_gather_umma -s 4 -c 8 -f -o gpurun_out/prof_gf $CMD > gpurun_out/ncu_gf.log 2>&1
       echo "gf rc=$?" >> gpurun_out/rc.txt
-      timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv_gather_umma -s 152 -c 12 -f -o gpurun_out/prof_gb $CMD > gpurun_out/ncu_gb.log 2>&1
+      timeout 600 ncu --set full --clock-control none -k regex:conv_gather_umma -s 152 -c 10 -f -o gpurun_out/prof_gb $CMD > gpurun_out/ncu_gb.log 2>&1
       echo "gb rc=$?" >> gpurun_out/rc.txt
-      timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv_reduce_umma -s 2 -c 8 -f -o gpurun_out/prof_wg $CMD > gpurun_out/ncu_wg.log 2>&1
+      timeout 600 ncu --set full --clock-control none -k regex:conv_reduce_umma -s 2 -c 6 -f -o gpurun_out/prof_wg $CMD > gpurun_out/ncu_wg.log 2>&1
       echo "wg rc=$?" >> gpurun_out/rc.txt
-      timeout 600 ncu --set full --clock-control none --import-source on -k regex:"gn_(apply_pre|bwd_pre)" -s 4 -c 8 -f -o gpurun_out/prof_gn $CMD > gpurun_out/ncu_gn.log 2>&1
+      timeout 600 ncu --set full --clock-control none -k regex:"gn_(apply_pre|bwd_pre)" -s 4 -c 6 -f -o gpurun_out/prof_gn $CMD > gpurun_out/ncu_gn.log 2>&1
       echo "gn rc=$?" >> gpurun_out/rc.txt;;
   esac
 done

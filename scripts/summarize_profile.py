@@ -20,7 +20,7 @@ for r in rows:
 tot = sum(v[1] for v in agg.values())
 with open(f"profiles/{tag}_launches_summary.txt", "w") as f:
     f.write(f"# ncu --metrics gpu__time_duration.sum --clock-control none (cold-cache, serialised: compare SHARES)\n")
-    f.write(f"# command: see scripts/gpu_profile.sh ; {len(rows)} launches, {tot / 1e6:.3f} ms total\n")
+    f.write(f"# command: scripts/gpu_round.sh list (one 256-image C4 micro-batch step, warm-up + 1 step) ; {len(rows)} launches, {tot / 1e6:.3f} ms total\n")
     f.write(f"# {'ms':>9} {'share':>6} {'count':>6}  kernel\n")
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         f.write(f"{v[1] / 1e6:11.3f} {100 * v[1] / tot:5.1f}% {v[0]:6d}  {k}\n")
@@ -33,7 +33,7 @@ with open(f"profiles/{tag}_launches.csv", "w") as f:
 WANT = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
-        "l1tex__m_xbar2l1tex_read_bytes.sum", "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic",
+        "l1tex__m_xbar2l1tex_read_bytes.sum", "lts__t_sector_hit_rate.pct", "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "sm__cycles_elapsed.max"]
 with open(f"profiles/{tag}_ncu_full.csv", "w") as f:
     w = csv.writer(f)
