@@ -38,6 +38,7 @@ class FusedAdamW:
         for p in self.params:
             if p.dtype != torch.float32 or not p.is_cuda or not p.is_contiguous():
                 raise L.MvaeError("FusedAdamW needs contiguous fp32 CUDA parameters (there is no CPU fallback)")
+        self.step_state: Optional[torch.Tensor] = None
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.weight_decay, self.decoupled, self.max_norm = float(weight_decay), bool(decoupled), float(max_norm)
         self.step_count = 0
@@ -47,9 +48,19 @@ class FusedAdamW:
         self._sqnorm = torch.zeros((), dtype=torch.float64, device=dev)
         self._tables = None   # (grad data_ptrs tuple) -> device pointer tables
         self._dev = dev
-        # device-resident {step, lr, Philox position} (train.TrainStep in CUDA-graph mode): when set, the kernel
-        # reads step / lr from it instead of the by-value arguments
-        self.step_state: Optional[torch.Tensor] = None
+        # step_state: device-resident {step, lr, Philox position} (train.TrainStep in CUDA-graph mode): when set, the
+        # kernel reads step / lr from it instead of the by-value arguments
+
+    @property
+    def lr(self) -> float:
+        return self._lr
+
+    @lr.setter
+    def lr(self, value: float):
+        """schedulers assign this; in graph mode the captured kernel reads the device copy"""
+        self._lr = float(value)
+        if self.step_state is not None:
+            self.step_state[1:2].fill_(self._lr)
 
     # ------------------------------------------------------------------ pointer tables
     def _ptr_table(self, tensors) -> torch.Tensor:

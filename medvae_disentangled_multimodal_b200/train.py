@@ -232,8 +232,9 @@ class TrainStep:
     def set_lr(self, lr: float):
         """learning rate for the next steps (what a scheduler calls in graph mode: the captured AdamW kernel
         reads it from the device)"""
-        self.optimizer.lr = float(lr)
-        self.step_state[1:2].fill_(float(lr))
+        self.optimizer.lr = float(lr)          # the setter mirrors it into step_state when the optimizer has one
+        if self.optimizer.step_state is None:
+            self.step_state[1:2].fill_(float(lr))
 
     def _graph_step(self, x, cond):
         from . import _lib as L

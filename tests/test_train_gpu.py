@@ -128,7 +128,7 @@ def test_cuda_graph_step_equals_eager_step():
         for i in range(7):
             x, onehot, _ = batches[i % 3]
             if i == 5:
-                ts.set_lr(3e-4) if use_graph else setattr(ts.optimizer, "lr", 3e-4)
+                ts.optimizer.lr = 3e-4          # what a scheduler does; graph mode mirrors it to the device
             curve.append(float(ts.step(x.to(DEV), onehot.to(DEV))["loss"]))
         assert (ts._graph is not None) == use_graph
         if use_graph:
