@@ -7,10 +7,13 @@ kernels behind the C ABI in include/medvae_b200.h.  There is no CPU fallback.
 """
 from .blocks import AttnBlock, Decoder, Downsample, Encoder, LinAttnBlock, LinearAttention, ResnetBlock, Upsample
 from .losses import VAELoss
+from .out_of_scope import BiomedCLIPLoss, LPIPSLoss, LPIPSWithDiscriminator, NLayerDiscriminator
 from .vae import BaseVAE, BetaVAE, ConditionalVAE, FiLMLayer
 
 __all__ = ["BaseVAE", "BetaVAE", "ConditionalVAE", "Encoder", "Decoder", "VAELoss", "ResnetBlock", "AttnBlock",
-           "Downsample", "Upsample", "FiLMLayer", "LinearAttention", "LinAttnBlock"]
+           "Downsample", "Upsample", "FiLMLayer", "LinearAttention", "LinAttnBlock",
+           # exported by the reference next to the hot path; stubs that say so (out_of_scope.py)
+           "LPIPSLoss", "BiomedCLIPLoss", "LPIPSWithDiscriminator", "NLayerDiscriminator"]
 
 try:  # the disentangled model lives in its own module
     from .disentangled import DisentangledConditionalVAE, DisentangledVAELoss  # noqa: F401

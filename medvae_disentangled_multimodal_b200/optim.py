@@ -142,3 +142,17 @@ class FusedAdamW:
         return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,
                 "lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay,
                 "decoupled": self.decoupled, "max_norm": self.max_norm}
+
+    def load_state_dict(self, sd):
+        """moments are copied IN PLACE (the kernel's pointer tables and a captured graph keep pointing at them)"""
+        if len(sd["exp_avg"]) != len(self.exp_avg):
+            raise ValueError(f"optimizer state has {len(sd['exp_avg'])} tensors, this optimizer {len(self.exp_avg)}")
+        with torch.no_grad():
+            for dst, src in zip(self.exp_avg, sd["exp_avg"]):
+                dst.copy_(src)
+            for dst, src in zip(self.exp_avg_sq, sd["exp_avg_sq"]):
+                dst.copy_(src)
+        self.step_count = int(sd["step"])
+        self.betas, self.eps = (float(sd["betas"][0]), float(sd["betas"][1])), float(sd["eps"])
+        self.weight_decay, self.decoupled, self.max_norm = float(sd["weight_decay"]), bool(sd["decoupled"]), float(sd["max_norm"])
+        self.lr = float(sd["lr"])

@@ -214,6 +214,35 @@ class TrainStep:
             if id(p) not in sunk:
                 self._hooks.append(p.register_post_accumulate_grad_hook(self.buckets.mark_ready))
 
+    # ------------------------------------------------------------------ checkpoint / resume
+    def state_dict(self) -> Dict[str, object]:
+        """everything a resumed run needs to continue bit for bit: weights, Adam moments, step count, learning rate
+        and the Philox stream positions (what Lightning's checkpoint holds for the reference, lightning_module.py +
+        configs/callbacks: model state_dict + optimizer state)"""
+        rng = {"model": getattr(self.model, "_rng_step", 0)}
+        for name in ("decoder", "encoder"):
+            stack = getattr(self.model, name, None)
+            if stack is not None and hasattr(stack, "_dropout_step"):
+                rng[name] = stack._dropout_step
+        return {"model": {k: v.detach().clone() for k, v in self.model.state_dict().items()},
+                "optimizer": {k: ([t.detach().clone() for t in v] if isinstance(v, list) else v)
+                              for k, v in self.optimizer.state_dict().items()},
+                "rng": rng, "step_state": self.step_state.detach().clone()}
+
+    def load_state_dict(self, sd: Dict[str, object]):
+        with torch.no_grad():
+            own = self.model.state_dict()
+            for k, v in sd["model"].items():
+                own[k].copy_(v)                 # in place: gradient views, pointer tables and graphs stay valid
+        self.optimizer.load_state_dict(sd["optimizer"])
+        self.step_state.copy_(sd["step_state"])
+        self.model._rng_step = int(sd["rng"].get("model", 0))
+        for name in ("decoder", "encoder"):
+            stack = getattr(self.model, name, None)
+            if stack is not None and name in sd["rng"]:
+                stack._dropout_step = int(sd["rng"][name])
+        torch._C._increment_version(self.optimizer.params)   # packed bf16 operand caches must be refreshed
+
     def close(self):
         for h in self._hooks:
             h.remove()
