@@ -408,6 +408,7 @@ def b200_arm(args):
             "step_frac_of_peak": round(step_flops / (ms_res / args.steps * 1e9) / peaks["bf16_sustained"], 4),
             "kernels": kernels,
             "cpu_baseline": cpu,
+            "hbm_peak_allocated_gb": round(torch.cuda.max_memory_allocated() / 1e9, 2),
             "clocks": clocks,
             "loss": loss_val,
         }
