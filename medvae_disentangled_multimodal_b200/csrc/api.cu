@@ -223,6 +223,12 @@ int mvae_conv2d_fuses_gn(const mvae_conv_desc* d, int32_t groups, int32_t direct
     const int np = direction ? lower_dgrad(g, ps) : lower_fprop(g, ps);
     if (!use_umma_gather(*d, ps, np)) return 0;
     const int c = direction ? g.Cin : g.Cout;
+    if (direction) {
+        // tuning knob 10: 1 = never fuse the GroupNorm backward, 2 / 3 = only behind a reduction longer than 1152 / 2304
+        const int knob = debug_knob(10);
+        const long long kred = (long long)g.Cout * d->ksize * d->ksize;
+        if (knob == 1 || (knob == 2 && kred <= 1152) || (knob == 3 && kred <= 2304)) return 0;
+    }
     return (gn_cpg_log2(c, groups) >= 0 && gn_pre_ok(c, groups)) ? 1 : 0;
 }
 

@@ -16,6 +16,7 @@
 //  reduce kernel (wgrad):  D[128 co, BN ci] (per slab, per K-split) = sum_pixels dy[pix, co] * x[pix+tap, ci]
 //      Both operands are "MN-major" (the channel index is contiguous in NHWC), loaded by the same
 //      4-D boxes; 128 pixels per pipeline stage, 8 MMAs (K=16 pixels) per stage.
+#include <type_traits>
 #include "conv_lower.h"
 #include "umma.cuh"
 
@@ -132,8 +133,11 @@ enum { EPI_PLAIN = 0, EPI_GN_STATS = 1, EPI_GN_BWD = 2 };
 // The GroupNorm epilogues do ~15 instructions and a 2-byte global read per element: eight epilogue
 // warps (two per TMEM lane quarter, each taking half of the tile's columns) keep them hidden under
 // the MMAs of the next tile; the plain epilogue keeps four.
-__host__ __device__ constexpr int gather_epi_warps(int epi) { return epi == EPI_PLAIN ? 4 : 8; }
-__host__ __device__ constexpr int gather_threads(int epi) { return 64 + 32 * gather_epi_warps(epi); }
+// CS = column strips of the tile = epilogue warps per TMEM lane quarter.  The GroupNorm-backward epilogue (a tanh
+// and ~18 dependent instructions per element) is latency-bound with two warps per scheduler; where the MMAs of a
+// tile are too short to cover it (K = 9 x 128) CS = 4, i.e. 16 epilogue warps, hides it.
+__host__ __device__ constexpr int gather_csplit(int epi) { return epi == EPI_PLAIN ? 1 : 2; }
+__host__ __device__ constexpr int gather_threads_cs(int cs) { return 64 + 128 * cs; }
 
 // Sum N per-lane values over the 32 lanes of a warp with a transposing butterfly (N-1 + log2(32/N)
 // shuffles instead of 5N): afterwards lane l holds in v[0] the total of value index l / (32/N).
@@ -158,6 +162,17 @@ struct WarpReduceScatter<1> {
     }
 };
 
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float2 lds_f2(uint32_t addr) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+    return v;
+}
+
 // sa / sb: the two per-row partial sums of the eight 4-channel sub-blocks of one 32-channel chunk.
 // NG = GroupNorm groups inside the chunk.  Rows of one warp that all belong to image n_ref are
 // summed in registers first (one atomic per value per warp); otherwise every valid row adds its own.
@@ -165,7 +180,7 @@ struct WarpReduceScatter<1> {
 // (uniform) or the thread's own image.
 template <int NG>
 __device__ __forceinline__ void gn_flush(const float* sa, const float* sb, float* dst, int lane, bool uniform,
-                                         bool valid) {
+                                         bool valid, float scale) {
     constexpr int PER = 8 / NG;
     float v[2 * NG];
 #pragma unroll
@@ -178,18 +193,18 @@ __device__ __forceinline__ void gn_flush(const float* sa, const float* sb, float
     if (uniform) {
         WarpReduceScatter<2 * NG>::run(v, lane, 16);
         constexpr int LOW = 32 / (2 * NG);
-        if ((lane & (LOW - 1)) == 0) atomicAdd(dst + lane / LOW, v[0]);
+        if ((lane & (LOW - 1)) == 0) atomicAdd(dst + lane / LOW, v[0] * scale);
     } else if (valid) {
 #pragma unroll
-        for (int i = 0; i < 2 * NG; ++i) atomicAdd(dst + i, v[i]);
+        for (int i = 0; i < 2 * NG; ++i) atomicAdd(dst + i, v[i] * scale);
     }
 }
 __device__ __forceinline__ void gn_flush_any(int cpg_log2, const float* sa, const float* sb, float* dst, int lane,
-                                             bool uniform, bool valid) {
-    if (cpg_log2 == 2) gn_flush<8>(sa, sb, dst, lane, uniform, valid);
-    else if (cpg_log2 == 3) gn_flush<4>(sa, sb, dst, lane, uniform, valid);
-    else if (cpg_log2 == 4) gn_flush<2>(sa, sb, dst, lane, uniform, valid);
-    else gn_flush<1>(sa, sb, dst, lane, uniform, valid);
+                                             bool uniform, bool valid, float scale = 1.f) {
+    if (cpg_log2 == 2) gn_flush<8>(sa, sb, dst, lane, uniform, valid, scale);
+    else if (cpg_log2 == 3) gn_flush<4>(sa, sb, dst, lane, uniform, valid, scale);
+    else if (cpg_log2 == 4) gn_flush<2>(sa, sb, dst, lane, uniform, valid, scale);
+    else gn_flush<1>(sa, sb, dst, lane, uniform, valid, scale);
 }
 
 // MT pixel tiles (128 rows each) share every weight stage: a CTA tile is (MT x 128) pixels x BN channels.
@@ -213,9 +228,16 @@ struct GatherCfg {
     static constexpr int TMEM_COLS = (ACC_BUFS * MT * BN < 32) ? 32 : ACC_BUFS * MT * BN;   // powers of two
     static constexpr int SMEM = 1024 + STAGES * (A_BYTES + B_BYTES) + 256;
 };
+// EPI_GN_BWD keeps two small tables behind the pipeline stages: {gamma/2, beta/2} of every output channel (filled
+// once per CTA) and, per epilogue warp and pixel tile, {rstd, -mean*rstd} of each 4-channel sub-block of the warp's
+// column strip (refilled per tile, before the accumulator wait) — the epilogue then reads its per-channel constants
+// with shared-memory broadcasts at compile-time offsets instead of dependent global loads in the inner loop.
+constexpr int GN_COEF_MAX = 1024;                                   // channels
+constexpr int GN_BWD_SMEM = GN_COEF_MAX * 8 + 8 * 2 * 32 * 8;       // coefficient table + per-warp statistics slots
+__host__ __device__ constexpr int gather_smem(int base, int epi) { return base + (epi == EPI_GN_BWD ? GN_BWD_SMEM : 0); }
 
-template <int BN, int EPI, int MT, int CG>
-__global__ void __launch_bounds__(gather_threads(EPI), 1)
+template <int BN, int EPI, int MT, int CG, int CS>
+__global__ void __launch_bounds__(gather_threads_cs(CS), 1)
 conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_constant__ GatherDev p) {
     using Cfg = GatherCfg<BN, MT, CG>;
     static_assert(CG == 1 || MT == 1, "a CTA pair takes one pixel tile per CTA");
@@ -233,12 +255,18 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
     uint64_t* tfull = empty + STAGES;
     uint64_t* tempty = tfull + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    float2* sCoef = reinterpret_cast<float2*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + 256);   // EPI_GN_BWD only
+    float2* sStat = sCoef + GN_COEF_MAX;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
+    if (EPI == EPI_GN_BWD) {
+        for (int c = threadIdx.x; c < p.N; c += gather_threads_cs(CS))
+            sCoef[c] = make_float2(0.5f * __ldg(p.gn_gamma + c), 0.5f * __ldg(p.gn_beta + c));
+    }
     if (p.rows < 128) {
         // rows the TMA box never writes feed accumulator rows nobody stores; keep them finite
-        for (int i = threadIdx.x; i < STAGES * Cfg::A_BYTES / 16; i += gather_threads(EPI))
+        for (int i = threadIdx.x; i < STAGES * Cfg::A_BYTES / 16; i += gather_threads_cs(CS))
             reinterpret_cast<uint4*>(sA)[i] = make_uint4(0, 0, 0, 0);
         fence_proxy_async_smem();
     }
@@ -250,7 +278,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
         if (lane == 0) {
             for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
             // pair: the epilogue warps of BOTH CTAs release the leader's accumulator barrier
-            for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], CG * 32 * gather_epi_warps(EPI)); }
+            for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], CG * 32 * (4 * CS)); }
             fence_barrier_init();
         }
         __syncwarp();
@@ -348,6 +376,147 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
         int acc = 0; uint32_t acc_phase = 0;
         for (int tile = sched_id; tile < p.total_tiles; tile += sched_n) {
             const int nt = tile % p.n_tiles;
+          if constexpr (EPI == EPI_GN_BWD) {
+            // dgrad + GroupNorm backward.  Everything that does not depend on the accumulator — the GN input x of
+            // this thread's pixel row for all MT pixel tiles, the statistics of the row's image — is fetched before
+            // the accumulator wait; the inner loop then runs on registers and shared-memory broadcasts only.
+            constexpr int CW = BN / CS, XCH = CW / 32, NSUB = CW / 4;
+            static_assert(4 * CS * MT * NSUB * 8 <= 8 * 2 * 32 * 8, "statistics slots");
+            const int chalf = (warp - 2) >> 2;                // which column strip of the tile
+            const int cw0 = nt * BN + chalf * CW;             // first channel of this warp's column strip
+            float2* wstat = sStat + (warp - 2) * (MT * NSUB);         // [MT][NSUB] {rstd, -mean*rstd} per 4-channel sub-block
+            const float2* stat2 = reinterpret_cast<const float2*>(p.gn_stat);
+            uint4 aux[4];                                     // GN input x of the chunk being worked on (32 channels)
+            long long pixj[MT];
+            int nj[MT], slotn[MT];
+            unsigned vmj[MT];
+            bool validj[MT];
+            __syncwarp();                                     // every lane is done with the previous tile's slots
+#pragma unroll
+            for (int j = 0; j < MT; ++j) {
+                int mt = (CG == 2) ? (tile / p.n_tiles) * 2 + (int)rank : (tile / p.n_tiles) * MT + j;
+                const int tx = mt % p.tiles_x; mt /= p.tiles_x;
+                const int ty = mt % p.tiles_y;
+                const int tn = mt / p.tiles_y;
+                const int x = tx * p.bw + ix, y = ty * p.bh + iy, n = tn * p.bn + in;
+                const bool valid = (row < p.rows) && x < p.OW && y < p.OH && n < p.B;
+                const long long pix = p.o_off + (long long)n * p.o_sn + (long long)y * p.o_sy + (long long)x * p.o_sx;
+                const unsigned vm = __ballot_sync(0xffffffffu, valid);
+                // image of the warp's first valid row: the slots start out holding its statistics
+                const int n_ref = vm ? __shfl_sync(0xffffffffu, n, __ffs(vm) - 1) : -1;
+                pixj[j] = pix; nj[j] = n; validj[j] = valid; vmj[j] = vm; slotn[j] = n_ref;
+                if (vm && lane < NSUB) {
+                    const float2 mr = __ldg(stat2 + (long long)n_ref * p.gn_G + ((cw0 + 4 * lane) >> p.gn_cpg_log2));
+                    wstat[j * NSUB + lane] = make_float2(mr.y, -mr.x * mr.y);
+                }
+            }
+            // chunk (j, ci)'s x is fetched while the chunk before it is reduced (the first one before the wait)
+            auto load_aux = [&](int j, int ci) {
+                if (validj[j]) {
+                    const uint4* ap = reinterpret_cast<const uint4*>(p.gn_x + pixj[j] + cw0 + ci * 32);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) aux[i] = __ldg(ap + i);
+                }
+            };
+            load_aux(0, 0);
+            __syncwarp();
+            mbar_wait(&tfull[acc], acc_phase);
+            tc_fence_after();
+#pragma unroll
+            for (int j = 0; j < MT; ++j) {
+                const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * MT * BN + j * BN + chalf * CW);
+#pragma unroll
+                for (int ci = 0; ci < XCH; ++ci) {
+                    const int cbase = cw0 + ci * 32;
+                    // one pass per image among the warp's valid rows: exactly one unless the images are smaller than
+                    // a warp's 32 pixel rows; rows of other images sit a pass out (their sums stay zero), so every
+                    // pass ends in one warp-reduced atomic per value
+                    unsigned todo = vmj[j];
+                    int ncur = slotn[j];
+                    while (todo) {
+                        const bool active = validj[j] && nj[j] == ncur;
+                        if (slotn[j] != ncur) {
+                            __syncwarp();
+                            if (lane < NSUB) {
+                                const float2 mr = __ldg(stat2 + (long long)ncur * p.gn_G + ((cw0 + 4 * lane) >> p.gn_cpg_log2));
+                                wstat[j * NSUB + lane] = make_float2(mr.y, -mr.x * mr.y);
+                            }
+                            slotn[j] = ncur;
+                            __syncwarp();
+                        }
+                        float sa[8], sb[8];   // GN partial sums of the eight 4-channel sub-blocks (of gamma/2 * du)
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) { sa[k] = 0.f; sb[k] = 0.f; }
+                        const uint32_t cf = smem_u32(sCoef + cbase), sf = smem_u32(wstat + j * NSUB + ci * 8);
+#pragma unroll
+                        for (int hf = 0; hf < 2; ++hf) {     // 16 accumulator columns at a time
+                            uint32_t v[16];
+                            tmem_ld_32x16(t0 + (uint32_t)(ci * 32 + hf * 16), v);
+                            tmem_ld_wait();
+                            if (active) {
+                                float f[16];
+#pragma unroll
+                                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+                                if (p.bias) {
+                                    const float4* bp = reinterpret_cast<const float4*>(p.bias + cbase + hf * 16);
+#pragma unroll
+                                    for (int i = 0; i < 4; ++i) {
+                                        float4 b4 = __ldg(bp + i);
+                                        f[4 * i] += b4.x; f[4 * i + 1] += b4.y; f[4 * i + 2] += b4.z; f[4 * i + 3] += b4.w;
+                                    }
+                                }
+                                // f = dL/da  ->  du = f * silu'(u), u = xhat*gamma + beta, xhat = (x - mean)*rstd.  With
+                                // h = u/2 and t = tanh(h):  silu'(u) = (1 + t + h*(1 - t*t)) / 2.
+#pragma unroll
+                                for (int i = 0; i < 2; ++i) {
+                                    Vec8<bf16> x8; x8.raw = aux[2 * hf + i];
+                                    float xf[8]; x8.unpack(xf);
+#pragma unroll
+                                    for (int hh = 0; hh < 2; ++hh) {
+                                        const int kl = 2 * i + hh, k = 4 * hf + kl;   // sub-block within the half / the chunk
+                                        const float2 s2 = lds_f2(sf + k * 8);
+                                        const float rs = s2.x, nm = s2.y;
+                                        const float4 c01 = lds_f4(cf + k * 32), c23 = lds_f4(cf + k * 32 + 16);   // {gamma/2, beta/2} x 4
+                                        const float gh[4] = {c01.x, c01.z, c23.x, c23.z}, bh[4] = {c01.y, c01.w, c23.y, c23.w};
+#pragma unroll
+                                        for (int q = 0; q < 4; ++q) {
+                                            const float xh = fmaf(xf[4 * hh + q], rs, nm);
+                                            float d = f[4 * kl + q];
+                                            if (p.gn_silu) {
+                                                const float h = fmaf(xh, gh[q], bh[q]);
+                                                const float t = tanh_approx(h);
+                                                const float r = fmaf(h, fmaf(-t, t, 1.f), t);
+                                                d *= fmaf(r, 0.5f, 0.5f);
+                                                f[4 * kl + q] = d;
+                                            }
+                                            const float gd = d * gh[q];
+                                            sa[k] += gd; sb[k] = fmaf(gd, xh, sb[k]);
+                                        }
+                                    }
+                                }
+                                uint4* op = reinterpret_cast<uint4*>(p.out + pixj[j] + cbase + hf * 16);
+#pragma unroll
+                                for (int i = 0; i < 2; ++i) {
+                                    Vec8<bf16> o8; o8.pack(f + 8 * i);
+                                    op[i] = o8.raw;
+                                }
+                            }
+                        }
+                        todo &= ~__ballot_sync(0xffffffffu, active);
+                        const int ndone = ncur;
+                        if (todo) ncur = __shfl_sync(0xffffffffu, nj[j], __ffs(todo) - 1);
+                        else if (ci + 1 < XCH) load_aux(j, ci + 1);      // x of the next chunk, under this chunk's reduction
+                        else if (j + 1 < MT) load_aux(j + 1, 0);
+                        float* dst = p.gn_sums + ((long long)ndone * p.gn_G + (cbase >> p.gn_cpg_log2)) * 2;
+                        gn_flush_any(p.gn_cpg_log2, sa, sb, dst, lane, true, active, 2.f);   // the sums carried gamma/2
+                    }
+                    if (vmj[j] == 0u) {                                  // no valid row in this pixel tile: nothing ran
+                        if (ci + 1 < XCH) load_aux(j, ci + 1);
+                        else if (j + 1 < MT) load_aux(j + 1, 0);
+                    }
+                }
+            }
+          } else {
 #pragma unroll 1
           for (int j = 0; j < MT; ++j) {
             const uint32_t acc_col = (uint32_t)(acc * MT * BN + j * BN);
@@ -410,7 +579,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 // the per-element global operand (GN input x / residual) does not depend on the
                 // accumulator: fetch the whole strip before waiting for the MMAs
                 uint4 aux[XCH][4];
-                const bf16* auxp = (EPI == EPI_GN_BWD) ? p.gn_x : p.res;
+                const bf16* auxp = p.res;
                 const bool have_aux = valid && auxp != nullptr;
                 if (have_aux) {
 #pragma unroll
@@ -453,41 +622,6 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                                 for (int j = 0; j < 8; ++j) f[8 * i + j] += rf[j];
                             }
                         }
-                        if (EPI == EPI_GN_BWD) {
-                            // f = dL/da  ->  du = f * silu'(u), u = xhat*gamma + beta, xhat = (x - mean)*rstd
-                            const float2* stp = reinterpret_cast<const float2*>(p.gn_stat) + (long long)n * p.gn_G;
-                            float rs = 0.f, nm = 0.f; int gprev = -1;
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                Vec8<bf16> x8; x8.raw = aux[ci][i];
-                                float xf[8]; x8.unpack(xf);
-#pragma unroll
-                                for (int h = 0; h < 2; ++h) {
-                                    const int k = 2 * i + h;
-                                    const int g = (cbase + 4 * k) >> p.gn_cpg_log2;
-                                    if (g != gprev) {
-                                        const float2 mr = __ldg(stp + g);
-                                        rs = mr.y; nm = -mr.x * mr.y; gprev = g;
-                                    }
-                                    const float4 ga = __ldg(reinterpret_cast<const float4*>(p.gn_gamma + cbase) + k);
-                                    const float4 be = __ldg(reinterpret_cast<const float4*>(p.gn_beta + cbase) + k);
-                                    const float gam[4] = {ga.x, ga.y, ga.z, ga.w}, bet[4] = {be.x, be.y, be.z, be.w};
-#pragma unroll
-                                    for (int j = 0; j < 4; ++j) {
-                                        const float xh = fmaf(xf[4 * h + j], rs, nm);
-                                        float d = f[4 * k + j];
-                                        if (p.gn_silu) {
-                                            const float u = fmaf(xh, gam[j], bet[j]);
-                                            const float sg = sigmoid_t<bf16>(u);
-                                            d *= sg * fmaf(u, 1.f - sg, 1.f);
-                                            f[4 * k + j] = d;
-                                        }
-                                        const float gd = d * gam[j];
-                                        sa[k] += gd; sb[k] = fmaf(gd, xh, sb[k]);
-                                    }
-                                }
-                            }
-                        }
                         uint4* op = reinterpret_cast<uint4*>(p.out + pix + cbase);
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
@@ -510,6 +644,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 }
             }
           }   // pixel tiles of this CTA tile
+          }
             tc_fence_before();
             if (CG == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty[acc]), 0));   // the leader issues the next MMAs
             else mbar_arrive(&tempty[acc]);
@@ -535,13 +670,13 @@ bool umma_gather_ok(const GatherProblem& p) {
     return true;
 }
 
-template <int BN, int EPI, int MT, int CG>
+template <int BN, int EPI, int MT, int CG, int CS = gather_csplit(EPI)>
 static int launch_gather_epi(const GatherTmaps& tm, GatherDev& d, cudaStream_t st) {
     using Cfg = GatherCfg<BN, MT, CG>;
     static bool attr_set = false;
     if (!attr_set) {
-        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI, MT, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       Cfg::SMEM));
+        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI, MT, CG, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       gather_smem(Cfg::SMEM, EPI)));
         attr_set = true;
     }
     if (CG == 2) {
@@ -551,27 +686,35 @@ static int launch_gather_epi(const GatherTmaps& tm, GatherDev& d, cudaStream_t s
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof(cfg));
         cfg.gridDim = dim3(2 * pairs);
-        cfg.blockDim = dim3(gather_threads(EPI));
-        cfg.dynamicSmemBytes = Cfg::SMEM;
+        cfg.blockDim = dim3(gather_threads_cs(CS));
+        cfg.dynamicSmemBytes = gather_smem(Cfg::SMEM, EPI);
         cfg.stream = st;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
         count_launch();
-        MVAE_CUDA(cudaLaunchKernelEx(&cfg, conv_gather_umma_kernel<BN, EPI, MT, CG>, tm, d));
+        MVAE_CUDA(cudaLaunchKernelEx(&cfg, conv_gather_umma_kernel<BN, EPI, MT, CG, CS>, tm, d));
         MVAE_CUDA(cudaGetLastError());
         return 0;
     }
     int grid = d.total_tiles < num_sms() ? d.total_tiles : num_sms();
-    conv_gather_umma_kernel<BN, EPI, MT, CG><<<grid, gather_threads(EPI), Cfg::SMEM, st>>>(tm, d);
+    conv_gather_umma_kernel<BN, EPI, MT, CG, CS><<<grid, gather_threads_cs(CS), gather_smem(Cfg::SMEM, EPI), st>>>(tm, d);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
 template <int BN, int MT, int CG = 1>
 static int launch_gather(const GatherTmaps& tm, GatherDev& d, int epi, cudaStream_t st) {
     if (epi == EPI_GN_STATS) return launch_gather_epi<BN, EPI_GN_STATS, MT, CG>(tm, d, st);
-    if (epi == EPI_GN_BWD) return launch_gather_epi<BN, EPI_GN_BWD, MT, CG>(tm, d, st);
+    if (epi == EPI_GN_BWD) {
+        if constexpr (BN >= 128) {
+            // MMA cycles of one CTA tile against the ~25k cycles the 8-warp epilogue takes for it (knob 9: 1 = never, 2 = always)
+            const long long mma_cycles = (long long)d.taps.ntaps * d.kchunks * 4 * MT * (BN / 2);
+            const int knob = debug_knob(9);
+            if (knob == 2 || (knob == 0 && mma_cycles <= 12288)) return launch_gather_epi<BN, EPI_GN_BWD, MT, CG, 4>(tm, d, st);
+        }
+        return launch_gather_epi<BN, EPI_GN_BWD, MT, CG>(tm, d, st);
+    }
     return launch_gather_epi<BN, EPI_PLAIN, MT, CG>(tm, d, st);
 }
 
@@ -628,6 +771,8 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
                    "umma_gather: GroupNorm hook needs >= 4 channels per group (power of two) over all N channels");
         MVAE_CHECK(hook->mode == EPI_GN_STATS || (hook->x && hook->stat && hook->gamma && hook->beta),
                    "umma_gather: GroupNorm backward hook needs x, stats, gamma, beta");
+        MVAE_CHECK(hook->mode != EPI_GN_BWD || p.N <= GN_COEF_MAX, "umma_gather: GroupNorm backward hook takes <= %d channels",
+                   GN_COEF_MAX);
         epi = hook->mode;
         d.gn_G = hook->G; d.gn_cpg_log2 = hook->cpg_log2; d.gn_silu = hook->silu;
         d.gn_sums = hook->sums; d.gn_x = (const bf16*)hook->x; d.gn_stat = hook->stat;
