@@ -14,40 +14,59 @@ __device__ __forceinline__ void up_rset(int a, int ui, int& lo, int& hi) {
     else        { lo = ui == 0 ? 0 : 2; hi = ui == 0 ? 1 : 2; }
 }
 
+// A CTA takes a 32 (co) x 32 (ci) tile with all R*R taps: the tile's rows are contiguous spans of the OIHW tensor
+// (coalesced reads into shared memory), and each slab of both operands is written from there in 64-byte row
+// pieces — ci-major for the fprop operand, co-major for the dgrad operand (row pitch 289 and tap stride 9 are odd:
+// both transposed reads are bank-conflict free).  8 bytes of HBM traffic per weight, once per optimizer step.
+constexpr int PK_T = 32, PK_PITCH = PK_T * 9 + 1;
+
 template <typename T>
-__global__ void pack_weights_kernel(const float* __restrict__ w, T* __restrict__ wf, T* __restrict__ wd,
-                                    int Cout, int Cin, int R, int mode, int nslabs, int Ctot, int co_off) {
-    long long total = (long long)nslabs * Cout * Cin;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
-        int ci = (int)(i % Cin);
-        long long r_ = i / Cin;
-        int co = (int)(r_ % Cout);
-        int slab = (int)(r_ / Cout);
-        const float* src = w + ((long long)co * Cin + ci) * R * R;
-        float v;
-        if (mode == MVAE_CONV_UP) {
-            int vi = slab & 1, ui = (slab >> 1) & 1, b = (slab >> 2) & 1, a = (slab >> 3) & 1;
-            int rlo, rhi, slo, shi;
-            up_rset(a, ui, rlo, rhi);
-            up_rset(b, vi, slo, shi);
-            v = 0.f;
-            for (int r = rlo; r <= rhi; ++r)
-                for (int s = slo; s <= shi; ++s) v += src[r * 3 + s];
-        } else {
-            v = src[slab];
+__global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ w, T* __restrict__ wf,
+                                                           T* __restrict__ wd, int Cout, int Cin, int R, int mode,
+                                                           int nslabs, int Ctot, int co_off) {
+    __shared__ float s[PK_T][PK_PITCH];
+    const int RR = R * R;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_ci = (Cin + PK_T - 1) / PK_T, tiles_co = (Cout + PK_T - 1) / PK_T;
+    for (int tile = blockIdx.x; tile < tiles_ci * tiles_co; tile += gridDim.x) {
+        const int co0 = (tile / tiles_ci) * PK_T, ci0 = (tile % tiles_ci) * PK_T;
+        const int nco = Cout - co0 < PK_T ? Cout - co0 : PK_T, nci = Cin - ci0 < PK_T ? Cin - ci0 : PK_T;
+        for (int r = warp; r < nco; r += 8) {
+            const float* src = w + ((long long)(co0 + r) * Cin + ci0) * RR;
+            for (int k = lane; k < nci * RR; k += 32) s[r][k] = src[k];
         }
-        if (wf) wf[((long long)slab * Ctot + co_off + co) * Cin + ci] = from_f<T>(v);
-        if (wd) wd[((long long)slab * Cin + ci) * Ctot + co_off + co] = from_f<T>(v);
+        __syncthreads();
+        for (int slab = 0; slab < nslabs; ++slab) {
+            int rlo = 0, rhi = 0, slo = 0, shi = 0;
+            if (mode == MVAE_CONV_UP) {
+                const int vi = slab & 1, ui = (slab >> 1) & 1, b = (slab >> 2) & 1, a = (slab >> 3) & 1;
+                up_rset(a, ui, rlo, rhi);
+                up_rset(b, vi, slo, shi);
+            }
+            auto value = [&](int co, int ci) -> float {
+                const float* e = &s[co][ci * RR];
+                if (mode != MVAE_CONV_UP) return e[slab];
+                float v = 0.f;
+                for (int r = rlo; r <= rhi; ++r)
+                    for (int q = slo; q <= shi; ++q) v += e[r * 3 + q];
+                return v;
+            };
+            if (wf && lane < nci)
+                for (int co = warp; co < nco; co += 8)
+                    wf[((long long)slab * Ctot + co_off + co0 + co) * Cin + ci0 + lane] = from_f<T>(value(co, lane));
+            if (wd && lane < nco)
+                for (int ci = warp; ci < nci; ci += 8)
+                    wd[((long long)slab * Cin + ci0 + ci) * Ctot + co_off + co0 + lane] = from_f<T>(value(lane, ci));
+        }
+        __syncthreads();
     }
 }
 
 int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot, int co_off, int dtype,
                  cudaStream_t st) {
     int nslabs = conv_num_slabs(g);
-    long long total = (long long)nslabs * g.Cout * g.Cin;
-    int blocks = (int)((total + 255) / 256);
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    long long tiles = (long long)((g.Cout + PK_T - 1) / PK_T) * ((g.Cin + PK_T - 1) / PK_T);
+    int blocks = (int)(tiles < 148 * 8 ? tiles : 148 * 8);
     if (dtype == MVAE_F32)
         pack_weights_kernel<float><<<blocks, 256, 0, st>>>(w, (float*)wf, (float*)wd, g.Cout, g.Cin, g.R, g.mode,
                                                             nslabs, Ctot, co_off);

@@ -24,15 +24,20 @@ for stage in $STAGES; do
     full)
       timeout 300 $CMD > gpurun_out/plain_full.log 2>&1 || { echo "plain rc=$?" >> gpurun_out/rc.txt; continue; }
       # (merged results must stay under 64 MiB: no --import-source here, few launches per report)
-      timeout 600 ncu --set full --clock-control none -k regex:conv_gather_umma -s 4 -c 8 -f -o gpurun_out/prof_gf $CMD > gpurun_out/ncu_gf.log 2>&1
+      timeout 600 ncu --set full --clock-control none -k regex:conv_gather_umma -s 4 -c 6 -f -o gpurun_out/prof_gf $CMD > gpurun_out/ncu_gf.log 2>&1
       echo "gf rc=$?" >> gpurun_out/rc.txt
-      timeout 600 ncu --set full --clock-control none -k regex:conv_gather_umma -s 152 -c 10 -f -o gpurun_out/prof_gb $CMD > gpurun_out/ncu_gb.log 2>&1
+      timeout 600 ncu --set full --clock-control none -k regex:conv_gather_umma -s 152 -c 8 -f -o gpurun_out/prof_gb $CMD > gpurun_out/ncu_gb.log 2>&1
       echo "gb rc=$?" >> gpurun_out/rc.txt
-      timeout 600 ncu --set full --clock-control none -k regex:conv_reduce_umma -s 2 -c 6 -f -o gpurun_out/prof_wg $CMD > gpurun_out/ncu_wg.log 2>&1
+      timeout 600 ncu --set full --clock-control none -k regex:conv_reduce_umma -s 2 -c 4 -f -o gpurun_out/prof_wg $CMD > gpurun_out/ncu_wg.log 2>&1
       echo "wg rc=$?" >> gpurun_out/rc.txt
-      timeout 600 ncu --set full --clock-control none -k regex:"gn_(apply_pre|bwd_pre)" -s 4 -c 6 -f -o gpurun_out/prof_gn $CMD > gpurun_out/ncu_gn.log 2>&1
+      timeout 600 ncu --set full --clock-control none -k regex:"gn_(apply_pre|bwd_pre)" -s 4 -c 4 -f -o gpurun_out/prof_gn $CMD > gpurun_out/ncu_gn.log 2>&1
       echo "gn rc=$?" >> gpurun_out/rc.txt;;
   esac
+done
+# gpurun merges at most 64 MiB back (and nothing at all beyond that): drop the largest reports until it fits
+while [ "$(du -sm gpurun_out | cut -f1)" -ge 60 ]; do
+  big=$(ls -S gpurun_out/*.ncu-rep 2>/dev/null | head -1); [ -z "$big" ] && break
+  echo "dropping $big ($(du -m "$big" | cut -f1) MiB) to stay under the merge limit" >> gpurun_out/rc.txt; rm -f "$big"
 done
 cat gpurun_out/rc.txt
 tail -n 12 gpurun_out/t_gpu.log gpurun_out/smoke.log gpurun_out/bench*.log 2>/dev/null

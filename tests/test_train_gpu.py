@@ -198,8 +198,9 @@ def test_checkpoint_resume_continues_bit_for_bit(use_graph):
     else:
         assert got == want, (got, want)
         # the global gradient norm is accumulated with fp64 atomics (order-dependent in the last bits), so the clipped
-        # update — not the loss sequence — may differ by an ulp
-        assert float((final - final2).abs().max()) <= 1e-7 * float(final.abs().max())
+        # update — not the loss sequence — may differ by an ulp (2^-23 relative; two allowed)
+        dmax, wmax = float((final - final2).abs().max()), float(final.abs().max())
+        assert dmax <= 2.5e-7 * wmax, (dmax, wmax, int(((final - final2) != 0).sum()), final.numel())
 
 
 def test_out_of_scope_names_fail_loudly():
