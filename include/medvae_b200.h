@@ -56,7 +56,11 @@ int mvae_abi_version(void);
 int mvae_device_ok(void);
 /* number of CUDA kernels this library has launched in this process (all threads) */
 uint64_t mvae_launch_count(void);
-/* debug knobs (descriptor variants for bring-up); key/value ints */
+/* tuning / bring-up knobs (key, value ints; every default is 0).  2: 1 = attention without tcgen05;  3: GroupNorm chunk
+ * budget in MB;  5: 1 = no two-pixel-tile stages on 128-channel tiles;  6: 1 = one filter tap per wgrad CTA;
+ * 7: 1 = 256 x 256 single-buffer tiles;  8: 1 = no CTA pairs;  9: GroupNorm-backward epilogue on 8 (1) / 16 (2) warps
+ * instead of the per-layer choice;  10: 1 = never fuse the GroupNorm backward into dgrad, 2 / 3 = only behind a
+ * reduction longer than 1152 / 2304. */
 int mvae_set_debug(int key, int value);
 
 /* output spatial size for a conv desc */

@@ -21,6 +21,10 @@ for stage in $STAGES; do
       timeout 300 $CMD > gpurun_out/plain_l256.log 2>&1 &&
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 12000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
       echo "list rc=$?" >> gpurun_out/rc.txt;;
+    gbonly)   # only the dgrad + GroupNorm-backward launches of the backward pass (short trips)
+      timeout 300 $CMD > gpurun_out/plain_full.log 2>&1 || { echo "plain rc=$?" >> gpurun_out/rc.txt; continue; }
+      timeout 600 ncu --set full --clock-control none -k regex:conv_gather_umma -s 152 -c 8 -f -o gpurun_out/prof_gb $CMD > gpurun_out/ncu_gb.log 2>&1
+      echo "gb rc=$?" >> gpurun_out/rc.txt;;
     full)
       timeout 300 $CMD > gpurun_out/plain_full.log 2>&1 || { echo "plain rc=$?" >> gpurun_out/rc.txt; continue; }
       # (merged results must stay under 64 MiB: no --import-source here, few launches per report)
