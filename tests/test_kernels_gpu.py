@@ -299,6 +299,7 @@ GN_FUSE_CASES = [
     (2, 14, 14, 256, 256, 3, 0, 32), (4, 4, 4, 128, 128, 3, 0, 32), (2, 64, 64, 128, 128, 3, 0, 32),
     (2, 32, 32, 128, 128, 3, 1, 32), (2, 16, 16, 256, 256, 3, 2, 32), (2, 16, 16, 64, 64, 3, 0, 16),
     (77, 32, 32, 128, 128, 3, 0, 32),   # 616 pixel tiles: the paired-tile gather variant with both GroupNorm epilogues
+    (40, 32, 32, 256, 128, 3, 0, 32),   # dgrad: 256 channels behind a short reduction (K = 1152) = CTA pairs + 16 epilogue warps
 ]
 
 
@@ -385,6 +386,21 @@ def test_conv_dgrad_gn_backward(case, silu, with_add):
     assert rel_err(dg1, dg0) < 2e-2 and rel_err(db1, db0) < 2e-2
     cs_ref = dx1.double().sum(dim=(0, 1, 2))
     assert float((cs1.double() - cs_ref).abs().max()) <= 2e-2 * float(cs_ref.abs().max()) + 1e-3
+
+
+@pytest.mark.umma
+@pytest.mark.parametrize("warps", [1, 2], ids=["8warps", "16warps"])
+@pytest.mark.parametrize("case", [(5, 7, 7, 512, 512, 3, 0, 32), (77, 32, 32, 128, 128, 3, 0, 32),
+                                  (40, 32, 32, 256, 128, 3, 0, 32), (2, 16, 16, 256, 256, 3, 2, 32)])
+def test_conv_dgrad_gn_backward_epilogue_warps(case, warps):
+    """the GroupNorm-backward epilogue on 8 and on 16 warps (knob 9 overrides the per-layer choice), incl. warps whose
+    rows span several images (7x7) and the upsampling conv's four parity problems"""
+    L, _ = _mods()
+    L.lib().mvae_set_debug(9, warps)
+    try:
+        test_conv_dgrad_gn_backward(case, True, True)
+    finally:
+        L.lib().mvae_set_debug(9, 0)
 
 
 # ------------------------------------------------------------------ CTA pairs (cta_group::2); knob 8 = 1 turns them off
