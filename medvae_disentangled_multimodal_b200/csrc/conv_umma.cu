@@ -10,8 +10,8 @@
 //      Epilogue variants (template EPI): the GroupNorm either side of the conv rides here —
 //      EPI_GN_STATS accumulates the consumer GroupNorm's per-(sample, group) sums of the output,
 //      EPI_GN_BWD turns dL/d[silu(GN(x))] into dL/du and accumulates the GroupNorm-backward group
-//      sums (warps 2-9: two warps per TMEM lane quarter, x / residual strips prefetched before the
-//      accumulator is ready).
+//      sums (warps 2..: CS = 2 or 4 warps per TMEM lane quarter, one column strip each; x / residual
+//      strips and the per-channel constants fetched before the accumulator is ready).
 //
 //  reduce kernel (wgrad):  D[128 co, BN ci] (per slab, per K-split) = sum_pixels dy[pix, co] * x[pix+tap, ci]
 //      Both operands are "MN-major" (the channel index is contiguous in NHWC), loaded by the same
@@ -130,7 +130,7 @@ struct GatherDev {
 
 constexpr int G_THREADS = 192;
 enum { EPI_PLAIN = 0, EPI_GN_STATS = 1, EPI_GN_BWD = 2 };
-// The GroupNorm epilogues do ~15 instructions and a 2-byte global read per element: eight epilogue
+// The GroupNorm epilogues do 8-18 instructions and a 2-byte global read per element: eight epilogue
 // warps (two per TMEM lane quarter, each taking half of the tile's columns) keep them hidden under
 // the MMAs of the next tile; the plain epilogue keeps four.
 // CS = column strips of the tile = epilogue warps per TMEM lane quarter.  The GroupNorm-backward epilogue (a tanh
