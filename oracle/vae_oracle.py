@@ -19,6 +19,7 @@ All tensors are NCHW, dtype follows the weights (fp32 or fp64).
 from __future__ import annotations
 
 import math
+import time
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -378,7 +379,11 @@ class ReferenceTrainer:
         for p in self.params.values():
             if p.grad is not None:
                 torch.nan_to_num_(p.grad, nan=0.0, posinf=0.0, neginf=0.0)
+        t0 = time.perf_counter()
         if self.max_norm and self.max_norm > 0:
             torch.nn.utils.clip_grad_norm_(list(self.params.values()), self.max_norm)
         self.opt.step()
+        # seconds of the per-step (batch-size independent) part: clip + optimizer; bench.py reports it
+        # next to the CPU baseline because a bounded CPU sample amortises it over few images
+        self.last_update_s = time.perf_counter() - t0
         return {k: float(v.detach()) for k, v in ld.items()}
