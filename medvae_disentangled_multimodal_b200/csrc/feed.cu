@@ -9,6 +9,7 @@
 //  * FiLMLayer (conditional_vae.py:191-203): features * (W_s c + b_s) + (W_t c + b_t), fwd + bwd.
 #include "../../include/medvae_b200.h"
 #include "common.cuh"
+#include "philox.cuh"
 
 namespace mvae {
 
@@ -59,24 +60,6 @@ int batch_feed_u8(const uint8_t* src, const int* src_c, const int* tgt_c, const 
 }
 
 // ------------------------------------------------------------------ dropout
-struct Philox4 {
-    uint32_t k0, k1;
-    __device__ Philox4(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
-    __device__ __forceinline__ uint4 operator()(uint64_t lo, uint64_t hi) const {
-        uint32_t c0 = (uint32_t)lo, c1 = (uint32_t)(lo >> 32), c2 = (uint32_t)hi, c3 = (uint32_t)(hi >> 32);
-        uint32_t a = k0, b = k1;
-#pragma unroll
-        for (int r = 0; r < 10; ++r) {
-            uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-            uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-            uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
-            c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-            a += 0x9E3779B9u; b += 0xBB67AE85u;
-        }
-        return make_uint4(c0, c1, c2, c3);
-    }
-};
-
 // y[e] = x[e] * keep(e) / (1 - p); keep(e) = u(e) >= p with u from Philox(seed; counter e/4, offset), or mask_in[e].
 // The backward is the same call on dy.  4 elements per thread (one Philox block).
 template <typename T>
@@ -85,10 +68,10 @@ __global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ x, T
                                                       const uint8_t* __restrict__ mask_in, uint8_t* __restrict__ mask_out) {
     if (dyn) offset += ((uint64_t)dyn[2]) << 20;   // device-side stream position (CUDA-graph replays advance it)
     const float scale = 1.f / (1.f - p);
-    const Philox4 ph(seed);
+    const Philox ph(seed);
     const long long quads = (n + 3) / 4;
     for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < quads; q += (long long)gridDim.x * blockDim.x) {
-        uint4 r = make_uint4(0, 0, 0, 0);
+        PhiloxWords r = {0u, 0u, 0u, 0u};
         if (!mask_in) r = ph((uint64_t)q, offset);
         const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
@@ -97,7 +80,7 @@ __global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ x, T
             if (e >= n) break;
             bool keep;
             if (mask_in) keep = mask_in[e] != 0;
-            else keep = ((float)(w[j] >> 8) * (1.0f / 16777216.0f)) >= p;
+            else keep = philox_u01_grid(w[j]) >= p;
             if (mask_out) mask_out[e] = keep ? 1 : 0;
             y[e] = keep ? from_f<T>(to_f<T>(x[e]) * scale) : from_f<T>(0.f);
         }

@@ -3,35 +3,19 @@
 // disentangled_conditional_vae.py:409-412 (clamps), :524-525 (KL sum).
 #include "../../include/medvae_b200.h"
 #include "common.cuh"
+#include "philox.cuh"
 
 namespace mvae {
 
-// ------------------------------------------------------------------ Philox4x32-10 (counter based)
-struct Philox {
-    uint32_t k0, k1;
-    __device__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
-    __device__ __forceinline__ uint4 operator()(uint64_t ctr_lo, uint64_t ctr_hi) const {
-        uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
-        uint32_t a = k0, b = k1;
-#pragma unroll
-        for (int r = 0; r < 10; ++r) {
-            uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-            uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-            uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
-            c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-            a += 0x9E3779B9u; b += 0xBB67AE85u;
-        }
-        return make_uint4(c0, c1, c2, c3);
-    }
-};
-__device__ __forceinline__ float u01(uint32_t x) { return ((float)(x >> 8) + 0.5f) * (1.0f / 16777216.0f); }
+// ------------------------------------------------------------------ Philox4x32-10 noise (philox.cuh)
 // one standard normal for element `e` of stream (seed, offset): Box-Muller on words (0,1) or (2,3)
 __device__ __forceinline__ float philox_normal(uint64_t seed, uint64_t offset, uint64_t e) {
-    Philox ph(seed);
-    uint4 r = ph(e >> 1, offset);
-    uint32_t a = (e & 1) ? r.z : r.x, b = (e & 1) ? r.w : r.y;
-    float u1 = u01(a), u2 = u01(b);
-    return sqrtf(-2.0f * __logf(u1)) * __cosf(6.283185307179586f * u2);
+    uint32_t a, b;
+    philox_normal_words(seed, offset, e, a, b);
+    const float u1 = philox_u01(a), u2 = philox_u01(b);
+    // u1 can round to 1 - 2^-24: the clamp keeps an approximate logarithm that lands on the wrong side of 0 from
+    // turning into a NaN under the root
+    return sqrtf(fmaxf(-2.0f * __logf(u1), 0.f)) * __cosf(6.283185307179586f * u2);
 }
 
 // ------------------------------------------------------------------ reparam + KL forward

@@ -1,0 +1,49 @@
+"""The device RNG against the numpy Philox restatement (oracle/philox_oracle.py, pinned to the Random123
+known-answer vectors by tests/test_philox_cpu.py): dropout keep masks bit for bit, reparameterisation
+noise to the accuracy of the fast log / cos intrinsics.  Streams are addressed exactly as the model does
+(seed, offset) through the C ABI."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import philox_oracle as P
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _ops():
+    from medvae_disentangled_multimodal_b200 import ops
+    return ops
+
+
+@pytest.mark.parametrize("n,p,seed,offset", [(7, 0.1, 1234, 5), (4096, 0.1, 0xDEADBEEFCAFE, 3 << 20),
+                                             (100003, 0.5, 2 ** 62 + 11, 2 ** 40), (1 << 20, 0.25, 42, 0)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_dropout_mask_is_the_philox_stream_bit_for_bit(n, p, seed, offset, dtype):
+    ops = _ops()
+    x = torch.randn(n, generator=torch.Generator().manual_seed(3)).to(DEV).to(dtype)
+    y, mask = ops.dropout_apply(x, p, seed, offset, want_mask=True)
+    torch.cuda.synchronize()
+    want = P.dropout_keep_mask(n, p, seed, offset)
+    assert np.array_equal(mask.cpu().numpy().astype(bool), want)
+    keep = torch.from_numpy(want).to(DEV)
+    scale = float(np.float32(1.0) / (np.float32(1.0) - np.float32(p)))     # fp32 arithmetic, as in the kernel
+    ref = torch.where(keep, (x.float() * scale).to(dtype), torch.zeros((), dtype=dtype, device=DEV))
+    assert torch.equal(y, ref)
+
+
+@pytest.mark.parametrize("B,zc,R,seed,offset", [(4, 8, 7, 1234, 1), (3, 5, 4, 2 ** 40 + 7, 2 ** 33), (64, 32, 8, 7, 0)])
+def test_reparam_noise_is_box_muller_on_the_philox_stream(B, zc, R, seed, offset):
+    ops = _ops()
+    mom = torch.zeros(B, R, R, 2 * zc, device=DEV)           # mu = 0, logvar = 0: z == eps
+    _, _, z, _, eps, _ = ops.reparam_kl_fwd(mom, None, zc, 0.0, seed, offset)
+    torch.cuda.synchronize()
+    got = eps.cpu().numpy().reshape(-1).astype(np.float64)   # NCHW element order = stream order
+    assert np.isfinite(got).all() and torch.equal(z, eps)
+    want = P.normal_noise(B * zc * R * R, seed, offset).astype(np.float64)
+    err = np.abs(got - want)
+    # __logf is good to ~4e-7 absolute near u1 = 1, which the root amplifies for the few samples with |z| << 1;
+    # everywhere else the fast intrinsics are good to ~1e-5.  A wrong word, block or stream gives O(1) errors.
+    assert err.max() < 5e-3, err.max()
+    assert np.median(err) < 1e-5 and (err > 2e-4).mean() < 1e-2
