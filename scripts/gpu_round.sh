@@ -18,7 +18,7 @@ for stage in $STAGES; do
     bench_c2) timeout 600 python bench.py --workload c2 --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_c2.log 2>&1; echo "bench_c2 rc=$?" >> gpurun_out/rc.txt;;
     bench_c1) timeout 600 python bench.py --workload c1 --precision fp32 --steps 10 --warmup 3 > gpurun_out/bench_c1.log 2>&1; echo "bench_c1 rc=$?" >> gpurun_out/rc.txt;;
     torchbase)   # the GPU baseline to beat: the reference's arithmetic on stock cuDNN / cuBLAS / ATen kernels
-      timeout 900 python scripts/gpu_torch_baseline.py --workload c4 --steps 5 --warmup 2 > gpurun_out/torch_baseline_c4.log 2>&1; echo "torchbase rc=$?" >> gpurun_out/rc.txt;;
+      timeout 900 python tests/gpu_torch_baseline.py --workload c4 --steps 5 --warmup 2 > gpurun_out/torch_baseline_c4.log 2>&1; echo "torchbase rc=$?" >> gpurun_out/rc.txt;;
     list)
       timeout 300 $CMD > gpurun_out/plain_l256.log 2>&1 &&
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 12000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1

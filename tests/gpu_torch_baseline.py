@@ -7,7 +7,7 @@ seeded weights.  Variants: fp32 with TF32 off / on, bf16 autocast, NCHW and chan
 NOT the product and not part of bench.py's arms: none of libmedvae_b200's kernels run here.  One JSON line
 per variant:
 
-    python scripts/gpu_torch_baseline.py [--workload c4] [--batch 128] [--steps 5] [--warmup 2]
+    python tests/gpu_torch_baseline.py [--workload c4] [--batch 128] [--steps 5] [--warmup 2]
 
 (--device cpu runs the same loop on the host for a syntax check in the build container.)"""
 from __future__ import annotations
