@@ -89,3 +89,53 @@ def test_no_cpu_fallback():
     with pytest.raises(L.MvaeError):
         M.VAELoss()(inputs=torch.zeros(1), reconstructions=torch.zeros(1),
                     posteriors=torch.distributions.Normal(torch.zeros(1), torch.ones(1)))
+
+
+def header_prototypes():
+    """-> {name: (return C type, [parameter C types])} parsed from include/medvae_b200.h"""
+    txt = open(os.path.join(ROOT, "include", "medvae_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    txt = re.sub(r"//[^\n]*", "", txt)
+    out = {}
+    for m in re.finditer(r"([A-Za-z_][A-Za-z0-9_ ]*?[\s\*]+)(mvae_[a-z0-9_]+)\s*\(([^)]*)\)\s*;", txt):
+        ret, name, args = m.group(1).strip(), m.group(2), m.group(3).strip()
+        params = [] if args in ("", "void") else [a.strip() for a in args.split(",")]
+        out[name] = (ret, params)
+    return out
+
+
+def _ctype_class(decl: str) -> str:
+    """coarse ABI class of a C parameter / return declaration"""
+    d = decl.replace("const", " ").strip()
+    if "*" in d:
+        return "ptr"
+    words = d.split()
+    ty = " ".join(words[:-1]) if len(words) > 1 and words[-1] not in ("int", "float", "double", "long") and \
+        not words[-1].endswith("_t") else " ".join(words)
+    return {"int": "i32", "int32_t": "i32", "int64_t": "i64", "long long": "i64", "uint64_t": "u64", "size_t": "u64",
+            "float": "f32", "double": "f64", "unsigned long long": "u64"}[ty]
+
+
+def _ctypes_class(t) -> str:
+    if t is None:
+        return "void"
+    if t in (C.c_void_p, C.c_char_p) or hasattr(t, "contents") or issubclass(t, C._Pointer):
+        return "ptr"
+    return {C.c_int: "i32", C.c_int32: "i32", C.c_int64: "i64", C.c_longlong: "i64", C.c_uint64: "u64",
+            C.c_size_t: "u64", C.c_ulonglong: "u64", C.c_float: "f32", C.c_double: "f64"}[t]
+
+
+def test_ctypes_signatures_match_the_header_prototypes():
+    """argument count and ABI class (pointer / 32-bit int / 64-bit int / float / double) of every entry of
+    _lib.SIGNATURES against the prototype in include/medvae_b200.h: a drifted binding would otherwise only show up
+    as garbage arguments on the GPU box."""
+    L = _lib()
+    protos = header_prototypes()
+    assert set(protos) == set(L.SIGNATURES), set(protos) ^ set(L.SIGNATURES)
+    for name, (ret, params) in sorted(protos.items()):
+        restype, argtypes = L.SIGNATURES[name]
+        assert len(argtypes) == len(params), f"{name}: header has {len(params)} parameters, ctypes table {len(argtypes)}"
+        got = [_ctypes_class(t) for t in argtypes]
+        want = [_ctype_class(p) for p in params]
+        assert got == want, f"{name}: header {want} vs ctypes {got}"
+        assert _ctypes_class(restype) == _ctype_class(ret + " x"), f"{name}: return type"
