@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define MVAE_ABI_VERSION 3
+#define MVAE_ABI_VERSION 4
 
 enum { MVAE_F32 = 0, MVAE_BF16 = 1 };
 
@@ -183,15 +183,17 @@ int mvae_nchw_f32_to_nhwc(const float* src, void* dst, int32_t batch, int32_t h,
 
 /* torch.chunk + BaseVAE.reparameterize (base_vae.py:76,83-87) + the KL integrand of
  * VAELoss (vae_losses.py:55), one pass.  moments: NHWC [B,R,R,2*zc].  eps: NCHW fp32 or NULL
- * (then Philox4x32-10 keyed by (seed, offset, element) generates it and, if eps_out != NULL,
- * stores it).  Outputs NCHW fp32 mean/logvar/z, optionally std = exp(0.5 logvar) (std_out) and
+ * (then Philox4x32-10 keyed by (seed, offset, elem_base + element) generates it and, if eps_out !=
+ * NULL, stores it; elem_base = this call's first sample in the GLOBAL batch x zc*r*r, so the noise of a
+ * sample does not depend on how the batch is split over ranks and micro-batches — SURVEY 8e).  Outputs NCHW fp32 mean/logvar/z, optionally std = exp(0.5 logvar) (std_out) and
  * NHWC z (z_nhwc, dtype), both may be NULL.  kl_sum:
  * one double, ACCUMULATED: sum 0.5(e^lv + mu^2 - 1 - lv).  clamp > 0 applies
  * clamp(mu,±clamp), clamp(logvar,±clamp) first (disentangled_conditional_vae.py:409-412). */
 int mvae_reparam_kl_fwd(const void* moments, const float* eps, float* eps_out, float* mean,
                         float* logvar, float* std_out, float* z_nchw, void* z_nhwc, double* kl_sum,
                         int32_t batch, int32_t zc, int32_t r, float clamp, uint64_t seed,
-                        uint64_t offset, const double* step_state, int32_t dtype, void* stream);
+                        uint64_t offset, uint64_t elem_base, const double* step_state, int32_t dtype,
+                        void* stream);
 /* d_moments (NHWC dtype) from d_mean, d_logvar, d_z (NCHW fp32, each may be NULL) and the
  * saved mean/logvar/eps; clamp masks the gradient like torch.clamp. */
 int mvae_reparam_kl_bwd(const float* d_mean, const float* d_logvar, const float* d_z,

@@ -69,7 +69,7 @@ SIGNATURES = {
     "mvae_nhwc_to_nchw_f32": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_nchw_f32_to_nhwc": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_reparam_kl_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _f32, _u64, _u64,
-                                      _vp, _i32, _vp]),
+                                      _u64, _vp, _i32, _vp]),
     "mvae_reparam_kl_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _f32, _i32, _vp]),
     "mvae_recon_loss_fwd_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _vp]),
     "mvae_kl_fwd": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),

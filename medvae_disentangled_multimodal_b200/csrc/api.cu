@@ -67,7 +67,7 @@ int attn_bwd(const void* qkv, const float* probs, const void* dout, void* dqkv, 
              int dtype, cudaStream_t st);
 int reparam_fwd(const void* mom, const float* eps, float* eps_out, float* mean, float* logvar, float* stdv,
                 float* z_nchw, void* z_nhwc, double* kl_sum, int B, int zc, int R, float clampv, uint64_t seed, uint64_t offset,
-                const double* dyn, int dtype, cudaStream_t st);
+                uint64_t elem_base, const double* dyn, int dtype, cudaStream_t st);
 int step_state_advance(double* dyn, double rng_inc, cudaStream_t st);
 int reparam_bwd(const float* d_mean, const float* d_logvar, const float* d_z, const float* logvar, const float* eps,
                 const void* mom, void* d_mom, int B, int zc, int R, float clampv, int dtype, cudaStream_t st);
@@ -391,10 +391,10 @@ int mvae_nchw_f32_to_nhwc(const float* src, void* dst, int32_t batch, int32_t h,
 
 int mvae_reparam_kl_fwd(const void* moments, const float* eps, float* eps_out, float* mean, float* logvar,
                         float* std_out, float* z_nchw, void* z_nhwc, double* kl_sum, int32_t batch, int32_t zc, int32_t r, float clamp, uint64_t seed,
-                        uint64_t offset, const double* step_state, int32_t dtype, void* stream) {
+                        uint64_t offset, uint64_t elem_base, const double* step_state, int32_t dtype, void* stream) {
     MVAE_CHECK(moments && mean && logvar && z_nchw && dtype_ok(dtype), "reparam_kl_fwd: bad argument");
     return reparam_fwd(moments, eps, eps_out, mean, logvar, std_out, z_nchw, z_nhwc, kl_sum, batch, zc, r, clamp, seed, offset,
-                       step_state, dtype, ST(stream));
+                       elem_base, step_state, dtype, ST(stream));
 }
 int mvae_reparam_kl_bwd(const float* d_mean, const float* d_logvar, const float* d_z, const float* mean_unused,
                         const float* logvar, const float* eps, const void* moments, void* d_moments, int32_t batch,

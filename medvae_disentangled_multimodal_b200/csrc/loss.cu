@@ -27,7 +27,8 @@ __global__ void __launch_bounds__(256) reparam_kl_fwd_kernel(const T* __restrict
                                                              float* __restrict__ z_nchw,
                                                              T* __restrict__ z_nhwc, double* __restrict__ kl_sum,
                                                              int B, int zc, int RR, float clampv, uint64_t seed,
-                                                             uint64_t offset, const double* __restrict__ dyn) {
+                                                             uint64_t offset, uint64_t elem_base,
+                                                             const double* __restrict__ dyn) {
     __shared__ double shd[32];
     if (dyn) offset += (uint64_t)dyn[2];   // device-side Philox stream position (CUDA-graph replays advance it)
     const long long total = (long long)B * zc * RR;
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(256) reparam_kl_fwd_kernel(const T* __restrict
             mu = fminf(fmaxf(mu, -clampv), clampv);
             lv = fminf(fmaxf(lv, -clampv), clampv);
         }
-        float ep = eps_in ? eps_in[e] : philox_normal(seed, offset, (uint64_t)e);
+        float ep = eps_in ? eps_in[e] : philox_normal(seed, offset, elem_base + (uint64_t)e);
         if (eps_out) eps_out[e] = ep;
         float sd = expf(0.5f * lv);
         float zz = fmaf(ep, sd, mu);
@@ -98,14 +99,14 @@ static int ew_blocks(long long total) {
 
 int reparam_fwd(const void* mom, const float* eps, float* eps_out, float* mean, float* logvar, float* stdv,
                 float* z_nchw, void* z_nhwc, double* kl_sum, int B, int zc, int R, float clampv, uint64_t seed, uint64_t offset,
-                const double* dyn, int dtype, cudaStream_t st) {
+                uint64_t elem_base, const double* dyn, int dtype, cudaStream_t st) {
     long long total = (long long)B * zc * R * R;
     if (dtype == MVAE_F32)
         reparam_kl_fwd_kernel<float><<<ew_blocks(total), 256, 0, st>>>((const float*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
-                                                                        (float*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset, dyn);
+                                                                        (float*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset, elem_base, dyn);
     else
         reparam_kl_fwd_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>((const bf16*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
-                                                                       (bf16*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset, dyn);
+                                                                       (bf16*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset, elem_base, dyn);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

@@ -238,7 +238,9 @@ def nchw_f32_to_nhwc(src, dtype):
     return dst
 
 
-def reparam_kl_fwd(moments, eps, zc, clamp, seed, offset, want_kl=True, want_std=True, step_state=None):
+def reparam_kl_fwd(moments, eps, zc, clamp, seed, offset, want_kl=True, want_std=True, step_state=None, sample_base=0):
+    """sample_base: index of this call's first sample in the global batch (rank and micro-batch start); the Philox
+    element counter starts at sample_base * zc * r * r"""
     b, r, _, c2 = moments.shape
     dev = moments.device
     mean = torch.empty((b, zc, r, r), dtype=torch.float32, device=dev)
@@ -250,7 +252,8 @@ def reparam_kl_fwd(moments, eps, zc, clamp, seed, offset, want_kl=True, want_std
         eps_out = torch.empty_like(mean)
     kl = torch.zeros((), dtype=torch.float64, device=dev) if want_kl else None
     check(lib().mvae_reparam_kl_fwd(ptr(moments), ptr(eps), ptr(eps_out), ptr(mean), ptr(logvar), ptr(std), ptr(z), None,
-                                    ptr(kl), b, zc, r, float(clamp), int(seed), int(offset), ptr(step_state),
+                                    ptr(kl), b, zc, r, float(clamp), int(seed), int(offset),
+                                    int(sample_base) * zc * r * r, ptr(step_state),
                                     L.code_of(moments.dtype), stream()), "reparam_kl_fwd")
     return mean, logvar, z, std, (eps if eps is not None else eps_out), kl
 

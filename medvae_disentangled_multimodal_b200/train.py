@@ -48,6 +48,7 @@ class GradBuckets:
         self.params = list(params)
         self.group = group
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.rank = dist.get_rank(group) if (dist.is_available() and dist.is_initialized()) else 0
         dev = self.params[0].device
         pad = lambda n: (n + self.ALIGN - 1) // self.ALIGN * self.ALIGN   # 256-byte aligned views: 16-byte accesses
         total = sum(pad(p.numel()) for p in self.params)
@@ -351,7 +352,14 @@ class TrainStep:
         totals: Dict[str, torch.Tensor] = {}
         # verification hook: externally supplied reparameterisation noise follows the micro-batch split
         eps_full = getattr(self.model, "eps_override", None)
+        # own Philox noise: one stream position per optimizer step for every micro-batch and rank, the element counter
+        # addressed by the sample's index in the global batch (equal shards) — ranks draw different noise and the
+        # noise of a sample does not depend on the number of ranks or the micro-batch split
+        rng0 = getattr(self.model, "_rng_step", None)
         for ci, (a, b) in enumerate(chunks):
+            if rng0 is not None:
+                self.model._rng_step = rng0
+                self.model._rng_sample_base = self.buckets.rank * n + a
             last = ci == len(chunks) - 1
             self.buckets.reduce_enabled = last
             self.buckets.begin_round()
@@ -376,6 +384,8 @@ class TrainStep:
             del out, ld
         if eps_full is not None:
             self.model.eps_override = eps_full
+        if rng0 is not None:
+            self.model._rng_sample_base = 0
         self.buckets.finish()
         self.optimizer.step()
         return totals

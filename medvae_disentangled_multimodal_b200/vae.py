@@ -41,7 +41,7 @@ class _EncodeSampleFn(torch.autograd.Function):
         seed, offset = model._next_rng()
         mean, logvar, z, std, eps_used, kl = ops.reparam_kl_fwd(
             moments_nhwc, eps, model.latent_dim, clamp, seed, offset, want_kl=True, want_std=True,
-            step_state=model._step_state)
+            step_state=model._step_state, sample_base=model._rng_sample_base)
         ctx.save_for_backward(moments_nhwc, logvar, eps_used, std)
         ctx.clamp = clamp
         ctx.mark_non_differentiable(eps_used, kl)
@@ -69,7 +69,8 @@ class _ReparamFn(torch.autograd.Function):
         mom = ops.nchw_f32_to_nhwc(torch.cat([mean, logvar], dim=1).float().contiguous(), torch.float32)
         seed, offset = model._next_rng()
         _m, _lv, z, _sd, eps_used, _kl = ops.reparam_kl_fwd(mom, eps, mean.shape[1], 0.0, seed, offset,
-                                                            want_kl=False, want_std=False)
+                                                            want_kl=False, want_std=False,
+                                                            sample_base=model._rng_sample_base)
         ctx.save_for_backward(mom, logvar.float().contiguous(), eps_used)
         return z
 
@@ -122,6 +123,9 @@ class BaseVAE(nn.Module):
         self.eps_override: Optional[torch.Tensor] = None
         self.rng_seed: Optional[int] = None
         self._rng_step = 0
+        # first sample of the current forward in the GLOBAL batch (TrainStep: rank * shard + micro-batch start): the
+        # Philox element counter starts there, so a sample's noise does not depend on the split
+        self._rng_sample_base = 0
         self._latent_clamp = 0.0
         self._prior_cache: dict = {}
         self._step_state: Optional[torch.Tensor] = None   # device-side Philox position (TrainStep graph mode)

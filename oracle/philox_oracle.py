@@ -55,9 +55,10 @@ def dropout_keep_mask(n: int, p: float, seed: int, offset: int) -> np.ndarray:
     return u >= np.float32(p)
 
 
-def normal_words(n: int, seed: int, offset: int):
-    """the two words element e draws: (x, y) of block e >> 1 for even e, (z, w) for odd e."""
-    e = np.arange(n, dtype=np.uint64)
+def normal_words(n: int, seed: int, offset: int, elem_base: int = 0):
+    """the two words element e draws: (x, y) of block e >> 1 for even e, (z, w) for odd e.  elem_base = the first
+    element's index in the global batch (first sample x latent elements per sample)."""
+    e = np.arange(n, dtype=np.uint64) + np.uint64(elem_base)
     x, y, z, w = block(seed, e >> np.uint64(1), np.full_like(e, offset))
     odd = (e & np.uint64(1)).astype(bool)
     return np.where(odd, z, x), np.where(odd, w, y)
@@ -69,10 +70,10 @@ def uniform_open(words) -> np.ndarray:
     return ((words >> np.uint32(8)).astype(np.float32) + np.float32(0.5)) * np.float32(1.0 / 16777216.0)
 
 
-def normal_noise(n: int, seed: int, offset: int) -> np.ndarray:
+def normal_noise(n: int, seed: int, offset: int, elem_base: int = 0) -> np.ndarray:
     """Box-Muller on uniforms ((word >> 8) + 0.5) * 2^-24 (csrc/loss.cu:philox_normal).  The device
     evaluates log / cos with fast intrinsics in fp32, so this agrees to ~1e-4 absolute, not bit for bit;
     the words are exact."""
-    a, b = normal_words(n, seed, offset)
+    a, b = normal_words(n, seed, offset, elem_base)
     u1, u2 = (uniform_open(w).astype(np.float64) for w in (a, b))
     return (np.sqrt(-2.0 * np.log(u1)) * np.cos(2.0 * np.pi * u2)).astype(np.float32)

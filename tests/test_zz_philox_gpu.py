@@ -47,3 +47,47 @@ def test_reparam_noise_is_box_muller_on_the_philox_stream(B, zc, R, seed, offset
     # everywhere else the fast intrinsics are good to ~1e-5.  A wrong word, block or stream gives O(1) errors.
     assert err.max() < 5e-3, err.max()
     assert np.median(err) < 1e-5 and (err > 2e-4).mean() < 1e-2
+
+
+def test_noise_of_a_sample_does_not_depend_on_the_split():
+    """the Philox element counter is the element's index in the GLOBAL batch, so two half batches
+    addressed by their first sample (what two ranks, or two micro-batches, do) draw the noise of the whole batch."""
+    ops = _ops()
+    B, zc, R, seed, offset = 8, 5, 3, 99, 7          # odd sample size: halves start on an odd element
+    mom = torch.zeros(B, R, R, 2 * zc, device=DEV)
+    whole = ops.reparam_kl_fwd(mom, None, zc, 0.0, seed, offset)[4]
+    lo = ops.reparam_kl_fwd(mom[:3].contiguous(), None, zc, 0.0, seed, offset, sample_base=0)[4]
+    hi = ops.reparam_kl_fwd(mom[3:].contiguous(), None, zc, 0.0, seed, offset, sample_base=3)[4]
+    torch.cuda.synchronize()
+    assert torch.equal(torch.cat([lo, hi]), whole)
+    assert not torch.equal(hi[:3], lo)                # different samples, different noise
+    want = P.normal_noise(5 * zc * R * R, seed, offset, elem_base=3 * zc * R * R)
+    assert np.abs(hi.cpu().numpy().reshape(-1) - want).max() < 5e-3
+
+
+def test_train_step_with_own_noise_is_independent_of_the_micro_batch_split():
+    """TrainStep addresses the noise by (optimizer step, global sample index): with the model's own Philox noise two
+    micro-batches of 4 take the same steps as one batch of 8 (fp32 verification mode)."""
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200.train import TrainStep
+    from oracle import vae_oracle as O
+    kw = dict(input_channels=3, latent_dim=8, hidden_channels=64, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=[8],
+              resolution=16, condition_method="concat")
+    batches = [O.synthetic_batch(8, 3, 16, seed=300 + i) for i in range(2)]
+    curves = []
+    for mb in (None, 4):
+        torch.manual_seed(3)
+        model = M.ConditionalVAE(compute_dtype="fp32", **kw).to(DEV)
+        model.rng_seed = 21
+        ts = TrainStep(model, M.VAELoss(recon_loss_type="mse", kl_weight=1.0, recon_weight=1.0), micro_batch=mb,
+                       lr=1e-4, weight_decay=1e-4, max_norm=1.0)
+        curve = []
+        for i in range(4):
+            x, onehot, _ = batches[i % 2]
+            curve.append(float(ts.step(x.to(DEV), onehot.to(DEV))["loss"]))
+        ts.close()
+        assert model._rng_step == 4 and model._rng_sample_base == 0
+        curves.append(curve)
+    for a, b in zip(*curves):
+        assert abs(a - b) <= 2e-5 * abs(a), curves
+    assert len(set(curves[0])) == 4
