@@ -139,3 +139,23 @@ def test_ctypes_signatures_match_the_header_prototypes():
         want = [_ctype_class(p) for p in params]
         assert got == want, f"{name}: header {want} vs ctypes {got}"
         assert _ctypes_class(restype) == _ctype_class(ret + " x"), f"{name}: return type"
+
+
+def test_plain_c99_host_compiles_links_and_runs():
+    """include/medvae_b200.h is a C header (no C++ / torch types) and the library links from a C program."""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("gcc not available")
+    L = _lib()
+    libdir = os.path.dirname(L.LIB_PATH)
+    out_dir = os.path.join(ROOT, "tests", "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    exe = os.path.join(out_dir, "c_host")
+    subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                    os.path.join(ROOT, "tests", "c_host.c"), "-o", exe, "-L", libdir, "-lmedvae_b200",
+                    f"-Wl,-rpath,{libdir}"], check=True, capture_output=True)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "c host ok" in r.stdout
