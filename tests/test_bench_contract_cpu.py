@@ -1,0 +1,70 @@
+"""bench.py without a GPU: the per-image FLOP figures its throughput -> TFLOP/s conversions rest on are recounted with
+torch's FlopCounterMode on the oracle's forward + backward (SURVEY 8d counted them the same way on the reference), and
+the reference arm (`--impl reference`: the CPU port of the reference step) prints the contract's JSON line."""
+import json
+import os
+import subprocess
+import sys
+import warnings
+
+import pytest
+import torch
+from torch.utils.flop_counter import FlopCounterMode
+
+from oracle import vae_oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+
+
+@pytest.mark.parametrize("wl", list(bench.WORKLOADS))
+def test_flops_per_image_match_a_recount(wl):
+    cls, kw, lkw, _bpg, _conditional, gflop, _scaling = bench.WORKLOADS[wl]
+    _ch, zc, dis = bench.wl_shape(wl)
+    _m, sd = bench.build_state_dict(wl)
+    sd = {k: v.requires_grad_(True) for k, v in sd.items()}
+    n = 2 if dis else 1                      # one gray + one RGB sample: the disentangled heads differ per modality
+    x, cond = bench.wl_batch(wl, n)
+    r = kw["resolution"] // 2 ** (len(kw["ch_mult"]) - 1)
+    eps = torch.zeros(n, zc, r, r)
+    with warnings.catch_warnings(), FlopCounterMode(display=False) as fc:
+        warnings.simplefilter("ignore")
+        if dis:
+            out = O.dis_forward(sd, x, cond, eps, kw["shared_latent_dim"], kw["modality_latent_dim"])
+            ld = O.dis_loss(out, x, **lkw)
+        else:
+            out = O.vae_forward(sd, x, eps, cond)
+            ld = O.vae_loss(out["reconstruction"], x, out["mean"], out["logvar"], **lkw)
+        ld["loss"].backward()
+    counted = fc.get_total_flops() / n / 1e9
+    assert abs(counted - gflop) <= 1e-3 * gflop, (wl, counted, gflop)
+
+
+def _run_reference_arm(extra_env=None):
+    env = dict(os.environ, **(extra_env or {}))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", "c1",
+                        "--cpu-batch", "2", "--steps", "1", "--warmup", "0"], capture_output=True, text=True, env=env,
+                       cwd=ROOT, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    return [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+
+
+def test_reference_arm_prints_the_contract_line():
+    lines = _run_reference_arm()
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "train images/sec" and d["unit"] == "images/s"
+    assert d["value"] > 0 and d["higher_is_better"] is True and d["vs_baseline"] is None
+    assert d["n_gpus"] == 1 and d["steps"] == 1 and d["warmup"] == 0 and d["ms_per_step"] > 0
+    assert d["dtype"] == "f32" and d["data"] == "synthetic" and d["scaling"] in ("weak", "strong")
+    assert d["config"]["workload"].startswith("c1: BaseVAE 1x28x28") and "model" not in d["config"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] == (os.cpu_count() or 1) and cb["value"] == d["value"]
+    assert "2 images" in cb["sample"] and cb["update_ms_per_step"] > 0 and cb["value_update_amortised"] >= cb["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["gpu_launches"] == 0
+
+
+def test_reference_arm_other_ranks_exit_quietly():
+    assert _run_reference_arm({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}) == []
