@@ -385,6 +385,10 @@ def b200_arm(args):
             roof = {"bound": "tensor", "kernel": "conv_gather_umma_kernel (implicit-GEMM conv fprop+dgrad, tcgen05)",
                     "achieved": round(ach, 2), "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
                     "frac": round(ach / peaks["bf16_sustained"], 4), "traffic": load_traffic(wl),
+                    "traffic_source": ("profiles/roofline_traffic.json: ncu --set full, mean DRAM read+write bytes of the "
+                                       "gather launches of a 256-image pass (the timed launches here take the whole "
+                                       f"{micro}-image pass: scale by the image count)"
+                                       if wl == "c4" else None),
                     "peak_source": f"{peaks['source']} (sustained: kernel timed inside a long step)",
                     "launches": n_l, "avg_launch_ms": round(ms / n_l, 4),
                     "algorithmic_gflop_per_launch": round(fl / n_l / 1e9, 2)}
