@@ -499,6 +499,7 @@ class _Stack(nn.Module):
         self.compute_dtype = torch.bfloat16
         self.dropout_seed: Optional[int] = None    # None: torch.initial_seed()
         self._dropout_step = 0
+        self._rng_sample_base = 0                  # first sample of this forward in the global batch (train.TrainStep)
         self.dropout_mask_override = None          # verification hook: {ResnetBlock module: uint8 NHWC keep mask}
         self._step_state = None                    # device-side Philox position (train.TrainStep graph mode)
 
@@ -524,7 +525,9 @@ class _StackFn(torch.autograd.Function):
             seed = stack.dropout_seed if stack.dropout_seed is not None else torch.initial_seed()
             # one Philox stream per (stack, forward call); sites within the call take consecutive offsets
             run.dropout_seed = (seed + 0x9E3779B97F4A7C15 * (2 if type(stack).__name__ == "Decoder" else 1)) & 0xFFFFFFFFFFFFFFFF
-            run.dropout_offset = stack._dropout_step << 16
+            # ... and per position of the forward's first sample in the global batch (bits 40+), so data-parallel
+            # ranks and micro-batches keep different masks
+            run.dropout_offset = (stack._dropout_step << 16) + (int(stack._rng_sample_base) << 40)
             run.step_state = stack._step_state
             if stack.dropout_mask_override:
                 run.dropout_masks = {id(k): v for k, v in stack.dropout_mask_override.items()}

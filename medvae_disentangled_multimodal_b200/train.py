@@ -360,6 +360,10 @@ class TrainStep:
             if rng0 is not None:
                 self.model._rng_step = rng0
                 self.model._rng_sample_base = self.buckets.rank * n + a
+                for name in ("decoder", "encoder"):
+                    stack = getattr(self.model, name, None)
+                    if stack is not None and hasattr(stack, "_rng_sample_base"):
+                        stack._rng_sample_base = self.buckets.rank * n + a
             last = ci == len(chunks) - 1
             self.buckets.reduce_enabled = last
             self.buckets.begin_round()
@@ -386,6 +390,10 @@ class TrainStep:
             self.model.eps_override = eps_full
         if rng0 is not None:
             self.model._rng_sample_base = 0
+            for name in ("decoder", "encoder"):
+                stack = getattr(self.model, name, None)
+                if stack is not None and hasattr(stack, "_rng_sample_base"):
+                    stack._rng_sample_base = 0
         self.buckets.finish()
         self.optimizer.step()
         return totals
