@@ -102,3 +102,43 @@ def test_shard_batch_rejects_ragged():
     from medvae_disentangled_multimodal_b200.train import shard_batch
     with pytest.raises(ValueError):
         shard_batch(10, 0, 4)
+
+
+def test_train_step_addresses_the_noise_by_global_sample_index(monkeypatch):
+    """SURVEY 8e, host side: every micro-batch of a step uses ONE stream position, and model / encoder / decoder are told
+    the position of the chunk's first sample in the global batch (rank * shard + chunk start); reset afterwards.  The
+    device half (elem_base of mvae_reparam_kl_fwd) is checked in tests/test_zz_philox_gpu.py.  No GPU here: the
+    optimizer and the model's forward are stand-ins, the chunk loop is the real TrainStep."""
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200 import optim, train
+
+    class NoOptimizer:
+        def __init__(self, params, **kw):
+            self.params, self.step_state, self.lr, self.step_count = list(params), None, kw.get("lr"), 0
+
+        def step(self):
+            self.step_count += 1
+
+    monkeypatch.setattr(optim, "FusedAdamW", NoOptimizer)
+    model = M.ConditionalVAE(input_channels=3, latent_dim=4, hidden_channels=8, ch_mult=(1, 2), num_res_blocks=1,
+                             attn_resolutions=[], resolution=16, dropout=0.1)
+    seen = []
+
+    def forward(xs, cond=None):
+        _seed, offset = model._next_rng()
+        seen.append((offset, model._rng_sample_base, model.encoder._rng_sample_base, model.decoder._rng_sample_base,
+                     xs.shape[0]))
+        return {"reconstruction": torch.zeros(1, requires_grad=True), "posterior": None, "prior": None}
+
+    model.forward = forward
+    crit = lambda inputs, reconstructions, posteriors, priors: {"loss": reconstructions.sum() * 0.0}
+    ts = train.TrainStep(model, crit, micro_batch=3)
+    ts.buckets.rank = 2                                   # as rank 2 of a larger job, shard of 8 samples
+    x, cond = torch.zeros(8, 3, 16, 16), torch.zeros(8, 12)
+    ts.step(x, cond)
+    ts.step(x, cond)
+    ts.close()
+    assert seen == [(1, 16, 16, 16, 3), (1, 19, 19, 19, 3), (1, 22, 22, 22, 2),
+                    (2, 16, 16, 16, 3), (2, 19, 19, 19, 3), (2, 22, 22, 22, 2)]
+    assert (model._rng_step, model._rng_sample_base, model.encoder._rng_sample_base) == (2, 0, 0)
+    assert ts.optimizer.step_count == 2
