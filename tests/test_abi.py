@@ -159,3 +159,48 @@ def test_plain_c99_host_compiles_links_and_runs():
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
     assert "c host ok" in r.stdout
+
+
+# every distinct conv of the C4 model (H, Cin, Cout, k, mode) and of C1-C3 (28 x 28)
+_C4_CONVS = [(8, 1024, 1024, 3, 0), (64, 128, 128, 3, 0), (32, 256, 256, 3, 0), (16, 512, 512, 3, 0),
+             (8, 1024, 1024, 3, 2), (16, 512, 512, 3, 2), (32, 256, 256, 3, 2),
+             (16, 1024, 512, 3, 0), (32, 512, 256, 3, 0), (64, 256, 128, 3, 0),
+             (32, 128, 256, 3, 0), (16, 256, 512, 3, 0), (8, 512, 1024, 3, 0),
+             (64, 128, 128, 3, 1), (32, 256, 256, 3, 1), (16, 512, 512, 3, 1),
+             (8, 1024, 256, 3, 0), (8, 128, 1024, 3, 0), (8, 1024, 3072, 1, 0), (8, 1024, 1024, 1, 0),
+             (16, 512, 1536, 1, 0), (16, 512, 512, 1, 0), (32, 128, 256, 1, 0), (16, 256, 512, 1, 0),
+             (8, 512, 1024, 1, 0), (16, 1024, 512, 1, 0), (32, 512, 256, 1, 0), (64, 256, 128, 1, 0)]
+_C123_CONVS = [(7, 512, 512, 3, 0), (28, 128, 128, 3, 0), (14, 256, 256, 3, 0), (14, 256, 256, 3, 2), (7, 512, 512, 3, 2),
+               (14, 512, 256, 3, 0), (28, 256, 128, 3, 0), (14, 128, 256, 3, 0), (7, 256, 512, 3, 0), (7, 512, 256, 3, 0),
+               (28, 128, 128, 3, 1), (14, 256, 256, 3, 1), (7, 128, 512, 3, 0), (7, 512, 1536, 1, 0), (14, 256, 768, 1, 0)]
+
+
+@pytest.mark.parametrize("h,cin,cout,k,mode", _C4_CONVS + _C123_CONVS)
+def test_every_hidden_conv_of_the_bench_models_takes_the_tcgen05_path(h, cin, cout, k, mode):
+    """north_star (a): the dense contractions run on tcgen05 — the engine selection (a host-side decision of the
+    library) says so for every hidden conv shape of SURVEY Appendix B in bf16, and the GroupNorm either side rides the
+    conv's epilogue wherever a GroupNorm consumes / produced the tensor (32 groups)."""
+    L = _lib()
+    from medvae_disentangled_multimodal_b200 import ops
+    lib = L.lib()
+    d = ops.conv_desc(256, h, h, cin, cout, k, mode, L.BF16)
+    assert lib.mvae_conv2d_uses_umma(C.byref(d)) == 1
+    if k == 3 and mode == 0:
+        assert lib.mvae_conv2d_fuses_gn(C.byref(d), 32, 0) == 1      # statistics of the consumer GroupNorm (fprop)
+        assert lib.mvae_conv2d_fuses_gn(C.byref(d), 32, 1) == 1      # GroupNorm backward behind the dgrad
+
+
+def test_skinny_edge_convs_are_padded_onto_the_tcgen05_path():
+    """encoder conv_in (6 -> 128) and decoder conv_out (128 -> 3) run with the skinny dimension zero-padded to 64
+    (blocks.ConvOp.pad_in / pad_out)"""
+    import torch.nn as nn
+    from medvae_disentangled_multimodal_b200 import blocks
+    L = _lib()
+    from medvae_disentangled_multimodal_b200 import ops
+    cin = blocks.ConvOp([nn.Conv2d(6, 128, 3, padding=1)], 0, pad_in=True)
+    cout = blocks.ConvOp([nn.Conv2d(128, 3, 3, padding=1)], 0, pad_out=True)
+    assert cin.cin_of(torch.bfloat16) == 64 and cin.cin_of(torch.float32) == 6
+    assert cout.cout_of(torch.bfloat16) == 64 and cout.cout_of(torch.float32) == 3
+    for op in (cin, cout):
+        d = ops.conv_desc(256, 64, 64, op.cin_of(torch.bfloat16), op.cout_of(torch.bfloat16), 3, 0, L.BF16)
+        assert L.lib().mvae_conv2d_uses_umma(C.byref(d)) == 1
