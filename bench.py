@@ -100,6 +100,10 @@ def parse():
     ap.add_argument("--cpu-batch", type=int, default=None, help="images per CPU step (reference arm / cpu_baseline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-parity-check", action="store_true", help="skip the first-step check against the committed "
+                    "reference values (tuning runs)")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip timing the reference on stock torch kernels")
+    ap.add_argument("--gpu-baseline-batch", type=int, default=None)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--knob", action="append", default=[], help="debug knob key=value for libmedvae_b200 (tuning)")
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
@@ -132,38 +136,53 @@ def build_state_dict(wl: str):
     return model, {k: v.detach().clone() for k, v in model.state_dict().items()}
 
 
+def cpu_kind() -> str:
+    """"reference": the unmodified reference classes (oracle/_ref, copied by oracle/build_ref.py) driven by the Lightning
+    step restated in oracle/ref_runner.py; "port": the functional oracle port (only when the copy is absent)"""
+    from oracle import ref_runner
+    return "reference" if ref_runner.available() else "port"
+
+
 def run_cpu_steps(wl: str, sd, batch: int, steps: int, warmup: int, budget_s: float = None):
-    """-> (images/s, steps timed, cores).  Each step: fwd + VAELoss + bwd + NaN guard + clip + AdamW."""
+    """-> (images/s with the per-step update amortised as in the full batch, steps timed, cores, seconds).
+    Each step: fwd + VAELoss + bwd + NaN guard + clip + AdamW on `batch` images of the workload."""
     import torch
-    from oracle import vae_oracle as O
     cls, kw, lkw, _b, conditional, _gf, _s = WORKLOADS[wl]
     _ch, zc, dis = wl_shape(wl)
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    tr = O.ReferenceTrainer(sd, lr=OPT["lr"], weight_decay=OPT["weight_decay"], betas=OPT["betas"],
-                            max_norm=OPT["max_norm"], loss_kwargs=lkw,
-                            disentangled=(kw["shared_latent_dim"], kw["modality_latent_dim"]) if dis else None)
     x, cond = wl_batch(wl, batch)
-    r = kw["resolution"] // 2 ** (len(kw["ch_mult"]) - 1)
-    g = torch.Generator().manual_seed(7)
-    done, t_total, t_update = 0, 0.0, 0.0
-    for i in range(warmup + steps):
-        eps = torch.randn(batch, zc, r, r, generator=g)
-        t0 = time.perf_counter()
-        tr.step(x, eps, cond)
-        dt = time.perf_counter() - t0
-        if i >= warmup:
-            done += 1
-            t_total += dt
-            t_update += tr.last_update_s
-            if budget_s is not None and t_total >= budget_s:
-                break
-    # the sample pays one clip + AdamW per `batch` images, the workload one per _b images: also report the rate
-    # with that per-step part amortised as in the full batch (the measured `value` stays the headline)
+    if cpu_kind() == "reference":
+        from oracle import ref_runner
+        r = ref_runner.time_reference(cls, kw, lkw, x, cond, device="cpu", steps=steps, warmup=warmup, opt=OPT,
+                                      budget_s=budget_s)
+        done, t_total, t_update = r["steps"], r["total_s"], r["update_ms_per_step"] * 1e-3 * r["steps"]
+    else:
+        from oracle import vae_oracle as O
+        tr = O.ReferenceTrainer(sd, lr=OPT["lr"], weight_decay=OPT["weight_decay"], betas=OPT["betas"],
+                                max_norm=OPT["max_norm"], loss_kwargs=lkw,
+                                disentangled=(kw["shared_latent_dim"], kw["modality_latent_dim"]) if dis else None)
+        r = kw["resolution"] // 2 ** (len(kw["ch_mult"]) - 1)
+        g = torch.Generator().manual_seed(7)
+        done, t_total, t_update = 0, 0.0, 0.0
+        for i in range(warmup + steps):
+            eps = torch.randn(batch, zc, r, r, generator=g)
+            t0 = time.perf_counter()
+            tr.step(x, eps, cond)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                done += 1
+                t_total += dt
+                t_update += tr.last_update_s
+                if budget_s is not None and t_total >= budget_s:
+                    break
+    # the sample pays one NaN scan + clip + AdamW per `batch` images, the workload one per _b images: the reported
+    # rate charges that per-step part as the full batch would (the raw rate of the sample is kept beside it)
     CPU_EXTRA.clear()
     CPU_EXTRA.update({"update_ms_per_step": round(1e3 * t_update / max(done, 1), 1),
-                      "value_update_amortised": round(batch * done / (t_total - t_update + t_update * batch / _b), 3)})
-    return batch * done / t_total, done, cores, t_total
+                      "value_sample_raw": round(batch * done / t_total, 3), "cpu_sample_batch": batch})
+    amortised = batch * done / (t_total - t_update + t_update * batch / _b)
+    return amortised, done, cores, t_total
 
 
 def reference_arm(args):
@@ -172,24 +191,27 @@ def reference_arm(args):
         return
     wl = args.workload
     cls, kw, lkw, bpg, conditional, gflop, scaling = WORKLOADS[wl]
-    _model, sd = build_state_dict(wl)
+    kind = cpu_kind()
+    sd = None if kind == "reference" else build_state_dict(wl)[1]
     b = cpu_sample_batch(wl, args.cpu_batch)
     ips, done, cores, t_total = run_cpu_steps(wl, sd, b, args.steps, args.warmup)
-    sample = f"{done} steps of {b} images ({cls} {wl_shape(wl)[0]}x{kw['resolution']}x{kw['resolution']}, fp32, " \
-             f"fwd+loss+bwd+clip+AdamW) on {cores} host threads"
+    sample = (f"{done} steps of {b} images of the workload's batch ({cls} {wl_shape(wl)[0]}x{kw['resolution']}x"
+              f"{kw['resolution']}, fp32, fwd+loss+bwd+NaN scan+clip+AdamW) on {cores} host threads; value charges the "
+              f"per-step update once per {bpg} images as the full batch does (raw sample rate: value_sample_raw)")
     line = {
         "impl": "reference", "metric": "train images/sec", "value": ips, "unit": "images/s", "n_gpus": args.gpus,
         "steps": done, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(done, 1), "higher_is_better": True,
         "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(wl, args, bpg, args.gpus, cpu=True),
-        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample, **CPU_EXTRA},
+        "config": workload_config(wl, args, bpg, args.gpus),
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": kind, "sample": sample, **CPU_EXTRA},
         "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
 
 
-def workload_config(wl, args, bpg, n, cpu=False):
+def workload_config(wl, args, bpg, n):
+    """the same dict in both arms (the CPU arm's bounded sample is described in its cpu_baseline object)"""
     cls, kw, lkw, _b, conditional, gflop, scaling = WORKLOADS[wl]
     ch, zc, dis = wl_shape(wl)
     return {
@@ -197,8 +219,8 @@ def workload_config(wl, args, bpg, n, cpu=False):
                     f"ch_mult {tuple(kw['ch_mult'])} res_blocks {kw['num_res_blocks']} attn {kw['attn_resolutions']} "
                     f"latent {zc}, {'DisentangledVAELoss' if dis else 'VAELoss'} {lkw['recon_loss_type']} "
                     f"kl_weight {lkw['kl_weight']}, AdamW lr 1e-4 wd 1e-4 clip 1.0",
-        "batch_per_gpu": bpg, "global_batch": bpg * n, "micro_batch": None if cpu else (args.micro_batch or min(bpg, default_micro(wl))),
-        "cuda_graph": False if cpu else (args.graph == "on" or (args.graph == "auto" and wl in ("c1", "c2", "c3"))),
+        "batch_per_gpu": bpg, "global_batch": bpg * n, "micro_batch": args.micro_batch or min(bpg, default_micro(wl)),
+        "cuda_graph": args.graph == "on" or (args.graph == "auto" and wl in ("c1", "c2", "c3")),
         "parallelism": f"dp{n}", "gflop_per_image_fwd_bwd": gflop,
         "cache": "inputs and activations larger than L2 (126 MB); no L2 flush needed",
     }
@@ -279,6 +301,87 @@ def load_traffic(wl):
         return None
 
 
+def first_step_check(model, crit, wl, dev, precision):
+    """Replay tests/golden/bench_first_step.json (the UNMODIFIED reference, fp32 CPU: oracle/make_bench_check.py) on the
+    GPU before anything is timed: same seeded weights, the first images of the bench batch, the same injected noise ->
+    loss terms and global gradient norm must agree.  A mismatch aborts the run (no number is printed)."""
+    import torch
+    path = os.path.join(ROOT, "tests", "golden", "bench_first_step.json")
+    if not os.path.exists(path):
+        return {"ok": None, "why": "tests/golden/bench_first_step.json missing"}
+    ref = json.load(open(path)).get(wl)
+    if ref is None:
+        return {"ok": None, "why": f"no committed reference values for {wl}"}
+    _cls, kw, *_ = WORKLOADS[wl]
+    _ch, zc, dis = wl_shape(wl)
+    n = ref["images"]
+    x, cond = wl_batch(wl, n)
+    r = kw["resolution"] // 2 ** (len(kw["ch_mult"]) - 1)
+    eps = torch.randn(n, zc, r, r, generator=torch.Generator().manual_seed(ref["eps_seed"]))
+    model.eps_override = eps.to(dev)
+    xd = x.to(dev)
+    try:
+        if dis:
+            out = model(xd, cond)
+            ld = crit(out, xd)
+        else:
+            out = model(xd, cond.to(dev)) if cond is not None else model(xd)
+            ld = crit(inputs=xd, reconstructions=out["reconstruction"], posteriors=out["posterior"], priors=out["prior"])
+        ld["loss"].backward()
+        torch.cuda.synchronize()
+        gn = sum(float(p.grad.double().pow(2).sum()) for p in model.parameters() if p.grad is not None) ** 0.5
+    finally:
+        model.eps_override = None
+        model.zero_grad(set_to_none=True)
+    tol_l, tol_g = (1e-2, 3e-2) if precision == "bf16" else (1e-4, 1e-3)
+    errs = {k: abs(float(ld[k].detach()) - v) / max(1.0, abs(v)) for k, v in ref["loss"].items()}
+    e_g = abs(gn - ref["grad_norm"]) / ref["grad_norm"]
+    ok = all(e <= tol_l for e in errs.values()) and e_g <= tol_g
+    res = {"ok": bool(ok), "images": n, "loss": float(ld["loss"].detach()), "reference_loss": ref["loss"]["loss"],
+           "loss_rel_err": round(max(errs.values()), 6), "grad_norm": gn, "reference_grad_norm": ref["grad_norm"],
+           "grad_norm_rel_err": round(e_g, 6), "tolerance": {"loss": tol_l, "grad_norm": tol_g},
+           "source": "tests/golden/bench_first_step.json (unmodified reference, fp32 CPU)"}
+    if not ok:
+        raise SystemExit(f"bench.py: first-step parity check against the reference FAILED for {wl}: {json.dumps(res)}")
+    return res
+
+
+GPU_BASE_BATCH = {"c1": 64, "c2": 256, "c3": 256, "c4": 128, "c5": 16}
+
+
+def gpu_baseline_leg(wl: str, dev, steps: int = 4, warmup: int = 3, batch: int = None):
+    """The GPU baseline to beat: the UNMODIFIED reference (oracle/_ref) on this B200 through the stock cuDNN /
+    cuBLAS / ATen kernels under torch.autocast(bfloat16), NCHW and channels_last, same step definition (forward + loss +
+    backward + NaN scan + clip + AdamW), same synthetic data, at the largest batch that fits comfortably (stated).  Runs
+    AFTER the timed regions of this repo's arm, on rank 0 at N = 1 only.  None of libmedvae_b200's kernels run here."""
+    import torch
+    from oracle import ref_runner
+    if not ref_runner.available():
+        return {"unavailable": "oracle/_ref missing (python oracle/build_ref.py in the build container)"}
+    cls, kw, lkw, bpg, *_ = WORKLOADS[wl]
+    b = batch or GPU_BASE_BATCH[wl]
+    x, cond = wl_batch(wl, b)
+    out = {"batch": b, "unit": "images/s", "dtype": "bf16 autocast (fp32 master weights, torch.optim.AdamW)",
+           "impl": "unmodified reference modules (oracle/_ref) on stock cuDNN/cuBLAS/ATen", "variants": {}}
+    sampler = ClockSampler(dev.index or 0)
+    sampler.start()
+    for name, cl in (("nchw", False), ("channels_last", True)):
+        try:
+            r = ref_runner.time_reference(cls, kw, lkw, x, cond, device=dev, steps=steps, warmup=warmup, opt=OPT,
+                                          autocast_dtype=torch.bfloat16, channels_last=cl)
+            out["variants"][name] = {"value": round(r["images_per_s"], 2), "ms_per_step": round(r["ms_per_step"], 3),
+                                     "loss": r["loss"], "hbm_peak_allocated_gb": r["hbm_peak_allocated_gb"]}
+        except torch.OutOfMemoryError as e:
+            out["variants"][name] = {"error": "out of memory: " + str(e).splitlines()[0]}
+            torch.cuda.empty_cache()
+    out["clocks"] = sampler.stop()
+    good = {k: v for k, v in out["variants"].items() if "value" in v}
+    if good:
+        best = max(good, key=lambda k: good[k]["value"])
+        out["value"], out["layout"] = good[best]["value"], best
+    return out
+
+
 def b200_arm(args):
     import torch
     import torch.distributed as dist
@@ -312,6 +415,9 @@ def b200_arm(args):
     dis = wl_shape(wl)[2]
     crit = (M.DisentangledVAELoss if dis else M.VAELoss)(**lkw)
     use_graph = args.graph == "on" or (args.graph == "auto" and wl in ("c1", "c2", "c3"))
+    parity = None
+    if not args.no_parity_check and (args.batch_per_gpu is None):
+        parity = first_step_check(model, crit, wl, dev, args.precision)
     ts = TrainStep(model, crit, micro_batch=micro, use_graph=use_graph, **OPT)
     x_h, cond_h = wl_batch(wl, bpg, first_index=rank * bpg, pin=True)
     x_d = x_h.to(dev)
@@ -363,6 +469,7 @@ def b200_arm(args):
     peaks = load_peaks()
 
     roof = None
+    hbm_roofs = []
     kernels = {}
     if not args.no_roofline:
         # one extra, untimed step with CUDA events around every launch; EVERY rank runs it (the step
@@ -392,17 +499,52 @@ def b200_arm(args):
                     "peak_source": f"{peaks['source']} (sustained: kernel timed inside a long step)",
                     "launches": n_l, "avg_launch_ms": round(ms / n_l, 4),
                     "algorithmic_gflop_per_launch": round(fl / n_l / 1e9, 2)}
+        # the HBM-bound families north_star targets at >= 70 % of peak HBM bandwidth: algorithmic bytes (SURVEY 8d:
+        # GroupNorm+SiLU 4 B/elem forward, 6 B/elem backward (+2 with the residual-branch add), bf16; loss kernels
+        # (8Z+3N) x 2 B / image) / summed CUDA-event time of the launches in the instrumented step
+        for fam, keys in (("groupnorm_silu_fwd+bwd", ("groupnorm_fwd", "groupnorm_bwd")),
+                          ("reparam+recon+kl loss fwd+bwd", ("loss_kernels",)),
+                          ("clip+adamw", ("adamw",))):
+            have = [k for k in keys if k in summ and summ[k]["ms"] > 0]
+            if not have:
+                continue
+            by = sum(summ[k]["bytes"] for k in have)
+            ms = sum(summ[k]["ms"] for k in have)
+            n_l = sum(summ[k]["launches"] for k in have)
+            hbm_roofs.append({"bound": "hbm", "kernel": fam, "achieved": round(by / (ms * 1e6), 1), "peak": peaks["hbm"],
+                              "unit": "GB/s", "frac": round(by / (ms * 1e6) / peaks["hbm"], 4), "launches": n_l,
+                              "avg_launch_ms": round(ms / n_l, 4), "algorithmic_mb_per_launch": round(by / n_l / 1e6, 2)})
     if world > 1:
         barrier()
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        _m, sd = build_state_dict(wl)
+        kind = cpu_kind()
+        sd = None if kind == "reference" else build_state_dict(wl)[1]
         b = cpu_sample_batch(wl, args.cpu_batch)
         ips, done, cores, t_total = run_cpu_steps(wl, sd, b, steps=5, warmup=1, budget_s=12.0)
-        cpu = {"value": round(ips, 3), "unit": "images/s", "cores": cores, "kind": "port",
-               "sample": f"{done} steps of {b} images of the same workload (fp32 oracle port of the reference step: "
-                         f"fwd+loss+bwd+clip+AdamW), {t_total:.1f} s", **CPU_EXTRA}
+        what = ("the unmodified reference modules (oracle/_ref) + the Lightning step restated in oracle/ref_runner.py"
+                if kind == "reference" else "fp32 oracle port of the reference step")
+        cpu = {"value": round(ips, 3), "unit": "images/s", "cores": cores, "kind": kind,
+               "sample": f"{done} steps of {b} images of the same workload ({what}: fwd+loss+bwd+NaN scan+clip+AdamW, "
+                         f"fp32), {t_total:.1f} s; value charges the per-step update once per {bpg} images",
+               **CPU_EXTRA}
+
+    gpu_base = None
+    if rank == 0 and world == 1 and not args.no_gpu_baseline:
+        hbm_peak = torch.cuda.max_memory_allocated()
+        ts.release_graph()
+        ts.close()
+        del ts, model, x_d
+        last.clear()
+        import gc
+        gc.collect()
+        from medvae_disentangled_multimodal_b200 import ops as _ops
+        _ops._scratch.clear()
+        torch.cuda.empty_cache()
+        gpu_base = gpu_baseline_leg(wl, dev, batch=args.gpu_baseline_batch)
+    else:
+        hbm_peak = torch.cuda.max_memory_allocated()
 
     if rank == 0:
         step_flops = gflop * 1e9 * bpg     # per GPU
@@ -418,11 +560,14 @@ def b200_arm(args):
                     "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 3)},
             "gpu_launches": int(launches),
             "roofline": roof,
+            "roofline_hbm": hbm_roofs,
             "step_tflops_per_gpu": round(step_flops / (ms_res / args.steps * 1e9), 2),
             "step_frac_of_peak": round(step_flops / (ms_res / args.steps * 1e9) / peaks["bf16_sustained"], 4),
             "kernels": kernels,
             "cpu_baseline": cpu,
-            "hbm_peak_allocated_gb": round(torch.cuda.max_memory_allocated() / 1e9, 2),
+            "gpu_baseline": gpu_base,
+            "parity_check": parity,
+            "hbm_peak_allocated_gb": round(hbm_peak / 1e9, 2),
             "clocks": clocks,
             "loss": loss_val,
         }

@@ -13,6 +13,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmedvae_b200.so")
 
+ABI_VERSION = 4          # include/medvae_b200.h MVAE_ABI_VERSION
 F32, BF16 = 0, 1
 CONV_S1, CONV_DOWN, CONV_UP = 0, 1, 2
 ENGINE_AUTO, ENGINE_SIMT, ENGINE_UMMA = 0, 1, 2

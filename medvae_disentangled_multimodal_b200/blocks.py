@@ -134,6 +134,16 @@ class Run:
         self.dropout_offset = 0
         self.dropout_masks = None      # verification hook: {id(ResnetBlock): uint8 NHWC keep mask}
         self.step_state = None         # device-side stream position (TrainStep graph mode)
+        self.taps = None               # verification hook: {reference module path: NHWC activation} (stack.tap_sink)
+        self.tap_names = None          # {id(module): path}
+
+    def tap(self, module, suffix: str, t: torch.Tensor):
+        """record a per-layer activation under the reference's module path (parity tests compare these with the
+        oracle's / the golden fixtures' taps); no-op unless the owning stack has a tap_sink"""
+        if self.taps is not None:
+            name = self.tap_names.get(id(module))
+            if name is not None:
+                self.taps[name + suffix] = t
 
     def next_dropout(self, blk):
         """-> (seed, offset, mask override or None) for the next dropout site of this forward"""
@@ -185,7 +195,9 @@ class ConvOp:
         return self.cout
 
     def desc(self, run: Run, b: int, h: int, w: int):
-        return ops.conv_desc(b, h, w, self.cin_of(run.dtype), self.cout_of(run.dtype), self.k, self.mode, run.code)
+        d = ops.conv_desc(b, h, w, self.cin_of(run.dtype), self.cout_of(run.dtype), self.k, self.mode, run.code)
+        d.real_channels = (self.cin, self.cout)     # for the FLOP accounting of the profiler (ops.conv_flops)
+        return d
 
     def params(self):
         out = []
@@ -327,6 +339,7 @@ class ResOp:
         blk = self.blk
         a1, st1 = gn_fwd(run, blk.norm1, x, True, x_sums)
         h1, h1_sums = self.c1.fwd(run, a1, gn_groups=blk.norm2.num_groups)
+        run.tap(blk, ".conv1", h1)
         a2, st2 = gn_fwd(run, blk.norm2, h1, True, h1_sums)
         drop = None
         if self.p_drop > 0.0 and run.training:
@@ -337,6 +350,7 @@ class ResOp:
         xs = self.nin.fwd(run, x)[0] if self.nin is not None else x
         out, out_sums = self.c2.fwd(run, a2, residual=xs, gn_groups=self.out_groups)
         run.tape.append((self, (x, st1, a1, h1, st2, a2, drop)))
+        run.tap(blk, "", out)
         return out, out_sums
 
     def bwd(self, run: Run, saved, dout, dout_cs=None):
@@ -375,6 +389,7 @@ class AttnOp:
         o, probs = ops.attn_fwd(qkv)
         out, out_sums = self.proj.fwd(run, o, residual=x, gn_groups=self.out_groups)
         run.tape.append((self, (x, st, hn, qkv, o, probs)))
+        run.tap(self.blk, "", out)
         return out, out_sums
 
     def bwd(self, run: Run, saved, dout, dout_cs=None):
@@ -405,6 +420,7 @@ class LinAttnOp:
         o, ks, ctx = ops.linattn_fwd(qkv)
         out, out_sums = self.proj.fwd(run, o, gn_groups=self.out_groups)
         run.tape.append((self, (x, qkv, o, ks, ctx)))
+        run.tap(self.blk, "", out)
         return out, out_sums
 
     def bwd(self, run: Run, saved, dout, dout_cs=None):
@@ -433,6 +449,7 @@ class PlainConvOp:
     def fwd(self, run: Run, x, x_sums=None):
         y, y_sums = self.op.fwd(run, x, gn_groups=self.out_groups)
         run.tape.append((self, (x,)))
+        run.tap(self.op.convs[0], "", y)
         return y, y_sums
 
     def bwd(self, run: Run, saved, dout, dout_cs=None):
@@ -454,6 +471,7 @@ class HeadOp:
         a, st = gn_fwd(run, self.norm, x, True, x_sums)
         y, _ = self.op.fwd(run, a)
         run.tape.append((self, (x, st, a)))
+        run.tap(self.op.convs[0], "", y)
         return y, None
 
     def bwd(self, run: Run, saved, dout, dout_cs=None):
@@ -502,6 +520,11 @@ class _Stack(nn.Module):
         self._rng_sample_base = 0                  # first sample of this forward in the global batch (train.TrainStep)
         self.dropout_mask_override = None          # verification hook: {ResnetBlock module: uint8 NHWC keep mask}
         self._step_state = None                    # device-side Philox position (train.TrainStep graph mode)
+        # verification hook: a dict that receives every stage's output (NHWC, compute dtype, padded channels) under the
+        # reference's module path, e.g. "down.0.block.1", "down.0.block.1.conv1", "mid.attn_1", "down.1.downsample",
+        # "conv_in", "conv_out" (the names oracle.vae_oracle's `taps` and the golden fixtures use, minus the
+        # "encoder." / "decoder." prefix)
+        self.tap_sink: Optional[dict] = None
 
     def stages(self, need_input_grad: bool):
         raise NotImplementedError
@@ -531,6 +554,10 @@ class _StackFn(torch.autograd.Function):
             run.step_state = stack._step_state
             if stack.dropout_mask_override:
                 run.dropout_masks = {id(k): v for k, v in stack.dropout_mask_override.items()}
+        if stack.tap_sink is not None:
+            run.taps = stack.tap_sink
+            # a Downsample / Upsample is tapped under its own path (its only child is `.conv`)
+            run.tap_names = {id(m): (n[:-5] if n.endswith("sample.conv") else n) for n, m in stack.named_modules()}
         with torch.no_grad():
             y = run_forward(stack.stages(need_input_grad), run, x)
         ctx.run = run

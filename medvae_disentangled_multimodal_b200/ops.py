@@ -50,7 +50,10 @@ def conv_flops(d: ConvDesc) -> float:
     """algorithmic FLOPs (2*MAC) of one direction of this conv as the reference executes it
     (Upsample = 9 taps on the 2x grid, although the kernels run 4 taps per output parity)."""
     oh, ow = conv_out_hw(d)
-    return 2.0 * d.batch * oh * ow * d.out_c * d.in_c * d.ksize * d.ksize
+    # a skinny conv run with zero-padded channels (blocks.ConvOp.pad_in / pad_out) counts its REAL channels:
+    # ConvOp.desc() leaves them on the descriptor object
+    cin, cout = getattr(d, "real_channels", (d.in_c, d.out_c))
+    return 2.0 * d.batch * oh * ow * cout * cin * d.ksize * d.ksize
 
 
 def conv_fprop(d: ConvDesc, x, wf, bias, residual, out=None):
@@ -251,19 +254,22 @@ def reparam_kl_fwd(moments, eps, zc, clamp, seed, offset, want_kl=True, want_std
     if eps is None:
         eps_out = torch.empty_like(mean)
     kl = torch.zeros((), dtype=torch.float64, device=dev) if want_kl else None
-    check(lib().mvae_reparam_kl_fwd(ptr(moments), ptr(eps), ptr(eps_out), ptr(mean), ptr(logvar), ptr(std), ptr(z), None,
-                                    ptr(kl), b, zc, r, float(clamp), int(seed), int(offset),
-                                    int(sample_base) * zc * r * r, ptr(step_state),
-                                    L.code_of(moments.dtype), stream()), "reparam_kl_fwd")
+    # algorithmic bytes: read the moments, write z (the API also returns fp32 mean / logvar / std / eps)
+    with P.region("loss_kernels", 0.0, moments.numel() * moments.element_size() + 4 * mean.numel()):
+        check(lib().mvae_reparam_kl_fwd(ptr(moments), ptr(eps), ptr(eps_out), ptr(mean), ptr(logvar), ptr(std), ptr(z),
+                                        None, ptr(kl), b, zc, r, float(clamp), int(seed), int(offset),
+                                        int(sample_base) * zc * r * r, ptr(step_state),
+                                        L.code_of(moments.dtype), stream()), "reparam_kl_fwd")
     return mean, logvar, z, std, (eps if eps is not None else eps_out), kl
 
 
 def reparam_kl_bwd(d_mean, d_logvar, d_z, logvar, eps, moments, clamp):
     b, r, _, c2 = moments.shape
     d_mom = torch.empty_like(moments)
-    check(lib().mvae_reparam_kl_bwd(ptr(d_mean), ptr(d_logvar), ptr(d_z), None, ptr(logvar), ptr(eps), ptr(moments),
-                                    ptr(d_mom), b, c2 // 2, r, float(clamp), L.code_of(moments.dtype), stream()),
-          "reparam_kl_bwd")
+    with P.region("loss_kernels", 0.0, 2 * moments.numel() * moments.element_size() + 4 * (moments.numel() // 2)):
+        check(lib().mvae_reparam_kl_bwd(ptr(d_mean), ptr(d_logvar), ptr(d_z), None, ptr(logvar), ptr(eps), ptr(moments),
+                                        ptr(d_mom), b, c2 // 2, r, float(clamp), L.code_of(moments.dtype), stream()),
+              "reparam_kl_bwd")
     return d_mom
 
 
@@ -271,7 +277,8 @@ def recon_loss(recon, x, kind, want_grad=True):
     n = recon.numel()
     s = torch.zeros((), dtype=torch.float64, device=recon.device)
     d_unit = torch.empty_like(recon) if want_grad else None
-    check(lib().mvae_recon_loss_fwd_bwd(ptr(recon), ptr(x), ptr(s), ptr(d_unit), n, kind, stream()), "recon_loss")
+    with P.region("loss_kernels", 0.0, (3 if want_grad else 2) * 4 * n):
+        check(lib().mvae_recon_loss_fwd_bwd(ptr(recon), ptr(x), ptr(s), ptr(d_unit), n, kind, stream()), "recon_loss")
     return s, d_unit
 
 
@@ -283,13 +290,15 @@ def kl_sum(mean, logvar):
 
 def kl_bwd(mean, logvar, coef):
     dm, dl = torch.empty_like(mean), torch.empty_like(logvar)
-    check(lib().mvae_kl_bwd(ptr(mean), ptr(logvar), ptr(coef), ptr(dm), ptr(dl), mean.numel(), stream()), "kl_bwd")
+    with P.region("loss_kernels", 0.0, 16 * mean.numel()):
+        check(lib().mvae_kl_bwd(ptr(mean), ptr(logvar), ptr(coef), ptr(dm), ptr(dl), mean.numel(), stream()), "kl_bwd")
     return dm, dl
 
 
 def scale_by(t, scale_dev):
     out = torch.empty_like(t)
-    check(lib().mvae_scale_by_device_scalar(ptr(t), ptr(scale_dev), ptr(out), t.numel(), stream()), "scale")
+    with P.region("loss_kernels", 0.0, 8 * t.numel()):
+        check(lib().mvae_scale_by_device_scalar(ptr(t), ptr(scale_dev), ptr(out), t.numel(), stream()), "scale")
     return out
 
 

@@ -127,6 +127,14 @@ class FusedAdamW:
         t = self._ensure_tables(plist, grads)
         self.step_count += 1
         self._sqnorm.zero_()
+        from . import profile as P
+        nel = sum(p.numel() for p in plist)
+        # 28 B / parameter: sqnorm reads g (4); the update reads p, g, m, v (16) and writes p, m, v (12) — minus the 4 above
+        with P.region("adamw", 0.0, 32.0 * nel):
+            self._launch(t, lr)
+        torch._C._increment_version(plist)
+
+    def _launch(self, t, lr):
         check(lib().mvae_grad_sqnorm_chunked(ptr(t["g"]), ptr(t["ct"]), ptr(t["co"]), ptr(t["cl"]), t["chunks"],
                                              ptr(self._sqnorm), stream()), "grad_sqnorm")
         check(lib().mvae_adamw_clip_step_chunked(ptr(t["p"]), ptr(t["g"]), ptr(t["m"]), ptr(t["v"]), ptr(t["ct"]),
@@ -134,9 +142,8 @@ class FusedAdamW:
                                                  self.max_norm, float(self.lr if lr is None else lr), self.betas[0],
                                                  self.betas[1], self.eps, self.weight_decay, int(self.decoupled),
                                                  self.step_count, ptr(self.step_state), stream()), "adamw_clip_step")
-        # parameters changed in place behind autograd's back: bump versions so the packed bf16
-        # operand caches (blocks.ConvOp.packed) are refreshed on the next forward
-        torch._C._increment_version(plist)
+        # (step() bumps the parameter versions afterwards: they changed in place behind autograd's back, and the packed
+        # bf16 operand caches (blocks.ConvOp.packed) are refreshed on the next forward)
 
     def state_dict(self):
         return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,

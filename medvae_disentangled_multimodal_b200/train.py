@@ -184,6 +184,13 @@ class TrainStep:
         from .optim import FusedAdamW
         self.model, self.criterion = model, criterion
         self.use_graph = bool(use_graph)
+        if self.use_graph and hasattr(criterion, "separation_weight"):
+            # the disentangled model takes its modality indices from the host: the input projector, the decoder heads,
+            # the reconstruction width (all-gray batch -> 1 channel) and the grouping of the two latent losses would be
+            # frozen at capture and replayed for later batches with other indices
+            raise NotImplementedError("TrainStep(use_graph=True) does not support DisentangledConditionalVAE / "
+                                      "DisentangledVAELoss: its host-side modality indices cannot be replayed from a "
+                                      "captured graph; use the eager step (the 128x128 workload gains nothing from a graph)")
         self._graph = None
         self._graph_key = None
         self._graph_eager_steps = 0
@@ -237,6 +244,9 @@ class TrainStep:
                 own[k].copy_(v)                 # in place: gradient views, pointer tables and graphs stay valid
         self.optimizer.load_state_dict(sd["optimizer"])
         self.step_state.copy_(sd["step_state"])
+        # a checkpoint written by an eager TrainStep never advanced step_state[0] (eager AdamW takes t from the host
+        # counter); a graph-mode step reads t from the device: keep the two in step whichever mode wrote the checkpoint
+        self.step_state[0:1].fill_(float(self.optimizer.step_count))
         self.model._rng_step = int(sd["rng"].get("model", 0))
         for name in ("decoder", "encoder"):
             stack = getattr(self.model, name, None)

@@ -203,6 +203,54 @@ def test_checkpoint_resume_continues_bit_for_bit(use_graph):
         assert dmax <= 2.5e-7 * wmax, (dmax, wmax, int(((final - final2) != 0).sum()), final.numel())
 
 
+def test_checkpoint_resume_across_modes_keeps_the_adam_step():
+    """a checkpoint written by an EAGER TrainStep resumed into a GRAPH-mode one: AdamW's bias correction must continue at
+    t = saved step + 1 (the captured kernel reads t from the device-side step_state, which eager steps never advance)"""
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200.train import TrainStep
+    x, onehot, _ = O.synthetic_batch(8, 3, 16, seed=77)
+    x, onehot = x.to(DEV), onehot.to(DEV)
+    eps = torch.randn(8, KW["latent_dim"], 8, 8, generator=torch.Generator().manual_seed(3)).to(DEV)
+
+    def make(use_graph):
+        torch.manual_seed(9)
+        model = M.ConditionalVAE(compute_dtype="fp32", **KW).to(DEV)
+        model.eps_override = eps                       # identical noise in both modes
+        return model, TrainStep(model, M.VAELoss(**LKW), use_graph=use_graph, **OPT)
+
+    model, ts = make(False)
+    for _ in range(5):
+        ts.step(x, onehot)
+    ckpt = ts.state_dict()
+    for _ in range(3):
+        ts.step(x, onehot)
+    want = torch.cat([p.detach().flatten() for p in model.parameters()]).clone()
+    ts.close()
+
+    model2, ts2 = make(True)
+    for _ in range(3):                                 # two eager warm-up steps + capture + first replay
+        ts2.step(x, onehot)
+    assert ts2._graph is not None
+    ts2.load_state_dict(ckpt)
+    assert float(ts2.step_state[0]) == 5.0
+    for _ in range(3):
+        ts2.step(x, onehot)
+    got = torch.cat([p.detach().flatten() for p in model2.parameters()])
+    ts2.close()
+    ts2.release_graph()
+    # with the bias correction restarted at t = 1 the three updates would be ~3x too small: ~1e-4 relative on the weights
+    assert float((got - want).norm() / want.norm()) < 2e-6
+
+
+def test_graph_mode_refuses_the_disentangled_model():
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200.train import TrainStep
+    model = M.DisentangledConditionalVAE(num_modalities=5, shared_latent_dim=4, modality_latent_dim=4, resolution=28,
+                                         hidden_channels=16, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=[]).to(DEV)
+    with pytest.raises(NotImplementedError, match="use_graph"):
+        TrainStep(model, M.DisentangledVAELoss("mse", 1.0, 1.0, 0.1, 0.05), use_graph=True)
+
+
 def test_out_of_scope_names_fail_loudly():
     import medvae_disentangled_multimodal_b200 as M
     for name in ("LPIPSLoss", "BiomedCLIPLoss", "LPIPSWithDiscriminator", "NLayerDiscriminator"):
