@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define MVAE_ABI_VERSION 4
+#define MVAE_ABI_VERSION 5
 
 enum { MVAE_F32 = 0, MVAE_BF16 = 1 };
 
@@ -161,6 +161,19 @@ int mvae_attn_core_bwd(const void* qkv, const float* probs, const void* dout, vo
                        float* dscratch, int32_t batch, int32_t tokens, int32_t c, int32_t dtype,
                        void* stream);
 
+/* The same AttnBlock core as ONE persistent tcgen05 kernel per direction (bf16 only; replaces the q/k/v -> softmax ->
+ * weighted-sum part of src/models/encoder_decoder.py:91-103): the scores of an image stay in TMEM / shared memory.
+ * mvae_attn_fused_ok: 1 when (tokens, c, dtype) is served by it (bf16, c % 64 == 0, tokens <= 256), else use
+ * mvae_attn_core_*.  lse2: [B, T] fp32, log2-domain log-sum-exp of the scaled scores per query, written by the forward
+ * and read by the backward, which recomputes the probabilities instead of storing [B, T, T].
+ * Backward: out = the forward's output, dscratch: B*T floats (row dots of dout and out). */
+int mvae_attn_fused_ok(int32_t tokens, int32_t c, int32_t dtype);
+int mvae_attn_fused_fwd(const void* qkv, void* out, float* lse2, int32_t batch, int32_t tokens, int32_t c,
+                        int32_t dtype, void* stream);
+int mvae_attn_fused_bwd(const void* qkv, const void* out, const float* lse2, const void* dout, void* dqkv,
+                        float* dscratch, int32_t batch, int32_t tokens, int32_t c, int32_t dtype,
+                        void* stream);
+
 /* ConditionalVAE.create_condition_map + torch.cat, conditional_vae.py:107-127 (concat path),
  * and the NCHW->NHWC conversion of x.  cond: [B, cond_dim] fp32 (one-hot or dense);
  * w: [C*64, cond_dim], b: [C*64] (condition_proj.0).  out: NHWC [B,H,W,out_c] with channels
@@ -230,16 +243,25 @@ int mvae_adamw_clip_step(float* const* params, const float* const* grads, float*
 
 /* the same two passes over a CHUNK TABLE (device arrays): chunk i covers elements
  * [chunk_offset[i], chunk_offset[i] + chunk_len[i]) of tensor chunk_tensor[i]; equal-sized chunks
- * balance the CTAs whatever the tensor sizes, and aligned chunks use 16-byte accesses. */
+ * balance the CTAs whatever the tensor sizes, and aligned chunks use 16-byte accesses.
+ * Per-tensor semantics of the reference (src/lightning_module.py:468-477, torch.optim):
+ *   - pass 1 accumulates tensor_sq[t] (sum of squares) and sets tensor_bad[t] when tensor t holds ANY NaN / Inf
+ *     (both arrays have n_tensors entries and must be zero on entry);
+ *   - pass 2 treats the WHOLE gradient of a bad tensor as zero (as `param.grad.zero_()` does), leaves a tensor
+ *     with tensor_skip[t] != 0 untouched (a parameter whose .grad is None is skipped by torch.optim: no weight
+ *     decay, no moment update; tensor_skip may be NULL), takes the global norm over the remaining tensors and
+ *     writes its square to *sqnorm_out (may be NULL). */
 int mvae_grad_sqnorm_chunked(const float* const* grads, const int32_t* chunk_tensor,
                              const int64_t* chunk_offset, const int32_t* chunk_len, int32_t n_chunks,
-                             double* sqnorm_dev, void* stream);
+                             double* tensor_sq, int32_t* tensor_bad, void* stream);
 int mvae_adamw_clip_step_chunked(float* const* params, const float* const* grads, float* const* exp_avg,
                                  float* const* exp_avg_sq, const int32_t* chunk_tensor,
                                  const int64_t* chunk_offset, const int32_t* chunk_len, int32_t n_chunks,
-                                 const double* sqnorm_dev, float max_norm, float lr, float beta1,
-                                 float beta2, float eps, float weight_decay, int32_t decoupled,
-                                 int32_t step, const double* step_state, void* stream);
+                                 const double* tensor_sq, const int32_t* tensor_bad,
+                                 const int32_t* tensor_skip, int32_t n_tensors, double* sqnorm_out,
+                                 float max_norm, float lr, float beta1, float beta2, float eps,
+                                 float weight_decay, int32_t decoupled, int32_t step,
+                                 const double* step_state, void* stream);
 
 /* Device-resident per-step scalars, so that a CUDA-graph capture of the training step does not bake
  * them into its kernel arguments: step_state = double[3] {optimizer step t, learning rate, Philox

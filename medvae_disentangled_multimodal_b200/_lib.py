@@ -13,7 +13,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmedvae_b200.so")
 
-ABI_VERSION = 4          # include/medvae_b200.h MVAE_ABI_VERSION
+ABI_VERSION = 5          # include/medvae_b200.h MVAE_ABI_VERSION
 F32, BF16 = 0, 1
 CONV_S1, CONV_DOWN, CONV_UP = 0, 1, 2
 ENGINE_AUTO, ENGINE_SIMT, ENGINE_UMMA = 0, 1, 2
@@ -65,6 +65,9 @@ SIGNATURES = {
                                            _vp]),
     "mvae_attn_core_fwd": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "mvae_attn_core_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
+    "mvae_attn_fused_ok": (C.c_int, [_i32, _i32, _i32]),
+    "mvae_attn_fused_fwd": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
+    "mvae_attn_fused_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "mvae_input_pack_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_input_pack_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_nhwc_to_nchw_f32": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
@@ -79,9 +82,9 @@ SIGNATURES = {
     "mvae_grad_sqnorm": (C.c_int, [_vp, _vp, _i32, _vp, _vp]),
     "mvae_adamw_clip_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _f32, _f32, _f32, _f32, _f32, _f32, _i32,
                                        _i32, _vp]),
-    "mvae_grad_sqnorm_chunked": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp]),
-    "mvae_adamw_clip_step_chunked": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _f32, _f32, _f32, _f32, _f32,
-                                               _f32, _i32, _i32, _vp, _vp]),
+    "mvae_grad_sqnorm_chunked": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
+    "mvae_adamw_clip_step_chunked": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp,
+                                               _f32, _f32, _f32, _f32, _f32, _f32, _i32, _i32, _vp, _vp]),
     "mvae_step_state_advance": (C.c_int, [_vp, C.c_double, _vp]),
     "mvae_dis_input_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "mvae_dis_input_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),

@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "csrc", "_obj")
 LIB = os.path.join(HERE, "libmedvae_b200.so")
-SOURCES = ["api.cu", "conv_simt.cu", "conv_umma.cu", "pack.cu", "norm.cu", "attn.cu", "attn_umma.cu", "loss.cu", "disent.cu", "metrics.cu",
+SOURCES = ["api.cu", "conv_simt.cu", "conv_umma.cu", "pack.cu", "norm.cu", "attn.cu", "attn_umma.cu", "attn_fused.cu", "loss.cu", "disent.cu", "metrics.cu",
            "feed.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]

@@ -82,12 +82,17 @@ int adamw_step(float* const* params, const float* const* grads, float* const* m1
                float eps, float wd, int decoupled, int step, cudaStream_t st);
 
 int grad_sqnorm_chunked(const float* const* grads, const int* ch_tensor, const long long* ch_off, const int* ch_len,
-                        int n_chunks, double* out, cudaStream_t st);
+                        int n_chunks, double* tensor_sq, int* tensor_bad, cudaStream_t st);
 int adamw_step_chunked(float* const* params, const float* const* grads, float* const* m1, float* const* m2,
                        const int* ch_tensor, const long long* ch_off, const int* ch_len, int n_chunks,
-                       const double* sqnorm, float max_norm, float lr, float b1, float b2, float eps, float wd,
+                       const double* tensor_sq, const int* tensor_bad, const int* tensor_skip, int n_tensors,
+                       double* sqnorm_out, float max_norm, float lr, float b1, float b2, float eps, float wd,
                        int decoupled, int step, const double* dyn, cudaStream_t st);
 
+bool attn_fused_ok(int Tn, int C);
+int attn_fused_fwd(const bf16* qkv, bf16* out, float* lse2, int B, int Tn, int C, cudaStream_t st);
+int attn_fused_bwd(const bf16* qkv, const bf16* out, const float* lse2, const bf16* dout, bf16* dqkv, float* dscratch,
+                   int B, int Tn, int C, cudaStream_t st);
 int linattn_fwd(const void* qkv, void* out, float* ks, float* ctx, int B, int Tn, int C, int dtype, cudaStream_t st);
 int linattn_bwd(const void* qkv, const float* ks, const float* ctx, const void* dout, void* dqkv, float* dctx, float* dks,
                 int B, int Tn, int C, int dtype, cudaStream_t st);
@@ -437,21 +442,26 @@ int mvae_adamw_clip_step(float* const* params, const float* const* grads, float*
 }
 
 int mvae_grad_sqnorm_chunked(const float* const* grads, const int32_t* chunk_tensor, const int64_t* chunk_offset,
-                             const int32_t* chunk_len, int32_t n_chunks, double* sqnorm_dev, void* stream) {
-    MVAE_CHECK(grads && chunk_tensor && chunk_offset && chunk_len && sqnorm_dev && n_chunks > 0, "grad_sqnorm_chunked: bad argument");
+                             const int32_t* chunk_len, int32_t n_chunks, double* tensor_sq, int32_t* tensor_bad,
+                             void* stream) {
+    MVAE_CHECK(grads && chunk_tensor && chunk_offset && chunk_len && tensor_sq && tensor_bad && n_chunks > 0,
+               "grad_sqnorm_chunked: bad argument");
     return grad_sqnorm_chunked(grads, chunk_tensor, reinterpret_cast<const long long*>(chunk_offset), chunk_len, n_chunks,
-                               sqnorm_dev, ST(stream));
+                               tensor_sq, tensor_bad, ST(stream));
 }
 int mvae_adamw_clip_step_chunked(float* const* params, const float* const* grads, float* const* exp_avg,
                                  float* const* exp_avg_sq, const int32_t* chunk_tensor, const int64_t* chunk_offset,
-                                 const int32_t* chunk_len, int32_t n_chunks, const double* sqnorm_dev, float max_norm,
-                                 float lr, float beta1, float beta2, float eps, float weight_decay, int32_t decoupled,
-                                 int32_t step, const double* step_state, void* stream) {
+                                 const int32_t* chunk_len, int32_t n_chunks, const double* tensor_sq,
+                                 const int32_t* tensor_bad, const int32_t* tensor_skip, int32_t n_tensors,
+                                 double* sqnorm_out, float max_norm, float lr, float beta1, float beta2, float eps,
+                                 float weight_decay, int32_t decoupled, int32_t step, const double* step_state,
+                                 void* stream) {
     MVAE_CHECK(params && grads && exp_avg && exp_avg_sq && chunk_tensor && chunk_offset && chunk_len && n_chunks > 0 &&
-                   (step >= 1 || step_state), "adamw_chunked: bad argument");
+                   tensor_sq && tensor_bad && n_tensors > 0 && (step >= 1 || step_state), "adamw_chunked: bad argument");
     return adamw_step_chunked(params, grads, exp_avg, exp_avg_sq, chunk_tensor,
-                              reinterpret_cast<const long long*>(chunk_offset), chunk_len, n_chunks, sqnorm_dev, max_norm,
-                              lr, beta1, beta2, eps, weight_decay, decoupled, step, step_state, ST(stream));
+                              reinterpret_cast<const long long*>(chunk_offset), chunk_len, n_chunks, tensor_sq, tensor_bad,
+                              tensor_skip, n_tensors, sqnorm_out, max_norm, lr, beta1, beta2, eps, weight_decay, decoupled,
+                              step, step_state, ST(stream));
 }
 
 int mvae_dis_input_fwd(const float* x, const int64_t* idx, const float* pw, const float* pb, const int32_t* is_gray,
@@ -511,6 +521,22 @@ int mvae_dis_loss_total(const float* recon, const float* kl, const float* sep, c
     return dis_total(recon, kl, sep, con, w_recon, w_kl, w_sep, w_con, out5, mask4, ST(stream));
 }
 
+int mvae_attn_fused_ok(int32_t tokens, int32_t c, int32_t dtype) {
+    return (dtype == MVAE_BF16 && attn_fused_ok(tokens, c) && debug_knob(11) == 0) ? 1 : 0;
+}
+int mvae_attn_fused_fwd(const void* qkv, void* out, float* lse2, int32_t batch, int32_t tokens, int32_t c, int32_t dtype,
+                        void* stream) {
+    MVAE_CHECK(qkv && out && lse2 && batch > 0, "attn_fused_fwd: bad argument");
+    MVAE_CHECK(dtype == MVAE_BF16, "attn_fused_fwd: bf16 only (the fp32 verification mode uses mvae_attn_core_fwd)");
+    return attn_fused_fwd((const bf16*)qkv, (bf16*)out, lse2, batch, tokens, c, ST(stream));
+}
+int mvae_attn_fused_bwd(const void* qkv, const void* out, const float* lse2, const void* dout, void* dqkv, float* dscratch,
+                        int32_t batch, int32_t tokens, int32_t c, int32_t dtype, void* stream) {
+    MVAE_CHECK(qkv && out && lse2 && dout && dqkv && dscratch && batch > 0, "attn_fused_bwd: bad argument");
+    MVAE_CHECK(dtype == MVAE_BF16, "attn_fused_bwd: bf16 only (the fp32 verification mode uses mvae_attn_core_bwd)");
+    return attn_fused_bwd((const bf16*)qkv, (const bf16*)out, lse2, (const bf16*)dout, (bf16*)dqkv, dscratch, batch, tokens,
+                          c, ST(stream));
+}
 int mvae_linattn_core_fwd(const void* qkv, void* out, float* ks, float* ctx, int32_t batch, int32_t tokens, int32_t c,
                           int32_t dtype, void* stream) {
     MVAE_CHECK(qkv && out && ks && ctx && dtype_ok(dtype) && batch > 0 && tokens > 0 && c > 0, "linattn_core_fwd: bad argument");

@@ -1,0 +1,501 @@
+// Fused AttnBlock core (encoder_decoder.py:91-103) on tcgen05 / TMEM: ONE persistent kernel per direction, the scores of
+// an image never leave the SM.
+//
+//   forward   item = (image, 128-query tile):   S = Q K^T  (TMEM)  ->  softmax on TMEM lanes (one thread = one query row)
+//                                               ->  P~ = exp2(S' - max) as bf16 into a swizzled shared-memory tile
+//                                               ->  O = (P~ V) / rowsum in 128-channel chunks (TMEM, double buffered)
+//             saved for the backward: ONE float per query row, lse2 = max + log2(rowsum)  (no [B][T][T] tensor)
+//   backward  recomputes P from lse2.  Two kinds of work item, both (image, 128-row tile):
+//     Q-side  rows = queries:  S = Q K^T, dP = dO V^T (TMEM)  ->  dS = P (dP - D) alpha  (shared)  ->  dQ = dS K
+//     K-side  rows = keys:     S^T = K Q^T, dP^T = V dO^T     ->  P^T, dS^T (shared)      ->  dV = P^T dO, dK = dS^T Q
+//     D[q] = sum_c dO[q][c] O[q][c] comes from a small row-dot kernel launched in front.
+//   A key tile needs the contributions of ALL queries (and vice versa), which is why the backward has the two transposed
+//   kinds instead of atomics: every output element is written exactly once, deterministically.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM allocation), warps 2-5 = epilogue (TMEM
+// lane quarter = warp & 3).  Operands are read in place from the fused NHWC qkv tensor [B][T][3C] and from dO / written to
+// dqkv through ONE 3-D tensor map per tensor with a {64 channels, 64 tokens} box: a K-major operand (reduction over
+// channels) and an N-major operand (reduction over tokens) are the same box seen through different UMMA descriptors.
+// Rows / tokens beyond T are TMA zero fill; the score columns beyond T are masked in the epilogue.
+#include "umma.cuh"
+
+namespace mvae {
+using namespace sm100;
+
+int encode_tmap_3d_bf16(CUtensorMap* m, const void* base, unsigned long long inner, unsigned long long rows,
+                        unsigned long long batch, unsigned long long pitch_elems, unsigned long long batch_elems,
+                        unsigned box_inner, unsigned box_rows);   // conv_umma.cu
+
+enum { AF_FWD = 0, AF_BWD_Q = 1, AF_BWD_K = 2 };
+
+struct alignas(64) AfTmaps {
+    CUtensorMap qkv, dy;   // dy = dO (backward only)
+};
+struct AfDev {
+    int B, T, C;
+    int Tp;            // N of the score GEMMs: T rounded up to 16
+    int kboxes;        // 64-token boxes covering T
+    int mtiles;        // 128-row tiles per image
+    int bwd;
+    int stages;
+    int bno;           // channel chunk of the output GEMMs (128, or 64 when C is not a multiple of 128)
+    int n_items;
+    int o_alias;       // output accumulators alias the score columns (backward, T > 128)
+    uint32_t stage_bytes, tile_bytes;
+    uint32_t col_s, col_dp, col_o0, col_o1;
+    uint32_t idesc_s, idesc_o;
+    float alpha, alpha_log2e;
+    bf16* out;         // forward [B][T][C]
+    float* lse2;       // [B][T]
+    const float* D;    // [B][T]
+    bf16* dqkv;        // backward [B][T][3C]
+};
+
+constexpr int AF_THREADS = 192;
+constexpr int AF_MAX_STAGES = 4;
+
+// one GEMM whose reduction runs over channels (scores): A rows r0.. of (map_a, channel offset ca), B all tokens of (map_b, cb)
+struct AfScoreJob { int a_dy, ca, b_dy, cb; uint32_t col; };
+// one GEMM whose reduction runs over tokens (outputs): A = shared tile `tile`, B = (map, channel offset cb) N-major
+struct AfOutJob { int tile, b_dy, cb; int out_off; };
+
+__device__ __forceinline__ void af_jobs(const AfDev& p, int kind, AfScoreJob* sj, int& ns, AfOutJob* oj, int& no) {
+    const int C = p.C;
+    if (kind == AF_FWD) {
+        ns = 1; sj[0] = {0, 0, 0, C, p.col_s};
+        no = 1; oj[0] = {0, 0, 2 * C, 0};
+    } else if (kind == AF_BWD_Q) {
+        ns = 2; sj[0] = {0, 0, 0, C, p.col_s}; sj[1] = {1, 0, 0, 2 * C, p.col_dp};
+        no = 1; oj[0] = {1, 0, C, 0};
+    } else {
+        ns = 2; sj[0] = {0, C, 0, 0, p.col_s}; sj[1] = {0, 2 * C, 1, 0, p.col_dp};
+        no = 2; oj[0] = {0, 1, 0, 2 * C}; oj[1] = {1, 0, 0, C};
+    }
+}
+__device__ __forceinline__ void af_item(const AfDev& p, int it, int& kind, int& img, int& r0) {
+    if (!p.bwd) {
+        kind = AF_FWD;
+    } else {
+        kind = (it & 1) ? AF_BWD_K : AF_BWD_Q;
+        it >>= 1;
+    }
+    img = it / p.mtiles;
+    r0 = (it % p.mtiles) * 128;
+}
+// 16-byte store of 8 bf16 into a K-major SWIZZLE_128B tile: rows of 128 B (64 elements), 16 KB per 64-column chunk
+__device__ __forceinline__ void af_tile_store8(uint8_t* tile, int row, int col, const float* f) {
+    Vec8<bf16> v;
+    v.pack(f);
+    const int chunk = col >> 6, unit = (col & 63) >> 3;
+    uint8_t* dst = tile + chunk * 16384 + row * 128 + ((unit ^ (row & 7)) << 4);
+    *reinterpret_cast<uint4*>(dst) = v.raw;
+}
+
+__global__ void __launch_bounds__(AF_THREADS, 1)
+attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ AfDev p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sTile0 = smem;                                         // P~ (forward) / P^T (K-side)
+    uint8_t* sTile1 = sTile0 + p.tile_bytes;                        // dS / dS^T (backward only)
+    uint8_t* sStage = sTile1 + (p.bwd ? p.tile_bytes : 0u);
+    uint64_t* full = reinterpret_cast<uint64_t*>(sStage + (uint32_t)p.stages * p.stage_bytes);
+    uint64_t* empty = full + AF_MAX_STAGES;
+    uint64_t* tfull_s = empty + AF_MAX_STAGES;    // scores (S and dP) complete in TMEM
+    uint64_t* pready = tfull_s + 1;               // shared-memory tiles written by the epilogue warps
+    uint64_t* tfull_o = pready + 1;               // [2] output accumulator complete
+    uint64_t* tempty_o = tfull_o + 2;             // [2] output accumulator drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_o + 2);
+    float* sStat = reinterpret_cast<float*>(tmem_slot + 4);   // [2][256]: lse2, D per query (K-side items)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if ((smem_u32(smem) & 1023u) != 0u) {   // SWIZZLE_128B tiles need 1024-byte alignment
+        if (threadIdx.x == 0) printf("mvae: attn_fused dynamic shared memory is not 1024-byte aligned\n");
+        __trap();
+    }
+    if (warp == 0 && lane == 0) { prefetch_tmap(&tm.qkv); if (p.bwd) prefetch_tmap(&tm.dy); }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < AF_MAX_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+            mbar_init(tfull_s, 1);
+            mbar_init(pready, 4);
+            for (int i = 0; i < 2; ++i) { mbar_init(&tfull_o[i], 1); mbar_init(&tempty_o[i], 4); }
+            fence_barrier_init();
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, 512);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int kiters = p.C / 64;            // channel chunks of a score GEMM
+    const int nchunks = p.C / p.bno;        // channel chunks of an output GEMM
+    const uint32_t score_stage_bytes = 16384u + (uint32_t)p.kboxes * 8192u;
+    const uint32_t out_stage_bytes = (uint32_t)p.bno * 128u;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+                int kind, img, r0, ns, no;
+                AfScoreJob sj[2]; AfOutJob oj[2];
+                af_item(p, it, kind, img, r0);
+                af_jobs(p, kind, sj, ns, oj, no);
+                for (int j = 0; j < ns; ++j) {
+                    const CUtensorMap* ma = sj[j].a_dy ? &tm.dy : &tm.qkv;
+                    const CUtensorMap* mb = sj[j].b_dy ? &tm.dy : &tm.qkv;
+                    for (int kb = 0; kb < kiters; ++kb) {
+                        mbar_wait(&empty[stage], phase ^ 1u);
+                        mbar_expect_tx(&full[stage], score_stage_bytes);
+                        uint8_t* a = sStage + (uint32_t)stage * p.stage_bytes;
+                        uint8_t* b = a + 16384;
+                        tma_load_3d(a, ma, &full[stage], sj[j].ca + kb * 64, r0, img);
+                        tma_load_3d(a + 8192, ma, &full[stage], sj[j].ca + kb * 64, r0 + 64, img);
+                        for (int r = 0; r < p.kboxes; ++r)
+                            tma_load_3d(b + r * 8192, mb, &full[stage], sj[j].cb + kb * 64, r * 64, img);
+                        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+                    }
+                }
+                for (int j = 0; j < no; ++j) {
+                    const CUtensorMap* mb = oj[j].b_dy ? &tm.dy : &tm.qkv;
+                    for (int nc = 0; nc < nchunks; ++nc) {
+                        for (int kc = 0; kc < p.kboxes; ++kc) {
+                            mbar_wait(&empty[stage], phase ^ 1u);
+                            mbar_expect_tx(&full[stage], out_stage_bytes);
+                            uint8_t* b = sStage + (uint32_t)stage * p.stage_bytes;
+                            for (int s = 0; s < p.bno / 64; ++s)
+                                tma_load_3d(b + s * 8192, mb, &full[stage], oj[j].cb + nc * p.bno + s * 64, kc * 64, img);
+                            if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================== MMA issuer
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            uint32_t n_local = 0;            // items done by this CTA (parity of tfull_s / pready)
+            uint32_t uses[2] = {0, 0};       // uses of each output accumulator so far
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++n_local) {
+                int kind, img, r0, ns, no;
+                AfScoreJob sj[2]; AfOutJob oj[2];
+                af_item(p, it, kind, img, r0);
+                af_jobs(p, kind, sj, ns, oj, no);
+                if (p.o_alias) {   // the score columns double as output accumulators: the last item's must be drained
+                    mbar_wait(&tempty_o[0], (uses[0] & 1u) ^ 1u);
+                    mbar_wait(&tempty_o[1], (uses[1] & 1u) ^ 1u);
+                    tc_fence_after();
+                }
+                for (int j = 0; j < ns; ++j) {
+                    for (int kb = 0; kb < kiters; ++kb) {
+                        mbar_wait(&full[stage], phase);
+                        tc_fence_after();
+                        const uint32_t a0 = smem_u32(sStage + (uint32_t)stage * p.stage_bytes);
+                        const uint32_t b0 = a0 + 16384u;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16(tmem_base + sj[j].col, smem_desc_sw128(a0 + k * 32, 16, 1024),
+                                      smem_desc_sw128(b0 + k * 32, 16, 1024), p.idesc_s, (kb | k) != 0 ? 1u : 0u);
+                        umma_commit(&empty[stage]);
+                        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+                    }
+                }
+                umma_commit(tfull_s);
+                mbar_wait(pready, n_local & 1u);
+                tc_fence_after();
+                for (int j = 0; j < no; ++j) {
+                    const uint32_t t0 = smem_u32(oj[j].tile ? sTile1 : sTile0);
+                    for (int nc = 0; nc < nchunks; ++nc) {
+                        const int buf = (int)((uses[0] + uses[1]) & 1u);
+                        mbar_wait(&tempty_o[buf], (uses[buf] & 1u) ^ 1u);
+                        tc_fence_after();
+                        const uint32_t dcol = tmem_base + (buf ? p.col_o1 : p.col_o0);
+                        for (int kc = 0; kc < p.kboxes; ++kc) {
+                            mbar_wait(&full[stage], phase);
+                            tc_fence_after();
+                            const uint32_t b0 = smem_u32(sStage + (uint32_t)stage * p.stage_bytes);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                umma_bf16(dcol, smem_desc_sw128(t0 + kc * 16384 + k * 32, 16, 1024),
+                                          smem_desc_sw128(b0 + k * 2048, 8192, 1024), p.idesc_o, (kc | k) != 0 ? 1u : 0u);
+                            umma_commit(&empty[stage]);
+                            if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+                        }
+                        umma_commit(&tfull_o[buf]);
+                        ++uses[buf];
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================================================== epilogue warps: one thread = one tile row (TMEM lane)
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        const int et = threadIdx.x - 64;     // 0..127
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        const int cols_tile = p.kboxes * 64;
+        uint32_t n_local = 0;
+        uint32_t uses[2] = {0, 0};
+        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++n_local) {
+            int kind, img, r0, ns, no;
+            AfScoreJob sj[2]; AfOutJob oj[2];
+            af_item(p, it, kind, img, r0);
+            af_jobs(p, kind, sj, ns, oj, no);
+            const int grow = r0 + row;
+            const bool valid = grow < p.T;
+            const long long tok0 = (long long)img * p.T;
+            float row_lse = 0.f, row_d = 0.f, inv_l = 1.f;
+            if (kind == AF_BWD_K) {
+                // per-QUERY statistics: the score columns of this kind are queries
+                asm volatile("bar.sync 1, 128;" ::: "memory");     // the previous item's readers are done
+                for (int q = et; q < cols_tile; q += 128) {
+                    sStat[q] = q < p.T ? p.lse2[tok0 + q] : 0.f;
+                    sStat[256 + q] = q < p.T ? p.D[tok0 + q] : 0.f;
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            } else if (kind == AF_BWD_Q && valid) {
+                row_lse = p.lse2[tok0 + grow];
+                row_d = p.D[tok0 + grow];
+            }
+            mbar_wait(tfull_s, n_local & 1u);
+            tc_fence_after();
+            if (kind == AF_FWD) {
+                float mx = -INFINITY;
+#pragma unroll 1
+                for (int c0 = 0; c0 < p.Tp; c0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c0 + i < p.T) mx = fmaxf(mx, __uint_as_float(v[i]) * p.alpha_log2e);
+                }
+                float sum = 0.f;
+#pragma unroll 1
+                for (int c0 = 0; c0 < cols_tile; c0 += 32) {
+                    uint32_t v[32];
+                    if (c0 < p.Tp) { tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, v); tmem_ld_wait(); }
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        float f[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int c = c0 + g * 8 + j;
+                            float e = (c < p.T) ? exp2f(__uint_as_float(v[g * 8 + j]) * p.alpha_log2e - mx) : 0.f;
+                            e = __bfloat162float(__float2bfloat16_rn(e));     // the value the PV GEMM sees
+                            f[j] = e;
+                            sum += e;
+                        }
+                        af_tile_store8(sTile0, row, c0 + g * 8, f);
+                    }
+                }
+                inv_l = 1.f / sum;
+                if (valid) p.lse2[tok0 + grow] = mx + log2f(sum);
+            } else if (kind == AF_BWD_Q) {
+#pragma unroll 1
+                for (int c0 = 0; c0 < cols_tile; c0 += 32) {
+                    uint32_t s[32], d[32];
+                    if (c0 < p.Tp) {
+                        tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, s);
+                        tmem_ld_32x32(lane_addr + p.col_dp + (uint32_t)c0, d);
+                        tmem_ld_wait();
+                    }
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        float f[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int c = c0 + g * 8 + j;
+                            const float pr = exp2f(__uint_as_float(s[g * 8 + j]) * p.alpha_log2e - row_lse);
+                            f[j] = (c < p.T) ? pr * (__uint_as_float(d[g * 8 + j]) - row_d) * p.alpha : 0.f;
+                        }
+                        af_tile_store8(sTile1, row, c0 + g * 8, f);
+                    }
+                }
+            } else {
+#pragma unroll 1
+                for (int c0 = 0; c0 < cols_tile; c0 += 32) {
+                    uint32_t s[32], d[32];
+                    if (c0 < p.Tp) {
+                        tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, s);
+                        tmem_ld_32x32(lane_addr + p.col_dp + (uint32_t)c0, d);
+                        tmem_ld_wait();
+                    }
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        float fp[8], fd[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int c = c0 + g * 8 + j;      // query index
+                            const float pr = (c < p.T) ? exp2f(__uint_as_float(s[g * 8 + j]) * p.alpha_log2e - sStat[c]) : 0.f;
+                            fp[j] = pr;
+                            fd[j] = (c < p.T) ? pr * (__uint_as_float(d[g * 8 + j]) - sStat[256 + c]) * p.alpha : 0.f;
+                        }
+                        af_tile_store8(sTile0, row, c0 + g * 8, fp);
+                        af_tile_store8(sTile1, row, c0 + g * 8, fd);
+                    }
+                }
+            }
+            // the tiles go to the tensor core through the async proxy; the score columns may be overwritten next
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(pready);
+
+            for (int j = 0; j < no; ++j) {
+                bf16* obase;
+                long long pitch;
+                if (kind == AF_FWD) { obase = p.out; pitch = p.C; }
+                else { obase = p.dqkv + oj[j].out_off; pitch = 3LL * p.C; }
+                bf16* orow = obase + (tok0 + grow) * pitch;
+                for (int nc = 0; nc < nchunks; ++nc) {
+                    const int buf = (int)((uses[0] + uses[1]) & 1u);
+                    mbar_wait(&tfull_o[buf], uses[buf] & 1u);
+                    tc_fence_after();
+                    const uint32_t ocol = lane_addr + (buf ? p.col_o1 : p.col_o0);
+#pragma unroll 1
+                    for (int c0 = 0; c0 < p.bno; c0 += 32) {
+                        uint32_t v[32];
+                        tmem_ld_32x32(ocol + (uint32_t)c0, v);
+                        tmem_ld_wait();
+                        if (valid) {
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                float f[8];
+#pragma unroll
+                                for (int jj = 0; jj < 8; ++jj) f[jj] = __uint_as_float(v[g * 8 + jj]) * inv_l;
+                                Vec8<bf16> o8; o8.pack(f);
+                                o8.store(orow + nc * p.bno + c0 + g * 8);
+                            }
+                        }
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty_o[buf]);
+                    ++uses[buf];
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// D[row] = sum_c dO[row][c] * O[row][c]  (rows = B*T tokens, one warp per row, 16-byte loads)
+__global__ void __launch_bounds__(256) attn_rowdot_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ out,
+                                                          float* __restrict__ D, long long rows, int C) {
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long r = warp0; r < rows; r += nwarps) {
+        const bf16* a = dout + r * C;
+        const bf16* b = out + r * C;
+        float acc = 0.f;
+        for (int c = lane * 8; c < C; c += 256) {
+            Vec8<bf16> va, vb;
+            va.load(a + c); vb.load(b + c);
+            float fa[8], fb[8];
+            va.unpack(fa); vb.unpack(fb);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc = fmaf(fa[j], fb[j], acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) D[r] = acc;
+    }
+}
+
+bool attn_fused_ok(int Tn, int C) { return C % 64 == 0 && C >= 64 && Tn >= 1 && Tn <= 256; }
+
+static int af_num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+static int af_launch(AfTmaps& tm, AfDev& d, cudaStream_t st) {
+    const int Tn = d.T, C = d.C;
+    d.Tp = (Tn + 15) / 16 * 16;
+    d.kboxes = (Tn + 63) / 64;
+    d.mtiles = (Tn + 127) / 128;
+    d.bno = (C % 128 == 0) ? 128 : 64;
+    d.tile_bytes = (uint32_t)d.kboxes * 16384u;
+    d.stage_bytes = 16384u + (uint32_t)d.kboxes * 8192u;     // >= one output-GEMM stage (bno * 128 <= 16384)
+    d.alpha = 1.0f / sqrtf((float)C);                         // int(c) ** (-0.5), encoder_decoder.py:94
+    d.alpha_log2e = d.alpha * 1.4426950408889634f;
+    d.idesc_s = make_idesc_bf16(128, d.Tp, 0, 0);
+    d.idesc_o = make_idesc_bf16(128, d.bno, 0, 1);
+    d.col_s = 0;
+    if (!d.bwd) {
+        d.col_dp = 0; d.col_o0 = 256; d.col_o1 = 384; d.o_alias = 0;
+    } else if (d.Tp <= 128) {
+        d.col_dp = 128; d.col_o0 = 256; d.col_o1 = 384; d.o_alias = 0;
+    } else {
+        d.col_dp = 256; d.col_o0 = 0; d.col_o1 = 128; d.o_alias = 1;
+    }
+    d.n_items = d.B * d.mtiles * (d.bwd ? 2 : 1);
+    const long long fixed = (long long)d.tile_bytes * (d.bwd ? 2 : 1) + 2048 /* sStat */ + 256 /* barriers */;
+    const long long budget = 232448;    // 227 KB of dynamic shared memory per CTA on sm_100
+    int stages = (int)((budget - fixed) / d.stage_bytes);
+    if (stages > AF_MAX_STAGES) stages = AF_MAX_STAGES;
+    MVAE_CHECK(stages >= 2, "attn_fused: T=%d does not leave room for a 2-stage pipeline", Tn);
+    d.stages = stages;
+    long long smem = fixed + (long long)stages * d.stage_bytes;
+    if (smem < 120 * 1024) smem = 120 * 1024;   // one CTA per SM: every CTA allocates all 512 TMEM columns
+    static bool attr_set = false;
+    if (!attr_set) {
+        MVAE_CUDA(cudaFuncSetAttribute(attn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+        attr_set = true;
+    }
+    int grid = d.n_items < af_num_sms() ? d.n_items : af_num_sms();
+    attn_fused_kernel<<<grid, AF_THREADS, (size_t)smem, st>>>(tm, d);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
+// qkv [B][T][3C] bf16 -> out [B][T][C] bf16, lse2 [B][T] fp32 (log2-domain log-sum-exp of the scaled scores, kept for
+// the backward)
+int attn_fused_fwd(const bf16* qkv, bf16* out, float* lse2, int B, int Tn, int C, cudaStream_t st) {
+    MVAE_CHECK(attn_fused_ok(Tn, C), "attn_fused_fwd: unsupported shape T=%d C=%d (needs C %% 64 == 0, T <= 256)", Tn, C);
+    AfTmaps tm;
+    memset(&tm, 0, sizeof(tm));
+    if (encode_tmap_3d_bf16(&tm.qkv, qkv, 3ULL * C, Tn, B, 3ULL * C, (unsigned long long)Tn * 3 * C, 64, 64)) return 1;
+    AfDev d;
+    memset(&d, 0, sizeof(d));
+    d.B = B; d.T = Tn; d.C = C; d.bwd = 0;
+    d.out = out; d.lse2 = lse2;
+    return af_launch(tm, d, st);
+}
+
+// dqkv [B][T][3C] from dout [B][T][C], the forward's out and lse2; dscratch: B*T floats
+int attn_fused_bwd(const bf16* qkv, const bf16* out, const float* lse2, const bf16* dout, bf16* dqkv, float* dscratch,
+                   int B, int Tn, int C, cudaStream_t st) {
+    MVAE_CHECK(attn_fused_ok(Tn, C), "attn_fused_bwd: unsupported shape T=%d C=%d (needs C %% 64 == 0, T <= 256)", Tn, C);
+    const long long rows = (long long)B * Tn;
+    long long blocks = (rows + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    attn_rowdot_kernel<<<(unsigned)blocks, 256, 0, st>>>(dout, out, dscratch, rows, C);
+    MVAE_LAUNCH_CHECK();
+    AfTmaps tm;
+    memset(&tm, 0, sizeof(tm));
+    if (encode_tmap_3d_bf16(&tm.qkv, qkv, 3ULL * C, Tn, B, 3ULL * C, (unsigned long long)Tn * 3 * C, 64, 64)) return 1;
+    if (encode_tmap_3d_bf16(&tm.dy, dout, (unsigned long long)C, Tn, B, (unsigned long long)C, (unsigned long long)Tn * C,
+                            64, 64)) return 1;
+    AfDev d;
+    memset(&d, 0, sizeof(d));
+    d.B = B; d.T = Tn; d.C = C; d.bwd = 1;
+    d.lse2 = const_cast<float*>(lse2); d.D = dscratch; d.dqkv = dqkv;
+    return af_launch(tm, d, st);
+}
+
+}  // namespace mvae

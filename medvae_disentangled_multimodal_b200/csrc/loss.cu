@@ -245,40 +245,54 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* const* __restrict__ p
 // ---- chunked variants: a table of (tensor, offset, length) chunks of <= 64 Ki elements gives every CTA
 // the same amount of work whatever the tensor sizes (the 17 9.4 M-element conv weights of C4 next to
 // 128-element biases), and 16-byte accesses whenever the four pointers allow it.
+// Pass 1 keeps one sum of squares and one "non-finite entry seen" flag PER TENSOR: the reference zeroes the WHOLE gradient
+// of a parameter that holds any NaN / Inf before it clips (src/lightning_module.py:468-477), so a poisoned tensor must
+// drop out of the global norm entirely — its finite entries included.
 __global__ void __launch_bounds__(256) grad_sqnorm_chunked_kernel(const float* const* __restrict__ grads,
                                                                   const int* __restrict__ ch_tensor,
                                                                   const long long* __restrict__ ch_off,
                                                                   const int* __restrict__ ch_len, int n_chunks,
-                                                                  double* __restrict__ out) {
+                                                                  double* __restrict__ tensor_sq,
+                                                                  int* __restrict__ tensor_bad) {
     __shared__ double shd[32];
-    double acc = 0.0;
+    __shared__ int sh_bad;
     for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
-        const float* g = grads[ch_tensor[c]] + ch_off[c];
+        const int t = ch_tensor[c];
+        const float* g = grads[t] + ch_off[c];
         const int n = ch_len[c];
+        if (threadIdx.x == 0) sh_bad = 0;
+        __syncthreads();
         float part = 0.f;
+        bool bad = false;
         if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
             const float4* g4 = reinterpret_cast<const float4*>(g);
             for (int i = threadIdx.x; i < n / 4; i += 256) {
                 const float4 v = g4[i];
-                if (isfinite(v.x)) part = fmaf(v.x, v.x, part);
-                if (isfinite(v.y)) part = fmaf(v.y, v.y, part);
-                if (isfinite(v.z)) part = fmaf(v.z, v.z, part);
-                if (isfinite(v.w)) part = fmaf(v.w, v.w, part);
+                bad |= !(isfinite(v.x) && isfinite(v.y) && isfinite(v.z) && isfinite(v.w));
+                part = fmaf(v.x, v.x, part); part = fmaf(v.y, v.y, part);
+                part = fmaf(v.z, v.z, part); part = fmaf(v.w, v.w, part);
             }
             for (int i = (n / 4) * 4 + threadIdx.x; i < n; i += 256) {
                 const float v = g[i];
-                if (isfinite(v)) part = fmaf(v, v, part);
+                bad |= !isfinite(v);
+                part = fmaf(v, v, part);
             }
         } else {
             for (int i = threadIdx.x; i < n; i += 256) {
                 const float v = g[i];
-                if (isfinite(v)) part = fmaf(v, v, part);
+                bad |= !isfinite(v);
+                part = fmaf(v, v, part);
             }
         }
-        acc += (double)part;   // <= 256 fp32 terms per thread per chunk, then fp64
+        if (bad) sh_bad = 1;                                  // (benign race: every writer stores 1)
+        const double acc = block_sum_d(bad ? 0.0 : (double)part, shd);   // <= 256 fp32 terms per thread, then fp64
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            if (sh_bad) atomicOr(&tensor_bad[t], 1);
+            else if (acc != 0.0) atomicAdd(&tensor_sq[t], acc);
+        }
+        __syncthreads();
     }
-    acc = block_sum_d(acc, shd);
-    if (threadIdx.x == 0 && acc != 0.0) atomicAdd(out, acc);
 }
 
 struct AdamArgs {
@@ -286,7 +300,7 @@ struct AdamArgs {
     int decoupled;
 };
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float clip, const AdamArgs& a) {
-    g = isfinite(g) ? g * clip : 0.f;
+    g = clip == 0.f ? 0.f : g * clip;      // clip == 0: a tensor whose gradient held a NaN / Inf counts as zero as a whole
     if (a.decoupled) p *= (1.f - a.lr * a.wd); else g = fmaf(a.wd, p, g);
     m = fmaf(a.b1, m, (1.f - a.b1) * g);
     v = fmaf(a.b2, v, (1.f - a.b2) * g * g);
@@ -299,7 +313,10 @@ __global__ void __launch_bounds__(256) adamw_chunked_kernel(float* const* __rest
                                                             const int* __restrict__ ch_tensor,
                                                             const long long* __restrict__ ch_off,
                                                             const int* __restrict__ ch_len, int n_chunks,
-                                                            const double* __restrict__ sqnorm, AdamArgs a,
+                                                            const double* __restrict__ tensor_sq,
+                                                            const int* __restrict__ tensor_bad,
+                                                            const int* __restrict__ tensor_skip, int n_tensors,
+                                                            double* __restrict__ sqnorm_out, AdamArgs a,
                                                             const double* __restrict__ dyn) {
     if (dyn) {   // step count and learning rate live on the device (CUDA-graph replays): dyn = {step, lr, rng}
         const float t = (float)dyn[0];
@@ -307,14 +324,28 @@ __global__ void __launch_bounds__(256) adamw_chunked_kernel(float* const* __rest
         a.bc1 = 1.f - powf(a.b1, t);
         a.bc2 = 1.f - powf(a.b2, t);
     }
-    float clip = 1.f;
-    if (a.max_norm > 0.f && sqnorm) {
-        const float norm = (float)sqrt(*sqnorm);
+    // global norm over the tensors that take part: not skipped (never produced a gradient this step) and not poisoned
+    __shared__ double shd[32];
+    __shared__ double sh_total;
+    double part = 0.0;
+    for (int t = threadIdx.x; t < n_tensors; t += 256)
+        if (!tensor_bad[t] && !(tensor_skip && tensor_skip[t])) part += tensor_sq[t];
+    part = block_sum_d(part, shd);
+    if (threadIdx.x == 0) {
+        sh_total = part;
+        if (blockIdx.x == 0 && sqnorm_out) *sqnorm_out = part;
+    }
+    __syncthreads();
+    float clip_all = 1.f;
+    if (a.max_norm > 0.f) {
+        const float norm = (float)sqrt(sh_total);
         const float c = a.max_norm / (norm + 1e-6f);
-        clip = c < 1.f ? c : 1.f;
+        clip_all = c < 1.f ? c : 1.f;
     }
     for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
         const int t = ch_tensor[c];
+        if (tensor_skip && tensor_skip[t]) continue;       // torch.optim skips a parameter whose .grad is None
+        const float clip = tensor_bad[t] ? 0.f : clip_all;
         const long long off = ch_off[c];
         const int n = ch_len[c];
         float* p = params[t] + off;
@@ -352,20 +383,23 @@ static int chunk_grid(int n_chunks) {
     return n_chunks < g ? n_chunks : g;
 }
 int grad_sqnorm_chunked(const float* const* grads, const int* ch_tensor, const long long* ch_off, const int* ch_len,
-                        int n_chunks, double* out, cudaStream_t st) {
-    grad_sqnorm_chunked_kernel<<<chunk_grid(n_chunks), 256, 0, st>>>(grads, ch_tensor, ch_off, ch_len, n_chunks, out);
+                        int n_chunks, double* tensor_sq, int* tensor_bad, cudaStream_t st) {
+    grad_sqnorm_chunked_kernel<<<chunk_grid(n_chunks), 256, 0, st>>>(grads, ch_tensor, ch_off, ch_len, n_chunks, tensor_sq,
+                                                                      tensor_bad);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
 int adamw_step_chunked(float* const* params, const float* const* grads, float* const* m1, float* const* m2,
                        const int* ch_tensor, const long long* ch_off, const int* ch_len, int n_chunks,
-                       const double* sqnorm, float max_norm, float lr, float b1, float b2, float eps, float wd,
+                       const double* tensor_sq, const int* tensor_bad, const int* tensor_skip, int n_tensors,
+                       double* sqnorm_out, float max_norm, float lr, float b1, float b2, float eps, float wd,
                        int decoupled, int step, const double* dyn, cudaStream_t st) {
     AdamArgs a;
     a.max_norm = max_norm; a.lr = lr; a.b1 = b1; a.b2 = b2; a.eps = eps; a.wd = wd; a.decoupled = decoupled;
     a.bc1 = 1.f - powf(b1, (float)step); a.bc2 = 1.f - powf(b2, (float)step);
     adamw_chunked_kernel<<<chunk_grid(n_chunks), 256, 0, st>>>(params, grads, m1, m2, ch_tensor, ch_off, ch_len, n_chunks,
-                                                                sqnorm, a, dyn);
+                                                                tensor_sq, tensor_bad, tensor_skip, n_tensors, sqnorm_out,
+                                                                a, dyn);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

@@ -186,23 +186,38 @@ def gn_bwd(dy, x, gamma, beta, stats, dx_add, groups, silu):
 
 
 def attn_fwd(qkv):
+    """-> (out, saved): saved is what attn_bwd needs besides qkv — ("fused", out, lse2 [B, T] fp32) on the fused tcgen05
+    kernel (bf16, C % 64 == 0, T <= 256: the probabilities are recomputed in the backward), else ("probs", [B, T, T])"""
     b, h, w, c3 = qkv.shape
     c, t = c3 // 3, h * w
     out = torch.empty((b, h, w, c), dtype=qkv.dtype, device=qkv.device)
+    code = L.code_of(qkv.dtype)
+    if lib().mvae_attn_fused_ok(t, c, code):
+        lse2 = torch.empty((b, t), dtype=torch.float32, device=qkv.device)
+        with P.region("attn_fwd", 4.0 * b * t * t * c, (qkv.numel() + out.numel()) * 2):
+            check(lib().mvae_attn_fused_fwd(ptr(qkv), ptr(out), ptr(lse2), b, t, c, code, stream()), "attn_fused_fwd")
+        return out, ("fused", out, lse2)
+    # the tcgen05 batched-GEMM path keeps P in bf16 (pad8(T) columns), the SIMT / fp32 path in fp32
     probs = torch.empty((b, t, t), dtype=torch.float32, device=qkv.device)
     with P.region("attn_fwd", 4.0 * b * t * t * c, 0.0):
-        check(lib().mvae_attn_core_fwd(ptr(qkv), ptr(out), ptr(probs), b, t, c, L.code_of(qkv.dtype), stream()),
-              "attn_core_fwd")
-    return out, probs
+        check(lib().mvae_attn_core_fwd(ptr(qkv), ptr(out), ptr(probs), b, t, c, code, stream()), "attn_core_fwd")
+    return out, ("probs", probs)
 
 
-def attn_bwd(qkv, probs, dout):
+def attn_bwd(qkv, saved, dout):
     b, h, w, c3 = qkv.shape
     c, t = c3 // 3, h * w
     dqkv = torch.empty_like(qkv)
+    if saved[0] == "fused":
+        _tag, out, lse2 = saved
+        rowdot = scratch("attn_rowdot", 4 * b * t, qkv.device)
+        with P.region("attn_bwd", 10.0 * b * t * t * c, (2 * qkv.numel() + 2 * dout.numel()) * 2):
+            check(lib().mvae_attn_fused_bwd(ptr(qkv), ptr(out), ptr(lse2), ptr(dout), ptr(dqkv), ptr(rowdot), b, t, c,
+                                            L.code_of(qkv.dtype), stream()), "attn_fused_bwd")
+        return dqkv
     ds = scratch("attn_ds", 4 * b * t * t, qkv.device)
     with P.region("attn_bwd", 8.0 * b * t * t * c, 0.0):
-        check(lib().mvae_attn_core_bwd(ptr(qkv), ptr(probs), ptr(dout), ptr(dqkv), ptr(ds), b, t, c,
+        check(lib().mvae_attn_core_bwd(ptr(qkv), ptr(saved[1]), ptr(dout), ptr(dqkv), ptr(ds), b, t, c,
                                        L.code_of(qkv.dtype), stream()), "attn_core_bwd")
     return dqkv
 

@@ -4,8 +4,10 @@ Replaces, for the hot path, what the reference's Lightning module does around ``
 (src/lightning_module.py:390-477): per-parameter NaN/Inf gradient zeroing
 (``on_before_optimizer_step``), global-norm clipping (``configure_gradient_clipping``,
 gradient_clip_val 1.0 by default) and ``torch.optim.Adam`` / ``AdamW`` (``configure_optimizers``).
-Two kernel launches per step (sum of squares of the finite gradient entries; clip + Adam update),
-no host synchronisation.  The arithmetic follows torch.optim.Adam/AdamW (single-tensor path):
+Two kernel launches per step (per-tensor sums of squares + non-finite flags; clip + Adam update), no host
+synchronisation.  Per-tensor semantics follow the reference: a parameter whose gradient holds ANY NaN / Inf has its whole
+gradient treated as zero before the norm is taken (``param.grad.zero_()``, :468-477), and a parameter that produced no
+gradient in the step (``skip``: torch.optim skips ``p.grad is None``) is left untouched — no weight decay, no moments.  The arithmetic follows torch.optim.Adam/AdamW (single-tensor path):
 bias corrections 1-beta^t, denom = sqrt(v)/sqrt(bc2) + eps, step size lr/bc1; AdamW decays the
 parameter by (1 - lr*wd) first, Adam adds wd*p to the gradient.
 """
@@ -46,6 +48,7 @@ class FusedAdamW:
         self.exp_avg = [torch.zeros_like(p) for p in self.params]
         self.exp_avg_sq = [torch.zeros_like(p) for p in self.params]
         self._sqnorm = torch.zeros((), dtype=torch.float64, device=dev)
+        self._skip_key, self._skip_dev = None, None
         self._tables = None   # (grad data_ptrs tuple) -> device pointer tables
         self._dev = dev
         # step_state: device-resident {step, lr, Philox position} (train.TrainStep in CUDA-graph mode): when set, the
@@ -90,6 +93,10 @@ class FusedAdamW:
                 "cl": torch.tensor(cl, dtype=torch.int32).to(self._dev),
                 "chunks": len(ct),
             })
+            # per-tensor pass-1 results, zeroed every step by ONE fill: [n] fp64 sums of squares | [n] int32 flags
+            n = len(plist)
+            st = torch.zeros(n * 12, dtype=torch.uint8, device=self._dev)
+            self._tables.update({"state": st, "tsq": st[:n * 8].view(torch.float64), "tbad": st[n * 8:].view(torch.int32)})
         return self._tables
 
     def _state_for(self, p):
@@ -108,11 +115,14 @@ class FusedAdamW:
                     p.grad.zero_()
 
     def grad_norm(self) -> torch.Tensor:
-        """global L2 norm (fp64, 0-d device tensor) of the finite gradient entries seen by the last step()."""
+        """global L2 norm (fp64, 0-d device tensor) of the gradients that took part in the last step() (poisoned and
+        skipped tensors excluded)."""
         return self._sqnorm.sqrt()
 
     @torch.no_grad()
-    def step(self, lr: Optional[float] = None):
+    def step(self, lr: Optional[float] = None, skip=None):
+        """skip: iterable of parameters that produced no gradient in this step (their ``.grad`` is a zero view of a
+        flat buffer rather than None): they are left untouched, as torch.optim leaves ``p.grad is None``"""
         L.require_device()
         plist = [p for p in self.params if p.grad is not None]
         if not plist:
@@ -126,24 +136,30 @@ class FusedAdamW:
             grads.append(g)
         t = self._ensure_tables(plist, grads)
         self.step_count += 1
-        self._sqnorm.zero_()
+        skip_ids = frozenset(id(p) for p in skip) if skip else frozenset()
+        if skip_ids != self._skip_key or (self._skip_dev is not None and self._skip_dev.numel() != len(plist)):
+            self._skip_key = skip_ids
+            self._skip_dev = (torch.tensor([int(id(p) in skip_ids) for p in plist], dtype=torch.int32).to(self._dev)
+                              if skip_ids else None)
+        t["state"].zero_()
         from . import profile as P
         nel = sum(p.numel() for p in plist)
-        # 28 B / parameter: sqnorm reads g (4); the update reads p, g, m, v (16) and writes p, m, v (12) — minus the 4 above
+        # 32 B / parameter: pass 1 reads g (4); the update reads p, g, m, v (16) and writes p, m, v (12)
         with P.region("adamw", 0.0, 32.0 * nel):
             self._launch(t, lr)
+        # parameters changed in place behind autograd's back: bump versions so the packed bf16 operand caches
+        # (blocks.ConvOp.packed) are refreshed on the next forward
         torch._C._increment_version(plist)
 
     def _launch(self, t, lr):
         check(lib().mvae_grad_sqnorm_chunked(ptr(t["g"]), ptr(t["ct"]), ptr(t["co"]), ptr(t["cl"]), t["chunks"],
-                                             ptr(self._sqnorm), stream()), "grad_sqnorm")
+                                             ptr(t["tsq"]), ptr(t["tbad"]), stream()), "grad_sqnorm")
         check(lib().mvae_adamw_clip_step_chunked(ptr(t["p"]), ptr(t["g"]), ptr(t["m"]), ptr(t["v"]), ptr(t["ct"]),
-                                                 ptr(t["co"]), ptr(t["cl"]), t["chunks"], ptr(self._sqnorm),
+                                                 ptr(t["co"]), ptr(t["cl"]), t["chunks"], ptr(t["tsq"]), ptr(t["tbad"]),
+                                                 ptr(self._skip_dev), t["count"], ptr(self._sqnorm),
                                                  self.max_norm, float(self.lr if lr is None else lr), self.betas[0],
                                                  self.betas[1], self.eps, self.weight_decay, int(self.decoupled),
                                                  self.step_count, ptr(self.step_state), stream()), "adamw_clip_step")
-        # (step() bumps the parameter versions afterwards: they changed in place behind autograd's back, and the packed
-        # bf16 operand caches (blocks.ConvOp.packed) are refreshed on the next forward)
 
     def state_dict(self):
         return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,

@@ -70,6 +70,7 @@ class GradBuckets:
         if count:
             self.bounds.append([start, off]); self.members.append(count)
         self._pending = list(self.members)
+        self._touched = set()
         self._works: list = []
         self._add_dst, self._add_src, self._add_par = [], [], []
         self.reduce_enabled = True
@@ -81,6 +82,12 @@ class GradBuckets:
     def zero(self):
         self.flat.zero_()
         self._pending = list(self.members)
+        self._touched = set()
+
+    def untouched(self):
+        """parameters no gradient was produced for since zero() (unused parameters: modality_embedding, FiLM / inject
+        layers, projectors of absent modalities): their .grad is a zero view, where autograd would leave None"""
+        return [p for p in self.params if id(p) not in self._touched]
 
     def begin_round(self):
         if self._add_par:
@@ -118,6 +125,7 @@ class GradBuckets:
         b = self.bucket_of.get(id(p))
         if b is None:
             return
+        self._touched.add(id(p))
         self._pending[b] -= 1
         if self._pending[b] == 0 and self.reduce_enabled and self.world > 1:
             self._launch(b)
@@ -405,7 +413,8 @@ class TrainStep:
                 if stack is not None and hasattr(stack, "_rng_sample_base"):
                     stack._rng_sample_base = 0
         self.buckets.finish()
-        self.optimizer.step()
+        # torch.optim leaves a parameter without a gradient alone (no weight decay, no moment update)
+        self.optimizer.step(skip=self.buckets.untouched())
         return totals
 
     @torch.no_grad()

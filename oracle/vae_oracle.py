@@ -376,9 +376,9 @@ class ReferenceTrainer:
             ld = vae_loss(out["reconstruction"], x, out["mean"], out["logvar"], **self.loss_kwargs)
         self.opt.zero_grad(set_to_none=True)
         ld["loss"].backward()
-        for p in self.params.values():
-            if p.grad is not None:
-                torch.nan_to_num_(p.grad, nan=0.0, posinf=0.0, neginf=0.0)
+        for p in self.params.values():      # :468-477 — ANY NaN / Inf zeroes the parameter's WHOLE gradient
+            if p.grad is not None and not bool(torch.isfinite(p.grad).all()):
+                p.grad.zero_()
         t0 = time.perf_counter()
         if self.max_norm and self.max_norm > 0:
             torch.nn.utils.clip_grad_norm_(list(self.params.values()), self.max_norm)

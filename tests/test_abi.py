@@ -30,7 +30,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in medvae_b200.h but not exported"
     assert set(L.SIGNATURES) == set(syms), set(L.SIGNATURES) ^ set(syms)
-    assert lib.mvae_abi_version() == 4
+    assert lib.mvae_abi_version() == 5
 
 
 @pytest.mark.parametrize("h,mode,k,expect", [(28, 0, 3, 28), (28, 1, 3, 14), (14, 1, 3, 7), (7, 1, 3, 3),

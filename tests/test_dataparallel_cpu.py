@@ -116,7 +116,7 @@ def test_train_step_addresses_the_noise_by_global_sample_index(monkeypatch):
         def __init__(self, params, **kw):
             self.params, self.step_state, self.lr, self.step_count = list(params), None, kw.get("lr"), 0
 
-        def step(self):
+        def step(self, skip=None):
             self.step_count += 1
 
     monkeypatch.setattr(optim, "FusedAdamW", NoOptimizer)

@@ -158,8 +158,20 @@ def test_groupnorm_silu(shape, dtype, silu):
                                    # tcgen05 path in bf16 (C % 64 == 0): ragged T = 9, 49, 196 and full tiles
                                    (5, 3, 3, 64), (2, 7, 7, 64), (3, 7, 7, 512), (2, 14, 14, 256), (2, 16, 16, 128),
                                    (2, 16, 16, 512), (3, 8, 8, 1024), (1, 12, 20, 192)])
-@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_attention_core(shape, dtype):
+@pytest.mark.parametrize("dtype,path", [(torch.float32, "simt"), (torch.bfloat16, "fused"), (torch.bfloat16, "bgemm")],
+                         ids=["fp32", "bf16-fused", "bf16-bgemm"])
+def test_attention_core(shape, dtype, path):
+    """bf16: the fused persistent tcgen05 kernel (one launch per direction, probabilities recomputed in the backward) and,
+    with debug knob 11 set, the batched-GEMM path it replaced (P kept as [B][T][T]); fp32: the SIMT verification path"""
+    L, ops = _mods()
+    L.lib().mvae_set_debug(11, 1 if path == "bgemm" else 0)
+    try:
+        _attention_case(shape, dtype, path)
+    finally:
+        L.lib().mvae_set_debug(11, 0)
+
+
+def _attention_case(shape, dtype, path):
     L, ops = _mods()
     B, H, W, C = shape
     T = H * W
@@ -177,8 +189,14 @@ def test_attention_core(shape, dtype):
     o_ref.backward(do)
     qg = qkv.detach().float().reshape(B, H, W, 3 * C).to(DEV, dtype)
     o, probs = ops.attn_fwd(qg)
+    if dtype == torch.bfloat16 and C % 64 == 0 and T <= 256:
+        assert probs[0] == ("fused" if path == "fused" else "probs")
     dq = ops.attn_bwd(qg, probs, do.float().reshape(B, H, W, C).to(DEV, dtype))
     torch.cuda.synchronize()
+    if probs[0] == "fused":
+        # the saved statistic: log2-domain log-sum-exp of the scaled scores
+        lse_ref = torch.logsumexp((q @ k.transpose(1, 2) * (C ** -0.5)).detach(), dim=2) / math.log(2.0)
+        assert float((probs[2].double().cpu() - lse_ref).abs().max()) < 2e-2
     tol = TOL[dtype]
     assert rel_err(o.reshape(B, T, C).double().cpu(), o_ref.detach()) < tol
     assert rel_err(dq.reshape(B, T, 3 * C).double().cpu(), qkv.grad) < 2 * tol
@@ -521,9 +539,9 @@ def test_disentangled_heads(dtype, idx, xc):
 
 @pytest.mark.parametrize("decoupled", [True, False])
 def test_fused_adamw_matches_torch(decoupled):
-    """grad_sqnorm + adamw_clip_step (chunk table, 16-byte path and scalar tails, NaN/Inf guard, global-norm
-    clip) against torch.optim.AdamW / Adam preceded by the reference's NaN zeroing and clip_grad_norm_
-    (src/lightning_module.py:390-477), three steps."""
+    """grad_sqnorm + adamw_clip_step (chunk table, 16-byte path and scalar tails, per-tensor NaN/Inf guard, skipped
+    parameter, global-norm clip) against torch.optim.AdamW / Adam preceded by the reference's whole-tensor NaN zeroing and
+    clip_grad_norm_ (src/lightning_module.py:390-477), three steps."""
     from medvae_disentangled_multimodal_b200.optim import FusedAdamW
     g = torch.Generator().manual_seed(12)
     shapes = [(70001,), (3,), (128, 9), (1 << 17,), (5, 7, 3)]
@@ -535,12 +553,21 @@ def test_fused_adamw_matches_torch(decoupled):
     for step in range(3):
         grads = [torch.randn(s, generator=g) * (3.0 if step == 0 else 0.01) for s in shapes]
         grads[0][5] = float("nan"); grads[3][77] = float("inf")
-        for p, d, gr in zip(ref_p, dev_p, grads):
-            p.grad = torch.nan_to_num(gr.clone(), nan=0.0, posinf=0.0, neginf=0.0)
+        for i, (p, d, gr) in enumerate(zip(ref_p, dev_p, grads)):
+            # on_before_optimizer_step (src/lightning_module.py:468-477): ANY NaN / Inf zeroes the WHOLE gradient tensor
+            p.grad = gr.clone() if bool(torch.isfinite(gr).all()) else torch.zeros_like(gr)
             d.grad = gr.clone().to(DEV)
+            if i == 4:          # a parameter that produced no gradient: torch.optim skips it (.grad is None)
+                p.grad = None
+                d.grad = torch.zeros_like(d)
         torch.nn.utils.clip_grad_norm_(ref_p, 1.0)
         ref_opt.step()
-        opt.step()
+        opt.step(skip=[dev_p[4]])
+        ref_norm = torch.sqrt(sum((q.grad.double() ** 2).sum() for q in ref_p if q.grad is not None))
+        # (clip_grad_norm_ scaled the reference gradients in place: compare the clip factor instead)
+        clip = min(1.0, 1.0 / (float(opt.grad_norm()) + 1e-6))
+        assert abs(float(ref_norm) - clip * float(opt.grad_norm())) <= 1e-5 * max(1.0, float(ref_norm))
     torch.cuda.synchronize()
     for p, d in zip(ref_p, dev_p):
         assert rel_err(d, p) < 2e-6
+    assert torch.equal(dev_p[4].detach().cpu(), ref_p[4].detach())      # untouched: no weight decay either
