@@ -374,6 +374,11 @@ def gpu_baseline_leg(wl: str, dev, steps: int = 4, warmup: int = 3, batch: int =
         except torch.OutOfMemoryError as e:
             out["variants"][name] = {"error": "out of memory: " + str(e).splitlines()[0]}
             torch.cuda.empty_cache()
+        except RuntimeError as e:
+            # e.g. the reference's DisentangledConditionalVAE calls z.view(B, -1) (disentangled_conditional_vae.py:199),
+            # which a channels_last latent does not support: that layout is simply not runnable for it
+            out["variants"][name] = {"error": "the reference fails in this layout: " + str(e).splitlines()[0][:160]}
+            torch.cuda.empty_cache()
     out["clocks"] = sampler.stop()
     good = {k: v for k, v in out["variants"].items() if "value" in v}
     if good:

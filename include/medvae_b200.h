@@ -335,12 +335,14 @@ int mvae_linattn_core_bwd(const void* qkv, const float* ks, const float* ctx, co
                           void* stream);
 
 /* nn.Dropout inside ResnetBlock (src/models/encoder_decoder.py:164): y = x * keep / (1-p) over n elements,
- * keep from Philox4x32-10 (seed, offset, element) or, if mask_in != NULL, from that byte mask
- * (verification hook).  mask_out (may be NULL) receives the mask used.  The backward is the same call
- * on the incoming gradient with the same (seed, offset) or mask. */
+ * keep from Philox4x32-10 (seed, offset, elem_base + element) or, if mask_in != NULL, from that byte mask
+ * (verification hook).  elem_base = index of the first element in the GLOBAL batch (first sample x elements per
+ * sample): a sample's mask then does not depend on the rank count or the micro-batch split.  mask_out (may be
+ * NULL) receives the mask used.  The backward is the same call on the incoming gradient with the same
+ * (seed, offset, elem_base) or mask. */
 int mvae_dropout_apply(const void* x, void* y, int64_t n, float p, uint64_t seed, uint64_t offset,
-                       const double* step_state, const uint8_t* mask_in, uint8_t* mask_out, int32_t dtype,
-                       void* stream);
+                       uint64_t elem_base, const double* step_state, const uint8_t* mask_in,
+                       uint8_t* mask_out, int32_t dtype, void* stream);
 
 /* FiLMLayer (src/models/conditional_vae.py:191-203): out = features * (Ws c + bs) + (Wt c + bt).
  * features/out: NCHW fp32 [B][C][HW]; cond: [B][K]; Ws, Wt: [C][K]; st: fp32 [2][B][C] receives the

@@ -98,7 +98,7 @@ SIGNATURES = {
     "mvae_dis_loss_total": (C.c_int, [_vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _vp, _vp, _vp]),
     "mvae_linattn_core_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "mvae_linattn_core_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
-    "mvae_dropout_apply": (C.c_int, [_vp, _vp, _i64, _f32, _u64, _u64, _vp, _vp, _vp, _i32, _vp]),
+    "mvae_dropout_apply": (C.c_int, [_vp, _vp, _i64, _f32, _u64, _u64, _u64, _vp, _vp, _vp, _i32, _vp]),
     "mvae_film_fwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "mvae_film_bwd": (C.c_int, [_vp] * 13 + [_i32, _i32, _i32, _i32, _vp]),
     "mvae_batch_feed_u8": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),

@@ -132,6 +132,7 @@ class Run:
         self.tape: list = []
         self.dropout_seed = 0          # set by _StackFn from the owning stack
         self.dropout_offset = 0
+        self.sample_base = 0           # first sample of this forward in the global batch (Philox element counter)
         self.dropout_masks = None      # verification hook: {id(ResnetBlock): uint8 NHWC keep mask}
         self.step_state = None         # device-side stream position (TrainStep graph mode)
         self.taps = None               # verification hook: {reference module path: NHWC activation} (stack.tap_sink)
@@ -345,8 +346,9 @@ class ResOp:
         if self.p_drop > 0.0 and run.training:
             # nn.Dropout between swish(norm2(h)) and conv2 (encoder_decoder.py:164): Philox keep mask, regenerated
             # in the backward from (seed, offset); a2 below is the dropped tensor conv2 consumes
-            drop = run.next_dropout(blk)
-            a2, _ = ops.dropout_apply(a2, self.p_drop, drop[0], drop[1], mask_in=drop[2], step_state=run.step_state)
+            drop = run.next_dropout(blk) + (run.sample_base * (a2.numel() // a2.shape[0]),)
+            a2, _ = ops.dropout_apply(a2, self.p_drop, drop[0], drop[1], mask_in=drop[2], step_state=run.step_state,
+                                      elem_base=drop[3])
         xs = self.nin.fwd(run, x)[0] if self.nin is not None else x
         out, out_sums = self.c2.fwd(run, a2, residual=xs, gn_groups=self.out_groups)
         run.tape.append((self, (x, st1, a1, h1, st2, a2, drop)))
@@ -359,7 +361,8 @@ class ResOp:
         if drop is not None:
             # the dropout sits between conv2's dgrad and the GroupNorm backward: no fused epilogue here
             d_a2, _ = self.c2.bwd(run, a2, dout, dy_colsum=dout_cs)
-            d_a2, _ = ops.dropout_apply(d_a2, self.p_drop, drop[0], drop[1], mask_in=drop[2], step_state=run.step_state)
+            d_a2, _ = ops.dropout_apply(d_a2, self.p_drop, drop[0], drop[1], mask_in=drop[2], step_state=run.step_state,
+                                        elem_base=drop[3])
             s12 = None
         else:
             d_a2, s12 = self.c2.bwd(run, a2, dout, dy_colsum=dout_cs, gn=(h1, st2, blk.norm2, True))
@@ -546,11 +549,13 @@ class _StackFn(torch.autograd.Function):
         if stack.training:
             stack._dropout_step += 1
             seed = stack.dropout_seed if stack.dropout_seed is not None else torch.initial_seed()
-            # one Philox stream per (stack, forward call); sites within the call take consecutive offsets
+            # one Philox stream per (stack, optimizer step); sites within the call take consecutive offsets, and the
+            # element counter is the element's index in the GLOBAL batch (sample_base): data-parallel ranks and
+            # micro-batches draw different masks, and a sample's mask does not depend on the split (train.TrainStep
+            # holds _dropout_step fixed over the micro-batches of a step)
             run.dropout_seed = (seed + 0x9E3779B97F4A7C15 * (2 if type(stack).__name__ == "Decoder" else 1)) & 0xFFFFFFFFFFFFFFFF
-            # ... and per position of the forward's first sample in the global batch (bits 40+), so data-parallel
-            # ranks and micro-batches keep different masks
-            run.dropout_offset = (stack._dropout_step << 16) + (int(stack._rng_sample_base) << 40)
+            run.dropout_offset = stack._dropout_step << 16
+            run.sample_base = int(stack._rng_sample_base)
             run.step_state = stack._step_state
             if stack.dropout_mask_override:
                 run.dropout_masks = {id(k): v for k, v in stack.dropout_mask_override.items()}

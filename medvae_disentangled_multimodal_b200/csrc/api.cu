@@ -96,7 +96,8 @@ int attn_fused_bwd(const bf16* qkv, const bf16* out, const float* lse2, const bf
 int linattn_fwd(const void* qkv, void* out, float* ks, float* ctx, int B, int Tn, int C, int dtype, cudaStream_t st);
 int linattn_bwd(const void* qkv, const float* ks, const float* ctx, const void* dout, void* dqkv, float* dctx, float* dks,
                 int B, int Tn, int C, int dtype, cudaStream_t st);
-int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, const double* dyn,
+int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, uint64_t elem_base,
+                  const double* dyn,
                   const uint8_t* mask_in, uint8_t* mask_out, int dtype, cudaStream_t st);
 int film_fwd(const float* f, const float* cond, const float* ws, const float* bs, const float* wt, const float* bt, float* out,
              float* st, int B, int C, int HW, int K, cudaStream_t s);
@@ -547,11 +548,11 @@ int mvae_linattn_core_bwd(const void* qkv, const float* ks, const float* ctx, co
     MVAE_CHECK(qkv && ks && ctx && dout && dqkv && dctx && dks && dtype_ok(dtype), "linattn_core_bwd: bad argument");
     return linattn_bwd(qkv, ks, ctx, dout, dqkv, dctx, dks, batch, tokens, c, dtype, ST(stream));
 }
-int mvae_dropout_apply(const void* x, void* y, int64_t n, float p, uint64_t seed, uint64_t offset, const double* step_state,
-                       const uint8_t* mask_in, uint8_t* mask_out, int32_t dtype, void* stream) {
+int mvae_dropout_apply(const void* x, void* y, int64_t n, float p, uint64_t seed, uint64_t offset, uint64_t elem_base,
+                       const double* step_state, const uint8_t* mask_in, uint8_t* mask_out, int32_t dtype, void* stream) {
     MVAE_CHECK(x && y && n > 0 && dtype_ok(dtype), "dropout_apply: bad argument");
     MVAE_CHECK(p >= 0.f && p < 1.f, "dropout_apply: p must be in [0, 1), got %f", (double)p);
-    return dropout_apply(x, y, n, p, seed, offset, step_state, mask_in, mask_out, dtype, ST(stream));
+    return dropout_apply(x, y, n, p, seed, offset, elem_base, step_state, mask_in, mask_out, dtype, ST(stream));
 }
 int mvae_step_state_advance(double* step_state, double rng_increment, void* stream) {
     MVAE_CHECK(step_state && rng_increment >= 0.0, "step_state_advance: bad argument");

@@ -60,41 +60,54 @@ int batch_feed_u8(const uint8_t* src, const int* src_c, const int* tgt_c, const 
 }
 
 // ------------------------------------------------------------------ dropout
-// y[e] = x[e] * keep(e) / (1 - p); keep(e) = u(e) >= p with u from Philox(seed; counter e/4, offset), or mask_in[e].
-// The backward is the same call on dy.  4 elements per thread (one Philox block).
+// y[e] = x[e] * keep(e) / (1 - p); keep(e) = u(e) >= p with u from word (g & 3) of Philox(seed; counter g / 4, offset),
+// g = elem_base + e the element's index in the GLOBAL batch (elem_base = first sample x elements per sample: a sample's
+// mask does not depend on the rank count or the micro-batch split), or mask_in[e].  The backward is the same call on dy.
+// 4 elements per thread (one Philox block, two when elem_base is not a multiple of 4).
 template <typename T>
 __global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, float p,
-                                                      uint64_t seed, uint64_t offset, const double* __restrict__ dyn,
+                                                      uint64_t seed, uint64_t offset, uint64_t elem_base,
+                                                      const double* __restrict__ dyn,
                                                       const uint8_t* __restrict__ mask_in, uint8_t* __restrict__ mask_out) {
     if (dyn) offset += ((uint64_t)dyn[2]) << 20;   // device-side stream position (CUDA-graph replays advance it)
     const float scale = 1.f / (1.f - p);
     const Philox ph(seed);
     const long long quads = (n + 3) / 4;
+    const int shift = (int)(elem_base & 3);
     for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < quads; q += (long long)gridDim.x * blockDim.x) {
-        PhiloxWords r = {0u, 0u, 0u, 0u};
-        if (!mask_in) r = ph((uint64_t)q, offset);
-        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+        uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        if (!mask_in) {
+            const uint64_t blk = (elem_base + (uint64_t)q * 4) >> 2;
+            const PhiloxWords r = ph(blk, offset);
+            w[0] = r.x; w[1] = r.y; w[2] = r.z; w[3] = r.w;
+            if (shift) {
+                const PhiloxWords r2 = ph(blk + 1, offset);
+                w[4] = r2.x; w[5] = r2.y; w[6] = r2.z; w[7] = r2.w;
+            }
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const long long e = q * 4 + j;
             if (e >= n) break;
             bool keep;
             if (mask_in) keep = mask_in[e] != 0;
-            else keep = philox_u01_grid(w[j]) >= p;
+            else keep = philox_u01_grid(w[shift + j]) >= p;
             if (mask_out) mask_out[e] = keep ? 1 : 0;
             y[e] = keep ? from_f<T>(to_f<T>(x[e]) * scale) : from_f<T>(0.f);
         }
     }
 }
 
-int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, const double* dyn,
-                  const uint8_t* mask_in, uint8_t* mask_out, int dtype, cudaStream_t st) {
+int dropout_apply(const void* x, void* y, long long n, float p, uint64_t seed, uint64_t offset, uint64_t elem_base,
+                  const double* dyn, const uint8_t* mask_in, uint8_t* mask_out, int dtype, cudaStream_t st) {
     long long g = ((n + 3) / 4 + 255) / 256;
     const int grid = (int)(g > 148 * 16 ? 148 * 16 : (g < 1 ? 1 : g));
     if (dtype == MVAE_BF16)
-        dropout_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)x, (bf16*)y, n, p, seed, offset, dyn, mask_in, mask_out);
+        dropout_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)x, (bf16*)y, n, p, seed, offset, elem_base, dyn, mask_in,
+                                                   mask_out);
     else
-        dropout_kernel<float><<<grid, 256, 0, st>>>((const float*)x, (float*)y, n, p, seed, offset, dyn, mask_in, mask_out);
+        dropout_kernel<float><<<grid, 256, 0, st>>>((const float*)x, (float*)y, n, p, seed, offset, elem_base, dyn, mask_in,
+                                                    mask_out);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

@@ -410,12 +410,14 @@ def linattn_bwd(qkv, ks, ctx, dout):
     return dqkv
 
 
-def dropout_apply(x, p, seed, offset, mask_in=None, want_mask=False, step_state=None):
-    """-> (y, mask or None); x any contiguous bf16/fp32 tensor, mask uint8 of the same shape"""
+def dropout_apply(x, p, seed, offset, mask_in=None, want_mask=False, step_state=None, elem_base=0):
+    """-> (y, mask or None); x any contiguous bf16/fp32 tensor, mask uint8 of the same shape.  elem_base: index of x's
+    first element in the global batch (first sample * elements per sample)"""
     y = torch.empty_like(x)
     mask = torch.empty(x.shape, dtype=torch.uint8, device=x.device) if want_mask else None
     check(lib().mvae_dropout_apply(ptr(x), ptr(y), x.numel(), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF, int(offset),
-                                   ptr(step_state), ptr(mask_in), ptr(mask), L.code_of(x.dtype), stream()), "dropout_apply")
+                                   int(elem_base), ptr(step_state), ptr(mask_in), ptr(mask), L.code_of(x.dtype), stream()),
+          "dropout_apply")
     return y, mask
 
 

@@ -374,6 +374,8 @@ class TrainStep:
         # addressed by the sample's index in the global batch (equal shards) — ranks draw different noise and the
         # noise of a sample does not depend on the number of ranks or the micro-batch split
         rng0 = getattr(self.model, "_rng_step", None)
+        drop0 = {name: getattr(self.model, name)._dropout_step for name in ("decoder", "encoder")
+                 if hasattr(getattr(self.model, name, None), "_dropout_step")}
         for ci, (a, b) in enumerate(chunks):
             if rng0 is not None:
                 self.model._rng_step = rng0
@@ -382,6 +384,7 @@ class TrainStep:
                     stack = getattr(self.model, name, None)
                     if stack is not None and hasattr(stack, "_rng_sample_base"):
                         stack._rng_sample_base = self.buckets.rank * n + a
+                        stack._dropout_step = drop0[name]     # one dropout stream position per optimizer step
             last = ci == len(chunks) - 1
             self.buckets.reduce_enabled = last
             self.buckets.begin_round()

@@ -46,11 +46,15 @@ def block(seed: int, ctr_lo, ctr_hi):
                          seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
 
 
-def dropout_keep_mask(n: int, p: float, seed: int, offset: int) -> np.ndarray:
-    """keep[e] = u >= p with u = (word >> 8) * 2^-24 (exact in fp32), word j of block e // 4 of stream
-    (seed, offset): csrc/feed.cu:dropout_kernel.  Integer work + one exact float compare: bit-exact."""
-    q = np.arange((n + 3) // 4, dtype=np.uint64)
-    words = np.stack(block(seed, q, np.full_like(q, offset)), axis=1).reshape(-1)[:n]
+def dropout_keep_mask(n: int, p: float, seed: int, offset: int, elem_base: int = 0) -> np.ndarray:
+    """keep[e] = u >= p with u = (word >> 8) * 2^-24 (exact in fp32), word (g & 3) of block g // 4 of stream
+    (seed, offset), g = elem_base + e the element's index in the global batch: csrc/feed.cu:dropout_kernel.
+    Integer work + one exact float compare: bit-exact."""
+    g = np.arange(n, dtype=np.uint64) + np.uint64(elem_base)
+    q0 = int(elem_base) // 4
+    q = np.arange(q0, (int(elem_base) + n + 3) // 4 + 1, dtype=np.uint64)
+    words = np.stack(block(seed, q, np.full_like(q, offset)), axis=1).reshape(-1)
+    words = words[(g - np.uint64(4 * q0)).astype(np.int64)]
     u = (words >> np.uint32(8)).astype(np.float32) * np.float32(1.0 / 16777216.0)
     return u >= np.float32(p)
 

@@ -18,6 +18,7 @@ for stage in $STAGES; do
   case $stage in
     tests) timeout 2400 python -m pytest tests -q -m gpu --timeout 900 -rf > gpurun_out/t_gpu.log 2>&1; echo "tests rc=$?" >> gpurun_out/rc.txt;;
     tests_new) timeout 2400 python -m pytest tests/test_configs_gpu.py tests/test_appendix_b_gpu.py -q -m gpu --timeout 900 -rf -s > gpurun_out/t_new.log 2>&1; echo "tests_new rc=$?" >> gpurun_out/rc.txt;;
+    attn) timeout 900 python -m pytest tests/test_kernels_gpu.py tests/test_appendix_b_gpu.py -q -m gpu -k "attention" --timeout 300 -rf > gpurun_out/t_attn.log 2>&1; echo "attn rc=$?" >> gpurun_out/rc.txt; tail -n 25 gpurun_out/t_attn.log;;
     smoke) timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/rc.txt;;
     torchbase)
       timeout 900 python tests/gpu_torch_baseline.py --workload c4 --steps 4 --warmup 3 > gpurun_out/torch_baseline_c4.log 2>&1; echo "torchbase c4 rc=$?" >> gpurun_out/rc.txt

@@ -79,6 +79,11 @@ def main():
                               "error": f"out of memory at batch {batch}: {str(e).splitlines()[0]}"}), flush=True)
             if dev.type == "cuda":
                 torch.cuda.empty_cache()
+        except RuntimeError as e:               # the disentangled reference cannot run channels_last (z.view)
+            print(json.dumps({"impl": "reference-on-stock-torch-kernels", "variant": name,
+                              "error": f"the reference fails in this variant: {str(e).splitlines()[0][:160]}"}), flush=True)
+            if dev.type == "cuda":
+                torch.cuda.empty_cache()
 
 
 if __name__ == "__main__":

@@ -91,3 +91,43 @@ def test_train_step_with_own_noise_is_independent_of_the_micro_batch_split():
     for a, b in zip(*curves):
         assert abs(a - b) <= 2e-5 * abs(a), curves
     assert len(set(curves[0])) == 4
+
+
+def test_dropout_mask_of_a_sample_does_not_depend_on_the_split():
+    """SURVEY 8e for the dropout masks: the Philox counter is the element's index in the GLOBAL batch (elem_base), so the
+    two parts of a split batch — even one that starts on an element index that is not a multiple of 4 — draw exactly
+    the masks of the whole batch, bit for bit, and match the numpy restatement."""
+    ops = _ops()
+    B, per = 6, 7 * 5 * 3                                 # odd elements per sample: parts start inside a Philox block
+    x = torch.ones(B, 7, 5, 3, device=DEV)
+    _, whole = ops.dropout_apply(x, 0.4, 77, 9, want_mask=True)
+    _, lo = ops.dropout_apply(x[:1].contiguous(), 0.4, 77, 9, want_mask=True, elem_base=0)
+    _, hi = ops.dropout_apply(x[1:].contiguous(), 0.4, 77, 9, want_mask=True, elem_base=1 * per)
+    torch.cuda.synchronize()
+    assert torch.equal(torch.cat([lo, hi]), whole)
+    want = P.dropout_keep_mask(5 * per, 0.4, 77, 9, elem_base=per)
+    assert np.array_equal(hi.cpu().numpy().reshape(-1).astype(bool), want)
+
+
+def test_model_dropout_masks_do_not_depend_on_the_micro_batch_split():
+    """through TrainStep: the same step with the batch in one pass and in micro-batches of 3 (fp32 mode, lr 0, injected
+    reparameterisation noise) gives the same loss: every sample kept its dropout masks"""
+    import medvae_disentangled_multimodal_b200 as M
+    from medvae_disentangled_multimodal_b200.train import TrainStep
+    from oracle import vae_oracle as O
+    kw = dict(input_channels=3, latent_dim=8, hidden_channels=32, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=[8],
+              resolution=16, dropout=0.3)
+    x, onehot, _ = O.synthetic_batch(8, 3, 16, seed=5)
+    eps = torch.randn(8, 8, 8, 8, generator=torch.Generator().manual_seed(2)).to(DEV)
+    losses = []
+    for mb in (None, 3):
+        torch.manual_seed(3)
+        model = M.ConditionalVAE(compute_dtype="fp32", **kw).to(DEV)
+        model.eps_override = eps
+        model.encoder.dropout_seed = model.decoder.dropout_seed = 11
+        ts = TrainStep(model, M.VAELoss("mse", 1.0, 1.0), micro_batch=mb, lr=0.0, weight_decay=0.0)
+        losses.append([float(ts.step(x.to(DEV), onehot.to(DEV))["loss"]) for _ in range(2)])
+        ts.close()
+    assert losses[0][0] != losses[0][1]                         # the stream advances from step to step
+    for a, b in zip(*losses):
+        assert abs(a - b) <= 2e-6 * abs(a), losses
