@@ -77,6 +77,23 @@ int mvae_conv2d_pack_weights(const mvae_conv_desc* d, const float* w_oihw, void*
                              void* w_dgrad, int32_t out_c_total, int32_t out_c_offset,
                              void* stream);
 
+/* The same for ALL convs of a model in one launch (once per optimizer step).  jobs: DEVICE array of n_jobs entries
+ * ordered by tile_begin; job i owns tiles [tile_begin, tile_begin + ceil(out_c/32) * ceil(in_c/32)) of the
+ * launch's total_tiles.  A job writes rows [out_c_offset, out_c_offset + out_c) x columns [0, in_c) of packed
+ * operands whose dimensions are out_c_total x in_c_pitch (fused q,k,v; conv_in / conv_out zero-padded to one
+ * tensor-core tile: the padding is left untouched) and copies the conv's bias (NULL: zeros) to
+ * bias_dst[out_c_offset ...] when bias_dst != NULL. */
+typedef struct mvae_pack_job {
+    const float* w_oihw;      /* [out_c][in_c][ksize][ksize] fp32 */
+    void* w_fprop;            /* [n_slabs][out_c_total][in_c_pitch] or NULL */
+    void* w_dgrad;            /* [n_slabs][in_c_pitch][out_c_total] or NULL */
+    const float* bias_src;    /* [out_c] or NULL */
+    float* bias_dst;          /* [out_c_total] or NULL */
+    int32_t out_c, in_c, ksize, mode, n_slabs, out_c_total, out_c_offset, in_c_pitch, tile_begin, reserved;
+} mvae_pack_job;
+int mvae_conv2d_pack_weights_batched(const mvae_pack_job* jobs_dev, int32_t n_jobs, int32_t total_tiles,
+                                     int32_t dtype, void* stream);
+
 /* y = conv(x) + bias (+ residual).  Replaces nn.Conv2d.forward at encoder_decoder.py:152,162,
  * 168 (ResnetBlock), :86-88,:105 (AttnBlock 1x1), :187, :208, :308,:327,:426,:450.
  * `residual` (same shape as y, may be NULL) fuses the `x + h` of :170 / :107. */

@@ -45,6 +45,7 @@ SIGNATURES = {
     "mvae_conv2d_num_slabs": (C.c_int, [_dp]),
     "mvae_conv2d_uses_umma": (C.c_int, [_dp]),
     "mvae_conv2d_pack_weights": (C.c_int, [_dp, _vp, _vp, _vp, _i32, _i32, _vp]),
+    "mvae_conv2d_pack_weights_batched": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
     "mvae_conv2d_fprop": (C.c_int, [_dp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "mvae_conv2d_dgrad": (C.c_int, [_dp, _vp, _vp, _vp, _vp]),
     "mvae_conv2d_wgrad_workspace_bytes": (_sz, [_dp]),

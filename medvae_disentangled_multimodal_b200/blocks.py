@@ -14,6 +14,7 @@ from __future__ import annotations
 import os
 from typing import Dict, List, Optional, Sequence, Tuple
 
+import numpy as np
 import torch
 import torch.nn as nn
 
@@ -163,6 +164,57 @@ class Run:
             self.grads[p] = g
 
 
+# include/medvae_b200.h: mvae_pack_job (80 bytes)
+_PACK_JOB = np.dtype([("w", "<u8"), ("wf", "<u8"), ("wd", "<u8"), ("bsrc", "<u8"), ("bdst", "<u8"), ("out_c", "<i4"),
+                      ("in_c", "<i4"), ("ksize", "<i4"), ("mode", "<i4"), ("n_slabs", "<i4"), ("ctot", "<i4"),
+                      ("coff", "<i4"), ("cinp", "<i4"), ("tile_begin", "<i4"), ("reserved", "<i4")])
+_pack_tables: dict = {}
+
+
+def pack_entries(entries, device):
+    """(re)pack the operands of these cache entries with ONE launch and mark them current"""
+    if not entries:
+        return
+    code = entries[0]["code"]
+    key = (tuple(id(e) for e in entries), tuple(c.weight.data_ptr() for e in entries for c, _ in e["jobs"]), str(device))
+    tab = _pack_tables.get(key)
+    if tab is None:
+        rows, tile = [], 0
+        for e in entries:
+            assert e["code"] == code
+            op = e["op"]
+            for conv, off in e["jobs"]:
+                cout, cin = conv.out_channels, conv.in_channels
+                rows.append((conv.weight.data_ptr(), e["wf"].data_ptr(), e["wd"].data_ptr(),
+                             conv.bias.data_ptr() if conv.bias is not None else 0,
+                             e["bias"].data_ptr() if e["own_bias"] else 0, cout, cin, op.k, op.mode, e["nslabs"], e["ctot"],
+                             off, e["cinp"], tile, 0))
+                tile += -(-cout // 32) * -(-cin // 32)
+        table = torch.from_numpy(np.array(rows, dtype=_PACK_JOB).view(np.uint8).copy()).to(device)
+        tab = (table, len(rows), tile)
+        if len(entries) > 1:          # the whole-model table of the per-step refresh is reused every step
+            _pack_tables.clear()
+            _pack_tables[key] = tab
+    ops.conv_pack_weights_batched(tab[0], tab[1], tab[2], code)
+    for e in entries:
+        e["ver"] = e["op"]._versions()
+
+
+def refresh_packed(stacks):
+    """one launch re-packing every conv operand of these stacks whose master weights changed (after the optimizer step)"""
+    stale, dev = [], None
+    for st in stacks:
+        for e in st._pack_cache.values():
+            if e["ver"] != e["op"]._versions():
+                stale.append(e)
+                dev = e["dev"]
+    by_code = {}
+    for e in stale:
+        by_code.setdefault(e["code"], []).append(e)
+    for es in by_code.values():
+        pack_entries(es, dev)
+
+
 PAD_C = 64   # skinny convs are zero-padded to one tcgen05 K / N tile in bf16 mode
 
 
@@ -206,37 +258,38 @@ class ConvOp:
             out += [c.weight] + ([c.bias] if c.bias is not None else [])
         return out
 
+    def _versions(self):
+        return tuple((c.weight._version, c.bias._version if c.bias is not None else 0) for c in self.convs)
+
     def packed(self, run: Run, device):
+        """-> cache entry {"wf", "wd", "bias"}: the packed bf16 / fp32 operands of this conv (group), refreshed when the
+        master weights changed.  train.TrainStep refreshes ALL entries of a model with one launch right after the
+        optimizer step (refresh_packed); this per-conv path serves the first use and externally modified weights."""
         key = (tuple(id(c.weight) for c in self.convs), run.code, self.mode)
-        ver = tuple((c.weight._version, c.bias._version if c.bias is not None else 0) for c in self.convs)
         ent = run.cache.get(key)
-        if ent is None or ent["ver"] != ver or ent["dev"] != device:
+        if ent is None or ent["dev"] != device:
             cin_p, cout_p = self.cin_of(run.dtype), self.cout_of(run.dtype)
             d1 = ops.conv_desc(1, 8, 8, cin_p, cout_p, self.k, self.mode, run.code)
             nslabs = ops.conv_num_slabs(d1)
-            wf = torch.empty((nslabs, cout_p, cin_p), dtype=run.dtype, device=device)
-            wd = torch.empty((nslabs, cin_p, cout_p), dtype=run.dtype, device=device)
-            if cin_p != self.cin or cout_p != self.cout:
-                c = self.convs[0]
-                wpad = torch.zeros((cout_p, cin_p, self.k, self.k), dtype=torch.float32, device=device)
-                wpad[:self.cout, :self.cin] = c.weight.detach()
-                ops.conv_pack_weights(d1, wpad, wf, wd, cout_p, 0)
-                bias = torch.zeros((cout_p,), dtype=torch.float32, device=device)
-                bias[:self.cout] = c.bias.detach()
+            padded = cin_p != self.cin or cout_p != self.cout
+            alloc = torch.zeros if padded else torch.empty      # the tile padding of a skinny conv stays zero
+            wf = alloc((nslabs, cout_p, cin_p), dtype=run.dtype, device=device)
+            wd = alloc((nslabs, cin_p, cout_p), dtype=run.dtype, device=device)
+            single = len(self.convs) == 1 and not padded and self.convs[0].bias is not None
+            if single:
+                bias, own_bias = self.convs[0].bias.detach(), False       # the parameter itself: always current
             else:
-                off = 0
-                for c in self.convs:
-                    dd = ops.conv_desc(1, 8, 8, self.cin, c.out_channels, self.k, self.mode, run.code)
-                    ops.conv_pack_weights(dd, c.weight.detach(), wf, wd, self.cout, off)
-                    off += c.out_channels
-                if len(self.convs) == 1 and self.convs[0].bias is None:
-                    bias = torch.zeros((self.cout,), dtype=torch.float32, device=device)   # Conv2d(bias=False)
-                elif len(self.convs) == 1:
-                    bias = self.convs[0].bias.detach()
-                else:
-                    bias = torch.cat([c.bias.detach() for c in self.convs]).contiguous()
-            ent = {"ver": ver, "dev": device, "wf": wf, "wd": wd, "bias": bias}
+                bias, own_bias = torch.zeros((cout_p,), dtype=torch.float32, device=device), True
+            jobs, off = [], 0
+            for c in self.convs:
+                jobs.append((c, off))
+                off += c.out_channels
+            ent = {"ver": None, "dev": device, "wf": wf, "wd": wd, "bias": bias, "own_bias": own_bias, "jobs": jobs,
+                   "op": self, "nslabs": nslabs, "ctot": cout_p, "cinp": cin_p, "code": run.code}
             run.cache[key] = ent
+        ver = self._versions()
+        if ent["ver"] != ver:
+            pack_entries([ent], device)
         return ent
 
     def fwd(self, run: Run, x: torch.Tensor, residual: Optional[torch.Tensor] = None, gn_groups: int = 0):

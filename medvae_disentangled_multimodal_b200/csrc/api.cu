@@ -22,6 +22,7 @@ int debug_knob(int key) { return (key >= 0 && key < 16) ? g_knobs[key] : 0; }
 
 // implemented in the other translation units
 int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot, int co_off, int dtype, cudaStream_t st);
+int pack_weights_batched(const mvae_pack_job* jobs_dev, int n_jobs, int total_tiles, int dtype, cudaStream_t st);
 int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int splits, float beta, cudaStream_t st);
 int colsum_parts(long long M);
 int colsum(const void* dy, float* db, float* scratch, long long M, int C, int dtype, float beta, cudaStream_t st);
@@ -179,6 +180,12 @@ int mvae_conv2d_pack_weights(const mvae_conv_desc* d, const float* w, void* wf, 
     MVAE_CHECK(w && (wf || wd), "pack_weights: null pointer");
     MVAE_CHECK(out_c_offset >= 0 && out_c_offset + g.Cout <= out_c_total, "pack_weights: bad channel window");
     return pack_weights(g, w, wf, wd, out_c_total, out_c_offset, d->dtype, ST(stream));
+}
+
+int mvae_conv2d_pack_weights_batched(const mvae_pack_job* jobs_dev, int32_t n_jobs, int32_t total_tiles, int32_t dtype,
+                                     void* stream) {
+    MVAE_CHECK(jobs_dev && n_jobs > 0 && total_tiles > 0 && dtype_ok(dtype), "pack_weights_batched: bad argument");
+    return pack_weights_batched(jobs_dev, n_jobs, total_tiles, dtype, ST(stream));
 }
 
 int mvae_conv2d_fprop(const mvae_conv_desc* d, const void* x, const void* wf, const float* bias, const void* residual,

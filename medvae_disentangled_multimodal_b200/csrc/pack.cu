@@ -77,6 +77,74 @@ int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot
     return 0;
 }
 
+// ---- all convs of a model in ONE launch (once per optimizer step): a device table of jobs, each job owning a contiguous
+// range of the launch's 32 x 32 tiles; a job may write into a window of a wider / zero-padded packed operand (q,k,v fused
+// along Cout; conv_in / conv_out padded to one tensor-core tile: cin_pitch / ctot are the operand's dimensions) and also
+// refreshes the fp32 bias vector the conv kernels read.
+template <typename T>
+__global__ void __launch_bounds__(256) pack_weights_batched_kernel(const mvae_pack_job* __restrict__ jobs, int n_jobs,
+                                                                   int total_tiles) {
+    __shared__ float s[PK_T][PK_PITCH];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
+        int lo = 0, hi = n_jobs - 1;
+        while (lo < hi) {                       // last job whose first tile is <= gt
+            const int mid = (lo + hi + 1) >> 1;
+            if (jobs[mid].tile_begin <= gt) lo = mid; else hi = mid - 1;
+        }
+        const mvae_pack_job j = jobs[lo];
+        const int tile = gt - j.tile_begin;
+        const int Cout = j.out_c, Cin = j.in_c, RR = j.ksize * j.ksize, Ctot = j.out_c_total, co_off = j.out_c_offset;
+        const int CinP = j.in_c_pitch;
+        const float* w = j.w_oihw;
+        T* wf = reinterpret_cast<T*>(j.w_fprop);
+        T* wd = reinterpret_cast<T*>(j.w_dgrad);
+        if (tile == 0 && j.bias_dst)
+            for (int c = threadIdx.x; c < Cout; c += 256) j.bias_dst[co_off + c] = j.bias_src ? j.bias_src[c] : 0.f;
+        const int tiles_ci = (Cin + PK_T - 1) / PK_T;
+        const int co0 = (tile / tiles_ci) * PK_T, ci0 = (tile % tiles_ci) * PK_T;
+        const int nco = Cout - co0 < PK_T ? Cout - co0 : PK_T, nci = Cin - ci0 < PK_T ? Cin - ci0 : PK_T;
+        for (int r = warp; r < nco; r += 8) {
+            const float* src = w + ((long long)(co0 + r) * Cin + ci0) * RR;
+            for (int k = lane; k < nci * RR; k += 32) s[r][k] = src[k];
+        }
+        __syncthreads();
+        for (int slab = 0; slab < j.n_slabs; ++slab) {
+            int rlo = 0, rhi = 0, slo = 0, shi = 0;
+            if (j.mode == MVAE_CONV_UP) {
+                const int vi = slab & 1, ui = (slab >> 1) & 1, b = (slab >> 2) & 1, a = (slab >> 3) & 1;
+                up_rset(a, ui, rlo, rhi);
+                up_rset(b, vi, slo, shi);
+            }
+            auto value = [&](int co, int ci) -> float {
+                const float* e = &s[co][ci * RR];
+                if (j.mode != MVAE_CONV_UP) return e[slab];
+                float v = 0.f;
+                for (int r = rlo; r <= rhi; ++r)
+                    for (int q = slo; q <= shi; ++q) v += e[r * 3 + q];
+                return v;
+            };
+            if (wf && lane < nci)
+                for (int co = warp; co < nco; co += 8)
+                    wf[((long long)slab * Ctot + co_off + co0 + co) * CinP + ci0 + lane] = from_f<T>(value(co, lane));
+            if (wd && lane < nco)
+                for (int ci = warp; ci < nci; ci += 8)
+                    wd[((long long)slab * CinP + ci0 + ci) * Ctot + co_off + co0 + lane] = from_f<T>(value(lane, ci));
+        }
+        __syncthreads();
+    }
+}
+
+int pack_weights_batched(const mvae_pack_job* jobs_dev, int n_jobs, int total_tiles, int dtype, cudaStream_t st) {
+    const int blocks = total_tiles < 148 * 8 ? total_tiles : 148 * 8;
+    if (dtype == MVAE_F32)
+        pack_weights_batched_kernel<float><<<blocks, 256, 0, st>>>(jobs_dev, n_jobs, total_tiles);
+    else
+        pack_weights_batched_kernel<bf16><<<blocks, 256, 0, st>>>(jobs_dev, n_jobs, total_tiles);
+    MVAE_LAUNCH_CHECK();
+    return 0;
+}
+
 // ------------------------------------------------------------------ wgrad finalisation
 // partial [splits][nslabs][Cout][Cin] fp32 -> dW [Cout][Cin][R][R] fp32 (sum over splits; UP
 // mode: each (r,s) receives the 4 slabs whose R-sets contain it).  dW = beta * dW + sum: beta = 1

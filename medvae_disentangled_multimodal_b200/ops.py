@@ -46,6 +46,13 @@ def conv_pack_weights(d: ConvDesc, w_oihw, wf, wd, ctot, coff):
           "conv2d_pack_weights")
 
 
+def conv_pack_weights_batched(table, n_jobs: int, total_tiles: int, dtype_code: int):
+    """table: device uint8 tensor holding n_jobs mvae_pack_job structs (blocks.pack_entries)"""
+    with P.region("pack_weights", 0.0, 0.0):
+        check(lib().mvae_conv2d_pack_weights_batched(ptr(table), int(n_jobs), int(total_tiles), int(dtype_code), stream()),
+              "conv2d_pack_weights_batched")
+
+
 def conv_flops(d: ConvDesc) -> float:
     """algorithmic FLOPs (2*MAC) of one direction of this conv as the reference executes it
     (Upsample = 9 taps on the 2x grid, although the kernels run 4 taps per output parity)."""

@@ -418,6 +418,11 @@ class TrainStep:
         self.buckets.finish()
         # torch.optim leaves a parameter without a gradient alone (no weight decay, no moment update)
         self.optimizer.step(skip=self.buckets.untouched())
+        # the bf16 operands of every conv follow their fp32 masters with ONE launch (instead of ~110 per-conv packs
+        # at the head of the next forward)
+        from .blocks import refresh_packed
+        refresh_packed([s for s in (getattr(self.model, "encoder", None), getattr(self.model, "decoder", None))
+                        if s is not None and hasattr(s, "_pack_cache")])
         return totals
 
     @torch.no_grad()
