@@ -519,7 +519,22 @@ def b200_arm(args):
             hbm_roofs.append({"bound": "hbm", "kernel": fam, "achieved": round(by / (ms * 1e6), 1), "peak": peaks["hbm"],
                               "unit": "GB/s", "frac": round(by / (ms * 1e6) / peaks["hbm"], 4), "launches": n_l,
                               "avg_launch_ms": round(ms / n_l, 4), "algorithmic_mb_per_launch": round(by / n_l / 1e6, 2)})
+    comm = None
     if world > 1:
+        # exposed part of the bucketed gradient all-reduce (untimed extra steps, CUDA events around the final waits)
+        ts.buckets.trace = []
+        for _ in range(3):
+            step_resident()
+        torch.cuda.synchronize()
+        ex = [a.elapsed_time(b) for a, b in ts.buckets.trace]
+        ts.buckets.trace = None
+        ex_t = torch.tensor([sum(ex) / max(len(ex), 1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(ex_t, op=dist.ReduceOp.MAX)
+        comm = {"allreduce_bytes_per_step": int(ts.buckets.flat.numel() * 4), "dtype": "f32", "op": "avg",
+                "buckets": len(ts.buckets.bounds), "bucket_mb": 32,
+                "exposed_ms_per_step_max_over_ranks": round(float(ex_t), 3),
+                "reserved_sms": int(os.environ.get("MVAE_RESERVE_SMS", "0")),
+                "nccl_max_ctas": os.environ.get("NCCL_MAX_CTAS")}
         barrier()
 
     cpu = None
@@ -569,6 +584,7 @@ def b200_arm(args):
             "step_tflops_per_gpu": round(step_flops / (ms_res / args.steps * 1e9), 2),
             "step_frac_of_peak": round(step_flops / (ms_res / args.steps * 1e9) / peaks["bf16_sustained"], 4),
             "kernels": kernels,
+            "comm": comm,
             "cpu_baseline": cpu,
             "gpu_baseline": gpu_base,
             "parity_check": parity,

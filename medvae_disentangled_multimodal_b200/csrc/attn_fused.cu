@@ -420,7 +420,9 @@ static int af_num_sms() {
         cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
         if (n <= 0) n = 148;
     }
-    return n;
+    int r = debug_knob(12);       // SMs left free for a concurrent collective (see conv_umma.cu:num_sms)
+    int m = n - (r > 0 ? r : 0);
+    return m < 8 ? 8 : m;
 }
 
 static int af_launch(AfTmaps& tm, AfDev& d, cudaStream_t st) {

@@ -101,7 +101,12 @@ static int num_sms() {
         cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
         if (n <= 0) n = 148;
     }
-    return n;
+    // knob 12: SMs left free for a concurrent collective (NCCL's CTAs cannot start while a persistent one-CTA-per-SM
+    // kernel holds every SM, and vice versa: data-parallel runs reserve a few, train.TrainStep sets the knob)
+    int r = debug_knob(12);
+    int m = n - (r > 0 ? r : 0);
+    if (m < 8) m = 8;
+    return m & ~1;
 }
 
 // ================================================================== gather (fprop / dgrad)

@@ -19,7 +19,11 @@ __device__ __forceinline__ float philox_normal(uint64_t seed, uint64_t offset, u
 }
 
 // ------------------------------------------------------------------ reparam + KL forward
-// index space: NCHW latent element e = ((n*zc + c)*R + y)*R + x ; moments NHWC [n][y][x][2zc]
+// The encoder hands over NHWC moments [n][p][2zc] (channels innermost), the model's contract wants NCHW fp32 mean /
+// logvar / z / std / eps [n][c][p] (positions innermost): a CTA moves one 32-position x 32-channel tile through shared
+// memory, so both sides see full 64 / 128-byte segments (a thread per NCHW element with strided NHWC accesses, the
+// first version, ran at 19-25 % of HBM bandwidth: profiles/r2a_ncu_full.csv).
+constexpr int RP_T = 32;
 template <typename T>
 __global__ void __launch_bounds__(256) reparam_kl_fwd_kernel(const T* __restrict__ mom, const float* __restrict__ eps_in,
                                                              float* __restrict__ eps_out, float* __restrict__ mean,
@@ -30,34 +34,60 @@ __global__ void __launch_bounds__(256) reparam_kl_fwd_kernel(const T* __restrict
                                                              uint64_t offset, uint64_t elem_base,
                                                              const double* __restrict__ dyn) {
     __shared__ double shd[32];
+    __shared__ float s_mu[RP_T][RP_T + 1], s_lv[RP_T][RP_T + 1], s_z[RP_T][RP_T + 1];
     if (dyn) offset += (uint64_t)dyn[2];   // device-side Philox stream position (CUDA-graph replays advance it)
-    const long long total = (long long)B * zc * RR;
-    double acc = 0.0;
-    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
-         e += (long long)gridDim.x * blockDim.x) {
-        int p = (int)(e % RR);
-        long long r = e / RR;
-        int c = (int)(r % zc);
-        int n = (int)(r / zc);
-        const T* m = mom + ((long long)n * RR + p) * (2 * zc);
-        float mu = to_f<T>(m[c]), lv = to_f<T>(m[zc + c]);
-        if (clampv > 0.f) {
-            mu = fminf(fmaxf(mu, -clampv), clampv);
-            lv = fminf(fmaxf(lv, -clampv), clampv);
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 32 x 8
+    const int tiles_p = (RR + RP_T - 1) / RP_T, tiles_c = (zc + RP_T - 1) / RP_T;
+    const long long tiles = (long long)B * tiles_p * tiles_c;
+    float acc = 0.f;
+    for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const int tc = (int)(t % tiles_c);
+        const int tp = (int)((t / tiles_c) % tiles_p);
+        const int n = (int)(t / ((long long)tiles_c * tiles_p));
+        const int p0 = tp * RP_T, c0 = tc * RP_T;
+        // NHWC side: tx = channel, rows = positions
+        for (int i = ty; i < RP_T; i += 8) {
+            const int p = p0 + i, c = c0 + tx;
+            if (p < RR && c < zc) {
+                const T* m = mom + ((long long)n * RR + p) * (2 * zc);
+                s_mu[i][tx] = to_f<T>(m[c]);
+                s_lv[i][tx] = to_f<T>(m[zc + c]);
+            }
         }
-        float ep = eps_in ? eps_in[e] : philox_normal(seed, offset, elem_base + (uint64_t)e);
-        if (eps_out) eps_out[e] = ep;
-        float sd = expf(0.5f * lv);
-        float zz = fmaf(ep, sd, mu);
-        mean[e] = mu; logvar[e] = lv; z_nchw[e] = zz;
-        // the disentangled model (the only clamping caller) also clamps std to [1e-6, 10] for its Normal
-        // objects (disentangled_conditional_vae.py:426-427); z above uses the unclamped std as the reference does
-        if (stdv) stdv[e] = clampv > 0.f ? fminf(fmaxf(sd, 1e-6f), 10.f) : sd;
-        if (z_nhwc) z_nhwc[((long long)n * RR + p) * zc + c] = from_f<T>(zz);
-        acc += 0.5 * ((double)(sd * sd) + (double)mu * mu - 1.0 - (double)lv);
+        __syncthreads();
+        // NCHW side: tx = position, rows = channels
+        for (int i = ty; i < RP_T; i += 8) {
+            const int p = p0 + tx, c = c0 + i;
+            if (p < RR && c < zc) {
+                float mu = s_mu[tx][i], lv = s_lv[tx][i];
+                if (clampv > 0.f) {
+                    mu = fminf(fmaxf(mu, -clampv), clampv);
+                    lv = fminf(fmaxf(lv, -clampv), clampv);
+                }
+                const long long e = ((long long)n * zc + c) * RR + p;
+                const float ep = eps_in ? eps_in[e] : philox_normal(seed, offset, elem_base + (uint64_t)e);
+                if (eps_out) eps_out[e] = ep;
+                const float sd = expf(0.5f * lv);
+                const float zz = fmaf(ep, sd, mu);
+                mean[e] = mu; logvar[e] = lv; z_nchw[e] = zz;
+                // the disentangled model (the only clamping caller) also clamps std to [1e-6, 10] for its Normal
+                // objects (disentangled_conditional_vae.py:426-427); z above uses the unclamped std as the reference does
+                if (stdv) stdv[e] = clampv > 0.f ? fminf(fmaxf(sd, 1e-6f), 10.f) : sd;
+                s_z[tx][i] = zz;
+                acc += 0.5f * (sd * sd + mu * mu - 1.0f - lv);      // 4 terms per thread per tile in fp32, fp64 across
+            }
+        }
+        if (z_nhwc) {
+            __syncthreads();
+            for (int i = ty; i < RP_T; i += 8) {
+                const int p = p0 + i, c = c0 + tx;
+                if (p < RR && c < zc) z_nhwc[((long long)n * RR + p) * zc + c] = from_f<T>(s_z[i][tx]);
+            }
+        }
+        __syncthreads();
     }
-    acc = block_sum_d(acc, shd);
-    if (threadIdx.x == 0 && kl_sum) atomicAdd(kl_sum, acc);
+    const double tot = block_sum_d((double)acc, shd);
+    if (threadIdx.x == 0 && kl_sum) atomicAdd(kl_sum, tot);
 }
 
 // d_moments[n][p][c]      = d_mean + d_z                       (masked by the clamp)
@@ -68,26 +98,47 @@ __global__ void __launch_bounds__(256) reparam_kl_bwd_kernel(const float* __rest
                                                              const float* __restrict__ d_z, const float* __restrict__ logvar,
                                                              const float* __restrict__ eps, const T* __restrict__ mom,
                                                              T* __restrict__ d_mom, int B, int zc, int RR, float clampv) {
-    const long long total = (long long)B * zc * RR;
-    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
-         e += (long long)gridDim.x * blockDim.x) {
-        int p = (int)(e % RR);
-        long long r = e / RR;
-        int c = (int)(r % zc);
-        int n = (int)(r / zc);
-        float dz = d_z ? d_z[e] : 0.f;
-        float gm = (d_mean ? d_mean[e] : 0.f) + dz;
-        float lv = logvar[e];
-        float gl = (d_logvar ? d_logvar[e] : 0.f) + dz * eps[e] * 0.5f * expf(0.5f * lv);
-        long long o = ((long long)n * RR + p) * (2 * zc);
-        if (clampv > 0.f) {
-            float mu_raw = to_f<T>(mom[o + c]), lv_raw = to_f<T>(mom[o + zc + c]);
-            if (mu_raw < -clampv || mu_raw > clampv) gm = 0.f;
-            if (lv_raw < -clampv || lv_raw > clampv) gl = 0.f;
+    __shared__ float s_gm[RP_T][RP_T + 1], s_gl[RP_T][RP_T + 1];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int tiles_p = (RR + RP_T - 1) / RP_T, tiles_c = (zc + RP_T - 1) / RP_T;
+    const long long tiles = (long long)B * tiles_p * tiles_c;
+    for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const int tc = (int)(t % tiles_c);
+        const int tp = (int)((t / tiles_c) % tiles_p);
+        const int n = (int)(t / ((long long)tiles_c * tiles_p));
+        const int p0 = tp * RP_T, c0 = tc * RP_T;
+        for (int i = ty; i < RP_T; i += 8) {          // NCHW side: tx = position
+            const int p = p0 + tx, c = c0 + i;
+            if (p < RR && c < zc) {
+                const long long e = ((long long)n * zc + c) * RR + p;
+                const float dz = d_z ? d_z[e] : 0.f;
+                s_gm[tx][i] = (d_mean ? d_mean[e] : 0.f) + dz;
+                s_gl[tx][i] = (d_logvar ? d_logvar[e] : 0.f) + dz * eps[e] * 0.5f * expf(0.5f * logvar[e]);
+            }
         }
-        d_mom[o + c] = from_f<T>(gm);
-        d_mom[o + zc + c] = from_f<T>(gl);
+        __syncthreads();
+        for (int i = ty; i < RP_T; i += 8) {          // NHWC side: tx = channel
+            const int p = p0 + i, c = c0 + tx;
+            if (p < RR && c < zc) {
+                const long long o = ((long long)n * RR + p) * (2 * zc);
+                float gm = s_gm[i][tx], gl = s_gl[i][tx];
+                if (clampv > 0.f) {
+                    const float mu_raw = to_f<T>(mom[o + c]), lv_raw = to_f<T>(mom[o + zc + c]);
+                    if (mu_raw < -clampv || mu_raw > clampv) gm = 0.f;
+                    if (lv_raw < -clampv || lv_raw > clampv) gl = 0.f;
+                }
+                d_mom[o + c] = from_f<T>(gm);
+                d_mom[o + zc + c] = from_f<T>(gl);
+            }
+        }
+        __syncthreads();
     }
+}
+
+static int rp_blocks(int B, int zc, int RR) {
+    long long t = (long long)B * ((RR + RP_T - 1) / RP_T) * ((zc + RP_T - 1) / RP_T);
+    if (t > 148LL * 8) t = 148LL * 8;
+    return (int)(t < 1 ? 1 : t);
 }
 
 static int ew_blocks(long long total) {
@@ -102,10 +153,10 @@ int reparam_fwd(const void* mom, const float* eps, float* eps_out, float* mean, 
                 uint64_t elem_base, const double* dyn, int dtype, cudaStream_t st) {
     long long total = (long long)B * zc * R * R;
     if (dtype == MVAE_F32)
-        reparam_kl_fwd_kernel<float><<<ew_blocks(total), 256, 0, st>>>((const float*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
+        reparam_kl_fwd_kernel<float><<<rp_blocks(B, zc, R * R), 256, 0, st>>>((const float*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
                                                                         (float*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset, elem_base, dyn);
     else
-        reparam_kl_fwd_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>((const bf16*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
+        reparam_kl_fwd_kernel<bf16><<<rp_blocks(B, zc, R * R), 256, 0, st>>>((const bf16*)mom, eps, eps_out, mean, logvar, stdv, z_nchw,
                                                                        (bf16*)z_nhwc, kl_sum, B, zc, R * R, clampv, seed, offset, elem_base, dyn);
     MVAE_LAUNCH_CHECK();
     return 0;
@@ -114,10 +165,10 @@ int reparam_bwd(const float* d_mean, const float* d_logvar, const float* d_z, co
                 const void* mom, void* d_mom, int B, int zc, int R, float clampv, int dtype, cudaStream_t st) {
     long long total = (long long)B * zc * R * R;
     if (dtype == MVAE_F32)
-        reparam_kl_bwd_kernel<float><<<ew_blocks(total), 256, 0, st>>>(d_mean, d_logvar, d_z, logvar, eps, (const float*)mom,
+        reparam_kl_bwd_kernel<float><<<rp_blocks(B, zc, R * R), 256, 0, st>>>(d_mean, d_logvar, d_z, logvar, eps, (const float*)mom,
                                                                         (float*)d_mom, B, zc, R * R, clampv);
     else
-        reparam_kl_bwd_kernel<bf16><<<ew_blocks(total), 256, 0, st>>>(d_mean, d_logvar, d_z, logvar, eps, (const bf16*)mom,
+        reparam_kl_bwd_kernel<bf16><<<rp_blocks(B, zc, R * R), 256, 0, st>>>(d_mean, d_logvar, d_z, logvar, eps, (const bf16*)mom,
                                                                        (bf16*)d_mom, B, zc, R * R, clampv);
     MVAE_LAUNCH_CHECK();
     return 0;

@@ -75,6 +75,7 @@ class GradBuckets:
         self._add_dst, self._add_src, self._add_par = [], [], []
         self.reduce_enabled = True
         self.launched = 0
+        self.trace = None            # set to a list to collect (start, end) CUDA events around finish()'s waits
         for p in self.params:
             p.grad = self.views[id(p)]
 
@@ -146,6 +147,12 @@ class GradBuckets:
         """wait for every outstanding bucket; buckets that never filled (unused parameters) are
         reduced now so all ranks stay in step."""
         self.flush()
+        ev = None
+        if self.trace is not None and torch.cuda.is_available():
+            # exposed part of the gradient all-reduce: time the compute stream spends between the end of backward and
+            # the last bucket's completion (the waits below are stream dependencies, not host blocks)
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
         if self.world > 1 and self.reduce_enabled:
             for b, left in enumerate(self._pending):
                 if left > 0:
@@ -156,6 +163,9 @@ class GradBuckets:
             if t is not None:
                 t.div_(self.world)
         self._works = []
+        if ev is not None:
+            ev[1].record()
+            self.trace.append(ev)
 
 
 def backward_order(model: nn.Module) -> List[nn.Parameter]:
@@ -209,6 +219,12 @@ class TrainStep:
         self.optimizer = FusedAdamW(self.order, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
                                     decoupled=decoupled, max_norm=max_norm)
         self.device = self.order[0].device
+        if self.buckets.world > 1 and self.device.type == "cuda":
+            # persistent one-CTA-per-SM kernels and NCCL's CTAs otherwise wait for each other: leave a few SMs to the
+            # overlapped gradient all-reduce (MVAE_RESERVE_SMS, default 0 = off until measured)
+            import os
+            from . import _lib as L
+            L.lib().mvae_set_debug(12, int(os.environ.get("MVAE_RESERVE_SMS", "0")))
         # device-resident {optimizer step, learning rate, Philox position}, advanced by one kernel per step
         self.step_state = torch.tensor([0.0, float(lr), 0.0], dtype=torch.float64, device=self.device)
         if self.use_graph:
