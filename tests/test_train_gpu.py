@@ -22,15 +22,16 @@ def _smooth(v, w=10):
     return torch.nn.functional.avg_pool1d(t.view(1, 1, -1), w, stride=1).view(-1)
 
 
-def _curves(dtype, steps, micro_batch=None):
+def _curves(dtype, steps, micro_batch=None, seed=3, kw=None):
     import medvae_disentangled_multimodal_b200 as M
     from medvae_disentangled_multimodal_b200.train import TrainStep
-    torch.manual_seed(3)
+    KW = kw or globals()["KW"]
+    torch.manual_seed(seed)
     model = M.ConditionalVAE(compute_dtype=dtype, **KW)
     sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
-    batches = [O.synthetic_batch(8, 3, 16, seed=100 + i) for i in range(4)]
-    g = torch.Generator().manual_seed(17)
-    eps = [torch.randn(8, 8, 8, 8, generator=g) for _ in range(steps)]
+    batches = [O.synthetic_batch(8, 3, 16, seed=100 * seed + i) for i in range(4)]
+    g = torch.Generator().manual_seed(17 + seed)
+    eps = [torch.randn(8, KW["latent_dim"], 8, 8, generator=g) for _ in range(steps)]
     ref = O.ReferenceTrainer(sd, loss_kwargs=LKW, **OPT)
     ref_curve = []
     for i in range(steps):
@@ -53,9 +54,18 @@ def _curves(dtype, steps, micro_batch=None):
     return curve, ref_curve, (num / max(den, 1e-30)) ** 0.5
 
 
+# hidden 128 = the width of every BASELINE configuration (configs/model/base_vae.yaml:5): 128 / 256-channel tcgen05 convs
+# with both GroupNorm epilogues, attention at T = 64, C = 256
+KW128 = dict(KW, hidden_channels=128, latent_dim=16)
+
+
 @pytest.mark.umma
-def test_loss_curve_200_steps_bf16():
-    curve, ref_curve, _drift = _curves("bf16", 200)
+@pytest.mark.parametrize("seed,kw", [(3, None), (4, None), (5, None), (3, KW128), (6, KW128), (7, KW128)],
+                         ids=["h64-s3", "h64-s4", "h64-s5", "h128-s3", "h128-s6", "h128-s7"])
+def test_loss_curve_200_steps_bf16(seed, kw):
+    """bf16 mode is not bit-reproducible run to run (fp32 atomics in the GroupNorm epilogues), so the 1 % bound of
+    north_star is held over several seeds (weights, data and noise all change with the seed) and at two widths"""
+    curve, ref_curve, _drift = _curves("bf16", 200, seed=seed, kw=kw)
     a, b = _smooth(curve), _smooth(ref_curve)
     dev = float(((a - b).abs() / b.abs()).max())
     assert dev < 1e-2, f"smoothed loss curves deviate by {dev:.3%}"
