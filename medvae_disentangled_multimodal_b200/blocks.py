@@ -200,6 +200,14 @@ def pack_entries(entries, device):
         e["ver"] = e["op"]._versions()
 
 
+def mark_packed_current(stacks):
+    """the packed operands were refreshed behind Python's back (a CUDA-graph replay ends with the re-pack launch): record
+    the parameters' current versions so eager consumers do not pack again"""
+    for st in stacks:
+        for e in st._pack_cache.values():
+            e["ver"] = e["op"]._versions()
+
+
 def refresh_packed(stacks):
     """one launch re-packing every conv operand of these stacks whose master weights changed (after the optimizer step)"""
     stale, dev = [], None

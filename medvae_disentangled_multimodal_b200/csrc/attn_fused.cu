@@ -52,7 +52,7 @@ struct AfDev {
 };
 
 constexpr int AF_THREADS = 192;
-constexpr int AF_MAX_STAGES = 4;
+constexpr int AF_MAX_STAGES = 8;
 
 // one GEMM whose reduction runs over channels (scores): A rows r0.. of (map_a, channel offset ca), B all tokens of (map_b, cb)
 struct AfScoreJob { int a_dy, ca, b_dy, cb; uint32_t col; };

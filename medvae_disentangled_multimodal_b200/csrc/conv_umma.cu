@@ -225,7 +225,9 @@ template <int BN, int MT, int CG = 1>
 struct GatherCfg {
     static constexpr int A_BYTES = MT * A_TILE_BYTES;
     static constexpr int B_BYTES = BN * 128 / CG;
-    static constexpr int STAGES = (A_BYTES + B_BYTES >= 65536) ? 3 : ((A_BYTES + B_BYTES >= 49152) ? 4 : (A_BYTES + B_BYTES >= 32768 ? 6 : 8));
+    // as many stages as fit 200 KB (the GroupNorm tables, barriers and alignment slack take the rest of the 227 KB), <= 8:
+    // 64 KB stages -> 3, 48 KB -> 4, 40 KB -> 5, 32 KB -> 6, 24 KB -> 8
+    static constexpr int STAGES = (204800 / (A_BYTES + B_BYTES)) > 8 ? 8 : (204800 / (A_BYTES + B_BYTES));
     // accumulators are double-buffered (the epilogue of one CTA tile runs under the MMAs of the next) while they fit
     // the 512 TMEM columns; the 256 x 256 tile (MT = 2, BN = 256) uses all 512 for one buffer and pays an exposed
     // epilogue for halving the bytes pulled per FLOP (64 KB per 1024 MMA cycles = 64 B/clk, the SM's ingest rate)
@@ -245,7 +247,7 @@ template <int BN, int EPI, int MT, int CG, int CS>
 __global__ void __launch_bounds__(gather_threads_cs(CS), 1)
 conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_constant__ GatherDev p) {
     using Cfg = GatherCfg<BN, MT, CG>;
-    static_assert(CG == 1 || MT == 1, "a CTA pair takes one pixel tile per CTA");
+    // a scheduled tile is CG * MT pixel tiles: MT per CTA, the CTAs of a pair side by side (rank * MT + j)
     // CTA pair: rank within the pair, pair index and number of pairs replace blockIdx / gridDim in the tile loop
     const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
     const int sched_id = (CG == 2) ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
@@ -310,7 +312,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 for (int j = 0; j < MT; ++j) {
                     // pixel tile (tile / n_tiles) * MT + j; one past the last decodes to n0 >= B: the box is
                     // entirely out of bounds, TMA zero-fills it and the epilogue stores nothing
-                    int mt = (CG == 2) ? (tile / p.n_tiles) * 2 + (int)rank : (tile / p.n_tiles) * MT + j;
+                    int mt = (tile / p.n_tiles) * (CG * MT) + (int)rank * MT + j;
                     const int tx = mt % p.tiles_x; mt /= p.tiles_x;
                     x0[j] = tx * p.bw; y0[j] = (mt % p.tiles_y) * p.bh; n0[j] = (mt / p.tiles_y) * p.bn;
                 }
@@ -321,8 +323,10 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                         if (CG == 2) {
                             if (rank == 0) mbar_expect_tx(&full[stage], stage_bytes);
                             const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
-                            tma2_load_4d(sA + stage * Cfg::A_BYTES, &tm.a[tp.view], lead_full, kc * 64, x0[0] + tp.dx,
-                                         y0[0] + tp.dy, n0[0]);
+#pragma unroll
+                            for (int j = 0; j < MT; ++j)
+                                tma2_load_4d(sA + stage * Cfg::A_BYTES + j * A_TILE_BYTES, &tm.a[tp.view], lead_full, kc * 64,
+                                             x0[j] + tp.dx, y0[j] + tp.dy, n0[j]);
                             tma2_load_3d(sB + stage * Cfg::B_BYTES, &tm.b, lead_full, kc * 64,
                                          nt * BN + (int)rank * (BN / 2), tp.slab);
                             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
@@ -359,7 +363,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
 #pragma unroll
                         for (int j = 0; j < MT; ++j) {
                             const uint64_t ad = smem_desc_sw128(a0 + j * A_TILE_BYTES + k * 32, 16, 1024);
-                            if (CG == 2) umma2_bf16(d_tmem, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                            if (CG == 2) umma2_bf16(d_tmem + (uint32_t)(j * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
                             else umma_bf16(d_tmem + (uint32_t)(j * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
                         }
                     }
@@ -399,7 +403,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
             __syncwarp();                                     // every lane is done with the previous tile's slots
 #pragma unroll
             for (int j = 0; j < MT; ++j) {
-                int mt = (CG == 2) ? (tile / p.n_tiles) * 2 + (int)rank : (tile / p.n_tiles) * MT + j;
+                int mt = (tile / p.n_tiles) * (CG * MT) + (int)rank * MT + j;
                 const int tx = mt % p.tiles_x; mt /= p.tiles_x;
                 const int ty = mt % p.tiles_y;
                 const int tn = mt / p.tiles_y;
@@ -525,7 +529,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
 #pragma unroll 1
           for (int j = 0; j < MT; ++j) {
             const uint32_t acc_col = (uint32_t)(acc * MT * BN + j * BN);
-            int mt = (CG == 2) ? (tile / p.n_tiles) * 2 + (int)rank : (tile / p.n_tiles) * MT + j;
+            int mt = (tile / p.n_tiles) * (CG * MT) + (int)rank * MT + j;
             const int tx = mt % p.tiles_x; mt /= p.tiles_x;
             const int ty = mt % p.tiles_y;
             const int tn = mt / p.tiles_y;
@@ -734,6 +738,10 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
         BoxGeom g0 = box_geom(p.B, p.OH, p.OW);
         const long long mt0 = (long long)g0.tiles_x * g0.tiles_y * g0.tiles_n;
         if (BN == 256 && debug_knob(8) == 0 && ((mt0 + 1) / 2) * (p.N / 256) >= num_sms() / 2) CG = 2;   // knob 8 = 1: off
+        // 128-channel tiles: a pair with TWO pixel tiles per CTA (2 x 2 x 128 pixels x 128 channels per scheduled tile),
+        // each CTA loading half of the weight tile: (32 + 8) KB per 512 MMA cycles = 80 B/clk of ingest instead of
+        // the 96 B/clk of the single-CTA two-tile variant (knob 13 = 1: off)
+        if (BN == 128 && debug_knob(13) == 0 && debug_knob(5) == 0 && ((mt0 + 3) / 4) * (p.N / 128) >= num_sms() / 2) CG = 2;
     }
     GatherTmaps tm;
     memset(&tm, 0, sizeof(tm));
@@ -755,6 +763,7 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     // 128-channel tiles take two pixel tiles per weight stage when that still leaves every SM a CTA tile
     const long long m_tiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
     int MT = (BN == 128 && debug_knob(5) == 0 && ((m_tiles + 1) / 2) * d.n_tiles >= num_sms()) ? 2 : 1;
+    if (BN == 128 && CG == 2) MT = 2;
     if (CG == 1 && BN == 256 && debug_knob(7) == 1) {
         // OPT-IN experiment (knob 7): 256 x 256 CTA tiles, 64 instead of 96 B/clk of ingest but a single accumulator
         // buffer, i.e. an exposed epilogue.  Measured on C4 (r1e): fprop 16.7 -> 17.9 ms, dgrad 19.6 -> 21.6 ms per
@@ -783,6 +792,7 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
         d.gn_sums = hook->sums; d.gn_x = (const bf16*)hook->x; d.gn_stat = hook->stat;
         d.gn_gamma = hook->gamma; d.gn_beta = hook->beta;
     }
+    if (CG == 2 && BN == 128) return launch_gather<128, 2, 2>(tm, d, epi, st);
     if (CG == 2) return launch_gather<256, 1, 2>(tm, d, epi, st);
     if (BN == 256 && MT == 2) return launch_gather<256, 2>(tm, d, epi, st);
     if (BN == 256) return launch_gather<256, 1>(tm, d, epi, st);

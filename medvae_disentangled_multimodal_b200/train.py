@@ -276,7 +276,15 @@ class TrainStep:
             stack = getattr(self.model, name, None)
             if stack is not None and name in sd["rng"]:
                 stack._dropout_step = int(sd["rng"][name])
-        torch._C._increment_version(self.optimizer.params)   # packed bf16 operand caches must be refreshed
+        torch._C._increment_version(self.optimizer.params)
+        # the packed operands follow NOW: a captured step assumes they are current when it starts (its own re-pack
+        # launch sits at its end)
+        from .blocks import refresh_packed
+        refresh_packed(self._stacks())
+
+    def _stacks(self):
+        return [s for s in (getattr(self.model, "encoder", None), getattr(self.model, "decoder", None))
+                if s is not None and hasattr(s, "_pack_cache")]
 
     def close(self):
         for h in self._hooks:
@@ -338,8 +346,11 @@ class TrainStep:
             self._gc.copy_(cond, non_blocking=True)
         self._graph.replay()
         self.optimizer.step_count += 1
-        # parameters changed behind autograd's back: eager consumers (validate, sample) must re-pack
+        # parameters changed behind autograd's back (version bump for any cache keyed on them); the graph's last node
+        # re-packed the conv operands, so those are current
         torch._C._increment_version(self.optimizer.params)
+        from .blocks import mark_packed_current
+        mark_packed_current(self._stacks())
         return dict(self._gout)
 
     def release_graph(self):
@@ -437,8 +448,7 @@ class TrainStep:
         # the bf16 operands of every conv follow their fp32 masters with ONE launch (instead of ~110 per-conv packs
         # at the head of the next forward)
         from .blocks import refresh_packed
-        refresh_packed([s for s in (getattr(self.model, "encoder", None), getattr(self.model, "decoder", None))
-                        if s is not None and hasattr(s, "_pack_cache")])
+        refresh_packed(self._stacks())
         return totals
 
     @torch.no_grad()

@@ -29,6 +29,13 @@ for stage in $STAGES; do
     bench_c3) timeout 600 python bench.py --workload c3 --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_c3.log 2>&1; echo "bench_c3 rc=$?" >> gpurun_out/rc.txt;;
     bench_c2) timeout 600 python bench.py --workload c2 --steps 10 --warmup 3 --no-cpu-baseline --no-gpu-baseline > gpurun_out/bench_c2.log 2>&1; echo "bench_c2 rc=$?" >> gpurun_out/rc.txt;;
     bench_c1) timeout 600 python bench.py --workload c1 --precision fp32 --steps 10 --warmup 3 --no-gpu-baseline > gpurun_out/bench_c1.log 2>&1; echo "bench_c1 rc=$?" >> gpurun_out/rc.txt;;
+    ab128)  # A/B on one box: CTA pairs for the 128-channel tiles (knob 13 = 1 switches them off)
+      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline > gpurun_out/bench_pairs128_on.log 2>&1; echo "ab on rc=$?" >> gpurun_out/rc.txt
+      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob 13=1 > gpurun_out/bench_pairs128_off.log 2>&1; echo "ab off rc=$?" >> gpurun_out/rc.txt;;
+    attnlist)
+      timeout 300 $CMD > gpurun_out/plain_attn.log 2>&1 &&
+      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"attn_|bgemm" -c 200 --csv --log-file gpurun_out/attn_launches.csv $CMD > gpurun_out/ncu_attnlist.log 2>&1
+      echo "attnlist rc=$?" >> gpurun_out/rc.txt;;
     list)
       timeout 300 $CMD > gpurun_out/plain_list.log 2>&1 &&
       timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 14000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
