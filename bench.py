@@ -497,10 +497,12 @@ def b200_arm(args):
             roof = {"bound": "tensor", "kernel": "conv_gather_umma_kernel (implicit-GEMM conv fprop+dgrad, tcgen05)",
                     "achieved": round(ach, 2), "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
                     "frac": round(ach / peaks["bf16_sustained"], 4), "traffic": load_traffic(wl),
-                    "traffic_source": ("profiles/roofline_traffic.json: ncu --set full, mean DRAM read+write bytes of the "
-                                       "gather launches of a 256-image pass (the timed launches here take the whole "
-                                       f"{micro}-image pass: scale by the image count)"
-                                       if wl == "c4" else None),
+                    "traffic_source": ("profiles/roofline_traffic.json <- profiles/r2a_ncu_full.csv: ncu --set full, mean "
+                                       "dram__bytes_read.sum + dram__bytes_write.sum over 30 gather launches (16 fprop, 14 "
+                                       "dgrad) of this very command shape (one 1024-image pass)" if wl == "c4" else None),
+                    # bytes the launches must move at least once: input + output tensors (+ the GroupNorm input read and
+                    # nothing else; the 9x tap re-read is served by L2): traffic / this ~ 0.85-1.0 = no wasted re-reads
+                    "algorithmic_bytes_per_launch": int(sum(summ[k]["bytes"] for k in gk) / n_l),
                     "peak_source": f"{peaks['source']} (sustained: kernel timed inside a long step)",
                     "launches": n_l, "avg_launch_ms": round(ms / n_l, 4),
                     "algorithmic_gflop_per_launch": round(fl / n_l / 1e9, 2)}

@@ -740,8 +740,10 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
         if (BN == 256 && debug_knob(8) == 0 && ((mt0 + 1) / 2) * (p.N / 256) >= num_sms() / 2) CG = 2;   // knob 8 = 1: off
         // 128-channel tiles: a pair with TWO pixel tiles per CTA (2 x 2 x 128 pixels x 128 channels per scheduled tile),
         // each CTA loading half of the weight tile: (32 + 8) KB per 512 MMA cycles = 80 B/clk of ingest instead of
-        // the 96 B/clk of the single-CTA two-tile variant (knob 13 = 1: off)
-        if (BN == 128 && debug_knob(13) == 0 && debug_knob(5) == 0 && ((mt0 + 3) / 4) * (p.N / 128) >= num_sms() / 2) CG = 2;
+        // the 96 B/clk of the single-CTA two-tile variant.  OPT-IN (knob 13 = 1): measured on C4 on one box (trip r2c)
+        // it changes nothing — fprop 64.0 ms with, 63.1 ms without, step 4113 vs 4119 img/s — so the 128-wide tiles
+        // are not bound by the weight half of the ingest; the single-CTA variant stays the default.
+        if (BN == 128 && debug_knob(13) == 1 && debug_knob(5) == 0 && ((mt0 + 3) / 4) * (p.N / 128) >= num_sms() / 2) CG = 2;
     }
     GatherTmaps tm;
     memset(&tm, 0, sizeof(tm));

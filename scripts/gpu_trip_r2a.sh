@@ -36,6 +36,11 @@ for stage in $STAGES; do
       timeout 300 $CMD > gpurun_out/plain_attn.log 2>&1 &&
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"attn_|bgemm" -c 200 --csv --log-file gpurun_out/attn_launches.csv $CMD > gpurun_out/ncu_attnlist.log 2>&1
       echo "attnlist rc=$?" >> gpurun_out/rc.txt;;
+    list_c3)   # launch list of the 28x28 workload (eager launches: --graph off), one 256-image step
+      C3CMD="python bench.py --workload c3 --graph off --steps 1 --warmup 1 --no-cpu-baseline --no-gpu-baseline --no-roofline --no-parity-check"
+      timeout 300 $C3CMD > gpurun_out/plain_list_c3.log 2>&1 &&
+      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 14000 --csv --log-file gpurun_out/launches_c3.csv $C3CMD > gpurun_out/ncu_list_c3.log 2>&1
+      echo "list_c3 rc=$?" >> gpurun_out/rc.txt;;
     list)
       timeout 300 $CMD > gpurun_out/plain_list.log 2>&1 &&
       timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 14000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1

@@ -449,6 +449,23 @@ def test_conv_gn_epilogues_cta_pair(cta_pairs):
     test_conv_dgrad_gn_backward((77, 32, 32, 256, 256, 3, 0, 32), True, True)
 
 
+@pytest.mark.umma
+def test_conv_umma_cta_pair_128_channel_tiles():
+    """the opt-in variant (knob 13 = 1): CTA pairs with two pixel tiles per CTA for 128-channel tiles, plain and with
+    both GroupNorm epilogues (not the default: it measured no faster)"""
+    L, _ = _mods()
+    L.lib().mvae_set_debug(13, 1)
+    try:
+        for case in [(80, 32, 32, 128, 128, 3, 0), (61, 24, 24, 128, 128, 3, 0), (300, 32, 32, 128, 128, 3, 1),
+                     (150, 16, 16, 128, 128, 3, 2), (80, 32, 32, 64, 384, 1, 0)]:
+            _conv_case(case, torch.bfloat16, L.ENGINE_UMMA)
+        test_conv_fprop_gn_statistics((77, 32, 32, 128, 128, 3, 0, 32))
+        test_conv_dgrad_gn_backward((77, 32, 32, 128, 128, 3, 0, 32), True, True)
+        test_conv_dgrad_gn_backward((77, 32, 32, 128, 128, 3, 0, 32), False, False)
+    finally:
+        L.lib().mvae_set_debug(13, 0)
+
+
 # ------------------------------------------------------------------ disentangled-model kernels
 def _ref_aux(z, idx, s, m, tau=0.1):
     zm = z.reshape(z.shape[0], -1)[:, s:s + m]
