@@ -12,8 +12,8 @@
 //   A key tile needs the contributions of ALL queries (and vice versa), which is why the backward has the two transposed
 //   kinds instead of atomics: every output element is written exactly once, deterministically.
 //
-// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM allocation), warps 2-9 = two epilogue
-// groups of four warps (TMEM lane quarter = warp & 3): the epilogue, not the MMAs, is the critical path of an item.  Operands are read in place from the fused NHWC qkv tensor [B][T][3C] and from dO / written to
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM allocation), warps 2-5 = epilogue (TMEM
+// lane quarter = warp & 3).  Operands are read in place from the fused NHWC qkv tensor [B][T][3C] and from dO / written to
 // dqkv through ONE 3-D tensor map per tensor with a {64 channels, 64 tokens} box: a K-major operand (reduction over
 // channels) and an N-major operand (reduction over tokens) are the same box seen through different UMMA descriptors.
 // Rows / tokens beyond T are TMA zero fill; the score columns beyond T are masked in the epilogue.
@@ -51,7 +51,7 @@ struct AfDev {
     bf16* dqkv;        // backward [B][T][3C]
 };
 
-constexpr int AF_THREADS = 320;   // TMA warp + MMA warp + two groups of four epilogue warps
+constexpr int AF_THREADS = 192;
 constexpr int AF_MAX_STAGES = 8;
 
 // one GEMM whose reduction runs over channels (scores): A rows r0.. of (map_a, channel offset ca), B all tokens of (map_b, cb)
@@ -116,7 +116,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
         if (lane == 0) {
             for (int s = 0; s < AF_MAX_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
             mbar_init(tfull_s, 1);
-            mbar_init(pready, 8);
+            mbar_init(pready, 4);
             for (int i = 0; i < 2; ++i) { mbar_init(&tfull_o[i], 1); mbar_init(&tempty_o[i], 4); }
             fence_barrier_init();
         }
@@ -232,10 +232,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
         // ===================================================== epilogue warps: one thread = one tile row (TMEM lane)
         const int quarter = warp & 3;
         const int row = quarter * 32 + lane;
-        const int et = threadIdx.x - 64;     // 0..255
-        // two epilogue warp groups (warps 2-5 and 6-9), each covering all four TMEM lane quarters: they split the score
-        // columns in interleaved 32-column chunks and take alternate output accumulators
-        const int group = (warp - 2) >> 2;
+        const int et = threadIdx.x - 64;     // 0..127
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const int cols_tile = p.kboxes * 64;
         uint32_t n_local = 0;
@@ -251,12 +248,12 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
             float row_lse = 0.f, row_d = 0.f, inv_l = 1.f;
             if (kind == AF_BWD_K) {
                 // per-QUERY statistics: the score columns of this kind are queries
-                asm volatile("bar.sync 1, 256;" ::: "memory");     // the previous item's readers are done
-                for (int q = et; q < cols_tile; q += 256) {
+                asm volatile("bar.sync 1, 128;" ::: "memory");     // the previous item's readers are done
+                for (int q = et; q < cols_tile; q += 128) {
                     sStat[q] = q < p.T ? p.lse2[tok0 + q] : 0.f;
                     sStat[256 + q] = q < p.T ? p.D[tok0 + q] : 0.f;
                 }
-                asm volatile("bar.sync 1, 256;" ::: "memory");
+                asm volatile("bar.sync 1, 128;" ::: "memory");
             } else if (kind == AF_BWD_Q && valid) {
                 row_lse = p.lse2[tok0 + grow];
                 row_d = p.D[tok0 + grow];
@@ -267,7 +264,6 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                 float mx = -INFINITY;
 #pragma unroll 1
                 for (int c0 = 0; c0 < p.Tp; c0 += 32) {
-                    if (((c0 >> 5) & 1) != group) continue;
                     uint32_t v[32];
                     tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, v);
                     tmem_ld_wait();
@@ -275,14 +271,9 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                     for (int i = 0; i < 32; ++i)
                         if (c0 + i < p.T) mx = fmaxf(mx, __uint_as_float(v[i]) * p.alpha_log2e);
                 }
-                // row maximum over both groups' columns (sStat is free in the forward: [0,256) maxima, [256,512) sums)
-                sStat[group * 128 + row] = mx;
-                asm volatile("bar.sync 1, 256;" ::: "memory");
-                mx = fmaxf(sStat[row], sStat[128 + row]);
                 float sum = 0.f;
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
-                    if (((c0 >> 5) & 1) != group) continue;
                     uint32_t v[32];
                     if (c0 < p.Tp) { tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, v); tmem_ld_wait(); }
 #pragma unroll
@@ -299,15 +290,11 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                         af_tile_store8(sTile0, row, c0 + g * 8, f);
                     }
                 }
-                sStat[256 + group * 128 + row] = sum;
-                asm volatile("bar.sync 1, 256;" ::: "memory");
-                sum = sStat[256 + row] + sStat[384 + row];
                 inv_l = 1.f / sum;
-                if (valid && group == 0) p.lse2[tok0 + grow] = mx + log2f(sum);
+                if (valid) p.lse2[tok0 + grow] = mx + log2f(sum);
             } else if (kind == AF_BWD_Q) {
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
-                    if (((c0 >> 5) & 1) != group) continue;
                     uint32_t s[32], d[32];
                     if (c0 < p.Tp) {
                         tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, s);
@@ -329,7 +316,6 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
             } else {
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
-                    if (((c0 >> 5) & 1) != group) continue;
                     uint32_t s[32], d[32];
                     if (c0 < p.Tp) {
                         tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, s);
@@ -365,7 +351,6 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                 bf16* orow = obase + (tok0 + grow) * pitch;
                 for (int nc = 0; nc < nchunks; ++nc) {
                     const int buf = (int)((uses[0] + uses[1]) & 1u);
-                    if (buf != group) { ++uses[buf]; continue; }      // the other group's accumulator
                     mbar_wait(&tfull_o[buf], uses[buf] & 1u);
                     tc_fence_after();
                     const uint32_t ocol = lane_addr + (buf ? p.col_o1 : p.col_o0);
