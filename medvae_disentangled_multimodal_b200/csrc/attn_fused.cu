@@ -28,8 +28,13 @@ int encode_tmap_3d_bf16(CUtensorMap* m, const void* base, unsigned long long inn
 
 enum { AF_FWD = 0, AF_BWD_Q = 1, AF_BWD_K = 2 };
 
+// Three boxes per tensor ([0] = qkv, [1] = dO): the kernel is bound by the rate at which ONE thread can issue TMA
+// instructions (~0.28 us each, measured: every shape cost 0.28-0.29 us per {64 x 64} box), so every operand moves in the
+// largest box its layout allows and the lanes of the producer warp issue the boxes of a stage in parallel.
 struct alignas(64) AfTmaps {
-    CUtensorMap qkv, dy;   // dy = dO (backward only)
+    CUtensorMap a[2];   // {64 channels, 128 tokens}: the A rows of a score GEMM
+    CUtensorMap b[2];   // {64 channels, kboxes * 64 tokens}: ALL tokens, the B operand of a score GEMM
+    CUtensorMap n[2];   // {64 channels, kg * 64 tokens}: a token group, the N-major B operand of an output GEMM
 };
 struct AfDev {
     int B, T, C;
@@ -39,6 +44,7 @@ struct AfDev {
     int bwd;
     int stages;
     int bno;           // channel chunk of the output GEMMs (128, or 64 when C is not a multiple of 128)
+    int kg;            // 64-token boxes per output-GEMM stage (a divisor of kboxes)
     int n_items;
     int o_alias;       // output accumulators alias the score columns (backward, T > 128)
     uint32_t stage_bytes, tile_bytes;
@@ -111,7 +117,10 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
         if (threadIdx.x == 0) printf("mvae: attn_fused dynamic shared memory is not 1024-byte aligned\n");
         __trap();
     }
-    if (warp == 0 && lane == 0) { prefetch_tmap(&tm.qkv); if (p.bwd) prefetch_tmap(&tm.dy); }
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tm.a[0]); prefetch_tmap(&tm.b[0]); prefetch_tmap(&tm.n[0]);
+        if (p.bwd) { prefetch_tmap(&tm.a[1]); prefetch_tmap(&tm.b[1]); prefetch_tmap(&tm.n[1]); }
+    }
     if (warp == 1) {
         if (lane == 0) {
             for (int s = 0; s < AF_MAX_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
@@ -130,43 +139,44 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
     const int kiters = p.C / 64;            // channel chunks of a score GEMM
     const int nchunks = p.C / p.bno;        // channel chunks of an output GEMM
     const uint32_t score_stage_bytes = 16384u + (uint32_t)p.kboxes * 8192u;
-    const uint32_t out_stage_bytes = (uint32_t)p.bno * 128u;
+    const uint32_t out_stage_bytes = (uint32_t)p.bno * 128u * (uint32_t)p.kg;
+    const int kgroups = p.kboxes / p.kg;
 
     if (warp == 0) {
-        // ===================================================== TMA producer
-        if (lane == 0) {
-            int stage = 0; uint32_t phase = 0;
-            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
-                int kind, img, r0, ns, no;
-                AfScoreJob sj[2]; AfOutJob oj[2];
-                af_item(p, it, kind, img, r0);
-                af_jobs(p, kind, sj, ns, oj, no);
-                for (int j = 0; j < ns; ++j) {
-                    const CUtensorMap* ma = sj[j].a_dy ? &tm.dy : &tm.qkv;
-                    const CUtensorMap* mb = sj[j].b_dy ? &tm.dy : &tm.qkv;
-                    for (int kb = 0; kb < kiters; ++kb) {
+        // ===================================================== TMA producer (whole warp: lane 0 owns the barriers, lanes
+        // 0..n-1 issue the n boxes of a stage)
+        int stage = 0; uint32_t phase = 0;
+        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+            int kind, img, r0, ns, no;
+            AfScoreJob sj[2]; AfOutJob oj[2];
+            af_item(p, it, kind, img, r0);
+            af_jobs(p, kind, sj, ns, oj, no);
+            for (int j = 0; j < ns; ++j) {
+                for (int kb = 0; kb < kiters; ++kb) {
+                    if (lane == 0) {
                         mbar_wait(&empty[stage], phase ^ 1u);
                         mbar_expect_tx(&full[stage], score_stage_bytes);
-                        uint8_t* a = sStage + (uint32_t)stage * p.stage_bytes;
-                        uint8_t* b = a + 16384;
-                        tma_load_3d(a, ma, &full[stage], sj[j].ca + kb * 64, r0, img);
-                        tma_load_3d(a + 8192, ma, &full[stage], sj[j].ca + kb * 64, r0 + 64, img);
-                        for (int r = 0; r < p.kboxes; ++r)
-                            tma_load_3d(b + r * 8192, mb, &full[stage], sj[j].cb + kb * 64, r * 64, img);
-                        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                     }
+                    __syncwarp();
+                    uint8_t* a = sStage + (uint32_t)stage * p.stage_bytes;
+                    if (lane == 0) tma_load_3d(a, &tm.a[sj[j].a_dy], &full[stage], sj[j].ca + kb * 64, r0, img);
+                    else if (lane == 1) tma_load_3d(a + 16384, &tm.b[sj[j].b_dy], &full[stage], sj[j].cb + kb * 64, 0, img);
+                    if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                 }
-                for (int j = 0; j < no; ++j) {
-                    const CUtensorMap* mb = oj[j].b_dy ? &tm.dy : &tm.qkv;
-                    for (int nc = 0; nc < nchunks; ++nc) {
-                        for (int kc = 0; kc < p.kboxes; ++kc) {
+            }
+            for (int j = 0; j < no; ++j) {
+                for (int nc = 0; nc < nchunks; ++nc) {
+                    for (int g = 0; g < kgroups; ++g) {
+                        if (lane == 0) {
                             mbar_wait(&empty[stage], phase ^ 1u);
                             mbar_expect_tx(&full[stage], out_stage_bytes);
-                            uint8_t* b = sStage + (uint32_t)stage * p.stage_bytes;
-                            for (int s = 0; s < p.bno / 64; ++s)
-                                tma_load_3d(b + s * 8192, mb, &full[stage], oj[j].cb + nc * p.bno + s * 64, kc * 64, img);
-                            if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                         }
+                        __syncwarp();
+                        uint8_t* b = sStage + (uint32_t)stage * p.stage_bytes;
+                        if (lane < p.bno / 64)
+                            tma_load_3d(b + lane * (p.kg * 8192), &tm.n[oj[j].b_dy], &full[stage],
+                                        oj[j].cb + nc * p.bno + lane * 64, g * p.kg * 64, img);
+                        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                     }
                 }
             }
@@ -211,14 +221,18 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                         mbar_wait(&tempty_o[buf], (uses[buf] & 1u) ^ 1u);
                         tc_fence_after();
                         const uint32_t dcol = tmem_base + (buf ? p.col_o1 : p.col_o0);
-                        for (int kc = 0; kc < p.kboxes; ++kc) {
+                        for (int g = 0; g < kgroups; ++g) {
                             mbar_wait(&full[stage], phase);
                             tc_fence_after();
                             const uint32_t b0 = smem_u32(sStage + (uint32_t)stage * p.stage_bytes);
+                            for (int kc = 0; kc < p.kg; ++kc) {
+                                const int kt = g * p.kg + kc;          // 64-token box of the reduction
 #pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                umma_bf16(dcol, smem_desc_sw128(t0 + kc * 16384 + k * 32, 16, 1024),
-                                          smem_desc_sw128(b0 + k * 2048, 8192, 1024), p.idesc_o, (kc | k) != 0 ? 1u : 0u);
+                                for (int k = 0; k < 4; ++k)
+                                    umma_bf16(dcol, smem_desc_sw128(t0 + kt * 16384 + k * 32, 16, 1024),
+                                              smem_desc_sw128(b0 + kc * 8192 + k * 2048, (uint32_t)p.kg * 8192u, 1024),
+                                              p.idesc_o, (kt | k) != 0 ? 1u : 0u);
+                            }
                             umma_commit(&empty[stage]);
                             if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                         }
@@ -425,14 +439,28 @@ static int af_num_sms() {
     return m < 8 ? 8 : m;
 }
 
-static int af_launch(AfTmaps& tm, AfDev& d, cudaStream_t st) {
+static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t st) {
     const int Tn = d.T, C = d.C;
     d.Tp = (Tn + 15) / 16 * 16;
     d.kboxes = (Tn + 63) / 64;
     d.mtiles = (Tn + 127) / 128;
     d.bno = (C % 128 == 0) ? 128 : 64;
     d.tile_bytes = (uint32_t)d.kboxes * 16384u;
-    d.stage_bytes = 16384u + (uint32_t)d.kboxes * 8192u;     // >= one output-GEMM stage (bno * 128 <= 16384)
+    d.stage_bytes = 16384u + (uint32_t)d.kboxes * 8192u;
+    // token boxes per output-GEMM stage: the largest divisor of kboxes whose (bno channels x kg * 64 tokens) fits a stage
+    d.kg = 1;
+    for (int k = d.kboxes; k >= 1; --k)
+        if (d.kboxes % k == 0 && (uint32_t)(d.bno * 128 * k) <= d.stage_bytes) { d.kg = k; break; }
+    AfTmaps tm;
+    memset(&tm, 0, sizeof(tm));
+    for (int t = 0; t < (d.bwd ? 2 : 1); ++t) {
+        const bf16* base = t ? dout : qkv;
+        const unsigned long long inner = t ? (unsigned long long)C : 3ULL * C;
+        const unsigned long long img = (unsigned long long)Tn * inner;
+        if (encode_tmap_3d_bf16(&tm.a[t], base, inner, Tn, d.B, inner, img, 64, 128)) return 1;
+        if (encode_tmap_3d_bf16(&tm.b[t], base, inner, Tn, d.B, inner, img, 64, (unsigned)(d.kboxes * 64))) return 1;
+        if (encode_tmap_3d_bf16(&tm.n[t], base, inner, Tn, d.B, inner, img, 64, (unsigned)(d.kg * 64))) return 1;
+    }
     d.alpha = 1.0f / sqrtf((float)C);                         // int(c) ** (-0.5), encoder_decoder.py:94
     d.alpha_log2e = d.alpha * 1.4426950408889634f;
     d.idesc_s = make_idesc_bf16(128, d.Tp, 0, 0);
@@ -469,14 +497,11 @@ static int af_launch(AfTmaps& tm, AfDev& d, cudaStream_t st) {
 // the backward)
 int attn_fused_fwd(const bf16* qkv, bf16* out, float* lse2, int B, int Tn, int C, cudaStream_t st) {
     MVAE_CHECK(attn_fused_ok(Tn, C), "attn_fused_fwd: unsupported shape T=%d C=%d (needs C %% 64 == 0, T <= 256)", Tn, C);
-    AfTmaps tm;
-    memset(&tm, 0, sizeof(tm));
-    if (encode_tmap_3d_bf16(&tm.qkv, qkv, 3ULL * C, Tn, B, 3ULL * C, (unsigned long long)Tn * 3 * C, 64, 64)) return 1;
     AfDev d;
     memset(&d, 0, sizeof(d));
     d.B = B; d.T = Tn; d.C = C; d.bwd = 0;
     d.out = out; d.lse2 = lse2;
-    return af_launch(tm, d, st);
+    return af_launch(qkv, nullptr, d, st);
 }
 
 // dqkv [B][T][3C] from dout [B][T][C], the forward's out and lse2; dscratch: B*T floats
@@ -488,16 +513,11 @@ int attn_fused_bwd(const bf16* qkv, const bf16* out, const float* lse2, const bf
     if (blocks > 148 * 8) blocks = 148 * 8;
     attn_rowdot_kernel<<<(unsigned)blocks, 256, 0, st>>>(dout, out, dscratch, rows, C);
     MVAE_LAUNCH_CHECK();
-    AfTmaps tm;
-    memset(&tm, 0, sizeof(tm));
-    if (encode_tmap_3d_bf16(&tm.qkv, qkv, 3ULL * C, Tn, B, 3ULL * C, (unsigned long long)Tn * 3 * C, 64, 64)) return 1;
-    if (encode_tmap_3d_bf16(&tm.dy, dout, (unsigned long long)C, Tn, B, (unsigned long long)C, (unsigned long long)Tn * C,
-                            64, 64)) return 1;
     AfDev d;
     memset(&d, 0, sizeof(d));
     d.B = B; d.T = Tn; d.C = C; d.bwd = 1;
     d.lse2 = const_cast<float*>(lse2); d.D = dscratch; d.dqkv = dqkv;
-    return af_launch(tm, d, st);
+    return af_launch(qkv, dout, d, st);
 }
 
 }  // namespace mvae
