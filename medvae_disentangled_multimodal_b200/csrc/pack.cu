@@ -152,41 +152,65 @@ int pack_weights_batched(const mvae_pack_job* jobs_dev, int n_jobs, int total_ti
 // A CTA owns 256 consecutive (co, ci) pairs: slab reads are coalesced along ci, the R*R values of a
 // pair are transposed through shared memory (stride 9: conflict-free) and the CTA's contiguous
 // 256*R*R-float span of OIHW is written with fully coalesced stores.
+// RR = taps per (co, ci) pair known at compile time: the RR x splits partial reads of a thread are independent loads
+// issued back to back (the first version walked them in a runtime-bounded nested loop, one L2 round trip after the
+// other: 22 us per launch for the 14x14 / 7x7 layers of the 28x28 workloads, profiles/r2d_launches_c3.csv).
+template <int RR, bool UP>
 __global__ void __launch_bounds__(256) wgrad_finalize_kernel(const float* __restrict__ partial, float* __restrict__ dw,
-                                                             int splits, int nslabs, int Cout, int Cin, int R, int mode,
-                                                             float beta) {
-    __shared__ float tile[256 * 9];
+                                                             int splits, int nslabs, int Cout, int Cin, float beta) {
+    __shared__ float tile[256 * RR];
     const long long pairs = (long long)Cout * Cin;
     const long long slab_stride = pairs;
     const long long split_stride = slab_stride * nslabs;
-    const int RR = R * R;
     for (long long i0 = blockIdx.x * 256LL; i0 < pairs; i0 += (long long)gridDim.x * 256) {
         const long long i = i0 + threadIdx.x;
         if (i < pairs) {
+            float acc[RR];
 #pragma unroll
-            for (int rs = 0; rs < 9; ++rs) {
-                if (rs >= RR) break;
-                float acc = 0.f;
-                if (mode == MVAE_CONV_UP) {
-                    const int r = rs / 3, s_ = rs % 3;
-                    for (int a = 0; a < 2; ++a) {
-                        int ui = (a == 0) ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0);
-                        for (int b = 0; b < 2; ++b) {
-                            int vi = (b == 0) ? (s_ == 0 ? 0 : 1) : (s_ == 2 ? 1 : 0);
-                            int slab = ((a * 2 + b) * 2 + ui) * 2 + vi;
-                            const float* p = partial + slab * slab_stride + i;
-                            for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
+            for (int rs = 0; rs < RR; ++rs) acc[rs] = 0.f;
+            if (UP) {
+                // tap (r, s) of the 3x3 kernel receives the four parity slabs whose 2x2 footprint contains it
+                for (int k = 0; k < splits; ++k) {
+                    const float* pk = partial + k * split_stride + i;
+                    float v[16];
+#pragma unroll
+                    for (int sl = 0; sl < 16; ++sl) v[sl] = pk[sl * slab_stride];
+#pragma unroll
+                    for (int rs = 0; rs < 9; ++rs) {
+                        const int r = rs / 3, s_ = rs % 3;
+#pragma unroll
+                        for (int a = 0; a < 2; ++a) {
+                            const int ui = (a == 0) ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0);
+#pragma unroll
+                            for (int b = 0; b < 2; ++b) {
+                                const int vi = (b == 0) ? (s_ == 0 ? 0 : 1) : (s_ == 2 ? 1 : 0);
+                                acc[rs] += v[((a * 2 + b) * 2 + ui) * 2 + vi];
+                            }
                         }
                     }
-                } else {
-                    const float* p = partial + rs * slab_stride + i;
-                    for (int k = 0; k < splits; ++k) acc += p[k * split_stride];
                 }
-                tile[threadIdx.x * RR + rs] = acc;
+            } else {
+                int k = 0;
+                for (; k + 2 <= splits; k += 2) {
+                    const float* p0 = partial + k * split_stride + i;
+                    const float* p1 = p0 + split_stride;
+                    float v0[RR], v1[RR];
+#pragma unroll
+                    for (int rs = 0; rs < RR; ++rs) { v0[rs] = p0[rs * slab_stride]; v1[rs] = p1[rs * slab_stride]; }
+#pragma unroll
+                    for (int rs = 0; rs < RR; ++rs) acc[rs] += v0[rs] + v1[rs];
+                }
+                if (k < splits) {
+                    const float* p0 = partial + k * split_stride + i;
+#pragma unroll
+                    for (int rs = 0; rs < RR; ++rs) acc[rs] += p0[rs * slab_stride];
+                }
             }
+#pragma unroll
+            for (int rs = 0; rs < RR; ++rs) tile[threadIdx.x * RR + rs] = acc[rs];
         }
         __syncthreads();
-        long long span = (pairs - i0 < 256 ? pairs - i0 : 256) * RR;
+        const long long span = (pairs - i0 < 256 ? pairs - i0 : 256) * RR;
         float* o = dw + i0 * RR;
         for (int k = threadIdx.x; k < span; k += 256) o[k] = (beta != 0.f) ? fmaf(beta, o[k], tile[k]) : tile[k];
         __syncthreads();
@@ -197,7 +221,13 @@ int wgrad_finalize(const ConvGeom& g, const float* partial, float* dw, int split
     long long total = (long long)g.Cout * g.Cin;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    wgrad_finalize_kernel<<<blocks, 256, 0, st>>>(partial, dw, splits, conv_num_slabs(g), g.Cout, g.Cin, g.R, g.mode, beta);
+    const int ns = conv_num_slabs(g);
+    if (g.mode == MVAE_CONV_UP)
+        wgrad_finalize_kernel<9, true><<<blocks, 256, 0, st>>>(partial, dw, splits, ns, g.Cout, g.Cin, beta);
+    else if (g.R == 3)
+        wgrad_finalize_kernel<9, false><<<blocks, 256, 0, st>>>(partial, dw, splits, ns, g.Cout, g.Cin, beta);
+    else
+        wgrad_finalize_kernel<1, false><<<blocks, 256, 0, st>>>(partial, dw, splits, ns, g.Cout, g.Cin, beta);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

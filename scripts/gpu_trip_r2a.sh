@@ -36,6 +36,16 @@ for stage in $STAGES; do
       timeout 300 $CMD > gpurun_out/plain_attn.log 2>&1 &&
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"attn_|bgemm" -c 200 --csv --log-file gpurun_out/attn_launches.csv $CMD > gpurun_out/ncu_attnlist.log 2>&1
       echo "attnlist rc=$?" >> gpurun_out/rc.txt;;
+    attnsrc)   # source-level stall samples of the fused attention kernel: one backward launch at T = 256 and one at T = 64
+      timeout 300 $CMD > gpurun_out/plain_attnsrc.log 2>&1 || { echo "plain rc=$?" >> gpurun_out/rc.txt; continue; }
+      for spec in "b256 12" "b64 15" "f256 0"; do
+        set -- $spec
+        timeout 600 ncu --set full --import-source on --clock-control none -k regex:attn_fused -s $2 -c 1 -f -o gpurun_out/attnsrc_$1 $CMD > gpurun_out/ncu_attnsrc_$1.log 2>&1
+        echo "attnsrc $1 rc=$?" >> gpurun_out/rc.txt
+        ncu -i gpurun_out/attnsrc_$1.ncu-rep --page source --csv > gpurun_out/attnsrc_$1_source.csv 2>/dev/null
+        ncu -i gpurun_out/attnsrc_$1.ncu-rep --page raw --csv > gpurun_out/attnsrc_$1_raw.csv 2>/dev/null
+        rm -f gpurun_out/attnsrc_$1.ncu-rep
+      done;;
     list_c3)   # launch list of the 28x28 workload (eager launches: --graph off), one 256-image step
       C3CMD="python bench.py --workload c3 --graph off --steps 1 --warmup 1 --no-cpu-baseline --no-gpu-baseline --no-roofline --no-parity-check"
       timeout 300 $C3CMD > gpurun_out/plain_list_c3.log 2>&1 &&
