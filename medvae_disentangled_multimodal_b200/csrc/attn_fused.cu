@@ -47,7 +47,6 @@ struct AfDev {
     int kg;            // 64-token boxes per output-GEMM stage (a divisor of kboxes)
     int n_items;
     int o_alias;       // output accumulators alias the score columns (backward, T > 128)
-    int overlap;       // interleave the next item's score GEMMs with this item's output GEMMs (knob 14 = 1: off)
     uint32_t stage_bytes, tile_bytes;
     uint32_t col_s, col_dp, col_o0, col_o1;
     uint32_t idesc_s, idesc_o;
@@ -143,127 +142,103 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
     const uint32_t out_stage_bytes = (uint32_t)p.bno * 128u * (uint32_t)p.kg;
     const int kgroups = p.kboxes / p.kg;
 
-    // ---- the order in which pipeline stages are produced and consumed (identical in the producer and the MMA warp).
-    // Block li of a CTA's item list = the OUTPUT-GEMM stages of item li merged with the SCORE-GEMM stages of item li + 1:
-    // once the softmax epilogue of item li has consumed its score columns (pready), the next item's score GEMMs — bound
-    // by their operand loads — run under the output GEMMs of this one — bound by the epilogue draining the accumulators.
-    // Where the output accumulators alias the score columns (backward, T > 128) the two run one after the other.
-    const int n_mine = (p.n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-    const bool overlap = !p.o_alias && p.overlap != 0;
-
     if (warp == 0) {
         // ===================================================== TMA producer (whole warp: lane 0 owns the barriers, lanes
         // 0..n-1 issue the n boxes of a stage)
         int stage = 0; uint32_t phase = 0;
-        for (int li = -1; li < n_mine; ++li) {
-            int kindO = 0, imgO = 0, r0O = 0, kindS = 0, imgS = 0, r0S = 0, nsO = 0, noO = 0, nsS = 0, noS = 0;
-            AfScoreJob sjO[2], sjS[2]; AfOutJob ojO[2], ojS[2];
-            int nS = 0, nO = 0;
-            if (li >= 0) {
-                af_item(p, (int)blockIdx.x + li * (int)gridDim.x, kindO, imgO, r0O);
-                af_jobs(p, kindO, sjO, nsO, ojO, noO);
-                nO = noO * nchunks * kgroups;
-            }
-            if (li + 1 < n_mine) {
-                af_item(p, (int)blockIdx.x + (li + 1) * (int)gridDim.x, kindS, imgS, r0S);
-                af_jobs(p, kindS, sjS, nsS, ojS, noS);
-                nS = nsS * kiters;
-            }
-            int cs = 0, co = 0;
-            while (cs < nS || co < nO) {
-                const bool takeS = (co >= nO) || (overlap && cs < nS && (long long)cs * nO <= (long long)co * nS);
-                if (lane == 0) {
-                    mbar_wait(&empty[stage], phase ^ 1u);
-                    mbar_expect_tx(&full[stage], takeS ? score_stage_bytes : out_stage_bytes);
+        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+            int kind, img, r0, ns, no;
+            AfScoreJob sj[2]; AfOutJob oj[2];
+            af_item(p, it, kind, img, r0);
+            af_jobs(p, kind, sj, ns, oj, no);
+            for (int j = 0; j < ns; ++j) {
+                for (int kb = 0; kb < kiters; ++kb) {
+                    if (lane == 0) {
+                        mbar_wait(&empty[stage], phase ^ 1u);
+                        mbar_expect_tx(&full[stage], score_stage_bytes);
+                    }
+                    __syncwarp();
+                    uint8_t* a = sStage + (uint32_t)stage * p.stage_bytes;
+                    if (lane == 0) tma_load_3d(a, &tm.a[sj[j].a_dy], &full[stage], sj[j].ca + kb * 64, r0, img);
+                    else if (lane == 1) tma_load_3d(a + 16384, &tm.b[sj[j].b_dy], &full[stage], sj[j].cb + kb * 64, 0, img);
+                    if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                 }
-                __syncwarp();
-                uint8_t* st = sStage + (uint32_t)stage * p.stage_bytes;
-                if (takeS) {
-                    const int j = cs / kiters, kb = cs % kiters;
-                    if (lane == 0) tma_load_3d(st, &tm.a[sjS[j].a_dy], &full[stage], sjS[j].ca + kb * 64, r0S, imgS);
-                    else if (lane == 1) tma_load_3d(st + 16384, &tm.b[sjS[j].b_dy], &full[stage], sjS[j].cb + kb * 64, 0, imgS);
-                    ++cs;
-                } else {
-                    const int j = co / (nchunks * kgroups), nc = (co / kgroups) % nchunks, g = co % kgroups;
-                    if (lane < p.bno / 64)
-                        tma_load_3d(st + lane * (p.kg * 8192), &tm.n[ojO[j].b_dy], &full[stage],
-                                    ojO[j].cb + nc * p.bno + lane * 64, g * p.kg * 64, imgO);
-                    ++co;
+            }
+            for (int j = 0; j < no; ++j) {
+                for (int nc = 0; nc < nchunks; ++nc) {
+                    for (int g = 0; g < kgroups; ++g) {
+                        if (lane == 0) {
+                            mbar_wait(&empty[stage], phase ^ 1u);
+                            mbar_expect_tx(&full[stage], out_stage_bytes);
+                        }
+                        __syncwarp();
+                        uint8_t* b = sStage + (uint32_t)stage * p.stage_bytes;
+                        if (lane < p.bno / 64)
+                            tma_load_3d(b + lane * (p.kg * 8192), &tm.n[oj[j].b_dy], &full[stage],
+                                        oj[j].cb + nc * p.bno + lane * 64, g * p.kg * 64, img);
+                        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+                    }
                 }
-                if (++stage == p.stages) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == 1) {
         // ===================================================== MMA issuer
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
+            uint32_t n_local = 0;            // items done by this CTA (parity of tfull_s / pready)
             uint32_t uses[2] = {0, 0};       // uses of each output accumulator so far
-            int buf = 0;
-            for (int li = -1; li < n_mine; ++li) {
-                int kindO = 0, imgO = 0, r0O = 0, kindS = 0, imgS = 0, r0S = 0, nsO = 0, noO = 0, nsS = 0, noS = 0;
-                AfScoreJob sjO[2], sjS[2]; AfOutJob ojO[2], ojS[2];
-                int nS = 0, nO = 0;
-                if (li >= 0) {
-                    af_item(p, (int)blockIdx.x + li * (int)gridDim.x, kindO, imgO, r0O);
-                    af_jobs(p, kindO, sjO, nsO, ojO, noO);
-                    nO = noO * nchunks * kgroups;
-                }
-                if (li + 1 < n_mine) {
-                    af_item(p, (int)blockIdx.x + (li + 1) * (int)gridDim.x, kindS, imgS, r0S);
-                    af_jobs(p, kindS, sjS, nsS, ojS, noS);
-                    nS = nsS * kiters;
-                }
-                // both halves of the block need the softmax epilogue of item li to be through with its score columns
-                // (the output GEMMs read the tiles it wrote, the next score GEMMs overwrite the columns it read)
-                if (li >= 0) {
-                    mbar_wait(pready, (uint32_t)li & 1u);
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++n_local) {
+                int kind, img, r0, ns, no;
+                AfScoreJob sj[2]; AfOutJob oj[2];
+                af_item(p, it, kind, img, r0);
+                af_jobs(p, kind, sj, ns, oj, no);
+                if (p.o_alias) {   // the score columns double as output accumulators: the last item's must be drained
+                    mbar_wait(&tempty_o[0], (uses[0] & 1u) ^ 1u);
+                    mbar_wait(&tempty_o[1], (uses[1] & 1u) ^ 1u);
                     tc_fence_after();
                 }
-                int cs = 0, co = 0;
-                while (cs < nS || co < nO) {
-                    const bool takeS = (co >= nO) || (overlap && cs < nS && (long long)cs * nO <= (long long)co * nS);
-                    if (takeS) {
-                        const int j = cs / kiters, kb = cs % kiters;
-                        if (cs == 0 && p.o_alias) {   // the score columns double as output accumulators: wait for the drains
-                            mbar_wait(&tempty_o[0], (uses[0] & 1u) ^ 1u);
-                            mbar_wait(&tempty_o[1], (uses[1] & 1u) ^ 1u);
-                            tc_fence_after();
-                        }
+                for (int j = 0; j < ns; ++j) {
+                    for (int kb = 0; kb < kiters; ++kb) {
                         mbar_wait(&full[stage], phase);
                         tc_fence_after();
                         const uint32_t a0 = smem_u32(sStage + (uint32_t)stage * p.stage_bytes);
                         const uint32_t b0 = a0 + 16384u;
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            umma_bf16(tmem_base + sjS[j].col, smem_desc_sw128(a0 + k * 32, 16, 1024),
+                            umma_bf16(tmem_base + sj[j].col, smem_desc_sw128(a0 + k * 32, 16, 1024),
                                       smem_desc_sw128(b0 + k * 32, 16, 1024), p.idesc_s, (kb | k) != 0 ? 1u : 0u);
                         umma_commit(&empty[stage]);
-                        if (++cs == nS) umma_commit(tfull_s);
-                    } else {
-                        const int j = co / (nchunks * kgroups), g = co % kgroups;
-                        const uint32_t t0 = smem_u32(ojO[j].tile ? sTile1 : sTile0);
-                        if (g == 0) {
-                            buf = (int)((uses[0] + uses[1]) & 1u);
-                            mbar_wait(&tempty_o[buf], (uses[buf] & 1u) ^ 1u);
-                            tc_fence_after();
-                        }
-                        const uint32_t dcol = tmem_base + (buf ? p.col_o1 : p.col_o0);
-                        mbar_wait(&full[stage], phase);
-                        tc_fence_after();
-                        const uint32_t b0 = smem_u32(sStage + (uint32_t)stage * p.stage_bytes);
-                        for (int kc = 0; kc < p.kg; ++kc) {
-                            const int kt = g * p.kg + kc;          // 64-token box of the reduction
-#pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                umma_bf16(dcol, smem_desc_sw128(t0 + kt * 16384 + k * 32, 16, 1024),
-                                          smem_desc_sw128(b0 + kc * 8192 + k * 2048, (uint32_t)p.kg * 8192u, 1024),
-                                          p.idesc_o, (kt | k) != 0 ? 1u : 0u);
-                        }
-                        umma_commit(&empty[stage]);
-                        if (g == kgroups - 1) { umma_commit(&tfull_o[buf]); ++uses[buf]; }
-                        ++co;
+                        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                     }
-                    if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(tfull_s);
+                mbar_wait(pready, n_local & 1u);
+                tc_fence_after();
+                for (int j = 0; j < no; ++j) {
+                    const uint32_t t0 = smem_u32(oj[j].tile ? sTile1 : sTile0);
+                    for (int nc = 0; nc < nchunks; ++nc) {
+                        const int buf = (int)((uses[0] + uses[1]) & 1u);
+                        mbar_wait(&tempty_o[buf], (uses[buf] & 1u) ^ 1u);
+                        tc_fence_after();
+                        const uint32_t dcol = tmem_base + (buf ? p.col_o1 : p.col_o0);
+                        for (int g = 0; g < kgroups; ++g) {
+                            mbar_wait(&full[stage], phase);
+                            tc_fence_after();
+                            const uint32_t b0 = smem_u32(sStage + (uint32_t)stage * p.stage_bytes);
+                            for (int kc = 0; kc < p.kg; ++kc) {
+                                const int kt = g * p.kg + kc;          // 64-token box of the reduction
+#pragma unroll
+                                for (int k = 0; k < 4; ++k)
+                                    umma_bf16(dcol, smem_desc_sw128(t0 + kt * 16384 + k * 32, 16, 1024),
+                                              smem_desc_sw128(b0 + kc * 8192 + k * 2048, (uint32_t)p.kg * 8192u, 1024),
+                                              p.idesc_o, (kt | k) != 0 ? 1u : 0u);
+                            }
+                            umma_commit(&empty[stage]);
+                            if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+                        }
+                        umma_commit(&tfull_o[buf]);
+                        ++uses[buf];
+                    }
                 }
             }
         }
@@ -499,7 +474,6 @@ static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t s
         d.col_dp = 256; d.col_o0 = 0; d.col_o1 = 128; d.o_alias = 1;
     }
     d.n_items = d.B * d.mtiles * (d.bwd ? 2 : 1);
-    d.overlap = debug_knob(14) == 0 ? 1 : 0;
     const long long fixed = (long long)d.tile_bytes * (d.bwd ? 2 : 1) + 2048 /* sStat */ + 256 /* barriers */;
     const long long budget = 232448;    // 227 KB of dynamic shared memory per CTA on sm_100
     int stages = (int)((budget - fixed) / d.stage_bytes);
