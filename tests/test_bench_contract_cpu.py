@@ -125,3 +125,32 @@ def test_oracle_port_matches_the_reference_at_the_real_widths(wl):
     for name, v in ref["param_grad_norms"].items():
         got = float(grads[name].double().norm())
         assert abs(got - v) <= 1e-4 * max(v, 1e-3 * ref["grad_norm"]), (name, got, v)
+
+
+def test_round2_launch_list_at_the_benchmarked_shape_agrees_with_the_bench_kernel_table():
+    """the same cross-check for round 2, where the ncu launch list was taken at the BENCHMARKED launch shape (one
+    1024-image pass per step, three steps in the list): kernel shares against the CUDA-event table of a bench line, and
+    the per-launch DRAM traffic in profiles/roofline_traffic.json against the line's algorithmic bytes"""
+    import csv
+    import re
+    prof = os.path.join(ROOT, "profiles")
+    rows = list(csv.DictReader(open(os.path.join(prof, "r2a_launches.csv"))))
+    total = sum(float(r["ns"]) for r in rows)
+    share = lambda pat: sum(float(r["ns"]) for r in rows if re.search(pat, r["kernel"])) / total
+    ncu = {"conv": share(r"conv_(gather|reduce)_umma"), "gn": share(r"gn_(apply|bwd)")}
+    line = json.loads(open(os.path.join(prof, "r2h_bench_c4.json")).read().strip().splitlines()[-1])
+    k, step = line["kernels"], line["ms_per_step"]
+    ev = {"conv": sum(k[n]["ms"] for n in ("conv_fprop_umma", "conv_wgrad_umma", "conv_dgrad_umma")) / step,
+          "gn": (k["groupnorm_fwd"]["ms"] + k["groupnorm_bwd"]["ms"]) / step}
+    for name in ncu:
+        assert abs(ncu[name] - ev[name]) < 0.08, (name, ncu[name], ev[name])
+    assert sum(float(r["ns"]) for r in rows if r["kernel"].startswith("mvae::")) / total > 0.95
+    roof = line["roofline"]
+    assert abs(roof["frac"] - roof["achieved"] / roof["peak"]) < 1e-3 and roof["bound"] == "tensor"
+    # real (unpadded) channel counts: 2 x 1024 images x (83.97 - 0.79) GFLOP of conv work / 176 gather launches
+    assert abs(roof["algorithmic_gflop_per_launch"] - 967.9) < 1.0
+    traffic = json.load(open(os.path.join(prof, "roofline_traffic.json")))
+    assert roof["traffic"] == traffic["dram_bytes_per_launch"] > 5e8
+    assert line["gpu_baseline"]["value"] > 0 and line["value"] > 4 * line["gpu_baseline"]["value"]
+    assert line["parity_check"]["ok"] is True and line["cpu_baseline"]["kind"] == "reference"
+    assert {h["kernel"] for h in line["roofline_hbm"]} >= {"groupnorm_silu_fwd+bwd", "clip+adamw"}
