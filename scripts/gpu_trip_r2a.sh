@@ -61,11 +61,12 @@ for stage in $STAGES; do
       cap gf -k regex:conv_gather_umma -s 2 -c 16       # forward gather launches (fprop incl. the GN-statistics epilogue)
       cap gb -k regex:conv_gather_umma -s 150 -c 14     # backward gather launches (dgrad incl. the GN-backward epilogue)
       cap wg -k regex:conv_reduce_umma -s 2 -c 10
-      cap gn -k regex:"gn_(apply_pre|bwd_pre)" -s 4 -c 8
-      cap at -k regex:"bgemm_umma|attn_" -s 0 -c 12
+      cap gn -k regex:"gn_apply_pre" -s 4 -c 6
+      cap gnb -k regex:"gn_bwd_pre" -s 4 -c 6
+      cap at -k regex:"bgemm_umma|attn_" -s 0 -c 36
       cap opt -k regex:"adamw_chunked|grad_sqnorm_chunked" -s 0 -c 2
       cap loss -k regex:"reparam_kl|recon_loss|kl_bwd|scale_kernel" -s 0 -c 5
-      cap misc -k regex:"pack_weights|wgrad_finalize|colsum_partial" -s 40 -c 6
+      cap misc -k regex:"pack_weights|wgrad_finalize|colsum_partial" -s 20 -c 8
       ;;
   esac
 done
