@@ -49,6 +49,8 @@ struct AfDev {
     int o_alias;       // output accumulators alias the score columns (backward, T > 128)
     uint32_t stage_bytes, tile_bytes;
     uint32_t col_s, col_dp, col_o0, col_o1;
+    int ts;            // P / dS go back to TENSOR memory as the A operand of the output GEMMs (no shared-memory tiles)
+    uint32_t col_p, col_ds;   // their first (packed bf16 pair) columns
     uint32_t idesc_s, idesc_o;
     float alpha, alpha_log2e;
     bf16* out;         // forward [B][T][C]
@@ -95,6 +97,15 @@ __device__ __forceinline__ void af_tile_store8(uint8_t* tile, int row, int col, 
     const int chunk = col >> 6, unit = (col & 63) >> 3;
     uint8_t* dst = tile + chunk * 16384 + row * 128 + ((unit ^ (row & 7)) << 4);
     *reinterpret_cast<uint4*>(dst) = v.raw;
+}
+
+// 8 floats -> 4 packed bf16 pairs
+__device__ __forceinline__ void af_pack8(uint32_t* dst, const float* f) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+        dst[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
 }
 
 __global__ void __launch_bounds__(AF_THREADS, 1)
@@ -228,10 +239,15 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                             for (int kc = 0; kc < p.kg; ++kc) {
                                 const int kt = g * p.kg + kc;          // 64-token box of the reduction
 #pragma unroll
-                                for (int k = 0; k < 4; ++k)
-                                    umma_bf16(dcol, smem_desc_sw128(t0 + kt * 16384 + k * 32, 16, 1024),
-                                              smem_desc_sw128(b0 + kc * 8192 + k * 2048, (uint32_t)p.kg * 8192u, 1024),
-                                              p.idesc_o, (kt | k) != 0 ? 1u : 0u);
+                                for (int k = 0; k < 4; ++k) {
+                                    const uint64_t bd = smem_desc_sw128(b0 + kc * 8192 + k * 2048, (uint32_t)p.kg * 8192u, 1024);
+                                    if (p.ts)
+                                        umma_bf16_ts(dcol, tmem_base + (oj[j].tile ? p.col_ds : p.col_p) + (uint32_t)(kt * 32 + k * 8),
+                                                     bd, p.idesc_o, (kt | k) != 0 ? 1u : 0u);
+                                    else
+                                        umma_bf16(dcol, smem_desc_sw128(t0 + kt * 16384 + k * 32, 16, 1024), bd, p.idesc_o,
+                                                  (kt | k) != 0 ? 1u : 0u);
+                                }
                             }
                             umma_commit(&empty[stage]);
                             if (++stage == p.stages) { stage = 0; phase ^= 1u; }
@@ -288,7 +304,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                 float sum = 0.f;
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
-                    uint32_t v[32];
+                    uint32_t v[32], pk[16];
                     if (c0 < p.Tp) { tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, v); tmem_ld_wait(); }
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
@@ -301,15 +317,17 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                             f[j] = e;
                             sum += e;
                         }
-                        af_tile_store8(sTile0, row, c0 + g * 8, f);
+                        if (p.ts) af_pack8(pk + g * 4, f);
+                        else af_tile_store8(sTile0, row, c0 + g * 8, f);
                     }
+                    if (p.ts) tmem_st_32x16(lane_addr + p.col_p + (uint32_t)(c0 >> 1), pk);
                 }
                 inv_l = 1.f / sum;
                 if (valid) p.lse2[tok0 + grow] = mx + log2f(sum);
             } else if (kind == AF_BWD_Q) {
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
-                    uint32_t s[32], d[32];
+                    uint32_t s[32], d[32], pk[16], pk2[16];
                     if (c0 < p.Tp) {
                         tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, s);
                         tmem_ld_32x32(lane_addr + p.col_dp + (uint32_t)c0, d);
@@ -324,13 +342,15 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                             const float pr = exp2f(__uint_as_float(s[g * 8 + j]) * p.alpha_log2e - row_lse);
                             f[j] = (c < p.T) ? pr * (__uint_as_float(d[g * 8 + j]) - row_d) * p.alpha : 0.f;
                         }
-                        af_tile_store8(sTile1, row, c0 + g * 8, f);
+                        if (p.ts) af_pack8(pk + g * 4, f);
+                        else af_tile_store8(sTile1, row, c0 + g * 8, f);
                     }
+                    if (p.ts) tmem_st_32x16(lane_addr + p.col_ds + (uint32_t)(c0 >> 1), pk);
                 }
             } else {
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
-                    uint32_t s[32], d[32];
+                    uint32_t s[32], d[32], pk[16], pk2[16];
                     if (c0 < p.Tp) {
                         tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, s);
                         tmem_ld_32x32(lane_addr + p.col_dp + (uint32_t)c0, d);
@@ -346,12 +366,20 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                             fp[j] = pr;
                             fd[j] = (c < p.T) ? pr * (__uint_as_float(d[g * 8 + j]) - sStat[256 + c]) * p.alpha : 0.f;
                         }
-                        af_tile_store8(sTile0, row, c0 + g * 8, fp);
-                        af_tile_store8(sTile1, row, c0 + g * 8, fd);
+                        if (p.ts) { af_pack8(pk + g * 4, fp); af_pack8(pk2 + g * 4, fd); }
+                        else {
+                            af_tile_store8(sTile0, row, c0 + g * 8, fp);
+                            af_tile_store8(sTile1, row, c0 + g * 8, fd);
+                        }
+                    }
+                    if (p.ts) {
+                        tmem_st_32x16(lane_addr + p.col_p + (uint32_t)(c0 >> 1), pk);
+                        tmem_st_32x16(lane_addr + p.col_ds + (uint32_t)(c0 >> 1), pk2);
                     }
                 }
             }
             // the tiles go to the tensor core through the async proxy; the score columns may be overwritten next
+            if (p.ts) tmem_st_wait();
             tc_fence_before();
             fence_proxy_async_smem();
             __syncwarp();
@@ -466,7 +494,16 @@ static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t s
     d.idesc_s = make_idesc_bf16(128, d.Tp, 0, 0);
     d.idesc_o = make_idesc_bf16(128, d.bno, 0, 1);
     d.col_s = 0;
-    if (!d.bwd) {
+    d.ts = debug_knob(15) == 1 ? 1 : 0;       // opt-in until measured
+    d.col_p = 0; d.col_ds = 256;
+    if (d.ts) {
+        // scores at [0, Tp) and [256, 256 + Tp); P / dS are packed IN PLACE into the lower halves of those ranges, the
+        // output accumulators take the upper halves (still holding score columns when Tp > 128: o_alias)
+        d.tile_bytes = 0;
+        d.col_dp = 256;
+        if (!d.bwd) { d.col_o0 = 256; d.col_o1 = 384; d.o_alias = 0; }
+        else { d.col_o0 = 128; d.col_o1 = 384; d.o_alias = d.Tp > 128 ? 1 : 0; }
+    } else if (!d.bwd) {
         d.col_dp = 0; d.col_o0 = 256; d.col_o1 = 384; d.o_alias = 0;
     } else if (d.Tp <= 128) {
         d.col_dp = 128; d.col_o0 = 256; d.col_o1 = 384; d.o_alias = 0;
