@@ -108,6 +108,7 @@ __device__ __forceinline__ void af_pack8(uint32_t* dst, const float* f) {
     }
 }
 
+template <bool TS>
 __global__ void __launch_bounds__(AF_THREADS, 1)
 attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ AfDev p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -241,7 +242,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
 #pragma unroll
                                 for (int k = 0; k < 4; ++k) {
                                     const uint64_t bd = smem_desc_sw128(b0 + kc * 8192 + k * 2048, (uint32_t)p.kg * 8192u, 1024);
-                                    if (p.ts)
+                                    if constexpr (TS)
                                         umma_bf16_ts(dcol, tmem_base + (oj[j].tile ? p.col_ds : p.col_p) + (uint32_t)(kt * 32 + k * 8),
                                                      bd, p.idesc_o, (kt | k) != 0 ? 1u : 0u);
                                     else
@@ -317,10 +318,10 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                             f[j] = e;
                             sum += e;
                         }
-                        if (p.ts) af_pack8(pk + g * 4, f);
+                        if constexpr (TS) af_pack8(pk + g * 4, f);
                         else af_tile_store8(sTile0, row, c0 + g * 8, f);
                     }
-                    if (p.ts) tmem_st_32x16(lane_addr + p.col_p + (uint32_t)(c0 >> 1), pk);
+                    if constexpr (TS) tmem_st_32x16(lane_addr + p.col_p + (uint32_t)(c0 >> 1), pk);
                 }
                 inv_l = 1.f / sum;
                 if (valid) p.lse2[tok0 + grow] = mx + log2f(sum);
@@ -342,10 +343,10 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                             const float pr = exp2f(__uint_as_float(s[g * 8 + j]) * p.alpha_log2e - row_lse);
                             f[j] = (c < p.T) ? pr * (__uint_as_float(d[g * 8 + j]) - row_d) * p.alpha : 0.f;
                         }
-                        if (p.ts) af_pack8(pk + g * 4, f);
+                        if constexpr (TS) af_pack8(pk + g * 4, f);
                         else af_tile_store8(sTile1, row, c0 + g * 8, f);
                     }
-                    if (p.ts) tmem_st_32x16(lane_addr + p.col_ds + (uint32_t)(c0 >> 1), pk);
+                    if constexpr (TS) tmem_st_32x16(lane_addr + p.col_ds + (uint32_t)(c0 >> 1), pk);
                 }
             } else {
 #pragma unroll 1
@@ -366,20 +367,20 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                             fp[j] = pr;
                             fd[j] = (c < p.T) ? pr * (__uint_as_float(d[g * 8 + j]) - sStat[256 + c]) * p.alpha : 0.f;
                         }
-                        if (p.ts) { af_pack8(pk + g * 4, fp); af_pack8(pk2 + g * 4, fd); }
+                        if constexpr (TS) { af_pack8(pk + g * 4, fp); af_pack8(pk2 + g * 4, fd); }
                         else {
                             af_tile_store8(sTile0, row, c0 + g * 8, fp);
                             af_tile_store8(sTile1, row, c0 + g * 8, fd);
                         }
                     }
-                    if (p.ts) {
+                    if constexpr (TS) {
                         tmem_st_32x16(lane_addr + p.col_p + (uint32_t)(c0 >> 1), pk);
                         tmem_st_32x16(lane_addr + p.col_ds + (uint32_t)(c0 >> 1), pk2);
                     }
                 }
             }
             // the tiles go to the tensor core through the async proxy; the score columns may be overwritten next
-            if (p.ts) tmem_st_wait();
+            if constexpr (TS) tmem_st_wait();
             tc_fence_before();
             fence_proxy_async_smem();
             __syncwarp();
@@ -521,11 +522,13 @@ static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t s
     if (smem < 120 * 1024) smem = 120 * 1024;   // one CTA per SM: every CTA allocates all 512 TMEM columns
     static bool attr_set = false;
     if (!attr_set) {
-        MVAE_CUDA(cudaFuncSetAttribute(attn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+        MVAE_CUDA(cudaFuncSetAttribute(attn_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+        MVAE_CUDA(cudaFuncSetAttribute(attn_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
         attr_set = true;
     }
     int grid = d.n_items < af_num_sms() ? d.n_items : af_num_sms();
-    attn_fused_kernel<<<grid, AF_THREADS, (size_t)smem, st>>>(tm, d);
+    if (d.ts) attn_fused_kernel<true><<<grid, AF_THREADS, (size_t)smem, st>>>(tm, d);
+    else attn_fused_kernel<false><<<grid, AF_THREADS, (size_t)smem, st>>>(tm, d);
     MVAE_LAUNCH_CHECK();
     return 0;
 }

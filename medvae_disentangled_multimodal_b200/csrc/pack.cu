@@ -81,6 +81,17 @@ int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot
 // range of the launch's 32 x 32 tiles; a job may write into a window of a wider / zero-padded packed operand (q,k,v fused
 // along Cout; conv_in / conv_out padded to one tensor-core tile: cin_pitch / ctot are the operand's dimensions) and also
 // refreshes the fp32 bias vector the conv kernels read.
+// two consecutive elements in one store (the destination is 4-byte aligned: even column, even row pitch), else two
+template <typename T> __device__ __forceinline__ void store2(T* dst, float a, float b);
+template <> __device__ __forceinline__ void store2<bf16>(bf16* dst, float a, float b) {
+    if ((reinterpret_cast<uintptr_t>(dst) & 3) == 0) *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(a, b);
+    else { dst[0] = __float2bfloat16_rn(a); dst[1] = __float2bfloat16_rn(b); }
+}
+template <> __device__ __forceinline__ void store2<float>(float* dst, float a, float b) {
+    if ((reinterpret_cast<uintptr_t>(dst) & 7) == 0) *reinterpret_cast<float2*>(dst) = make_float2(a, b);
+    else { dst[0] = a; dst[1] = b; }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) pack_weights_batched_kernel(const mvae_pack_job* __restrict__ jobs, int n_jobs,
                                                                    int total_tiles) {
@@ -124,12 +135,21 @@ __global__ void __launch_bounds__(256) pack_weights_batched_kernel(const mvae_pa
                     for (int q = slo; q <= shi; ++q) v += e[r * 3 + q];
                 return v;
             };
-            if (wf && lane < nci)
-                for (int co = warp; co < nco; co += 8)
-                    wf[((long long)slab * Ctot + co_off + co0 + co) * CinP + ci0 + lane] = from_f<T>(value(co, lane));
-            if (wd && lane < nco)
-                for (int ci = warp; ci < nci; ci += 8)
-                    wd[((long long)slab * CinP + ci0 + ci) * Ctot + co_off + co0 + lane] = from_f<T>(value(lane, ci));
+            // two adjacent elements per lane, two rows per warp instruction: 4-byte stores (the LSU handles 2-byte lanes
+            // at a fraction of its rate: the one-element-per-lane version ran at 1.2 TB/s, profiles/r2k_ncu_full.csv)
+            const int half = lane >> 4, e2 = (lane & 15) * 2;
+            if (wf)
+                for (int co = warp * 2 + half; co < nco; co += 16) {
+                    T* dst = wf + ((long long)slab * Ctot + co_off + co0 + co) * CinP + ci0 + e2;
+                    if (e2 + 1 < nci) store2<T>(dst, value(co, e2), value(co, e2 + 1));
+                    else if (e2 < nci) dst[0] = from_f<T>(value(co, e2));
+                }
+            if (wd)
+                for (int ci = warp * 2 + half; ci < nci; ci += 16) {
+                    T* dst = wd + ((long long)slab * CinP + ci0 + ci) * Ctot + co_off + co0 + e2;
+                    if (e2 + 1 < nco) store2<T>(dst, value(e2, ci), value(e2 + 1, ci));
+                    else if (e2 < nco) dst[0] = from_f<T>(value(e2, ci));
+                }
         }
         __syncthreads();
     }
