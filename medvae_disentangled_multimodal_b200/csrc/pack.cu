@@ -115,9 +115,30 @@ __global__ void __launch_bounds__(256) pack_weights_batched_kernel(const mvae_pa
         const int tiles_ci = (Cin + PK_T - 1) / PK_T;
         const int co0 = (tile / tiles_ci) * PK_T, ci0 = (tile % tiles_ci) * PK_T;
         const int nco = Cout - co0 < PK_T ? Cout - co0 : PK_T, nci = Cin - ci0 < PK_T ? Cin - ci0 : PK_T;
-        for (int r = warp; r < nco; r += 8) {
-            const float* src = w + ((long long)(co0 + r) * Cin + ci0) * RR;
-            for (int k = lane; k < nci * RR; k += 32) s[r][k] = src[k];
+        {
+            // all (up to 4 rows x 9) loads of a thread are issued before the first shared-memory store: a loop with a
+            // runtime trip count exposed one DRAM round trip per iteration (29 us per tile, profiles/r2k_ncu_full.csv)
+            float v[4][9];
+            const int n = nci * RR;
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr) {
+                const int r = warp + 8 * rr;
+                const float* src = w + ((long long)(co0 + r) * Cin + ci0) * RR;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) {
+                    const int k = lane + 32 * i;
+                    v[rr][i] = (r < nco && k < n) ? __ldg(src + k) : 0.f;
+                }
+            }
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr) {
+                const int r = warp + 8 * rr;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) {
+                    const int k = lane + 32 * i;
+                    if (r < nco && k < n) s[r][k] = v[rr][i];
+                }
+            }
         }
         __syncthreads();
         for (int slab = 0; slab < j.n_slabs; ++slab) {

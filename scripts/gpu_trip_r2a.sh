@@ -33,8 +33,8 @@ for stage in $STAGES; do
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline > gpurun_out/bench_pairs128_on.log 2>&1; echo "ab on rc=$?" >> gpurun_out/rc.txt
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob 13=1 > gpurun_out/bench_pairs128_off.log 2>&1; echo "ab off rc=$?" >> gpurun_out/rc.txt;;
     ab_ts)  # A/B on one box: attention with P / dS in tensor memory (knob 15 = 1) against the shared-memory tiles
-      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob 15=1 > gpurun_out/bench_attn_ts_on.log 2>&1; echo "ts on rc=$?" >> gpurun_out/rc.txt
-      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline > gpurun_out/bench_attn_ts_off.log 2>&1; echo "ts off rc=$?" >> gpurun_out/rc.txt;;
+      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline > gpurun_out/bench_attn_ts_on.log 2>&1; echo "ts on rc=$?" >> gpurun_out/rc.txt
+      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob 15=1 > gpurun_out/bench_attn_ts_off.log 2>&1; echo "ts off rc=$?" >> gpurun_out/rc.txt;;
     attnlist)
       timeout 300 $CMD > gpurun_out/plain_attn.log 2>&1 &&
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"attn_|bgemm" -c 200 --csv --log-file gpurun_out/attn_launches.csv $CMD > gpurun_out/ncu_attnlist.log 2>&1

@@ -158,15 +158,15 @@ def test_groupnorm_silu(shape, dtype, silu):
                                    # tcgen05 path in bf16 (C % 64 == 0): ragged T = 9, 49, 196 and full tiles
                                    (5, 3, 3, 64), (2, 7, 7, 64), (3, 7, 7, 512), (2, 14, 14, 256), (2, 16, 16, 128),
                                    (2, 16, 16, 512), (3, 8, 8, 1024), (1, 12, 20, 192)])
-@pytest.mark.parametrize("dtype,path", [(torch.float32, "simt"), (torch.bfloat16, "fused"), (torch.bfloat16, "fused-ts"),
+@pytest.mark.parametrize("dtype,path", [(torch.float32, "simt"), (torch.bfloat16, "fused"), (torch.bfloat16, "fused-smem"),
                                         (torch.bfloat16, "bgemm")],
-                         ids=["fp32", "bf16-fused", "bf16-fused-ts", "bf16-bgemm"])
+                         ids=["fp32", "bf16-fused", "bf16-fused-smem", "bf16-bgemm"])
 def test_attention_core(shape, dtype, path):
     """bf16: the fused persistent tcgen05 kernel (one launch per direction, probabilities recomputed in the backward) and,
     with debug knob 11 set, the batched-GEMM path it replaced (P kept as [B][T][T]); fp32: the SIMT verification path"""
     L, ops = _mods()
     L.lib().mvae_set_debug(11, 1 if path == "bgemm" else 0)
-    L.lib().mvae_set_debug(15, 1 if path == "fused-ts" else 0)      # P / dS as the A operand from tensor memory
+    L.lib().mvae_set_debug(15, 1 if path == "fused-smem" else 0)    # P / dS in shared-memory tiles instead of tensor memory
     try:
         _attention_case(shape, dtype, path)
     finally:
