@@ -236,6 +236,7 @@ class DisentangledConditionalVAE(BaseVAE):
         sep, con = self._aux_losses(z, modality_indices)
         zeros, ones = self._prior_constants(mean)
         prior = Normal(zeros, ones, validate_args=False)
+        prior._mvae_std_normal = True      # losses._is_standard_normal
         posterior = Normal(mean, std, validate_args=False)    # std already clamped to [1e-6, 10] (:426-427)
         posterior._mvae_logvar = logvar
         posterior._mvae_kl_sum = kl

@@ -84,6 +84,13 @@ class VAELoss(nn.Module):
 
 
 def _is_standard_normal(prior) -> bool:
-    # the models in this package share cached zeros/ones tensors for the prior; anything else is
-    # checked by value only when it is cheap (host tensors), otherwise trusted.
-    return True
+    """the kernels implement KL(posterior || N(0, 1)) in closed form.  Priors built by this package's models carry a
+    marker (their loc / scale are the models' cached zeros / ones); any other prior is checked by value — one
+    device->host read, paid only by foreign callers — and anything but N(0, 1) is refused by the caller."""
+    if getattr(prior, "_mvae_std_normal", False):
+        return True
+    loc, scale = getattr(prior, "loc", None), getattr(prior, "scale", None)
+    if loc is None or scale is None:
+        return False
+    with torch.no_grad():
+        return bool(((loc == 0).all() & (scale == 1).all()).item())

@@ -189,6 +189,7 @@ class BaseVAE(nn.Module):
     def _make_outputs(self, reconstruction, mean, logvar, z, std, kl, return_latents, extra=None):
         zeros, ones = self._prior_constants(mean)
         prior = Normal(zeros, ones, validate_args=False)
+        prior._mvae_std_normal = True      # losses._is_standard_normal
         posterior = Normal(mean, std, validate_args=False)
         # side channel for VAELoss: the raw logvar and the KL partial sum the fused kernel produced
         posterior._mvae_logvar = logvar

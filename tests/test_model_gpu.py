@@ -282,3 +282,20 @@ def test_disentangled_api_surface():
     assert out2["reconstruction"].shape == (4, 3, 28, 28)
     with pytest.raises(ValueError):
         M.DisentangledVAELoss("bce")
+
+
+def test_vae_loss_refuses_a_prior_that_is_not_standard_normal():
+    """VAELoss computes KL(posterior || N(0, 1)) in closed form: the models' own prior passes by its marker, a foreign
+    N(0, 1) prior passes by value, anything else is refused instead of being silently treated as N(0, 1)"""
+    import medvae_disentangled_multimodal_b200 as M
+    from torch.distributions import Normal
+    model = M.BaseVAE(1, 4, 16, [1, 2], 1, [], resolution=16, compute_dtype="fp32").to(DEV)
+    x = torch.randn(2, 1, 16, 16, device=DEV)
+    out = model(x)
+    crit = M.VAELoss("mse", 1.0, 1.0)
+    kw = dict(inputs=x, reconstructions=out["reconstruction"], posteriors=out["posterior"])
+    a = crit(priors=out["prior"], **kw)
+    b = crit(priors=Normal(torch.zeros_like(out["mean"]), torch.ones_like(out["mean"])), **kw)
+    assert float(a["loss"]) == float(b["loss"])
+    with pytest.raises(NotImplementedError):
+        crit(priors=Normal(torch.zeros_like(out["mean"]), 2.0 * torch.ones_like(out["mean"])), **kw)
