@@ -17,8 +17,8 @@ void set_error(const char* fmt, ...) {
 }
 static unsigned long long g_launches = 0;
 void count_launch() { __atomic_fetch_add(&g_launches, 1ull, __ATOMIC_RELAXED); }
-static int g_knobs[16] = {0};
-int debug_knob(int key) { return (key >= 0 && key < 16) ? g_knobs[key] : 0; }
+static int g_knobs[32] = {0};
+int debug_knob(int key) { return (key >= 0 && key < 32) ? g_knobs[key] : 0; }
 
 // implemented in the other translation units
 int pack_weights(const ConvGeom& g, const float* w, void* wf, void* wd, int Ctot, int co_off, int dtype, cudaStream_t st);
@@ -149,7 +149,7 @@ int mvae_device_ok(void) {
 uint64_t mvae_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
 int mvae_set_debug(int key, int value) {
-    MVAE_CHECK(key >= 0 && key < 16, "debug key out of range");
+    MVAE_CHECK(key >= 0 && key < 32, "debug key out of range");
     g_knobs[key] = value;
     return 0;
 }

@@ -578,7 +578,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 }
             } else {
                 // this warp's half of the tile's columns: XCH chunks of 32
-                constexpr int CW = BN / 2, XCH = CW / 32;
+                constexpr int CW = BN / CS, XCH = CW / 32;
                 const int chalf = (warp - 2) >> 2;
                 // are all valid rows of this warp in one image?  (then one atomic per value per warp)
                 const unsigned vm = __ballot_sync(0xffffffffu, valid);
@@ -714,7 +714,16 @@ static int launch_gather_epi(const GatherTmaps& tm, GatherDev& d, cudaStream_t s
 }
 template <int BN, int MT, int CG = 1>
 static int launch_gather(const GatherTmaps& tm, GatherDev& d, int epi, cudaStream_t st) {
-    if (epi == EPI_GN_STATS) return launch_gather_epi<BN, EPI_GN_STATS, MT, CG>(tm, d, st);
+    if (epi == EPI_GN_STATS) {
+        if constexpr (BN == 128) {
+            // the 64x64 layers (K = 9 x 128): the MMAs of a CTA tile are as short as its epilogue, four column strips
+            // (16 epilogue warps) instead of two (knob 16: 1 = never, 2 = always)
+            const long long mma_cycles = (long long)d.taps.ntaps * d.kchunks * 4 * MT * (BN / 2);
+            const int knob = debug_knob(16);
+            if (knob == 2 || (knob == 0 && mma_cycles <= 12288)) return launch_gather_epi<BN, EPI_GN_STATS, MT, CG, 4>(tm, d, st);
+        }
+        return launch_gather_epi<BN, EPI_GN_STATS, MT, CG>(tm, d, st);
+    }
     if (epi == EPI_GN_BWD) {
         if constexpr (BN >= 128) {
             // MMA cycles of one CTA tile against the ~25k cycles the 8-warp epilogue takes for it (knob 9: 1 = never, 2 = always)

@@ -35,6 +35,9 @@ for stage in $STAGES; do
     ab_ts)  # A/B on one box: attention with P / dS in tensor memory (knob 15 = 1) against the shared-memory tiles
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline > gpurun_out/bench_attn_ts_on.log 2>&1; echo "ts on rc=$?" >> gpurun_out/rc.txt
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob 15=1 > gpurun_out/bench_attn_ts_off.log 2>&1; echo "ts off rc=$?" >> gpurun_out/rc.txt;;
+    ab_cs)  # A/B on one box: 16 epilogue warps for the GN-statistics fprop on 128-channel tiles (knob 16 = 1: off)
+      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline > gpurun_out/bench_stats16_on.log 2>&1; echo "cs on rc=$?" >> gpurun_out/rc.txt
+      timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob 16=1 > gpurun_out/bench_stats16_off.log 2>&1; echo "cs off rc=$?" >> gpurun_out/rc.txt;;
     attnlist)
       timeout 300 $CMD > gpurun_out/plain_attn.log 2>&1 &&
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"attn_|bgemm" -c 200 --csv --log-file gpurun_out/attn_launches.csv $CMD > gpurun_out/ncu_attnlist.log 2>&1
