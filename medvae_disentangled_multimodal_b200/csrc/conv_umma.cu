@@ -716,11 +716,10 @@ template <int BN, int MT, int CG = 1>
 static int launch_gather(const GatherTmaps& tm, GatherDev& d, int epi, cudaStream_t st) {
     if (epi == EPI_GN_STATS) {
         if constexpr (BN == 128) {
-            // the 64x64 layers (K = 9 x 128): the MMAs of a CTA tile are as short as its epilogue, four column strips
-            // (16 epilogue warps) instead of two (knob 16: 1 = never, 2 = always)
-            const long long mma_cycles = (long long)d.taps.ntaps * d.kchunks * 4 * MT * (BN / 2);
-            const int knob = debug_knob(16);
-            if (knob == 2 || (knob == 0 && mma_cycles <= 12288)) return launch_gather_epi<BN, EPI_GN_STATS, MT, CG, 4>(tm, d, st);
+            // OPT-IN (knob 16 = 2): four column strips (16 epilogue warps) instead of two for the statistics epilogue of
+            // the 64x64 layers.  Measured on one box (trip r2n): fprop 62.7 ms with, 62.6 ms without — unlike the
+            // GroupNorm-backward epilogue this one is not what holds the 128-channel tiles at ~50 % tensor-pipe.
+            if (debug_knob(16) == 2) return launch_gather_epi<BN, EPI_GN_STATS, MT, CG, 4>(tm, d, st);
         }
         return launch_gather_epi<BN, EPI_GN_STATS, MT, CG>(tm, d, st);
     }
