@@ -469,6 +469,18 @@ def test_conv_umma_cta_pair_128_channel_tiles():
         L.lib().mvae_set_debug(13, 0)
 
 
+@pytest.mark.umma
+def test_conv_fprop_gn_statistics_sixteen_epilogue_warps():
+    """the opt-in variant (knob 16 = 2): four column strips for the statistics epilogue of 128-channel tiles"""
+    L, _ = _mods()
+    L.lib().mvae_set_debug(16, 2)
+    try:
+        for case in [(77, 32, 32, 128, 128, 3, 0, 32), (2, 64, 64, 128, 128, 3, 0, 32), (2, 32, 32, 128, 128, 3, 1, 32)]:
+            test_conv_fprop_gn_statistics(case)
+    finally:
+        L.lib().mvae_set_debug(16, 0)
+
+
 # ------------------------------------------------------------------ disentangled-model kernels
 def _ref_aux(z, idx, s, m, tau=0.1):
     zm = z.reshape(z.shape[0], -1)[:, s:s + m]
