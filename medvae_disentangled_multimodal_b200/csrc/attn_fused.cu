@@ -151,6 +151,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (tmem_base != 0u) __trap();          // all 512 columns: the allocation starts at column 0 (the MMA issuer relies on it)
     const int kiters = p.C / 64;            // channel chunks of a score GEMM
     const int nchunks = p.C / p.bno;        // channel chunks of an output GEMM
     const uint32_t score_stage_bytes = 16384u + (uint32_t)p.kboxes * 8192u;
@@ -158,47 +159,45 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
     const int kgroups = p.kboxes / p.kg;
 
     if (warp == 0) {
-        // ===================================================== TMA producer (whole warp: lane 0 owns the barriers, lanes
-        // 0..n-1 issue the n boxes of a stage)
-        int stage = 0; uint32_t phase = 0;
-        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
-            int kind, img, r0, ns, no;
-            AfScoreJob sj[2]; AfOutJob oj[2];
-            af_item(p, it, kind, img, r0);
-            af_jobs(p, kind, sj, ns, oj, no);
-            for (int j = 0; j < ns; ++j) {
-                for (int kb = 0; kb < kiters; ++kb) {
-                    if (lane == 0) {
+        // ===================================================== TMA producer: one elected thread (elect.sync: the assembler
+        // then emits each UTMALDG once, without the any-number-of-lanes loop a `lane == 0` region gets)
+        if (elect_one_sync()) {
+            int stage = 0; uint32_t phase = 0;
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+                int kind, img, r0, ns, no;
+                AfScoreJob sj[2]; AfOutJob oj[2];
+                af_item(p, it, kind, img, r0);
+                af_jobs(p, kind, sj, ns, oj, no);
+                for (int j = 0; j < ns; ++j) {
+                    for (int kb = 0; kb < kiters; ++kb) {
                         mbar_wait(&empty[stage], phase ^ 1u);
                         mbar_expect_tx(&full[stage], score_stage_bytes);
+                        uint8_t* a = sStage + (uint32_t)stage * p.stage_bytes;
+                        tma_load_3d(a, &tm.a[sj[j].a_dy], &full[stage], sj[j].ca + kb * 64, r0, img);
+                        tma_load_3d(a + 16384, &tm.b[sj[j].b_dy], &full[stage], sj[j].cb + kb * 64, 0, img);
+                        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                     }
-                    __syncwarp();
-                    uint8_t* a = sStage + (uint32_t)stage * p.stage_bytes;
-                    if (lane == 0) tma_load_3d(a, &tm.a[sj[j].a_dy], &full[stage], sj[j].ca + kb * 64, r0, img);
-                    else if (lane == 1) tma_load_3d(a + 16384, &tm.b[sj[j].b_dy], &full[stage], sj[j].cb + kb * 64, 0, img);
-                    if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                 }
-            }
-            for (int j = 0; j < no; ++j) {
-                for (int nc = 0; nc < nchunks; ++nc) {
-                    for (int g = 0; g < kgroups; ++g) {
-                        if (lane == 0) {
+                for (int j = 0; j < no; ++j) {
+                    for (int nc = 0; nc < nchunks; ++nc) {
+                        for (int g = 0; g < kgroups; ++g) {
                             mbar_wait(&empty[stage], phase ^ 1u);
                             mbar_expect_tx(&full[stage], out_stage_bytes);
+                            uint8_t* b = sStage + (uint32_t)stage * p.stage_bytes;
+                            for (int c = 0; c < p.bno / 64; ++c)
+                                tma_load_3d(b + c * (p.kg * 8192), &tm.n[oj[j].b_dy], &full[stage],
+                                            oj[j].cb + nc * p.bno + c * 64, g * p.kg * 64, img);
+                            if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                         }
-                        __syncwarp();
-                        uint8_t* b = sStage + (uint32_t)stage * p.stage_bytes;
-                        if (lane < p.bno / 64)
-                            tma_load_3d(b + lane * (p.kg * 8192), &tm.n[oj[j].b_dy], &full[stage],
-                                        oj[j].cb + nc * p.bno + lane * 64, g * p.kg * 64, img);
-                        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================================================== MMA issuer
-        if (lane == 0) {
+        // ===================================================== MMA issuer (one elected thread; accumulator and operand
+        // addresses in tensor memory are plain column numbers: the allocation starts at 0)
+        if (elect_one_sync()) {
+            constexpr uint32_t dhi = smem_desc_hi_sw128(1024);
             int stage = 0; uint32_t phase = 0;
             uint32_t n_local = 0;            // items done by this CTA (parity of tfull_s / pready)
             uint32_t uses[2] = {0, 0};       // uses of each output accumulator so far
@@ -216,12 +215,11 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                     for (int kb = 0; kb < kiters; ++kb) {
                         mbar_wait(&full[stage], phase);
                         tc_fence_after();
-                        const uint32_t a0 = smem_u32(sStage + (uint32_t)stage * p.stage_bytes);
-                        const uint32_t b0 = a0 + 16384u;
+                        const uint32_t a_lo = smem_desc_lo(smem_u32(sStage + (uint32_t)stage * p.stage_bytes));
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            umma_bf16(tmem_base + sj[j].col, smem_desc_sw128(a0 + k * 32, 16, 1024),
-                                      smem_desc_sw128(b0 + k * 32, 16, 1024), p.idesc_s, (kb | k) != 0 ? 1u : 0u);
+                            umma_bf16_lohi(sj[j].col, a_lo + (uint32_t)(k * 2), dhi, a_lo + (uint32_t)(1024 + k * 2), dhi, p.idesc_s,
+                                           (kb | k) != 0 ? 1u : 0u);
                         umma_commit(&empty[stage]);
                         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
                     }
@@ -235,22 +233,23 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                         const int buf = (int)((uses[0] + uses[1]) & 1u);
                         mbar_wait(&tempty_o[buf], (uses[buf] & 1u) ^ 1u);
                         tc_fence_after();
-                        const uint32_t dcol = tmem_base + (buf ? p.col_o1 : p.col_o0);
+                        const uint32_t dcol = buf ? p.col_o1 : p.col_o0;
                         for (int g = 0; g < kgroups; ++g) {
                             mbar_wait(&full[stage], phase);
                             tc_fence_after();
-                            const uint32_t b0 = smem_u32(sStage + (uint32_t)stage * p.stage_bytes);
+                            const uint32_t b_lo = smem_desc_lo(smem_u32(sStage + (uint32_t)stage * p.stage_bytes), (uint32_t)p.kg * 8192u);
+                            const uint32_t pcol = oj[j].tile ? p.col_ds : p.col_p;
                             for (int kc = 0; kc < p.kg; ++kc) {
                                 const int kt = g * p.kg + kc;          // 64-token box of the reduction
 #pragma unroll
                                 for (int k = 0; k < 4; ++k) {
-                                    const uint64_t bd = smem_desc_sw128(b0 + kc * 8192 + k * 2048, (uint32_t)p.kg * 8192u, 1024);
+                                    const uint32_t bl = b_lo + (uint32_t)(kc * 512 + k * 128);
                                     if constexpr (TS)
-                                        umma_bf16_ts(dcol, tmem_base + (oj[j].tile ? p.col_ds : p.col_p) + (uint32_t)(kt * 32 + k * 8),
-                                                     bd, p.idesc_o, (kt | k) != 0 ? 1u : 0u);
+                                        umma_bf16_ts(dcol, pcol + (uint32_t)(kt * 32 + k * 8),
+                                                     ((uint64_t)dhi << 32) | bl, p.idesc_o, (kt | k) != 0 ? 1u : 0u);
                                     else
-                                        umma_bf16(dcol, smem_desc_sw128(t0 + kt * 16384 + k * 32, 16, 1024), bd, p.idesc_o,
-                                                  (kt | k) != 0 ? 1u : 0u);
+                                        umma_bf16_lohi(dcol, smem_desc_lo(t0 + kt * 16384) + (uint32_t)(k * 2), dhi, bl, dhi, p.idesc_o,
+                                                       (kt | k) != 0 ? 1u : 0u);
                                 }
                             }
                             umma_commit(&empty[stage]);

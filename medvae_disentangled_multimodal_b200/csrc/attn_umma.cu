@@ -85,7 +85,7 @@ bgemm_umma_kernel(const __grid_constant__ BgemmTmaps tm, const __grid_constant__
     const uint32_t stage_bytes = (uint32_t)(BG_A_BYTES + b_bytes);
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             int stage = 0; uint32_t phase = 0;
             for (int kb = 0; kb < kiters; ++kb) {
                 mbar_wait(&empty[stage], phase ^ 1u);
@@ -108,7 +108,7 @@ bgemm_umma_kernel(const __grid_constant__ BgemmTmaps tm, const __grid_constant__
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             int stage = 0; uint32_t phase = 0;
             for (int kb = 0; kb < kiters; ++kb) {
                 mbar_wait(&full[stage], phase);

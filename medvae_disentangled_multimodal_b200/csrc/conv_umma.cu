@@ -113,6 +113,7 @@ static int num_sms() {
 struct alignas(64) GatherTmaps {
     CUtensorMap a[MAX_VIEWS];
     CUtensorMap b;
+    CUtensorMap h;   // halo variant: box {64 ch, 16, 18, 1} over view 0
 };
 struct GatherDev {
     int bw, bh, bn, rows;
@@ -131,6 +132,8 @@ struct GatherDev {
     const float* gn_stat;
     const float* gn_gamma;
     const float* gn_beta;
+    int halo_bo;   // halo variant: 1 = put (start >> 7) & 7 into the descriptor's base-offset field (knob 18)
+    int dbg;       // knob 19 = 1: block 0's MMA thread prints where its cycles went (waits on loads / on the epilogue)
 };
 
 constexpr int G_THREADS = 192;
@@ -243,10 +246,33 @@ constexpr int GN_COEF_MAX = 1024;                                   // channels
 constexpr int GN_BWD_SMEM = GN_COEF_MAX * 8 + 8 * 2 * 32 * 8;       // coefficient table + per-warp statistics slots
 __host__ __device__ constexpr int gather_smem(int base, int epi) { return base + (epi == EPI_GN_BWD ? GN_BWD_SMEM : 0); }
 
-template <int BN, int EPI, int MT, int CG, int CS>
+// HALO variant (HL = 1; stride-1 3x3 convs, output grid a multiple of 8 x 16).  Everything above pulls each input
+// pixel from L2 once per TAP, and what bounds these kernels is L2 -> SM throughput (~6300 B/clk chip-wide = 42.6
+// B/clk/SM: every gather launch in profiles/r2k_ncu_full.csv sits at 11-13 TB/s of l1tex__m_xbar2l1tex_read_bytes).
+// Here a pixel tile is 8 wide x 16 tall and ONE TMA box {64 ch, 16, 18} brings its (1-pixel) halo per 64-channel
+// chunk; the nine taps are nine views of that box: descriptor start = ((dy+1) * 16 + (dx+1)) * 128 B into it, stride
+// between 8-row groups (= 8 pixels of one image row) = the 16-pixel pitch = 2048 B.  The 128B swizzle is a function
+// of the absolute shared-memory address bits, so a start that is not 1024-aligned reads what TMA wrote.  Activation
+// bytes per pixel tile and chunk: 36 KB instead of 9 x 16 KB; the weights still stream per (chunk, tap), through their
+// own ring.  The k loop runs chunk-major (chunk outer, tap inner).
+constexpr int HALO_W = 16, HALO_H = 18;
+constexpr int HALO_TILE_BYTES = HALO_W * HALO_H * 128;   // 36864
+template <int BN, int MT>
+struct HaloCfg {
+    static constexpr int A_STAGE = MT * HALO_TILE_BYTES;
+    static constexpr int B_BYTES = BN * 128;
+    static constexpr int AS = 2;
+    static constexpr int BS_RAW = (212992 - AS * A_STAGE) / B_BYTES;
+    static constexpr int BS = BS_RAW > 8 ? 8 : BS_RAW;
+    static constexpr int SMEM = 1024 + AS * A_STAGE + BS * B_BYTES + 256;
+};
+
+template <int BN, int EPI, int MT, int CG, int CS, int HL = 0>
 __global__ void __launch_bounds__(gather_threads_cs(CS), 1)
 conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_constant__ GatherDev p) {
     using Cfg = GatherCfg<BN, MT, CG>;
+    using HCfg = HaloCfg<BN, MT>;
+    static_assert(HL == 0 || CG == 1, "the halo variant is single-CTA");
     // a scheduled tile is CG * MT pixel tiles: MT per CTA, the CTAs of a pair side by side (rank * MT + j)
     // CTA pair: rank within the pair, pair index and number of pairs replace blockIdx / gridDim in the tile loop
     const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
@@ -255,14 +281,19 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // halo variant: ring of AS halo stages (MT boxes each), ring of BS weight stages; `full` / `empty` = fullA, emptyA
+    // (AS each) followed by fullB, emptyB (BS each)
+    constexpr int PIPE_BYTES = HL ? (HCfg::AS * HCfg::A_STAGE + HCfg::BS * HCfg::B_BYTES) : STAGES * (Cfg::A_BYTES + Cfg::B_BYTES);
+    constexpr int NBAR = HL ? (HCfg::AS + HCfg::BS) : STAGES;
     uint8_t* sA = smem;
-    uint8_t* sB = sA + STAGES * Cfg::A_BYTES;
-    uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * Cfg::B_BYTES);
-    uint64_t* empty = full + STAGES;
-    uint64_t* tfull = empty + STAGES;
+    uint8_t* sB = sA + (HL ? HCfg::AS * HCfg::A_STAGE : STAGES * Cfg::A_BYTES);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + PIPE_BYTES);
+    uint64_t* empty = full + NBAR;
+    uint64_t* tfull = empty + NBAR;
     uint64_t* tempty = tfull + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-    float2* sCoef = reinterpret_cast<float2*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + 256);   // EPI_GN_BWD only
+    static_assert((2 * NBAR + 4) * 8 + 4 <= 256, "barrier block");
+    float2* sCoef = reinterpret_cast<float2*>(smem + PIPE_BYTES + 256);   // EPI_GN_BWD only
     float2* sStat = sCoef + GN_COEF_MAX;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -271,19 +302,20 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
         for (int c = threadIdx.x; c < p.N; c += gather_threads_cs(CS))
             sCoef[c] = make_float2(0.5f * __ldg(p.gn_gamma + c), 0.5f * __ldg(p.gn_beta + c));
     }
-    if (p.rows < 128) {
+    if (!HL && p.rows < 128) {
         // rows the TMA box never writes feed accumulator rows nobody stores; keep them finite
         for (int i = threadIdx.x; i < STAGES * Cfg::A_BYTES / 16; i += gather_threads_cs(CS))
             reinterpret_cast<uint4*>(sA)[i] = make_uint4(0, 0, 0, 0);
         fence_proxy_async_smem();
     }
     if (warp == 0 && lane == 0) {
-        for (int v = 0; v < MAX_VIEWS; ++v) prefetch_tmap(&tm.a[v]);
+        if (HL) prefetch_tmap(&tm.h);
+        else for (int v = 0; v < MAX_VIEWS; ++v) prefetch_tmap(&tm.a[v]);
         prefetch_tmap(&tm.b);
     }
     if (warp == 1) {
         if (lane == 0) {
-            for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+            for (int s = 0; s < NBAR; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
             // pair: the epilogue warps of BOTH CTAs release the leader's accumulator barrier
             for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], CG * 32 * (4 * CS)); }
             fence_barrier_init();
@@ -297,13 +329,109 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
     if (CG == 2) cluster_sync_all();   // the peer's barriers exist before anything arrives on them remotely
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // An allocation of all 512 columns can only start at column 0: the MMA issuer then forms its accumulator addresses
+    // from loop counters alone (uniform registers; a value read from shared memory costs an ELECT / R2UR.BROADCAST
+    // loop around every tcgen05.mma)
+    if (Cfg::TMEM_COLS == 512 && tmem_base != 0u) __trap();
+    const uint32_t tmem_mma = (Cfg::TMEM_COLS == 512) ? 0u : tmem_base;
 
     const int kiters = p.taps.ntaps * p.kchunks;
     // bytes that complete on one "full" barrier: both CTAs' loads land on the leader's barrier in a pair
     const uint32_t stage_bytes = (uint32_t)CG * ((uint32_t)(MT * p.rows) * 128u + (uint32_t)Cfg::B_BYTES);
 
-    if (warp == 0) {
-        if (lane == 0) {
+    if (HL && warp == 0) {
+        if (elect_one_sync()) {
+            // one issuing thread, two rings: whichever has a free slot goes next (neither cursor ever blocks the other)
+            uint64_t* fullA = full; uint64_t* emptyA = empty;
+            uint64_t* fullB = full + HCfg::AS; uint64_t* emptyB = empty + HCfg::AS;
+            int ta = sched_id, kca = 0, sa = 0; uint32_t pa = 0;              // halo cursor: (tile, chunk)
+            int tb = sched_id, kcb = 0, tpb = 0, sb = 0; uint32_t pb = 0;     // weight cursor: (tile, chunk, tap)
+            bool a_live = ta < p.total_tiles, b_live = a_live;
+            long long t_idle = clock64();   // bounded like mbar_wait: a protocol bug traps instead of hanging the GPU
+            while (a_live || b_live) {
+                if (clock64() - t_idle > 4000000000LL) {
+                    printf("mvae: halo producer stalled (block %d)\n", (int)blockIdx.x);
+                    __trap();
+                }
+                if (a_live && mbar_try_wait(&emptyA[sa], pa ^ 1u)) {
+                    t_idle = clock64();
+                    mbar_expect_tx(&fullA[sa], (uint32_t)HCfg::A_STAGE);
+#pragma unroll
+                    for (int j = 0; j < MT; ++j) {
+                        int mt = (ta / p.n_tiles) * MT + j;   // one past the last: n0 >= B, the box is zero-filled
+                        const int tx = mt % p.tiles_x; mt /= p.tiles_x;
+                        tma_load_4d(sA + sa * HCfg::A_STAGE + j * HALO_TILE_BYTES, &tm.h, &fullA[sa], kca * 64,
+                                    tx * p.bw - 1, (mt % p.tiles_y) * p.bh - 1, mt / p.tiles_y);
+                    }
+                    if (++sa == HCfg::AS) { sa = 0; pa ^= 1u; }
+                    if (++kca == p.kchunks) { kca = 0; ta += sched_n; a_live = ta < p.total_tiles; }
+                }
+                if (b_live && mbar_try_wait(&emptyB[sb], pb ^ 1u)) {
+                    t_idle = clock64();
+                    mbar_expect_tx(&fullB[sb], (uint32_t)HCfg::B_BYTES);
+                    tma_load_3d(sB + sb * HCfg::B_BYTES, &tm.b, &fullB[sb], kcb * 64, (tb % p.n_tiles) * BN,
+                                p.taps.t[tpb].slab);
+                    if (++sb == HCfg::BS) { sb = 0; pb ^= 1u; }
+                    if (++tpb == p.taps.ntaps) {
+                        tpb = 0;
+                        if (++kcb == p.kchunks) { kcb = 0; tb += sched_n; b_live = tb < p.total_tiles; }
+                    }
+                }
+            }
+        }
+    } else if (HL && warp == 1) {
+        if (elect_one_sync()) {
+            uint64_t* fullA = full; uint64_t* emptyA = empty;
+            uint64_t* fullB = full + HCfg::AS; uint64_t* emptyB = empty + HCfg::AS;
+            constexpr uint32_t idesc = make_idesc_bf16(128, BN, 0, 0);
+            int sa = 0; uint32_t pa = 0; int sb = 0; uint32_t pb = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            long long w_acc = 0, w_a = 0, w_b = 0, c0 = 0; int ntl = 0;
+            const long long t_begin = clock64();
+            for (int tile = sched_id; tile < p.total_tiles; tile += sched_n) {
+                if (p.dbg) c0 = clock64();
+                mbar_wait(&tempty[acc], acc_phase ^ 1u);
+                if (p.dbg) { w_acc += clock64() - c0; ++ntl; }
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_mma + (uint32_t)(acc * MT * BN);
+                for (int kc = 0; kc < p.kchunks; ++kc) {
+                    if (p.dbg) c0 = clock64();
+                    mbar_wait(&fullA[sa], pa);
+                    if (p.dbg) w_a += clock64() - c0;
+                    const uint32_t h0 = smem_u32(sA + sa * HCfg::A_STAGE);
+                    for (int t = 0; t < p.taps.ntaps; ++t) {
+                        if (p.dbg) c0 = clock64();
+                        mbar_wait(&fullB[sb], pb);
+                        if (p.dbg) w_b += clock64() - c0;
+                        tc_fence_after();
+                        const Tap tp = p.taps.t[t];
+                        const uint32_t a0 = h0 + (uint32_t)(((tp.dy + 1) * HALO_W + (tp.dx + 1)) * 128);
+                        const uint32_t a_lo = smem_desc_lo(a0), b_lo = smem_desc_lo(smem_u32(sB + sb * HCfg::B_BYTES));
+                        // knob 18 (probe only): the descriptor's base-offset field set from the start address — wrong on
+                        // this hardware (the swizzle follows the absolute address bits), kept to show it
+                        const uint32_t a_hi = smem_desc_hi_sw128(HALO_W * 128) | (p.halo_bo ? (((a0 >> 7) & 7u) << 17) : 0u);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+#pragma unroll
+                            for (int j = 0; j < MT; ++j)
+                                umma_bf16_lohi(d_tmem + (uint32_t)(j * BN), a_lo + (uint32_t)((j * HALO_TILE_BYTES + k * 32) >> 4), a_hi,
+                                               b_lo + (uint32_t)(k * 2), smem_desc_hi_sw128(1024), idesc, (kc | t | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit(&emptyB[sb]);
+                        if (++sb == HCfg::BS) { sb = 0; pb ^= 1u; }
+                    }
+                    umma_commit(&emptyA[sa]);
+                    if (++sa == HCfg::AS) { sa = 0; pa ^= 1u; }
+                }
+                umma_commit(&tfull[acc]);
+                if (++acc == Cfg::ACC_BUFS) { acc = 0; acc_phase ^= 1u; }
+            }
+            if (p.dbg && blockIdx.x == 0)
+                printf("mvae gather dbg (halo BN %d MT %d EPI %d): %d tiles, %lld clk issuing; waited %lld on the epilogue, "
+                       "%lld on halo boxes, %lld on weight boxes\n", BN, MT, EPI, ntl, clock64() - t_begin, w_acc, w_a, w_b);
+        }
+    } else if (warp == 0) {
+        if (elect_one_sync()) {
             int stage = 0; uint32_t phase = 0;
             for (int tile = sched_id; tile < p.total_tiles; tile += sched_n) {
                 const int nt = tile % p.n_tiles;
@@ -344,27 +472,39 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && rank == 0) {
+        if (rank == 0 && elect_one_sync()) {
             constexpr uint32_t idesc = make_idesc_bf16(128 * CG, BN, 0, 0);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
+            long long w_acc = 0, w_f = 0, c0 = 0; int ntl = 0;
+            const long long t_begin = clock64();
             for (int tile = sched_id; tile < p.total_tiles; tile += sched_n) {
+                if (p.dbg) c0 = clock64();
                 mbar_wait(&tempty[acc], acc_phase ^ 1u);
+                if (p.dbg) { w_acc += clock64() - c0; ++ntl; }
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * MT * BN);
+                const uint32_t d_tmem = tmem_mma + (uint32_t)(acc * MT * BN);
                 for (int it = 0; it < kiters; ++it) {
+                    if (p.dbg) c0 = clock64();
                     mbar_wait(&full[stage], phase);
+                    if (p.dbg) w_f += clock64() - c0;
                     tc_fence_after();
                     const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES);
                     const uint32_t b0 = smem_u32(sB + stage * Cfg::B_BYTES);
+                    const uint32_t a_lo = smem_desc_lo(a0), b_lo = smem_desc_lo(b0);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        const uint64_t bd = smem_desc_sw128(b0 + k * 32, 16, 1024);
 #pragma unroll
                         for (int j = 0; j < MT; ++j) {
-                            const uint64_t ad = smem_desc_sw128(a0 + j * A_TILE_BYTES + k * 32, 16, 1024);
-                            if (CG == 2) umma2_bf16(d_tmem + (uint32_t)(j * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
-                            else umma_bf16(d_tmem + (uint32_t)(j * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                            if (CG == 2) {
+                                const uint64_t bd = smem_desc_sw128(b0 + k * 32, 16, 1024);
+                                const uint64_t ad = smem_desc_sw128(a0 + j * A_TILE_BYTES + k * 32, 16, 1024);
+                                umma2_bf16(d_tmem + (uint32_t)(j * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+                            } else {
+                                umma_bf16_lohi(d_tmem + (uint32_t)(j * BN), a_lo + (uint32_t)((j * A_TILE_BYTES + k * 32) >> 4),
+                                               smem_desc_hi_sw128(1024), b_lo + (uint32_t)(k * 2), smem_desc_hi_sw128(1024), idesc,
+                                               (it | k) != 0 ? 1u : 0u);
+                            }
                         }
                     }
                     if (CG == 2) umma2_commit(&empty[stage]);
@@ -375,6 +515,9 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 else umma_commit(&tfull[acc]);
                 if (++acc == Cfg::ACC_BUFS) { acc = 0; acc_phase ^= 1u; }
             }
+            if (p.dbg && blockIdx.x == 0)
+                printf("mvae gather dbg (BN %d MT %d CG %d EPI %d): %d tiles, %lld clk issuing; waited %lld on the epilogue, "
+                       "%lld on operand boxes\n", BN, MT, CG, EPI, ntl, clock64() - t_begin, w_acc, w_f);
         }
     } else {
         const int quarter = warp & 3;            // TMEM lane quarter this warp may read
@@ -679,13 +822,15 @@ bool umma_gather_ok(const GatherProblem& p) {
     return true;
 }
 
-template <int BN, int EPI, int MT, int CG, int CS = gather_csplit(EPI)>
+template <int BN, int EPI, int MT, int CG, int CS = gather_csplit(EPI), int HL = 0>
 static int launch_gather_epi(const GatherTmaps& tm, GatherDev& d, cudaStream_t st) {
     using Cfg = GatherCfg<BN, MT, CG>;
+    constexpr int SMEM = gather_smem(HL ? HaloCfg<BN, MT>::SMEM : Cfg::SMEM, EPI);
+    static_assert(SMEM <= 232448, "shared memory of one CTA");
     static bool attr_set = false;
     if (!attr_set) {
-        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI, MT, CG, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       gather_smem(Cfg::SMEM, EPI)));
+        MVAE_CUDA(cudaFuncSetAttribute(conv_gather_umma_kernel<BN, EPI, MT, CG, CS, HL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       SMEM));
         attr_set = true;
     }
     if (CG == 2) {
@@ -696,43 +841,54 @@ static int launch_gather_epi(const GatherTmaps& tm, GatherDev& d, cudaStream_t s
         memset(&cfg, 0, sizeof(cfg));
         cfg.gridDim = dim3(2 * pairs);
         cfg.blockDim = dim3(gather_threads_cs(CS));
-        cfg.dynamicSmemBytes = gather_smem(Cfg::SMEM, EPI);
+        cfg.dynamicSmemBytes = SMEM;
         cfg.stream = st;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
         count_launch();
-        MVAE_CUDA(cudaLaunchKernelEx(&cfg, conv_gather_umma_kernel<BN, EPI, MT, CG, CS>, tm, d));
+        MVAE_CUDA(cudaLaunchKernelEx(&cfg, conv_gather_umma_kernel<BN, EPI, MT, CG, CS, HL>, tm, d));
         MVAE_CUDA(cudaGetLastError());
         return 0;
     }
     int grid = d.total_tiles < num_sms() ? d.total_tiles : num_sms();
-    conv_gather_umma_kernel<BN, EPI, MT, CG, CS><<<grid, gather_threads_cs(CS), gather_smem(Cfg::SMEM, EPI), st>>>(tm, d);
+    conv_gather_umma_kernel<BN, EPI, MT, CG, CS, HL><<<grid, gather_threads_cs(CS), SMEM, st>>>(tm, d);
     MVAE_LAUNCH_CHECK();
     return 0;
 }
-template <int BN, int MT, int CG = 1>
+template <int BN, int MT, int CG = 1, int HL = 0>
 static int launch_gather(const GatherTmaps& tm, GatherDev& d, int epi, cudaStream_t st) {
     if (epi == EPI_GN_STATS) {
-        if constexpr (BN == 128) {
+        if constexpr (BN == 128 && HL == 0) {
             // OPT-IN (knob 16 = 2): four column strips (16 epilogue warps) instead of two for the statistics epilogue of
             // the 64x64 layers.  Measured on one box (trip r2n): fprop 62.7 ms with, 62.6 ms without — unlike the
             // GroupNorm-backward epilogue this one is not what holds the 128-channel tiles at ~50 % tensor-pipe.
             if (debug_knob(16) == 2) return launch_gather_epi<BN, EPI_GN_STATS, MT, CG, 4>(tm, d, st);
         }
-        return launch_gather_epi<BN, EPI_GN_STATS, MT, CG>(tm, d, st);
+        return launch_gather_epi<BN, EPI_GN_STATS, MT, CG, gather_csplit(EPI_GN_STATS), HL>(tm, d, st);
     }
     if (epi == EPI_GN_BWD) {
         if constexpr (BN >= 128) {
             // MMA cycles of one CTA tile against the ~25k cycles the 8-warp epilogue takes for it (knob 9: 1 = never, 2 = always)
             const long long mma_cycles = (long long)d.taps.ntaps * d.kchunks * 4 * MT * (BN / 2);
             const int knob = debug_knob(9);
-            if (knob == 2 || (knob == 0 && mma_cycles <= 12288)) return launch_gather_epi<BN, EPI_GN_BWD, MT, CG, 4>(tm, d, st);
+            if (knob == 2 || (knob == 0 && mma_cycles <= 12288)) return launch_gather_epi<BN, EPI_GN_BWD, MT, CG, 4, HL>(tm, d, st);
         }
-        return launch_gather_epi<BN, EPI_GN_BWD, MT, CG>(tm, d, st);
+        return launch_gather_epi<BN, EPI_GN_BWD, MT, CG, gather_csplit(EPI_GN_BWD), HL>(tm, d, st);
     }
-    return launch_gather_epi<BN, EPI_PLAIN, MT, CG>(tm, d, st);
+    return launch_gather_epi<BN, EPI_PLAIN, MT, CG, gather_csplit(EPI_PLAIN), HL>(tm, d, st);
+}
+
+// halo variant: a stride-1 3 x 3 tap program over one view, output grid in whole 8 x 16 pixel tiles
+static bool halo_ok(const GatherProblem& p) {
+    if (p.nviews != 1 || p.taps.ntaps != 9 || p.OW % 8 != 0 || p.OH % HALO_W != 0) return false;
+    if (p.in_views[0].Ws < HALO_W || p.in_views[0].Hs < HALO_H) return false;
+    for (int t = 0; t < 9; ++t) {
+        const Tap& tp = p.taps.t[t];
+        if (tp.view != 0 || tp.dx < -1 || tp.dx > 1 || tp.dy < -1 || tp.dy > 1) return false;
+    }
+    return true;
 }
 
 int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslabs, const float* bias,
@@ -771,7 +927,7 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
     d.tiles_x = g.tiles_x; d.tiles_y = g.tiles_y; d.tiles_n = g.tiles_n;
     d.n_tiles = p.N / BN; d.kchunks = p.K / 64;
     // 128-channel tiles take two pixel tiles per weight stage when that still leaves every SM a CTA tile
-    const long long m_tiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
+    long long m_tiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
     int MT = (BN == 128 && debug_knob(5) == 0 && ((m_tiles + 1) / 2) * d.n_tiles >= num_sms()) ? 2 : 1;
     if (BN == 128 && CG == 2) MT = 2;
     if (CG == 1 && BN == 256 && debug_knob(7) == 1) {
@@ -780,6 +936,18 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
         // 256-image micro-batch — slower, so the default stays 128 x 256 with double-buffered accumulators.
         const long long t1 = m_tiles * d.n_tiles, t2 = ((m_tiles + 1) / 2) * d.n_tiles, sms = num_sms();
         if (t2 >= sms && 3 * ((t2 + sms - 1) / sms) < 2 * ((t1 + sms - 1) / sms)) MT = 2;
+    }
+    // 128-channel tiles of stride-1 3x3 convs: 8 x 16 pixel tiles fed by one halo box per chunk (knob 17 = 1: off)
+    const bool halo = BN == 128 && MT == 2 && CG == 1 && debug_knob(17) != 1 && halo_ok(p);
+    d.halo_bo = debug_knob(18) == 1 ? 1 : 0;
+    d.dbg = debug_knob(19) == 1 ? 1 : 0;
+    if (halo) {
+        g.bw = 8; g.bh = 16; g.bn = 1; g.rows = 128;
+        g.tiles_x = p.OW / 8; g.tiles_y = p.OH / 16; g.tiles_n = p.B;
+        d.bw = g.bw; d.bh = g.bh; d.bn = g.bn; d.rows = g.rows;
+        d.tiles_x = g.tiles_x; d.tiles_y = g.tiles_y; d.tiles_n = g.tiles_n;
+        m_tiles = (long long)g.tiles_x * g.tiles_y * g.tiles_n;
+        if (view_tmap(&tm.h, (const bf16*)in, p.in_views[0], p.K, p.B, HALO_W, HALO_H, 1)) return 1;
     }
     const int m_per_tile = MT * CG;   // pixel tiles per scheduled tile: MT per CTA, one per CTA of a pair
     d.total_tiles = (int)((m_tiles + m_per_tile - 1) / m_per_tile) * d.n_tiles;
@@ -802,6 +970,7 @@ int umma_gather(const GatherProblem& p, const void* in, const void* w, int nslab
         d.gn_sums = hook->sums; d.gn_x = (const bf16*)hook->x; d.gn_stat = hook->stat;
         d.gn_gamma = hook->gamma; d.gn_beta = hook->beta;
     }
+    if (halo) return launch_gather<128, 2, 1, 1>(tm, d, epi, st);
     if (CG == 2 && BN == 128) return launch_gather<128, 2, 2>(tm, d, epi, st);
     if (CG == 2) return launch_gather<256, 1, 2>(tm, d, epi, st);
     if (BN == 256 && MT == 2) return launch_gather<256, 2>(tm, d, epi, st);
@@ -897,10 +1066,12 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (Cfg::TMEM_COLS == 512 && tmem_base != 0u) __trap();   // all 512 columns start at column 0 (see the gather kernel)
+    const uint32_t tmem_mma = (Cfg::TMEM_COLS == 512) ? 0u : tmem_base;
     const uint32_t stage_bytes = (uint32_t)p.rows * 128u * (MT * 2 + NT * (BN / 64));
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             int stage = 0; uint32_t phase = 0;
             for (int pt = pt_beg; pt < pt_end; ++pt) {
                 int mt = pt;
@@ -927,24 +1098,23 @@ conv_reduce_umma_kernel(const __grid_constant__ ReduceTmaps tm, const __grid_con
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             constexpr uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);
+            constexpr uint32_t dhi = smem_desc_hi_sw128(1024);
             int stage = 0; uint32_t phase = 0;
             for (int it = 0; it < kiters; ++it) {
                 mbar_wait(&full[stage], phase);
                 tc_fence_after();
-                const uint32_t a0 = smem_u32(sA + stage * Cfg::A_BYTES);
-                const uint32_t b0 = smem_u32(sB + stage * Cfg::B_BYTES);
+                const uint32_t a_lo = smem_desc_lo(smem_u32(sA + stage * Cfg::A_BYTES), R_CHUNK);
+                const uint32_t b_lo = smem_desc_lo(smem_u32(sB + stage * Cfg::B_BYTES), R_CHUNK);
 #pragma unroll
                 for (int m = 0; m < MT; ++m) {
 #pragma unroll
                     for (int k = 0; k < R_PIX / 16; ++k) {   // 16 pixels (= 16 rows of 128 B) per MMA
-                        const uint64_t ad = smem_desc_sw128(a0 + m * 2 * R_CHUNK + k * 2048, R_CHUNK, 1024);
 #pragma unroll
-                        for (int j = 0; j < NT; ++j) {
-                            const uint64_t bd = smem_desc_sw128(b0 + j * Cfg::B_TAP + k * 2048, R_CHUNK, 1024);
-                            umma_bf16(tmem_base + (uint32_t)((m * NT + j) * BN), ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
-                        }
+                        for (int j = 0; j < NT; ++j)
+                            umma_bf16_lohi(tmem_mma + (uint32_t)((m * NT + j) * BN), a_lo + (uint32_t)((m * 2 * R_CHUNK + k * 2048) >> 4), dhi,
+                                           b_lo + (uint32_t)((j * Cfg::B_TAP + k * 2048) >> 4), dhi, idesc, (it | k) != 0 ? 1u : 0u);
                     }
                 }
                 umma_commit(&empty[stage]);

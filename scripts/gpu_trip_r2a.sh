@@ -38,6 +38,29 @@ for stage in $STAGES; do
     ab_cs)  # A/B on one box: 16 epilogue warps for the GN-statistics fprop on 128-channel tiles (knob 16 = 1: off)
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline > gpurun_out/bench_stats16_on.log 2>&1; echo "cs on rc=$?" >> gpurun_out/rc.txt
       timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob 16=1 > gpurun_out/bench_stats16_off.log 2>&1; echo "cs off rc=$?" >> gpurun_out/rc.txt;;
+    halo)   # probe of the halo variant of the 128-channel gather kernel, then an A/B on this box if it is correct
+      timeout 600 python scripts/halo_probe.py > gpurun_out/halo_probe.log 2>&1; echo "halo probe rc=$?" >> gpurun_out/rc.txt
+      cat gpurun_out/halo_probe.log
+      HK=$(python - <<'PY'
+import re
+ok = {"halo, base offset 0": True, "halo, base offset = (addr>>7)&7": True}
+seen = set()
+for line in open("gpurun_out/halo_probe.log"):
+    for k in ok:
+        if line.startswith(k):
+            seen.add(k)
+            m = re.search(r"fprop ([0-9.e+-]+) dgrad ([0-9.e+-]+)", line)
+            if not m or float(m.group(1)) > 2e-2 or float(m.group(2)) > 2e-2: ok[k] = False
+if "halo, base offset 0" in seen and ok["halo, base offset 0"]: print("18=0")
+elif "halo, base offset = (addr>>7)&7" in seen and ok["halo, base offset = (addr>>7)&7"]: print("18=1")
+else: print("none")
+PY
+)
+      echo "halo mode: $HK" >> gpurun_out/rc.txt
+      if [ "$HK" != "none" ]; then
+        timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob $HK > gpurun_out/bench_halo_on.log 2>&1; echo "halo on rc=$?" >> gpurun_out/rc.txt
+        timeout 600 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-gpu-baseline --knob 17=1 > gpurun_out/bench_halo_off.log 2>&1; echo "halo off rc=$?" >> gpurun_out/rc.txt
+      fi;;
     attnlist)
       timeout 300 $CMD > gpurun_out/plain_attn.log 2>&1 &&
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"attn_|bgemm" -c 200 --csv --log-file gpurun_out/attn_launches.csv $CMD > gpurun_out/ncu_attnlist.log 2>&1

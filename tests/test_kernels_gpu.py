@@ -481,6 +481,37 @@ def test_conv_fprop_gn_statistics_sixteen_epilogue_warps():
         L.lib().mvae_set_debug(16, 0)
 
 
+# ------------------------------------------------------------------ halo tiles (128-channel gather); knob 17 = 1 turns them off
+HALO_CASES = [(12, 64, 64, 128, 128, 3, 0), (80, 32, 32, 128, 128, 3, 0), (300, 16, 16, 128, 128, 3, 0),
+              (40, 32, 32, 256, 128, 3, 0), (40, 32, 32, 64, 128, 3, 0), (75, 32, 48, 128, 128, 3, 0)]
+
+
+@pytest.fixture(params=[0, 1], ids=["halo", "per-tap"])
+def halo_tiles(request):
+    L, _ = _mods()
+    L.lib().mvae_set_debug(17, request.param)
+    yield
+    L.lib().mvae_set_debug(17, 0)
+
+
+@pytest.mark.umma
+@pytest.mark.parametrize("case", HALO_CASES)
+def test_conv_umma_halo_tiles(case, halo_tiles):
+    """stride-1 3x3 convs on 128-channel tiles with >= 2 x 148 pixel tiles and an output grid in whole 8 x 16 pixel
+    tiles read each pixel tile's halo box once per 64-channel chunk and run the nine taps as shifted views of it;
+    the same cases with the variant switched off (one box per tap)"""
+    L, _ = _mods()
+    _conv_case(case, torch.bfloat16, L.ENGINE_UMMA)
+
+
+@pytest.mark.umma
+def test_conv_gn_epilogues_halo_tiles(halo_tiles):
+    for case in [(77, 32, 32, 128, 128, 3, 0, 32), (10, 64, 64, 128, 128, 3, 0, 32)]:
+        test_conv_fprop_gn_statistics(case)
+        test_conv_dgrad_gn_backward(case, True, True)
+        test_conv_dgrad_gn_backward(case, False, False)
+
+
 # ------------------------------------------------------------------ disentangled-model kernels
 def _ref_aux(z, idx, s, m, tau=0.1):
     zm = z.reshape(z.shape[0], -1)[:, s:s + m]
