@@ -60,6 +60,8 @@ struct AfDev {
     float* lse2;       // [B][T]
     const float* D;    // [B][T]
     bf16* dqkv;        // backward [B][T][3C]
+    int dbg;           // knob 19 = 1: block 0's MMA thread prints where its cycles went
+    int so;            // 1: output rows leave through the shared-memory transpose (0: no room for it, one row per thread)
 };
 
 constexpr int AF_THREADS = 192;
@@ -87,6 +89,10 @@ __device__ __forceinline__ void af_item(const AfDev& p, int it, int& kind, int& 
     if (!p.bwd) {
         kind = AF_FWD;
     } else {
+        // the two kinds of one (image, row tile) are items 2k and 2k+1; a K-side item costs ~1.5x a Q-side one, and with
+        // an even grid `it & 1 == blockIdx & 1` would give every odd CTA nothing but K-side items.  Odd rounds swap
+        // the pair (grid and n_items are even: a permutation within each round).
+        it ^= (it / (int)gridDim.x) & 1;
         kind = (it & 1) ? AF_BWD_K : AF_BWD_Q;
         it >>= 1;
     }
@@ -100,6 +106,23 @@ __device__ __forceinline__ void af_tile_store8(uint8_t* tile, int row, int col, 
     const int chunk = col >> 6, unit = (col & 63) >> 3;
     uint8_t* dst = tile + chunk * 16384 + row * 128 + ((unit ^ (row & 7)) << 4);
     *reinterpret_cast<uint4*>(dst) = v.raw;
+}
+
+// 32 packed bf16 (16 words: columns col .. col+31 of one row) into the same tile: four 16-byte stores
+__device__ __forceinline__ void af_tile_store32(uint8_t* tile, int row, int col, const uint32_t* pk) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const int c = col + g * 8;
+        const int chunk = c >> 6, unit = (c & 63) >> 3;
+        uint8_t* dst = tile + chunk * 16384 + row * 128 + ((unit ^ (row & 7)) << 4);
+        *reinterpret_cast<uint4*>(dst) = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+    }
+}
+// 2^x in one MUFU (flushes results below 2^-126 to zero; the arguments here are <= 0 up to rounding)
+__device__ __forceinline__ float af_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 
 // 8 floats -> 4 packed bf16 pairs
@@ -126,6 +149,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
     uint64_t* tempty_o = tfull_o + 2;             // [2] output accumulator drained
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_o + 2);
     float* sStat = reinterpret_cast<float*>(tmem_slot + 4);   // [2][256]: lse2, D per query (K-side items)
+    uint8_t* sOut = reinterpret_cast<uint8_t*>(sStat) + 2048; // [4 warps][32 rows][128 B]: output rows on their way to global
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if ((smem_u32(smem) & 1023u) != 0u) {   // SWIZZLE_128B tiles need 1024-byte alignment
@@ -201,19 +225,21 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
             int stage = 0; uint32_t phase = 0;
             uint32_t n_local = 0;            // items done by this CTA (parity of tfull_s / pready)
             uint32_t uses[2] = {0, 0};       // uses of each output accumulator so far
+            long long w_ls = 0, w_pr = 0, w_te = 0, w_lo = 0, c0 = 0;
+            const long long t_begin = clock64();
+#define AF_TIMED(acc, stmt) do { if (p.dbg) c0 = clock64(); stmt; if (p.dbg) acc += clock64() - c0; } while (0)
             for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++n_local) {
                 int kind, img, r0, ns, no;
                 AfScoreJob sj[2]; AfOutJob oj[2];
                 af_item(p, it, kind, img, r0);
                 af_jobs(p, kind, sj, ns, oj, no);
                 if (p.o_alias) {   // the score columns double as output accumulators: the last item's must be drained
-                    mbar_wait(&tempty_o[0], (uses[0] & 1u) ^ 1u);
-                    mbar_wait(&tempty_o[1], (uses[1] & 1u) ^ 1u);
+                    AF_TIMED(w_te, mbar_wait(&tempty_o[0], (uses[0] & 1u) ^ 1u); mbar_wait(&tempty_o[1], (uses[1] & 1u) ^ 1u));
                     tc_fence_after();
                 }
                 for (int j = 0; j < ns; ++j) {
                     for (int kb = 0; kb < kiters; ++kb) {
-                        mbar_wait(&full[stage], phase);
+                        AF_TIMED(w_ls, mbar_wait(&full[stage], phase));
                         tc_fence_after();
                         const uint32_t a_lo = smem_desc_lo(smem_u32(sStage + (uint32_t)stage * p.stage_bytes));
 #pragma unroll
@@ -225,17 +251,17 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                     }
                 }
                 umma_commit(tfull_s);
-                mbar_wait(pready, n_local & 1u);
+                AF_TIMED(w_pr, mbar_wait(pready, n_local & 1u));
                 tc_fence_after();
                 for (int j = 0; j < no; ++j) {
                     const uint32_t t0 = smem_u32(oj[j].tile ? sTile1 : sTile0);
                     for (int nc = 0; nc < nchunks; ++nc) {
                         const int buf = (int)((uses[0] + uses[1]) & 1u);
-                        mbar_wait(&tempty_o[buf], (uses[buf] & 1u) ^ 1u);
+                        AF_TIMED(w_te, mbar_wait(&tempty_o[buf], (uses[buf] & 1u) ^ 1u));
                         tc_fence_after();
                         const uint32_t dcol = buf ? p.col_o1 : p.col_o0;
                         for (int g = 0; g < kgroups; ++g) {
-                            mbar_wait(&full[stage], phase);
+                            AF_TIMED(w_lo, mbar_wait(&full[stage], phase));
                             tc_fence_after();
                             const uint32_t b_lo = smem_desc_lo(smem_u32(sStage + (uint32_t)stage * p.stage_bytes), (uint32_t)p.kg * 8192u);
                             const uint32_t pcol = oj[j].tile ? p.col_ds : p.col_p;
@@ -260,6 +286,11 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                     }
                 }
             }
+#undef AF_TIMED
+            if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x / 2 || blockIdx.x == gridDim.x - 1))
+                printf("mvae attn dbg (bwd %d T %d C %d): %u items, %lld clk issuing; waited %lld on score operand boxes, %lld on the "
+                       "softmax / dS warps, %lld on drained output accumulators, %lld on output operand boxes\n", p.bwd, p.T, p.C,
+                       n_local, clock64() - t_begin, w_ls, w_pr, w_te, w_lo);
         }
     } else {
         // ===================================================== epilogue warps: one thread = one tile row (TMEM lane)
@@ -270,6 +301,8 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
         const int cols_tile = p.kboxes * 64;
         uint32_t n_local = 0;
         uint32_t uses[2] = {0, 0};
+        long long e_ws = 0, e_cs = 0, e_wo = 0, e_co = 0, e0 = 0;   // knob 19: waits / work of the score and the output phases
+        const long long e_begin = clock64();
         for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++n_local) {
             int kind, img, r0, ns, no;
             AfScoreJob sj[2]; AfOutJob oj[2];
@@ -284,15 +317,22 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                 asm volatile("bar.sync 1, 128;" ::: "memory");     // the previous item's readers are done
                 for (int q = et; q < cols_tile; q += 128) {
                     sStat[q] = q < p.T ? p.lse2[tok0 + q] : 0.f;
-                    sStat[256 + q] = q < p.T ? p.D[tok0 + q] : 0.f;
+                    sStat[256 + q] = q < p.T ? p.D[tok0 + q] * p.alpha : 0.f;    // D * alpha: the dS loop folds the scale
                 }
                 asm volatile("bar.sync 1, 128;" ::: "memory");
             } else if (kind == AF_BWD_Q && valid) {
                 row_lse = p.lse2[tok0 + grow];
                 row_d = p.D[tok0 + grow];
             }
+            if (p.dbg) e0 = clock64();
             mbar_wait(tfull_s, n_local & 1u);
+            if (p.dbg) { const long long t = clock64(); e_ws += t - e0; e0 = t; }
             tc_fence_after();
+            // P / dS of 32 score columns at a time.  One warp per scheduler does this, so the instruction count per element
+            // is what matters (scripts/attn_stall_probe.py): full chunks run without per-element predicates (only the
+            // chunk that holds column T selects), exp2 is one MUFU (ex2.approx.ftz), constants are folded (D * alpha).
+            const float a2 = p.alpha_log2e, alpha = p.alpha;
+            const int T = p.T;
             if (kind == AF_FWD) {
                 float mx = -INFINITY;
 #pragma unroll 1
@@ -300,84 +340,134 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                     uint32_t v[32];
                     tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, v);
                     tmem_ld_wait();
+                    if (c0 + 32 <= T) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (c0 + i < p.T) mx = fmaxf(mx, __uint_as_float(v[i]) * p.alpha_log2e);
+                        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (c0 + i < T) mx = fmaxf(mx, __uint_as_float(v[i]));
+                    }
                 }
+                mx *= a2;                       // alpha > 0: the maximum commutes with the scale
                 float sum = 0.f;
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
                     uint32_t v[32], pk[16];
-                    if (c0 < p.Tp) { tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, v); tmem_ld_wait(); }
+                    const bool live = c0 < p.Tp;
+                    if (live) { tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, v); tmem_ld_wait(); }
+                    if (live && c0 + 32 <= T) {
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        float f[8];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int c = c0 + g * 8 + j;
-                            float e = (c < p.T) ? exp2f(__uint_as_float(v[g * 8 + j]) * p.alpha_log2e - mx) : 0.f;
-                            e = __bfloat162float(__float2bfloat16_rn(e));     // the value the PV GEMM sees
-                            f[j] = e;
-                            sum += e;
+                        for (int i = 0; i < 16; ++i) {
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(af_ex2(fmaf(__uint_as_float(v[2 * i]), a2, -mx)),
+                                                                           af_ex2(fmaf(__uint_as_float(v[2 * i + 1]), a2, -mx)));
+                            pk[i] = *reinterpret_cast<const uint32_t*>(&h);
+                            sum += __low2float(h) + __high2float(h);      // the values the PV GEMM sees
                         }
-                        if constexpr (TS) af_pack8(pk + g * 4, f);
-                        else af_tile_store8(sTile0, row, c0 + g * 8, f);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float e0 = (live && c0 + 2 * i < T) ? af_ex2(fmaf(__uint_as_float(v[2 * i]), a2, -mx)) : 0.f;
+                            const float e1 = (live && c0 + 2 * i + 1 < T) ? af_ex2(fmaf(__uint_as_float(v[2 * i + 1]), a2, -mx)) : 0.f;
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(e0, e1);
+                            pk[i] = *reinterpret_cast<const uint32_t*>(&h);
+                            sum += __low2float(h) + __high2float(h);
+                        }
                     }
                     if constexpr (TS) tmem_st_32x16(lane_addr + p.col_p + (uint32_t)(c0 >> 1), pk);
+                    else af_tile_store32(sTile0, row, c0, pk);
                 }
                 inv_l = 1.f / sum;
                 if (valid) p.lse2[tok0 + grow] = mx + log2f(sum);
             } else if (kind == AF_BWD_Q) {
+                const float row_da = row_d * alpha;
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
-                    uint32_t s[32], d[32], pk[16], pk2[16];
-                    if (c0 < p.Tp) {
-                        tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, s);
-                        tmem_ld_32x32(lane_addr + p.col_dp + (uint32_t)c0, d);
+                    uint32_t sv[32], dv[32], pk[16];
+                    const bool live = c0 < p.Tp;
+                    if (live) {
+                        tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, sv);
+                        tmem_ld_32x32(lane_addr + p.col_dp + (uint32_t)c0, dv);
                         tmem_ld_wait();
                     }
+                    if (live && c0 + 32 <= T) {
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        float f[8];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int c = c0 + g * 8 + j;
-                            const float pr = exp2f(__uint_as_float(s[g * 8 + j]) * p.alpha_log2e - row_lse);
-                            f[j] = (c < p.T) ? pr * (__uint_as_float(d[g * 8 + j]) - row_d) * p.alpha : 0.f;
+                        for (int i = 0; i < 16; ++i) {
+                            const float f0 = af_ex2(fmaf(__uint_as_float(sv[2 * i]), a2, -row_lse)) * fmaf(__uint_as_float(dv[2 * i]), alpha, -row_da);
+                            const float f1 = af_ex2(fmaf(__uint_as_float(sv[2 * i + 1]), a2, -row_lse)) * fmaf(__uint_as_float(dv[2 * i + 1]), alpha, -row_da);
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
+                            pk[i] = *reinterpret_cast<const uint32_t*>(&h);
                         }
-                        if constexpr (TS) af_pack8(pk + g * 4, f);
-                        else af_tile_store8(sTile1, row, c0 + g * 8, f);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            float f[2];
+#pragma unroll
+                            for (int u = 0; u < 2; ++u)
+                                f[u] = (live && c0 + 2 * i + u < T)
+                                           ? af_ex2(fmaf(__uint_as_float(sv[2 * i + u]), a2, -row_lse)) * fmaf(__uint_as_float(dv[2 * i + u]), alpha, -row_da)
+                                           : 0.f;
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(f[0], f[1]);
+                            pk[i] = *reinterpret_cast<const uint32_t*>(&h);
+                        }
                     }
                     if constexpr (TS) tmem_st_32x16(lane_addr + p.col_ds + (uint32_t)(c0 >> 1), pk);
+                    else af_tile_store32(sTile1, row, c0, pk);
                 }
             } else {
 #pragma unroll 1
                 for (int c0 = 0; c0 < cols_tile; c0 += 32) {
-                    uint32_t s[32], d[32], pk[16], pk2[16];
-                    if (c0 < p.Tp) {
-                        tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, s);
-                        tmem_ld_32x32(lane_addr + p.col_dp + (uint32_t)c0, d);
+                    uint32_t sv[32], dv[32], pk[16], pk2[16];
+                    const bool live = c0 < p.Tp;
+                    if (live) {
+                        tmem_ld_32x32(lane_addr + p.col_s + (uint32_t)c0, sv);
+                        tmem_ld_32x32(lane_addr + p.col_dp + (uint32_t)c0, dv);
                         tmem_ld_wait();
                     }
+                    if (live && c0 + 32 <= T) {
+                        const float4* ls4 = reinterpret_cast<const float4*>(sStat + c0);          // lse2 of the queries
+                        const float4* da4 = reinterpret_cast<const float4*>(sStat + 256 + c0);    // D * alpha of the queries
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        float fp[8], fd[8];
+                        for (int g = 0; g < 8; ++g) {
+                            const float4 l4 = ls4[g], d4 = da4[g];
+                            const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, da[4] = {d4.x, d4.y, d4.z, d4.w};
+                            float pr[4], fd[4];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int c = c0 + g * 8 + j;      // query index
-                            const float pr = (c < p.T) ? exp2f(__uint_as_float(s[g * 8 + j]) * p.alpha_log2e - sStat[c]) : 0.f;
-                            fp[j] = pr;
-                            fd[j] = (c < p.T) ? pr * (__uint_as_float(d[g * 8 + j]) - sStat[256 + c]) * p.alpha : 0.f;
+                            for (int u = 0; u < 4; ++u) {
+                                pr[u] = af_ex2(fmaf(__uint_as_float(sv[4 * g + u]), a2, -ls[u]));
+                                fd[u] = pr[u] * fmaf(__uint_as_float(dv[4 * g + u]), alpha, -da[u]);
+                            }
+#pragma unroll
+                            for (int u = 0; u < 2; ++u) {
+                                const __nv_bfloat162 h = __floats2bfloat162_rn(pr[2 * u], pr[2 * u + 1]);
+                                const __nv_bfloat162 h2 = __floats2bfloat162_rn(fd[2 * u], fd[2 * u + 1]);
+                                pk[2 * g + u] = *reinterpret_cast<const uint32_t*>(&h);
+                                pk2[2 * g + u] = *reinterpret_cast<const uint32_t*>(&h2);
+                            }
                         }
-                        if constexpr (TS) { af_pack8(pk + g * 4, fp); af_pack8(pk2 + g * 4, fd); }
-                        else {
-                            af_tile_store8(sTile0, row, c0 + g * 8, fp);
-                            af_tile_store8(sTile1, row, c0 + g * 8, fd);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            float pr[2], fd[2];
+#pragma unroll
+                            for (int u = 0; u < 2; ++u) {
+                                const int c = c0 + 2 * i + u;      // query index
+                                const bool on = live && c < T;
+                                pr[u] = on ? af_ex2(fmaf(__uint_as_float(sv[2 * i + u]), a2, -sStat[c])) : 0.f;
+                                fd[u] = on ? pr[u] * fmaf(__uint_as_float(dv[2 * i + u]), alpha, -sStat[256 + c]) : 0.f;
+                            }
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(pr[0], pr[1]);
+                            const __nv_bfloat162 h2 = __floats2bfloat162_rn(fd[0], fd[1]);
+                            pk[i] = *reinterpret_cast<const uint32_t*>(&h);
+                            pk2[i] = *reinterpret_cast<const uint32_t*>(&h2);
                         }
                     }
                     if constexpr (TS) {
                         tmem_st_32x16(lane_addr + p.col_p + (uint32_t)(c0 >> 1), pk);
                         tmem_st_32x16(lane_addr + p.col_ds + (uint32_t)(c0 >> 1), pk2);
+                    } else {
+                        af_tile_store32(sTile0, row, c0, pk);
+                        af_tile_store32(sTile1, row, c0, pk2);
                     }
                 }
             }
@@ -387,6 +477,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(pready);
+            if (p.dbg) e_cs += clock64() - e0;
 
             for (int j = 0; j < no; ++j) {
                 bf16* obase;
@@ -396,32 +487,64 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                 bf16* orow = obase + (tok0 + grow) * pitch;
                 for (int nc = 0; nc < nchunks; ++nc) {
                     const int buf = (int)((uses[0] + uses[1]) & 1u);
+                    if (p.dbg) e0 = clock64();
                     mbar_wait(&tfull_o[buf], uses[buf] & 1u);
+                    if (p.dbg) { const long long t = clock64(); e_wo += t - e0; e0 = t; }
                     tc_fence_after();
                     const uint32_t ocol = lane_addr + (buf ? p.col_o1 : p.col_o0);
+                    // A thread owns one accumulator row; stored as it is, every 16-byte store instruction of a warp would touch
+                    // 32 different 128-byte lines (32 LSU wavefronts: the drain was wavefront-bound, ~1 clk per 16 B per SM).
+                    // The warp's 32 rows x 64 columns go through a swizzled shared-memory tile instead and leave as 128 B per
+                    // row per eight lanes: 4 wavefronts per instruction.
+                    uint8_t* so = sOut + (warp - 2) * 4096;
+                    const uint32_t so_w = smem_u32(so) + (uint32_t)lane * 128u;
+                    const int rsub = lane >> 3, unit = lane & 7;
 #pragma unroll 1
-                    for (int c0 = 0; c0 < p.bno; c0 += 32) {
-                        uint32_t v[32];
+                    for (int c0 = 0; c0 < p.bno; c0 += 64) {      // bno is 64 or 128: two loads in flight per wait
+                        uint32_t v[64];
                         tmem_ld_32x32(ocol + (uint32_t)c0, v);
+                        tmem_ld_32x32(ocol + (uint32_t)(c0 + 32), v + 32);
                         tmem_ld_wait();
-                        if (valid) {
 #pragma unroll
-                            for (int g = 0; g < 4; ++g) {
-                                float f[8];
+                        for (int g = 0; g < 8; ++g) {
+                            uint32_t w[4];
 #pragma unroll
-                                for (int jj = 0; jj < 8; ++jj) f[jj] = __uint_as_float(v[g * 8 + jj]) * inv_l;
-                                Vec8<bf16> o8; o8.pack(f);
-                                o8.store(orow + nc * p.bno + c0 + g * 8);
+                            for (int u = 0; u < 4; ++u) {
+                                const __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[g * 8 + 2 * u]) * inv_l,
+                                                                               __uint_as_float(v[g * 8 + 2 * u + 1]) * inv_l);
+                                w[u] = *reinterpret_cast<const uint32_t*>(&h);
                             }
+                            if (p.so)
+                                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_w + (uint32_t)((g ^ (lane & 7)) << 4)),
+                                             "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+                            else if (valid)
+                                *reinterpret_cast<uint4*>(orow + nc * p.bno + c0 + g * 8) = make_uint4(w[0], w[1], w[2], w[3]);
                         }
+                        if (!p.so) continue;
+                        __syncwarp();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int rr = i * 4 + rsub;                   // row within the warp's 32
+                            uint32_t w0, w1, w2, w3;
+                            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3)
+                                         : "r"(smem_u32(so) + (uint32_t)(rr * 128 + ((unit ^ (rr & 7)) << 4))) : "memory");
+                            const int gr = r0 + quarter * 32 + rr;
+                            if (gr < p.T)
+                                *reinterpret_cast<uint4*>(obase + (tok0 + gr) * pitch + nc * p.bno + c0 + unit * 8) = make_uint4(w0, w1, w2, w3);
+                        }
+                        __syncwarp();
                     }
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_o[buf]);
                     ++uses[buf];
+                    if (p.dbg) e_co += clock64() - e0;
                 }
             }
         }
+        if (p.dbg && blockIdx.x == 0 && threadIdx.x == 64)
+            printf("mvae attn dbg, epilogue warp: %lld clk; waited %lld for scores, %lld computing P / dS, waited %lld for output "
+                   "accumulators, %lld draining them\n", clock64() - e_begin, e_ws, e_cs, e_wo, e_co);
     }
     tc_fence_before();
     __syncthreads();
@@ -497,6 +620,7 @@ static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t s
     d.idesc_s = make_idesc_bf16(128, d.Tp, 0, 0);
     d.idesc_o = make_idesc_bf16(128, d.bno, 0, 1);
     d.col_s = 0;
+    d.dbg = debug_knob(19) == 1 ? 1 : 0;
     d.ts = debug_knob(15) == 0 ? 1 : 0;       // knob 15 = 1: the shared-memory-tile variant (A/B: 12.3 vs 11.6 ms backward at C4)
     d.col_p = 0; d.col_ds = 256;
     if (d.ts) {
@@ -514,8 +638,12 @@ static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t s
         d.col_dp = 256; d.col_o0 = 0; d.col_o1 = 128; d.o_alias = 1;
     }
     d.n_items = d.B * d.mtiles * (d.bwd ? 2 : 1);
-    const long long fixed = (long long)d.tile_bytes * (d.bwd ? 2 : 1) + 2048 /* sStat */ + 256 /* barriers */;
     const long long budget = 232448;    // 227 KB of dynamic shared memory per CTA on sm_100
+    long long fixed = (long long)d.tile_bytes * (d.bwd ? 2 : 1) + 2048 /* sStat */ + 256 /* barriers */;
+    // sOut (4 warps x 32 rows x 128 B) unless it would cost the pipeline its second stage (the shared-memory-tile
+    // variant's backward at T > 192)
+    d.so = (budget - fixed - 16384) / d.stage_bytes >= 2 ? 1 : 0;
+    if (d.so) fixed += 16384;
     int stages = (int)((budget - fixed) / d.stage_bytes);
     if (stages > AF_MAX_STAGES) stages = AF_MAX_STAGES;
     MVAE_CHECK(stages >= 2, "attn_fused: T=%d does not leave room for a 2-stage pipeline", Tn);
@@ -529,6 +657,7 @@ static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t s
         attr_set = true;
     }
     int grid = d.n_items < af_num_sms() ? d.n_items : af_num_sms();
+    if (d.bwd && grid > 1) grid &= ~1;      // af_item's pair swap
     if (d.ts) attn_fused_kernel<true><<<grid, AF_THREADS, (size_t)smem, st>>>(tm, d);
     else attn_fused_kernel<false><<<grid, AF_THREADS, (size_t)smem, st>>>(tm, d);
     MVAE_LAUNCH_CHECK();
