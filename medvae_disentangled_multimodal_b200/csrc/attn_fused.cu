@@ -333,7 +333,12 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
             // chunk that holds column T selects), exp2 is one MUFU (ex2.approx.ftz), constants are folded (D * alpha).
             const float a2 = p.alpha_log2e, alpha = p.alpha;
             const int T = p.T;
-            if (kind == AF_FWD) {
+            // a warp whose 32 rows all lie beyond T (the upper warps of a T <= 64 or T = 196 tile) has nothing to compute
+            // or store: its rows of P / dS stay whatever tensor memory holds — operand rows only reach their own,
+            // never-stored, output rows — and it only keeps the barrier protocol going
+            const bool wlive = r0 + quarter * 32 < T;
+            if (!wlive) {
+            } else if (kind == AF_FWD) {
                 float mx = -INFINITY;
 #pragma unroll 1
                 for (int c0 = 0; c0 < p.Tp; c0 += 32) {
@@ -500,7 +505,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                     const uint32_t so_w = smem_u32(so) + (uint32_t)lane * 128u;
                     const int rsub = lane >> 3, unit = lane & 7;
 #pragma unroll 1
-                    for (int c0 = 0; c0 < p.bno; c0 += 64) {      // bno is 64 or 128: two loads in flight per wait
+                    for (int c0 = 0; wlive && c0 < p.bno; c0 += 64) {      // bno is 64 or 128: two loads in flight per wait
                         uint32_t v[64];
                         tmem_ld_32x32(ocol + (uint32_t)c0, v);
                         tmem_ld_32x32(ocol + (uint32_t)(c0 + 32), v + 32);
