@@ -567,7 +567,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 if (validj[j]) {
                     const uint4* ap = reinterpret_cast<const uint4*>(p.gn_x + pixj[j] + cw0 + ci * 32);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) aux[i] = __ldg(ap + i);
+                    for (int i = 0; i < 4; i += 2) ldg256_nc(ap + i, aux[i], aux[i + 1]);
                 }
             };
             load_aux(0, 0);
@@ -646,12 +646,9 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                                         }
                                     }
                                 }
-                                uint4* op = reinterpret_cast<uint4*>(p.out + pixj[j] + cbase + hf * 16);
-#pragma unroll
-                                for (int i = 0; i < 2; ++i) {
-                                    Vec8<bf16> o8; o8.pack(f + 8 * i);
-                                    op[i] = o8.raw;
-                                }
+                                Vec8<bf16> o8a, o8b;
+                                o8a.pack(f); o8b.pack(f + 8);
+                                stg256(p.out + pixj[j] + cbase + hf * 16, o8a.raw, o8b.raw);
                             }
                         }
                         todo &= ~__ballot_sync(0xffffffffu, active);
@@ -680,6 +677,16 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
             const bool valid = (row < p.rows) && x < p.OW && y < p.OH && n < p.B;
             const long long pix = p.o_off + (long long)n * p.o_sn + (long long)y * p.o_sy + (long long)x * p.o_sx;
             if (EPI == EPI_PLAIN) {
+                // the residual of a 32-channel chunk is fetched one chunk ahead (the first before the accumulator wait): a
+                // dependent global load per chunk inside the loop left the MMA warp waiting on this epilogue for up to 40 %
+                // of a 128-channel tile (scripts/gather_stall_probe.py)
+                uint4 rcur[4], rnext[4];
+                const bool have_res = valid && p.res != nullptr;
+                const uint4* rp0 = reinterpret_cast<const uint4*>(p.res + pix + nt * BN);
+                if (have_res) {
+#pragma unroll
+                    for (int i = 0; i < 4; i += 2) ldg256_nc(rp0 + i, rcur[i], rcur[i + 1]);
+                }
                 mbar_wait(&tfull[acc], acc_phase);
                 tc_fence_after();
                 const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc_col;
@@ -687,6 +694,10 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 for (int c0 = 0; c0 < BN; c0 += 32) {
                     uint32_t v[32];
                     tmem_ld_32x32(t0 + (uint32_t)c0, v);
+                    if (have_res && c0 + 32 < BN) {
+#pragma unroll
+                        for (int i = 0; i < 4; i += 2) ldg256_nc(rp0 + (c0 + 32) / 8 + i, rnext[i], rnext[i + 1]);
+                    }
                     tmem_ld_wait();
                     if (valid) {
                         const int cbase = nt * BN + c0;
@@ -702,22 +713,23 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                             }
                         }
                         if (p.res) {
-                            const uint4* rp = reinterpret_cast<const uint4*>(p.res + pix + cbase);
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
-                                Vec8<bf16> r8; r8.raw = __ldg(rp + i);
+                                Vec8<bf16> r8; r8.raw = rcur[i];
                                 float rf[8]; r8.unpack(rf);
 #pragma unroll
                                 for (int j = 0; j < 8; ++j) f[8 * i + j] += rf[j];
                             }
                         }
-                        uint4* op = reinterpret_cast<uint4*>(p.out + pix + cbase);
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            Vec8<bf16> o8; o8.pack(f + 8 * i);
-                            op[i] = o8.raw;
+                        for (int i = 0; i < 4; i += 2) {
+                            Vec8<bf16> o8a, o8b;
+                            o8a.pack(f + 8 * i); o8b.pack(f + 8 * i + 8);
+                            stg256(p.out + pix + cbase + 8 * i, o8a.raw, o8b.raw);
                         }
                     }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) rcur[i] = rnext[i];
                 }
             } else {
                 // this warp's half of the tile's columns: XCH chunks of 32
@@ -738,7 +750,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                     for (int ci = 0; ci < XCH; ++ci) {
                         const uint4* ap = reinterpret_cast<const uint4*>(auxp + pix + nt * BN + chalf * CW + ci * 32);
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) aux[ci][i] = __ldg(ap + i);
+                        for (int i = 0; i < 4; i += 2) ldg256_nc(ap + i, aux[ci][i], aux[ci][i + 1]);
                     }
                 }
                 mbar_wait(&tfull[acc], acc_phase);
@@ -774,11 +786,11 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                                 for (int j = 0; j < 8; ++j) f[8 * i + j] += rf[j];
                             }
                         }
-                        uint4* op = reinterpret_cast<uint4*>(p.out + pix + cbase);
+                        uint4 ov[4];
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             Vec8<bf16> o8; o8.pack(f + 8 * i);
-                            op[i] = o8.raw;
+                            ov[i] = o8.raw;
                             if (EPI == EPI_GN_STATS) {
                                 float yf[8]; o8.unpack(yf);   // statistics of the values as stored
 #pragma unroll
@@ -788,6 +800,8 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                                 }
                             }
                         }
+                        stg256(p.out + pix + cbase, ov[0], ov[1]);
+                        stg256(p.out + pix + cbase + 16, ov[2], ov[3]);
                     }
                     if (any_valid) {
                         float* dst = p.gn_sums + ((long long)(uniform ? n_ref : n) * p.gn_G + (cbase >> p.gn_cpg_log2)) * 2;
