@@ -497,7 +497,7 @@ def b200_arm(args):
             roof = {"bound": "tensor", "kernel": "conv_gather_umma_kernel (implicit-GEMM conv fprop+dgrad, tcgen05)",
                     "achieved": round(ach, 2), "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
                     "frac": round(ach / peaks["bf16_sustained"], 4), "traffic": load_traffic(wl),
-                    "traffic_source": ("profiles/roofline_traffic.json <- profiles/r2a_ncu_full.csv: ncu --set full, mean "
+                    "traffic_source": ("profiles/roofline_traffic.json <- profiles/r2p_ncu_full.csv: ncu --set full, mean "
                                        "dram__bytes_read.sum + dram__bytes_write.sum over 30 gather launches (16 fprop, 14 "
                                        "dgrad) of this very command shape (one 1024-image pass)" if wl == "c4" else None),
                     # bytes the launches must move at least once: input + output tensors (+ the GroupNorm input read and
