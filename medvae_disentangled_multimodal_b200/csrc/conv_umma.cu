@@ -4,9 +4,12 @@
 //      A tiles: TMA 4-D boxes {64 ch, bw, bh, bn} over an NHWC view, shifted per tap; the conv's
 //      zero padding (and the Downsample pad) is TMA out-of-bounds zero fill.  K-major, 128B swizzle.
 //      B tiles: TMA 3-D boxes {64 ch, BN, 1 slab} of the packed weights.  K-major, 128B swizzle.
-//      warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM alloc), warps 2-5 = epilogue
-//      (tcgen05.ld -> +bias (+residual) -> bf16 -> global).  Persistent CTAs, 2 TMEM accumulator
+//      warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM alloc) — one thread each, chosen with elect.sync so that
+//      the assembler emits every UTMALDG / UTCHMMA once (umma.cuh) — warps 2-5 = epilogue
+//      (tcgen05.ld -> +bias (+residual) -> bf16 -> global, 32 bytes per access).  Persistent CTAs, 2 TMEM accumulator
 //      stages so the epilogue of tile i overlaps the MMAs of tile i+1.
+//      Halo variant (HL = 1, 128-channel stride-1 3x3 layers): 8 x 16 pixel tiles, ONE box {64 ch, 16, 18} per tile and
+//      64-channel chunk, the nine taps are nine descriptor views of it; weights through their own ring (see HaloCfg).
 //      Epilogue variants (template EPI): the GroupNorm either side of the conv rides here —
 //      EPI_GN_STATS accumulates the consumer GroupNorm's per-(sample, group) sums of the output,
 //      EPI_GN_BWD turns dL/d[silu(GN(x))] into dL/du and accumulates the GroupNorm-backward group
