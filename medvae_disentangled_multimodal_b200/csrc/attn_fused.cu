@@ -38,6 +38,7 @@ struct alignas(64) AfTmaps {
     CUtensorMap a[2];   // {64 channels, 128 tokens}: the A rows of a score GEMM
     CUtensorMap b[2];   // {64 channels, kboxes * 64 tokens}: ALL tokens, the B operand of a score GEMM
     CUtensorMap n[2];   // {64 channels, kg * 64 tokens}: a token group, the N-major B operand of an output GEMM
+    CUtensorMap o;      // {64 channels, 32 tokens} of the OUTPUT (out, or dqkv): one epilogue warp's rows, TMA-stored
 };
 struct AfDev {
     int B, T, C;
@@ -61,7 +62,7 @@ struct AfDev {
     const float* D;    // [B][T]
     bf16* dqkv;        // backward [B][T][3C]
     int dbg;           // knob 19 = 1: block 0's MMA thread prints where its cycles went
-    int so;            // 1: output rows leave through the shared-memory transpose (0: no room for it, one row per thread)
+    int so;            // 1: output rows leave as TMA stores of swizzled shared-memory boxes (0: no room for them, one row per thread)
 };
 
 constexpr int AF_THREADS = 192;
@@ -141,7 +142,9 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
     uint8_t* sTile0 = smem;                                         // P~ (forward) / P^T (K-side)
     uint8_t* sTile1 = sTile0 + p.tile_bytes;                        // dS / dS^T (backward only)
     uint8_t* sStage = sTile1 + (p.bwd ? p.tile_bytes : 0u);
-    uint64_t* full = reinterpret_cast<uint64_t*>(sStage + (uint32_t)p.stages * p.stage_bytes);
+    // [4 epilogue warps][2 buffers][32 rows x 128 B]: output boxes on their way to global (1024-byte aligned: swizzled)
+    uint8_t* sOut = sStage + (uint32_t)p.stages * p.stage_bytes;
+    uint64_t* full = reinterpret_cast<uint64_t*>(sOut + (p.so ? 32768u : 0u));
     uint64_t* empty = full + AF_MAX_STAGES;
     uint64_t* tfull_s = empty + AF_MAX_STAGES;    // scores (S and dP) complete in TMEM
     uint64_t* pready = tfull_s + 1;               // shared-memory tiles written by the epilogue warps
@@ -149,7 +152,6 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
     uint64_t* tempty_o = tfull_o + 2;             // [2] output accumulator drained
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_o + 2);
     float* sStat = reinterpret_cast<float*>(tmem_slot + 4);   // [2][256]: lse2, D per query (K-side items)
-    uint8_t* sOut = reinterpret_cast<uint8_t*>(sStat) + 2048; // [4 warps][32 rows][128 B]: output rows on their way to global
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if ((smem_u32(smem) & 1023u) != 0u) {   // SWIZZLE_128B tiles need 1024-byte alignment
@@ -157,7 +159,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
         __trap();
     }
     if (warp == 0 && lane == 0) {
-        prefetch_tmap(&tm.a[0]); prefetch_tmap(&tm.b[0]); prefetch_tmap(&tm.n[0]);
+        prefetch_tmap(&tm.a[0]); prefetch_tmap(&tm.b[0]); prefetch_tmap(&tm.n[0]); prefetch_tmap(&tm.o);
         if (p.bwd) { prefetch_tmap(&tm.a[1]); prefetch_tmap(&tm.b[1]); prefetch_tmap(&tm.n[1]); }
     }
     if (warp == 1) {
@@ -301,6 +303,7 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
         const int cols_tile = p.kboxes * 64;
         uint32_t n_local = 0;
         uint32_t uses[2] = {0, 0};
+        uint32_t obuf = 0;               // which of the warp's two output boxes the next TMA store takes
         long long e_ws = 0, e_cs = 0, e_wo = 0, e_co = 0, e0 = 0;   // knob 19: waits / work of the score and the output phases
         const long long e_begin = clock64();
         for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++n_local) {
@@ -497,18 +500,22 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                     if (p.dbg) { const long long t = clock64(); e_wo += t - e0; e0 = t; }
                     tc_fence_after();
                     const uint32_t ocol = lane_addr + (buf ? p.col_o1 : p.col_o0);
-                    // A thread owns one accumulator row; stored as it is, every 16-byte store instruction of a warp would touch
-                    // 32 different 128-byte lines (32 LSU wavefronts: the drain was wavefront-bound, ~1 clk per 16 B per SM).
-                    // The warp's 32 rows x 64 columns go through a swizzled shared-memory tile instead and leave as 128 B per
-                    // row per eight lanes: 4 wavefronts per instruction.
-                    uint8_t* so = sOut + (warp - 2) * 4096;
-                    const uint32_t so_w = smem_u32(so) + (uint32_t)lane * 128u;
-                    const int rsub = lane >> 3, unit = lane & 7;
+                    // A thread owns one accumulator row; stored as it is, every 16-byte store instruction of a warp touches 32
+                    // different 128-byte lines (32 LSU wavefronts: the drain was wavefront-bound, ~1 clk per 16 B per SM).  The
+                    // warp's 32 rows x 64 columns are written as a SWIZZLE_128B box into shared memory instead (conflict-free
+                    // 16-byte stores) and one elected lane hands the box to TMA; two boxes per warp alternate, a box is reused
+                    // once the store before last has finished reading (rows beyond T are clipped by the tensor map).
+                    const uint32_t so_w = smem_u32(sOut) + (uint32_t)((warp - 2) * 8192 + lane * 128);
+                    const int col0 = (kind == AF_FWD ? 0 : (int)oj[j].out_off) + nc * p.bno;
 #pragma unroll 1
                     for (int c0 = 0; wlive && c0 < p.bno; c0 += 64) {      // bno is 64 or 128: two loads in flight per wait
                         uint32_t v[64];
                         tmem_ld_32x32(ocol + (uint32_t)c0, v);
                         tmem_ld_32x32(ocol + (uint32_t)(c0 + 32), v + 32);
+                        if (p.so) {
+                            if (elect_one_sync()) tma_store_wait_read<1>();
+                            __syncwarp();
+                        }
                         tmem_ld_wait();
 #pragma unroll
                         for (int g = 0; g < 8; ++g) {
@@ -520,24 +527,17 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                                 w[u] = *reinterpret_cast<const uint32_t*>(&h);
                             }
                             if (p.so)
-                                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_w + (uint32_t)((g ^ (lane & 7)) << 4)),
+                                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(so_w + obuf * 4096u + (uint32_t)((g ^ (lane & 7)) << 4)),
                                              "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
                             else if (valid)
                                 *reinterpret_cast<uint4*>(orow + nc * p.bno + c0 + g * 8) = make_uint4(w[0], w[1], w[2], w[3]);
                         }
                         if (!p.so) continue;
+                        fence_proxy_async_smem();
                         __syncwarp();
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int rr = i * 4 + rsub;                   // row within the warp's 32
-                            uint32_t w0, w1, w2, w3;
-                            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3)
-                                         : "r"(smem_u32(so) + (uint32_t)(rr * 128 + ((unit ^ (rr & 7)) << 4))) : "memory");
-                            const int gr = r0 + quarter * 32 + rr;
-                            if (gr < p.T)
-                                *reinterpret_cast<uint4*>(obase + (tok0 + gr) * pitch + nc * p.bno + c0 + unit * 8) = make_uint4(w0, w1, w2, w3);
-                        }
-                        __syncwarp();
+                        if (elect_one_sync())
+                            tma_store_3d(&tm.o, sOut + (warp - 2) * 8192 + obuf * 4096u, col0 + c0, r0 + quarter * 32, img);
+                        obuf ^= 1u;
                     }
                     tc_fence_before();
                     __syncwarp();
@@ -546,6 +546,10 @@ attn_fused_kernel(const __grid_constant__ AfTmaps tm, const __grid_constant__ Af
                     if (p.dbg) e_co += clock64() - e0;
                 }
             }
+        }
+        if (p.so) {      // the shared-memory boxes must outlive their stores
+            if (elect_one_sync()) tma_store_wait_all();
+            __syncwarp();
         }
         if (p.dbg && blockIdx.x == 0 && threadIdx.x == 64)
             printf("mvae attn dbg, epilogue warp: %lld clk; waited %lld for scores, %lld computing P / dS, waited %lld for output "
@@ -620,6 +624,11 @@ static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t s
         if (encode_tmap_3d_bf16(&tm.b[t], base, inner, Tn, d.B, inner, img, 64, (unsigned)(d.kboxes * 64))) return 1;
         if (encode_tmap_3d_bf16(&tm.n[t], base, inner, Tn, d.B, inner, img, 64, (unsigned)(d.kg * 64))) return 1;
     }
+    {   // the output: out [B][T][C] (forward) or dqkv [B][T][3C] (backward), boxes of 64 channels x 32 tokens
+        const void* obase = d.bwd ? (const void*)d.dqkv : (const void*)d.out;
+        const unsigned long long inner = d.bwd ? 3ULL * C : (unsigned long long)C;
+        if (encode_tmap_3d_bf16(&tm.o, obase, inner, Tn, d.B, inner, (unsigned long long)Tn * inner, 64, 32)) return 1;
+    }
     d.alpha = 1.0f / sqrtf((float)C);                         // int(c) ** (-0.5), encoder_decoder.py:94
     d.alpha_log2e = d.alpha * 1.4426950408889634f;
     d.idesc_s = make_idesc_bf16(128, d.Tp, 0, 0);
@@ -645,10 +654,10 @@ static int af_launch(const bf16* qkv, const bf16* dout, AfDev& d, cudaStream_t s
     d.n_items = d.B * d.mtiles * (d.bwd ? 2 : 1);
     const long long budget = 232448;    // 227 KB of dynamic shared memory per CTA on sm_100
     long long fixed = (long long)d.tile_bytes * (d.bwd ? 2 : 1) + 2048 /* sStat */ + 256 /* barriers */;
-    // sOut (4 warps x 32 rows x 128 B) unless it would cost the pipeline its second stage (the shared-memory-tile
+    // sOut (4 warps x 2 boxes x 32 rows x 128 B) unless it would cost the pipeline its second stage (the shared-memory-tile
     // variant's backward at T > 192)
-    d.so = (budget - fixed - 16384) / d.stage_bytes >= 2 ? 1 : 0;
-    if (d.so) fixed += 16384;
+    d.so = (budget - fixed - 32768) / d.stage_bytes >= 2 ? 1 : 0;
+    if (d.so) fixed += 32768;
     int stages = (int)((budget - fixed) / d.stage_bytes);
     if (stages > AF_MAX_STAGES) stages = AF_MAX_STAGES;
     MVAE_CHECK(stages >= 2, "attn_fused: T=%d does not leave room for a 2-stage pipeline", Tn);
