@@ -190,6 +190,17 @@ int mvae_attn_fused_fwd(const void* qkv, void* out, float* lse2, int32_t batch, 
 int mvae_attn_fused_bwd(const void* qkv, const void* out, const float* lse2, const void* dout, void* dqkv,
                         float* dscratch, int32_t batch, int32_t tokens, int32_t c, int32_t dtype,
                         void* stream);
+/* mvae_attn_fused_bwd without a caller-provided scratch buffer.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  The B*T row dots live in a file-scope static __device__ array of MVAE_ATTN_STATIC_MAX_ROWS floats
+ * (4 MiB, held by every GPU that loads the library until exit); the call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine) and returns an error when batch * tokens exceeds the maximum.  Same results as
+ * mvae_attn_fused_bwd.  All calls share the array (it keeps the last call's contents; nothing needs clearing: each call
+ * overwrites the range it reads): calls that overlap on the GPU — different streams without an ordering between
+ * them — race. */
+#define MVAE_ATTN_STATIC_MAX_ROWS 1048576
+int mvae_attn_fused_bwd_static(const void* qkv, const void* out, const float* lse2, const void* dout, void* dqkv,
+                               int32_t batch, int32_t tokens, int32_t c, int32_t dtype, void* stream);
 
 /* ConditionalVAE.create_condition_map + torch.cat, conditional_vae.py:107-127 (concat path),
  * and the NCHW->NHWC conversion of x.  cond: [B, cond_dim] fp32 (one-hot or dense);

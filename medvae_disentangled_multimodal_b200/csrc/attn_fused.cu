@@ -20,6 +20,8 @@
 // dqkv through ONE 3-D tensor map per tensor with a {64 channels, 64 tokens} box: a K-major operand (reduction over
 // channels) and an N-major operand (reduction over tokens) are the same box seen through different UMMA descriptors.
 // Rows / tokens beyond T are TMA zero fill; the score columns beyond T are masked in the epilogue.
+#include <mutex>
+#include "../../include/medvae_b200.h"
 #include "umma.cuh"
 
 namespace mvae {
@@ -705,4 +707,50 @@ int attn_fused_bwd(const bf16* qkv, const bf16* out, const float* lse2, const bf
     return af_launch(qkv, dout, d, st);
 }
 
+// ------------------------------------------------------------------ no-allocation variant of the backward
+// For callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+// it): the row-dot scratch D[B*T] of the backward lives in a file-scope device array of a fixed, modest size instead of a
+// caller-provided buffer.  Every GPU that loads the library holds these 4 MiB until exit.
+//   * `g_af_static_rowdot` in HOST code is a host-side stand-in for the symbol, not a device address: the address the
+//     kernels get comes from cudaGetSymbolAddress, resolved once per device with that device current.
+//   * Every call shares the array and it keeps the last call's contents.  Nothing has to start at zero: the row-dot
+//     kernel writes D[0, B*T) completely before the fused kernel reads exactly that range on the same stream.
+//   * Two calls that overlap on the GPU (different streams, or graph branches without an edge between them) RACE on it.
+static __device__ __align__(256) float g_af_static_rowdot[MVAE_ATTN_STATIC_MAX_ROWS];
+
+static int af_static_rowdot(float** out) {
+    constexpr int MAX_DEV = 64;
+    static float* ptrs[MAX_DEV];
+    static std::mutex mu;
+    int dev = -1;
+    MVAE_CUDA(cudaGetDevice(&dev));
+    MVAE_CHECK(dev >= 0 && dev < MAX_DEV, "attn_fused_bwd_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptrs[dev] == nullptr) {
+        void* p = nullptr;
+        MVAE_CUDA(cudaGetSymbolAddress(&p, g_af_static_rowdot));
+        MVAE_CHECK(p != nullptr, "attn_fused_bwd_static: cudaGetSymbolAddress returned a null address");
+        ptrs[dev] = static_cast<float*>(p);
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
 }  // namespace mvae
+
+// include/medvae_b200.h: no counterpart in the reference
+extern "C" int mvae_attn_fused_bwd_static(const void* qkv, const void* out, const float* lse2, const void* dout, void* dqkv,
+                                          int32_t batch, int32_t tokens, int32_t c, int32_t dtype, void* stream) {
+    using namespace mvae;
+    MVAE_CHECK(qkv && out && lse2 && dout && dqkv && batch > 0 && tokens > 0 && c > 0, "attn_fused_bwd_static: bad argument");
+    MVAE_CHECK(dtype == MVAE_BF16, "attn_fused_bwd_static: bf16 only");
+    const long long rows = (long long)batch * tokens;
+    MVAE_CHECK(rows <= (long long)MVAE_ATTN_STATIC_MAX_ROWS,
+               "attn_fused_bwd_static: batch * tokens = %lld exceeds the static scratch of %d rows "
+               "(MVAE_ATTN_STATIC_MAX_ROWS); use mvae_attn_fused_bwd with a caller-provided buffer",
+               rows, (int)MVAE_ATTN_STATIC_MAX_ROWS);
+    float* scratch = nullptr;
+    if (af_static_rowdot(&scratch)) return 1;
+    return attn_fused_bwd((const bf16*)qkv, (const bf16*)out, lse2, (const bf16*)dout, (bf16*)dqkv, scratch, batch, tokens, c,
+                          (cudaStream_t)stream);
+}
