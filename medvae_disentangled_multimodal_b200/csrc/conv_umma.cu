@@ -252,14 +252,20 @@ __host__ __device__ constexpr int gather_smem(int base, int epi) { return base +
 // HALO variant (HL = 1; stride-1 3x3 convs, output grid a multiple of 8 x 16).  Everything above pulls each input
 // pixel from L2 once per TAP, and what bounds these kernels is L2 -> SM throughput (~6300 B/clk chip-wide = 42.6
 // B/clk/SM: every gather launch in profiles/r2k_ncu_full.csv sits at 11-13 TB/s of l1tex__m_xbar2l1tex_read_bytes).
-// Here a pixel tile is 8 wide x 16 tall and ONE TMA box {64 ch, 16, 18} brings its (1-pixel) halo per 64-channel
-// chunk; the nine taps are nine views of that box: descriptor start = ((dy+1) * 16 + (dx+1)) * 128 B into it, stride
-// between 8-row groups (= 8 pixels of one image row) = the 16-pixel pitch = 2048 B.  The 128B swizzle is a function
+// Here a pixel tile is 8 wide x 16 tall and ONE TMA box {64 ch, W, 18} brings its (1-pixel) halo per 64-channel
+// chunk; the nine taps are nine views of that box: descriptor start = ((dy+1) * W + (dx+1)) * 128 B into it, stride
+// between 8-row groups (= 8 pixels of one image row) = the box pitch W * 128 B.  The 128B swizzle is a function
 // of the absolute shared-memory address bits, so a start that is not 1024-aligned reads what TMA wrote.  Activation
-// bytes per pixel tile and chunk: 36 KB instead of 9 x 16 KB; the weights still stream per (chunk, tap), through their
+// bytes per pixel tile and chunk: 22.5 KB instead of 9 x 16 KB; the weights still stream per (chunk, tap), through their
 // own ring.  The k loop runs chunk-major (chunk outer, tap inner).
-constexpr int HALO_W = 16, HALO_H = 18;
-constexpr int HALO_TILE_BYTES = HALO_W * HALO_H * 128;   // 36864
+// Box = the 8 x 16 pixel tile plus one pixel all round: 10 x 18 pixels, dense in shared memory (pitch 10 pixels = 1280 B:
+// the stride between 8-row groups need not be a multiple of the 1024-byte swizzle atom, for the same reason the start
+// need not be).  The first version padded the pitch to 16 pixels (36 KB per box); 22.5 KB leave room for a weight ring of
+// seven stages instead of four, and the issuing thread waited on weight boxes for 15 % of its cycles.
+constexpr int HALO_TW = 8, HALO_TH = 16;                 // pixel tile
+constexpr int HALO_W = HALO_TW + 2, HALO_H = HALO_TH + 2;
+constexpr int HALO_BOX_BYTES = HALO_W * HALO_H * 128;    // 23040: what one TMA box delivers
+constexpr int HALO_TILE_BYTES = (HALO_BOX_BYTES + 1023) / 1024 * 1024;   // its 1024-byte aligned slot
 template <int BN, int MT>
 struct HaloCfg {
     static constexpr int A_STAGE = MT * HALO_TILE_BYTES;
@@ -358,7 +364,7 @@ conv_gather_umma_kernel(const __grid_constant__ GatherTmaps tm, const __grid_con
                 }
                 if (a_live && mbar_try_wait(&emptyA[sa], pa ^ 1u)) {
                     t_idle = clock64();
-                    mbar_expect_tx(&fullA[sa], (uint32_t)HCfg::A_STAGE);
+                    mbar_expect_tx(&fullA[sa], (uint32_t)(MT * HALO_BOX_BYTES));
 #pragma unroll
                     for (int j = 0; j < MT; ++j) {
                         int mt = (ta / p.n_tiles) * MT + j;   // one past the last: n0 >= B, the box is zero-filled
@@ -899,7 +905,7 @@ static int launch_gather(const GatherTmaps& tm, GatherDev& d, int epi, cudaStrea
 
 // halo variant: a stride-1 3 x 3 tap program over one view, output grid in whole 8 x 16 pixel tiles
 static bool halo_ok(const GatherProblem& p) {
-    if (p.nviews != 1 || p.taps.ntaps != 9 || p.OW % 8 != 0 || p.OH % HALO_W != 0) return false;
+    if (p.nviews != 1 || p.taps.ntaps != 9 || p.OW % HALO_TW != 0 || p.OH % HALO_TH != 0) return false;
     if (p.in_views[0].Ws < HALO_W || p.in_views[0].Hs < HALO_H) return false;
     for (int t = 0; t < 9; ++t) {
         const Tap& tp = p.taps.t[t];
